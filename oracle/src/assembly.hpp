@@ -223,6 +223,8 @@ class Oracle {
     auto module = importPhysics<EvalT>(cfg.physics, cfg.settings, cfg.dim);
     module->defineFunctions(cfg.functions, &fm);
     for (auto& f : sideFunctions) fm.addFunction(f.first, f.second, "side ip");
+    // every entry of the user "Functions" list, both locations (physicsInterface.cpp:466-483)
+    for (auto& f : cfg.functions) { fm.addFunction(f.first, f.second, "ip"); fm.addFunction(f.first, f.second, "side ip"); }
     module->setWorkset(&wk);
     fm.decomposeFunctions();
     const int seedwhat = compute_jacobian ? 1 : 0;

@@ -1,0 +1,115 @@
+"""Pin the CPU oracle against the reference's own golden numbers (CPU only, no product code involved).
+
+  * regression/discretization/HGRAD/mrhyde.gold : basis values and physical gradients, unit quad and hex
+  * regression/{thermal,cdr,le,navierstokes}/**/mrhyde.gold : 6-digit L2 errors after a Newton solve
+The golden numbers live in tests/golden/reference_golds.json (made by tests/golden/make_golden.py).
+"""
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import scipy.sparse.linalg as spl
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+
+import problems  # noqa: E402
+from oracle.pyoracle import Oracle, config_text  # noqa: E402
+
+GOLD = json.load(open(os.path.join(HERE, "golden", "reference_golds.json")))
+
+
+def sig6(x):
+    return float(f"{x:.6g}")
+
+
+def newton(o, iters=8, tol=1e-9):
+    u = np.zeros(o.nlocal)
+    rp, ci = o.crs()
+    for _ in range(iters):
+        res, jac = o.assemble(u, jacobian=True)
+        if np.max(np.abs(res)) < tol:
+            break
+        J = sp.csr_matrix((jac, ci, rp), shape=(o.nlocal, o.nlocal)).tocsc()
+        u = u + spl.spsolve(J, res)
+    return u
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_hgrad_basis_known_answers(dim):
+    o = Oracle(config_text(mesh=problems._mesh(dim, (1, 1, 1)), physics="thermal", order=1))
+    b, bg, w, ip = o.group_basis(0, 1)
+    key = "quad" if dim == 2 else "hex"
+    for dof, pt, val in GOLD["hgrad"][key + "_basis"]:
+        assert sig6(b[0, dof, pt]) == pytest.approx(val, rel=2e-6), (dof, pt)
+    for dof, pt, g in GOLD["hgrad"][key + "_grad"]:
+        for c in range(dim):
+            assert sig6(bg[0, dof, pt, c]) == pytest.approx(g[c], rel=2e-6), (dof, pt, c)
+    assert np.sum(w) == pytest.approx(1.0, rel=1e-14)
+
+
+CASES = [
+    ("thermal/2D_verification", problems.regression_thermal_2d),
+    ("thermal/3D_verification", problems.regression_thermal_3d),
+    ("cdr/2D_manufactured", problems.regression_cdr_2d),
+    ("le/2D_manufactured", problems.regression_le_2d),
+    ("le/3D_manufactured", problems.regression_le_3d),
+    ("navierstokes/channel", problems.regression_ns_channel),
+]
+
+
+@pytest.mark.parametrize("path,make", CASES, ids=[c[0] for c in CASES])
+def test_regression_l2_errors(path, make):
+    p = make()
+    o = Oracle(config_text(**p))
+    u = newton(o)
+    names = {"thermal": ["e"], "cdr": ["c"], "linearelasticity": ["dx", "dy", "dz"][: o.dim],
+             "navierstokes": ["ux", "pr", "uy", "uz"][: o.dim + 1]}[p["physics"]]
+    for var, gold in GOLD["l2"][path].items():
+        if var not in p["true"]:
+            continue
+        err = o.l2_error(u, names.index(var), p["true"][var])
+        assert err == pytest.approx(gold, rel=2e-5, abs=1e-9), (path, var, err, gold)
+
+
+def test_interpreter_quirks():
+    o = Oracle(config_text(mesh=problems._mesh(2, (2, 2)), physics="thermal", order=1,
+                           functions={"A": "2.0", "f": "A*x+1.0"}))
+    x = o.eval_expression("x", 0, 4)
+    y = o.eval_expression("y", 0, 4)
+    np.testing.assert_allclose(o.eval_expression("8*(pi*pi)*sin(2*pi*x)*sin(2*pi*y)", 0, 4),
+                               8 * np.pi ** 2 * np.sin(2 * np.pi * x) * np.sin(2 * np.pi * y), rtol=1e-14)
+    # left-to-right within a precedence class: a/b*c == (a/b)*c ; a-b+c == (a-b)+c
+    np.testing.assert_allclose(o.eval_expression("x/2.0*4.0", 0, 4), x / 2.0 * 4.0, rtol=1e-15)
+    np.testing.assert_allclose(o.eval_expression("-x+y", 0, 4), (0.0 - x) + y, rtol=1e-15, atol=1e-16)
+    # a '^' binds tighter than '*', user functions resolve by name, comparison yields 0/1
+    np.testing.assert_allclose(o.eval_expression("3.0*x^2", 0, 4), 3.0 * x ** 2, rtol=1e-15)
+    np.testing.assert_allclose(o.eval_expression("f*f", 0, 4), (2.0 * x + 1.0) ** 2, rtol=1e-15)
+    np.testing.assert_array_equal(o.eval_expression("x<0.5", 0, 4), (x < 0.5).astype(float))
+    np.testing.assert_allclose(o.eval_expression("exp(sin((x+1.0)*2.0))", 0, 4), np.exp(np.sin((x + 1.0) * 2.0)),
+                               rtol=1e-15)
+    np.testing.assert_allclose(o.eval_expression("max(x,y)+min(x,0.25)", 0, 4), np.maximum(x, y) + np.minimum(x, 0.25),
+                               rtol=1e-15)
+    # unary minus is rewritten as 0.0-...; nested calls go through the generic "name(...)" split
+    np.testing.assert_allclose(o.eval_expression("-1.0*(A*pi)*cos(A*pi*x)", 0, 4), -2.0 * np.pi * np.cos(2 * np.pi * x),
+                               rtol=1e-15)
+
+
+def test_numbering_conventions():
+    o = Oracle(config_text(mesh=problems._mesh(2, (3, 2)), physics="linearelasticity", order=1))
+    lids, offs, fixed, xyz, var = o.dofmap()
+    # Q1 quad offsets per variable follow {0,1,3,2} (discretizationInterface.cpp:302) interleaved by field
+    np.testing.assert_array_equal(offs, [[0, 2, 6, 4], [1, 3, 7, 5]])
+    # first-encounter LIDs: element 0 introduces 0..7, element 1 introduces 4 more
+    np.testing.assert_array_equal(lids[0], np.arange(8))
+    assert lids[1].max() == 11 and set(lids[1]) & set(lids[0]) == {2, 3, 4, 5}
+    rp, ci = o.crs()
+    assert rp[-1] == len(ci) and all(np.all(np.diff(ci[rp[r]:rp[r + 1]]) > 0) for r in range(o.nlocal))
+    o2 = Oracle(config_text(mesh=problems._mesh(3, (2, 2, 2)), physics="cdr", order=2))
+    assert (o2.nb, o2.nq, o2.nlocal, o2.type_AD) == (27, 27, 125, 32)
+    l2, off2, *_ = o2.dofmap()
+    assert sorted(off2[0].tolist()) == list(range(27)) and off2[0][0] == 0 and off2[0][13] == 26
