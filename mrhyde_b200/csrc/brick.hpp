@@ -1,0 +1,234 @@
+// Host-side structured brick mesh, DOF numbering, side sets, fixed-DOF flags and CRS graph.
+// In a MrHyDE build these come from Panzer-STK / Panzer DOFManager / Tpetra (third party); a caller that
+// already has them passes them through mrh_set_mesh / mrh_set_dofmap / mrh_set_crs instead.  This builder
+// exists so the engine can run standalone on the synthetic meshes of BASELINE.json and produces the same
+// conventions (checked bit-exactly against the oracle in tests/):
+//   node id i + j(NX+1) + k(NX+1)(NY+1), element id i + j NX + k NX NY, shards vertex order
+//       (/root/reference/src/tools/simplemeshmanager.hpp:892-977 is the in-repo analogue)
+//   element DOF slots: vertices, edges, faces, interior (shards order), fields interleaved per entity;
+//       offsets(var, basis) = slot*nvar + var; LIDs in first-encounter order
+//       (/root/reference/src/interfaces/discretizationInterface.cpp:2324-2418; Q1 quad {0,1,3,2} at :302)
+//   fixed DOFs = closure of strong-Dirichlet sides (:2744-2822); isFixedDOF assemblyManager.cpp:185-265
+//   CRS graph = insertGlobalIndices(gid, elemGIDs) per element + fillComplete => sorted unique columns
+//       (/root/reference/src/interfaces/linearAlgebraInterface.cpp:186-234)
+#pragma once
+#include <algorithm>
+#include <array>
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <vector>
+
+namespace mrh {
+
+struct SideSet { std::string name; int local_side = 0; std::vector<int> elems; };
+
+struct HostMesh {
+  int dim = 3, nvert = 8;
+  int64_t nelem = 0, nnode = 0;
+  std::vector<double> nodes;        // (nnode, dim)
+  std::vector<int> elem2node;       // (nelem, nvert)
+  std::vector<SideSet> sides;
+  // brick metadata (zero when the mesh was supplied by the caller)
+  int NXYZ[3] = {0, 0, 0};
+  double lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
+  int side_index(const std::string& n) const { for (size_t i = 0; i < sides.size(); ++i) if (sides[i].name == n) return (int)i; return -1; }
+};
+
+inline void build_brick(HostMesh& M, int dim, const int* Nin, const double* lo, const double* hi) {
+  M.dim = dim; M.nvert = (dim == 3) ? 8 : 4;
+  int N[3];
+  for (int d = 0; d < 3; ++d) { N[d] = (d < dim) ? Nin[d] : 1; M.NXYZ[d] = N[d]; M.lo[d] = lo[d]; M.hi[d] = hi[d]; }
+  const int64_t nx = N[0] + 1, ny = N[1] + 1, nz = (dim == 3) ? N[2] + 1 : 1, ez = (dim == 3) ? N[2] : 1;
+  M.nnode = nx * ny * nz; M.nelem = (int64_t)N[0] * N[1] * ez;
+  if (M.nnode > 2000000000LL) throw std::runtime_error("mesh too large for 32-bit node ids");
+  M.nodes.resize((size_t)M.nnode * dim);
+  for (int64_t k = 0; k < nz; ++k) for (int64_t j = 0; j < ny; ++j) for (int64_t i = 0; i < nx; ++i) {
+    const int64_t id = i + nx * (j + ny * k), g[3] = {i, j, k};
+    for (int d = 0; d < dim; ++d) M.nodes[id * dim + d] = lo[d] + (hi[d] - lo[d]) * ((double)g[d] / (double)N[d]);
+  }
+  M.elem2node.resize((size_t)M.nelem * M.nvert);
+  for (int64_t k = 0; k < ez; ++k) for (int64_t j = 0; j < N[1]; ++j) for (int64_t i = 0; i < N[0]; ++i) {
+    int* v = &M.elem2node[(size_t)(i + N[0] * (j + N[1] * k)) * M.nvert];
+    const int64_t base = i + nx * (j + ny * k);
+    v[0] = (int)base; v[1] = (int)(base + 1); v[2] = (int)(base + 1 + nx); v[3] = (int)(base + nx);
+    if (dim == 3) for (int a = 0; a < 4; ++a) v[4 + a] = v[a] + (int)(nx * ny);
+  }
+  // side sets in alphabetical order with their shards local side id
+  struct Def { const char* name; int ls, axis, high; };
+  static const Def d2[4] = {{"bottom", 0, 1, 0}, {"left", 3, 0, 0}, {"right", 1, 0, 1}, {"top", 2, 1, 1}};
+  static const Def d3[6] = {{"back", 2, 1, 1}, {"bottom", 4, 2, 0}, {"front", 0, 1, 0}, {"left", 3, 0, 0}, {"right", 1, 0, 1}, {"top", 5, 2, 1}};
+  M.sides.clear();
+  for (int s = 0; s < ((dim == 3) ? 6 : 4); ++s) {
+    const Def& D = (dim == 3) ? d3[s] : d2[s];
+    SideSet S; S.name = D.name; S.local_side = D.ls;
+    const int64_t E[3] = {N[0], N[1], ez};
+    int64_t lo3[3] = {0, 0, 0}, hi3[3] = {E[0], E[1], E[2]};
+    lo3[D.axis] = D.high ? E[D.axis] - 1 : 0; hi3[D.axis] = lo3[D.axis] + 1;
+    for (int64_t k = lo3[2]; k < hi3[2]; ++k) for (int64_t j = lo3[1]; j < hi3[1]; ++j) for (int64_t i = lo3[0]; i < hi3[0]; ++i)
+      S.elems.push_back((int)(i + E[0] * (j + E[1] * k)));
+    M.sides.push_back(S);
+  }
+}
+
+// HGRAD_Cn tensor ordinal -> entity slot of the element's DOF list, and the side closures.
+struct LocalLayout {
+  int dim = 3, p = 1, nb = 8;
+  std::vector<int> slot;                       // basis ordinal -> entity slot
+  std::vector<std::array<int, 3>> tix;         // basis ordinal -> tensor index (a,b,c) in [0,p]
+  void build(int dim_, int p_) {
+    dim = dim_; p = p_;
+    if (p != 1 && p != 2) throw std::runtime_error("only HGRAD order 1 and 2 are numbered");
+    const int m = p + 1; nb = (dim == 3) ? m * m * m : m * m;
+    // shards vertex coordinates in {0,2}^dim, then edges / faces as vertex tuples; an entity's tensor index
+    // at order 2 is the mean of its vertices' coordinates.
+    static const int vx[8][3] = {{0,0,0},{2,0,0},{2,2,0},{0,2,0},{0,0,2},{2,0,2},{2,2,2},{0,2,2}};
+    static const int hexedge[12][2] = {{0,1},{1,2},{2,3},{3,0},{4,5},{5,6},{6,7},{7,4},{0,4},{1,5},{2,6},{3,7}};
+    static const int hexface[6][4] = {{0,1,5,4},{1,2,6,5},{2,3,7,6},{0,4,7,3},{0,3,2,1},{4,5,6,7}};
+    const int nv = (dim == 3) ? 8 : 4, ne = (dim == 3) ? 12 : 4, nf = (dim == 3) ? 6 : 0;
+    std::vector<std::array<int, 3>> ent;       // entity slot -> coordinates on the {0,1,2} grid
+    for (int v = 0; v < nv; ++v) ent.push_back({vx[v][0], vx[v][1], (dim == 3) ? vx[v][2] : 0});
+    if (p == 2) {
+      for (int e = 0; e < ne; ++e) { std::array<int, 3> c{}; for (int d = 0; d < 3; ++d) c[d] = (vx[hexedge[e][0]][d] + vx[hexedge[e][1]][d]) / 2; if (dim == 2) c[2] = 0; ent.push_back(c); }
+      for (int f = 0; f < nf; ++f) { std::array<int, 3> c{}; for (int d = 0; d < 3; ++d) { int s = 0; for (int a = 0; a < 4; ++a) s += vx[hexface[f][a]][d]; c[d] = s / 4; } ent.push_back(c); }
+      ent.push_back({1, 1, (dim == 3) ? 1 : 0});
+    }
+    slot.assign(nb, -1); tix.resize(nb);
+    for (int o = 0; o < nb; ++o) {
+      const int a = o % m, b = (o / m) % m, c = (dim == 3) ? o / (m * m) : 0;
+      tix[o] = {a, b, c};
+      const int scale = (p == 1) ? 2 : 1;
+      for (size_t s = 0; s < ent.size(); ++s) if (ent[s][0] == a * scale && ent[s][1] == b * scale && ent[s][2] == c * scale) slot[o] = (int)s;
+      if (slot[o] < 0) throw std::runtime_error("entity slot lookup failed");
+    }
+  }
+  std::vector<int> side_dofs(int ls) const {    // basis ordinals in the closure of local side ls, ascending
+    static const int ax2[4] = {1, 0, 1, 0}, hi2[4] = {0, 1, 1, 0}, ax3[6] = {1, 0, 1, 0, 2, 2}, hi3[6] = {0, 1, 1, 0, 0, 1};
+    const int axis = (dim == 2) ? ax2[ls] : ax3[ls], high = (dim == 2) ? hi2[ls] : hi3[ls];
+    std::vector<int> r;
+    for (int o = 0; o < nb; ++o) if (tix[o][axis] == (high ? p : 0)) r.push_back(o);
+    return r;
+  }
+};
+
+struct HostDofs {
+  int nvar = 1, nb = 8, N = 8;
+  int64_t nlocal = 0;
+  std::vector<int> lids, offsets;      // (nelem, N), (nvar, nb)
+  std::vector<double> dofxyz;          // (nlocal, dim)
+  std::vector<int> dofvar;             // (nlocal)
+};
+
+inline void build_brick_dofs(HostDofs& D, const HostMesh& M, const LocalLayout& L, int nvar) {
+  D.nvar = nvar; D.nb = L.nb; D.N = nvar * L.nb;
+  D.offsets.resize((size_t)nvar * L.nb);
+  for (int f = 0; f < nvar; ++f) for (int o = 0; o < L.nb; ++o) D.offsets[(size_t)f * L.nb + o] = L.slot[o] * nvar + f;
+  std::vector<int> ord_of_slot(L.nb);
+  for (int o = 0; o < L.nb; ++o) ord_of_slot[L.slot[o]] = o;
+  const int p = L.p, dim = M.dim;
+  const int64_t gx = (int64_t)p * M.NXYZ[0] + 1, gy = (int64_t)p * M.NXYZ[1] + 1, gz = (dim == 3) ? (int64_t)p * M.NXYZ[2] + 1 : 1;
+  if (gx * gy * gz * nvar > 2000000000LL) throw std::runtime_error("too many DOFs for 32-bit local ids");
+  std::vector<int> first((size_t)(gx * gy * gz), -1);
+  D.lids.resize((size_t)M.nelem * D.N);
+  D.dofxyz.clear(); D.dofvar.clear();
+  D.dofxyz.reserve((size_t)(gx * gy * gz) * nvar * dim); D.dofvar.reserve((size_t)(gx * gy * gz) * nvar);
+  int next = 0;
+  const int ez = (dim == 3) ? M.NXYZ[2] : 1;
+  for (int k = 0; k < ez; ++k) for (int j = 0; j < M.NXYZ[1]; ++j) for (int i = 0; i < M.NXYZ[0]; ++i) {
+    const int64_t e = i + (int64_t)M.NXYZ[0] * (j + (int64_t)M.NXYZ[1] * k);
+    int* l = &D.lids[(size_t)e * D.N];
+    for (int s = 0; s < L.nb; ++s) {
+      const auto& t = L.tix[ord_of_slot[s]];
+      const int g[3] = {p * i + t[0], p * j + t[1], p * k + t[2]};
+      const int64_t key = g[0] + gx * (g[1] + gy * (int64_t)g[2]);
+      if (first[key] < 0) {
+        first[key] = next; next += nvar;
+        for (int f = 0; f < nvar; ++f) {
+          D.dofvar.push_back(f);
+          for (int d = 0; d < dim; ++d) D.dofxyz.push_back(M.lo[d] + (M.hi[d] - M.lo[d]) * ((double)g[d] / (double)(p * M.NXYZ[d])));
+        }
+      }
+      for (int f = 0; f < nvar; ++f) l[s * nvar + f] = first[key] + f;
+    }
+  }
+  D.nlocal = next;
+}
+
+struct HostCrs { int64_t nrows = 0; std::vector<int64_t> rowptr; std::vector<int> colind; };
+
+namespace detail {
+inline int host_threads() { unsigned n = std::thread::hardware_concurrency(); if (n == 0) n = 1; return (int)std::min(n, 64u); }
+
+// sorted-unique adjacency of every "row id" over the elements that contain it (ids: (nelem, n))
+inline void graph_from_ids(const int* ids, int64_t nelem, int n, int64_t nrows, std::vector<int64_t>& rowptr, std::vector<int>& colind) {
+  std::vector<int64_t> aptr((size_t)nrows + 1, 0);
+  for (int64_t k = 0; k < nelem * n; ++k) aptr[(size_t)ids[k] + 1]++;
+  for (int64_t r = 0; r < nrows; ++r) aptr[r + 1] += aptr[r];
+  std::vector<int> adj((size_t)aptr[nrows]);
+  { std::vector<int64_t> pos(aptr.begin(), aptr.end() - 1);
+    for (int64_t e = 0; e < nelem; ++e) for (int k = 0; k < n; ++k) adj[(size_t)pos[ids[e * n + k]]++] = (int)e; }
+  const int nt = (nrows < 4096) ? 1 : host_threads();
+  std::vector<std::vector<int>> chunk_cols(nt);
+  std::vector<int64_t> counts((size_t)nrows);
+  auto work = [&](int t) {
+    const int64_t r0 = nrows * t / nt, r1 = nrows * (t + 1) / nt;
+    std::vector<int> tmp; auto& out = chunk_cols[t];
+    for (int64_t r = r0; r < r1; ++r) {
+      tmp.clear();
+      for (int64_t a = aptr[r]; a < aptr[r + 1]; ++a) { const int* l = ids + (int64_t)adj[a] * n; tmp.insert(tmp.end(), l, l + n); }
+      std::sort(tmp.begin(), tmp.end());
+      tmp.erase(std::unique(tmp.begin(), tmp.end()), tmp.end());
+      counts[r] = (int64_t)tmp.size();
+      out.insert(out.end(), tmp.begin(), tmp.end());
+    }
+  };
+  if (nt == 1) work(0);
+  else { std::vector<std::thread> th; for (int t = 0; t < nt; ++t) th.emplace_back(work, t); for (auto& x : th) x.join(); }
+  rowptr.assign((size_t)nrows + 1, 0);
+  for (int64_t r = 0; r < nrows; ++r) rowptr[r + 1] = rowptr[r] + counts[r];
+  colind.resize((size_t)rowptr[nrows]);
+  for (int t = 0; t < nt; ++t) {
+    const int64_t r0 = nrows * t / nt;
+    if (!chunk_cols[t].empty()) memcpy(&colind[(size_t)rowptr[r0]], chunk_cols[t].data(), chunk_cols[t].size() * sizeof(int));
+  }
+}
+}  // namespace detail
+
+inline void build_crs(HostCrs& G, const int* lids, int64_t nelem, int N, int64_t nlocal, int nvar) {
+  G.nrows = nlocal;
+  // entity-blocked numbering (lid = entity*nvar + field for every slot): build the entity graph, then expand
+  bool blocked = nvar > 1 && N % nvar == 0 && nlocal % nvar == 0;
+  if (blocked) {
+    for (int64_t e = 0; e < nelem && blocked; ++e)
+      for (int s = 0; s < N / nvar && blocked; ++s) {
+        const int b = lids[e * N + s * nvar];
+        if (b % nvar != 0) blocked = false;
+        for (int f = 1; f < nvar && blocked; ++f) if (lids[e * N + s * nvar + f] != b + f) blocked = false;
+      }
+  }
+  if (!blocked) { detail::graph_from_ids(lids, nelem, N, nlocal, G.rowptr, G.colind); return; }
+  const int nbe = N / nvar;
+  std::vector<int> ent((size_t)nelem * nbe);
+  for (int64_t e = 0; e < nelem; ++e) for (int s = 0; s < nbe; ++s) ent[(size_t)e * nbe + s] = lids[e * N + s * nvar] / nvar;
+  std::vector<int64_t> erp; std::vector<int> eci;
+  detail::graph_from_ids(ent.data(), nelem, nbe, nlocal / nvar, erp, eci);
+  const int64_t nent = nlocal / nvar;
+  G.rowptr.assign((size_t)nlocal + 1, 0);
+  for (int64_t r = 0; r < nent; ++r) for (int f = 0; f < nvar; ++f) G.rowptr[(size_t)(r * nvar + f) + 1] = (erp[r + 1] - erp[r]) * nvar;
+  for (int64_t r = 0; r < nlocal; ++r) G.rowptr[r + 1] += G.rowptr[r];
+  G.colind.resize((size_t)G.rowptr[nlocal]);
+  const int nt = (nent < 4096) ? 1 : detail::host_threads();
+  auto work = [&](int t) {
+    for (int64_t r = nent * t / nt; r < nent * (t + 1) / nt; ++r)
+      for (int f = 0; f < nvar; ++f) {
+        int* out = &G.colind[(size_t)G.rowptr[r * nvar + f]];
+        for (int64_t a = erp[r]; a < erp[r + 1]; ++a) for (int g = 0; g < nvar; ++g) *out++ = eci[a] * nvar + g;
+      }
+  };
+  if (nt == 1) work(0);
+  else { std::vector<std::thread> th; for (int t = 0; t < nt; ++t) th.emplace_back(work, t); for (auto& x : th) x.join(); }
+}
+
+}  // namespace mrh

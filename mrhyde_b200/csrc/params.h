@@ -1,0 +1,69 @@
+// Launch parameter block shared by every assembly kernel (plain data, passed by value).
+#pragma once
+#include <cstdint>
+#include "bytecode.h"
+
+namespace mrh {
+
+enum Phys { PHYS_THERMAL = 0, PHYS_CDR = 1, PHYS_LE = 2, PHYS_NS = 3 };
+enum BC { BC_NONE = 0, BC_DIRICHLET = 1, BC_WEAK_DIRICHLET = 2, BC_NEUMANN = 3, BC_FLUX = 4 };
+
+// program slots inside KParams::progs
+enum { TH_SOURCE = 0, TH_DIFF, TH_CP, TH_RHO, TH_BX, TH_BY, TH_BZ };                      // thermal, "ip"
+enum { CDR_SOURCE = 0, CDR_DIFF, CDR_CP, CDR_RHO, CDR_REACTION, CDR_XVEL, CDR_YVEL, CDR_ZVEL };
+enum { LE_LAMBDA = 0, LE_MU, LE_SRC0, LE_SRC1, LE_SRC2 };
+enum { NS_SRC_UX = 0, NS_SRC_PR, NS_SRC_UY, NS_SRC_UZ, NS_DENSITY, NS_VISCOSITY };
+enum { SIDE_DIFF = 0, SIDE_LAMBDA = 0, SIDE_MU = 1, SIDE_BCSRC = 8, SIDE_FLUX = 12 };     // "side ip"
+
+struct RefTab {          // reference-element tables of one point set (volume rule, or the rule of one local side)
+  const double* B;       // [nq][NB]       field basis values
+  const double* G;       // [nq][NB][DIM]  field basis reference gradients
+  const double* VB;      // [nq][NV]       vertex (geometry) basis values, shards vertex order
+  const double* VG;      // [nq][NV][DIM]  vertex basis reference gradients
+  const double* W;       // [nq]           reference weights
+  int nq;
+  int pad_;
+  double tanU[3], tanV[3];   // reference side tangents (side launches only)
+};
+
+struct TimeParams {      // Workset::computeSolnTransientSeeded coefficients (workset.cpp:594-620)
+  int transient, nsteps, nstages, stage;
+  double alpha_u, alpha_t, timewt, time, dt;
+  double a_over_b[8];    // butcher_A(stage,s)/butcher_b(s), s < stage
+  double bdf[8];         // BDF weights
+};
+
+struct PhysParams {
+  int have_advection;    // thermal "include advection"
+  int useSUPG, usePSPG;  // navierstokes
+  int bc[4];             // BC code per variable on the current side
+  double formparam;      // thermal/LE "form_param"
+  double le_penalty;     // LE "penalty"
+};
+
+struct KParams {
+  const double* nodes;       // (nnode, DIM)
+  const int* e2n;            // (nelem, NV)
+  const int* lids;           // (nelem, N)     dof_lids
+  const uint8_t* fixed;      // (nlocal)       isFixedDOF
+  const int64_t* rowptr;     // (nlocal+1)
+  const uint16_t* pat;       // (npattern, N*N) row-relative CRS slot of (row slot, col slot)
+  const int* pat_id;         // (nelem)        pattern of each element
+  const int* elem_list;      // elements of this launch (side sets); null = 0..nwork-1
+  int64_t nwork;
+  const double* u;           // (nlocal)
+  const double* u_prev;      // (nlocal, nsteps)   transient only
+  const double* u_stage;     // (nlocal, nstages)  transient only
+  double* res;               // (nlocal)   += -r
+  double* jac;               // (nnz)      += dr/du
+  const Instr* code;
+  const double* cpool;
+  RefTab tab;
+  TimeParams tp;
+  PhysParams ph;
+  Prog progs[MRH_MAXPROG];
+  int offsets[4 * 27];       // offsets(var, basis dof) -> element slot
+  int is_side, lump_mass, compute_jac, elems_per_block;
+};
+
+}  // namespace mrh
