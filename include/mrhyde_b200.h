@@ -1,0 +1,146 @@
+/* mrhyde_b200 — C ABI of the B200-native finite-element assembly engine.
+ *
+ * The reference (dannys4/MrHyDE) has no FFI: its assembly path is C++ classes compiled into one
+ * executable.  This header is the boundary a MrHyDE maintainer would bind instead of the Kokkos loops;
+ * every entry point names the reference interface it replaces (paths relative to /root/reference).
+ * INTEGRATION.md shows the reference-side glue (AssemblyManager / PhysicsBase / FunctionManager shims).
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative MRH_E* code; mrh_last_error() gives the text;
+ *     nothing throws across the ABI.
+ *   - set-up arrays (mesh, LIDs, CRS graph, side sets) are HOST pointers, copied by the engine.
+ *   - hot-path arrays (solution, residual, Jacobian values) are DEVICE pointers owned by the caller —
+ *     the Tpetra local views the reference extracts at src/managers/assemblyManager.cpp:2172-2178 —
+ *     except in the *_host convenience calls.
+ *   - residual is SUBTRACTED (res += -r), Jacobian is ADDED (assemblyManager.cpp:4094-4141); the caller
+ *     zeroes both beforehand (src/managers/solverManager.cpp:1528-1533).
+ *   - one handle per GPU; a handle is not re-entrant (same contract as one AssemblyManager per rank).
+ */
+#ifndef MRHYDE_B200_H
+#define MRHYDE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mrh_engine* mrh_handle;
+
+enum {
+  MRH_OK = 0,
+  MRH_EINVAL = -1,      /* bad argument / call order */
+  MRH_EPARSE = -2,      /* expression could not be decomposed (functionManager.cpp:431) */
+  MRH_EUNSUPPORTED = -3,/* feature outside the hot-path scope */
+  MRH_ECUDA = -4,       /* CUDA runtime error (no CPU fallback exists) */
+  MRH_ENOMEM = -5
+};
+
+/* BC codes of var_bcs(var, side): src/interfaces/discretizationInterface.cpp:2556-2593 */
+enum { MRH_BC_NONE = 0, MRH_BC_DIRICHLET = 1, MRH_BC_WEAK_DIRICHLET = 2, MRH_BC_NEUMANN = 3, MRH_BC_FLUX = 4 };
+
+/* Replaces the slice of the YAML ParameterList the path reads (src/interfaces/userInterface.hpp):
+ * Physics/modules, Discretization/order + quadrature, Solver/{use strong DBCs, fix zero rows, lump mass},
+ * module settings (thermal.cpp:24-41, linearelasticity.cpp:21-61, navierstokes.cpp:20-62). */
+typedef struct mrh_config {
+  int32_t dim;                /* 2 or 3 */
+  const char* physics;        /* "thermal" | "cdr" | "linearelasticity" | "navierstokes" */
+  int32_t order;              /* HGRAD order, 1 or 2 */
+  int32_t quadrature;         /* volume cubature degree; <0 = 2*order (discretizationInterface.cpp:166) */
+  int32_t side_quadrature;    /* side cubature degree;   <0 = 2*order (:203) */
+  int32_t use_strong_dbc;     /* Solver/use strong DBCs   (assemblyManager.cpp:34) */
+  int32_t fix_zero_rows;      /* Solver/fix zero rows     (:37) */
+  int32_t lump_mass;          /* Solver/lump mass         (:40) */
+  int32_t include_advection;  /* thermal "include advection" */
+  int32_t use_supg;           /* navierstokes "useSUPG" */
+  int32_t use_pspg;           /* navierstokes "usePSPG" */
+  double form_param;          /* thermal / LE "form_param" (default 1.0) */
+  double le_penalty;          /* LE "penalty" (default 10.0) */
+  int32_t device;             /* CUDA device ordinal */
+  int32_t reserved;
+} mrh_config;
+
+/* Workset time data: Workset::{time,deltat,isTransient,current_stage,butcher_A,butcher_b,BDF_wts}
+ * (src/tools/workset.hpp; set by AssemblyManager::setWorksetButcher/BDF, updateStage, updateTimeStep). */
+typedef struct mrh_state {
+  const double* u;            /* device (nlocal)            current / stage solution   sol[set]       */
+  const double* u_prev;       /* device (nlocal, nsteps)    previous steps, or NULL    sol_prev[set]  */
+  const double* u_stage;      /* device (nlocal, nstages)   previous stages, or NULL   sol_stage[set] */
+  int32_t is_transient;
+  int32_t nstages, nsteps, stage;
+  const double* butcher_A;    /* host (nstages,nstages) */
+  const double* butcher_b;    /* host (nstages) */
+  const double* bdf_wts;      /* host (nsteps+1) */
+  double time, deltat;
+  void* stream;               /* cudaStream_t, NULL = default stream */
+} mrh_state;
+
+void mrh_default_config(mrh_config* cfg);
+int mrh_create(const mrh_config* cfg, mrh_handle* out);
+int mrh_destroy(mrh_handle h);
+const char* mrh_last_error(mrh_handle h);            /* h may be NULL: error of the last failed mrh_create */
+
+/* ---- set-up: either build the synthetic brick ... ------------------------------------------------ */
+/* Stands in for panzer_stk::{SquareQuad,CubeHex}MeshFactory (src/interfaces/meshInterface.cpp:128-171),
+ * Panzer DOFManager (discretizationInterface.cpp:2324-2418) and LinearAlgebraInterface::setupLinearAlgebra
+ * (src/interfaces/linearAlgebraInterface.cpp:145-239) on a uniform brick. */
+int mrh_build_brick(mrh_handle h, const int32_t* nxyz, const double* lo, const double* hi);
+
+/* ---- ... or hand over what Panzer/Tpetra already built ------------------------------------------- */
+/* nodes (nnode,dim), elem2node (nelem, 4|8) shards vertex order: Group::nodes, assemblyManager.cpp:684-688 */
+int mrh_set_mesh(mrh_handle h, const double* nodes, int64_t nnode, const int32_t* elem2node, int64_t nelem);
+/* lids (nelem, nvar*nb) = disc->dof_lids, offsets (nvar, nb) = wkset->offsets (assemblyManager.cpp:656-669) */
+int mrh_set_dofmap(mrh_handle h, const int32_t* lids, const int32_t* offsets, int64_t nlocal);
+/* local graph of the overlapped matrix (linearAlgebraInterface.cpp:219-234); columns ascending per row */
+int mrh_set_crs(mrh_handle h, const int64_t* rowptr, const int32_t* colind, int64_t nrows);
+/* one boundary side set: BoundaryGroup key (sideset, local side id), assemblyManager.cpp:397-503 */
+int mrh_add_side(mrh_handle h, const char* name, int32_t local_side, const int32_t* elems, int64_t n);
+
+/* ---- boundary conditions and coefficient functions ----------------------------------------------- */
+/* Dirichlet/Neumann/Flux condition of `var` on `side` ("all boundaries" allowed): registers the function
+ * "<Dirichlet|Neumann|Flux> <var> <side>" at "side ip" (src/interfaces/physicsInterface.cpp:156-478) and
+ * sets var_bcs; a Dirichlet entry with weak=0 marks the side's closure DOFs fixed (createFixedDOFs,
+ * assemblyManager.cpp:185-265). */
+int mrh_set_bc(mrh_handle h, const char* var, const char* side, int32_t bc_code, const char* expr);
+/* FunctionManager::addFunction(name, expr, location) — src/managers/functionManager.cpp:49-69.
+ * Entries of the user's Functions list are added at both "ip" and "side ip" (physicsInterface.cpp:466-483). */
+int mrh_add_function(mrh_handle h, const char* name, const char* expr, const char* location);
+
+/* AssemblyManager::{createGroups, allocateGroupStorage, createWorkset, finalizeFunctions, createFixedDOFs}:
+ * compiles the expressions, builds slot-pattern dictionary and fixed-DOF tables, uploads everything. */
+int mrh_finalize(mrh_handle h);
+/* Host-only part of mrh_finalize (expression compilation, fixed DOFs); needs no GPU.  mrh_finalize calls it. */
+int mrh_finalize_host(mrh_handle h);
+
+/* ---- the hot path --------------------------------------------------------------------------------- */
+/* AssemblyManager::assembleRes  (assemblyManager.cpp:2916-3150): res += -r(u) */
+int mrh_assemble_res(mrh_handle h, const mrh_state* st, double* res);
+/* AssemblyManager::assembleJacRes (assemblyManager.cpp:2045-2665) incl. dofConstraints/updateJacDBC (:3158, :1167)
+ * and fix-zero-rows (:2644-2663): res += -r(u), jac += dr/du on the CRS values aligned with colind. */
+int mrh_assemble_jacres(mrh_handle h, const mrh_state* st, double* res, double* jac);
+/* Same call with HOST buffers (pinned or pageable): copies u in, zeroes, assembles, copies res and jac out. */
+int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res_host, double* jac_host);
+
+/* ---- introspection (parity tests, bindings) ------------------------------------------------------ */
+/* out[16]: dim, nelem, nnode, nvert, nvar, nb, ndof_elem, nlocal, nnz, nq, nqs, nsides, npatterns, nfixed, 0, 0 */
+int mrh_get_sizes(mrh_handle h, int64_t* out);
+int mrh_get_mesh(mrh_handle h, double* nodes, int32_t* elem2node);
+int mrh_get_dofmap(mrh_handle h, int32_t* lids, int32_t* offsets, uint8_t* is_fixed, double* dofxyz, int32_t* dofvar);
+int mrh_get_crs(mrh_handle h, int64_t* rowptr, int32_t* colind);
+int mrh_get_side(mrh_handle h, int32_t s, char* name, int32_t namelen, int32_t* local_side, int32_t* elems);
+int mrh_get_bc(mrh_handle h, int32_t var, int32_t side);
+const char* mrh_get_varname(mrh_handle h, int32_t var);
+/* evaluate a registered "ip" function on host doubles at given points (parser known-answer tests) */
+int mrh_eval_function_host(mrh_handle h, const char* name, const char* location, int64_t npts, const double* xyz,
+                           double time, double* out);
+/* number of kernels launched by the last assemble call (bench.py "gpu_launches") */
+int64_t mrh_last_launch_count(mrh_handle h);
+/* device time of the dominant (volume) kernel of the last assemble call, ms (CUDA events on the caller's stream) */
+double mrh_last_volume_kernel_ms(mrh_handle h);
+/* micro-benchmarks used for the roofline denominators: FP64 FMA peak (TFLOP/s) and RED.F64 throughput (G/s) */
+int mrh_microbench(int32_t device, double* dfma_tflops, double* red_gops, double* copy_gbs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MRHYDE_B200_H */

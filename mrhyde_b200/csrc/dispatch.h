@@ -1,0 +1,18 @@
+// Run-time (physics, dim, order) -> compile-time kernel configuration.
+#pragma once
+#include "assemble.h"
+
+namespace mrh {
+
+template <class F>
+inline bool dispatch_cfg(int phys, int dim, int order, F&& f) {
+#define MRH_CASE(PH, D, O) if (phys == PH && dim == D && order == O) { f(GenCfg<PH, D, O>{}); return true; }
+  MRH_CASE(PHYS_THERMAL, 2, 1) MRH_CASE(PHYS_THERMAL, 2, 2) MRH_CASE(PHYS_THERMAL, 3, 1) MRH_CASE(PHYS_THERMAL, 3, 2)
+  MRH_CASE(PHYS_CDR, 2, 1) MRH_CASE(PHYS_CDR, 2, 2) MRH_CASE(PHYS_CDR, 3, 1) MRH_CASE(PHYS_CDR, 3, 2)
+  MRH_CASE(PHYS_LE, 2, 1) MRH_CASE(PHYS_LE, 2, 2) MRH_CASE(PHYS_LE, 3, 1)
+  MRH_CASE(PHYS_NS, 2, 1) MRH_CASE(PHYS_NS, 2, 2) MRH_CASE(PHYS_NS, 3, 1)
+#undef MRH_CASE
+  return false;
+}
+
+}  // namespace mrh

@@ -1,0 +1,309 @@
+"""ctypes binding of include/mrhyde_b200.h (test / bench harness; not on the hot path)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIBS = {}
+
+
+class MrhError(RuntimeError):
+    pass
+
+
+class MrhConfig(C.Structure):
+    _fields_ = [("dim", C.c_int32), ("physics", C.c_char_p), ("order", C.c_int32), ("quadrature", C.c_int32),
+                ("side_quadrature", C.c_int32), ("use_strong_dbc", C.c_int32), ("fix_zero_rows", C.c_int32),
+                ("lump_mass", C.c_int32), ("include_advection", C.c_int32), ("use_supg", C.c_int32),
+                ("use_pspg", C.c_int32), ("form_param", C.c_double), ("le_penalty", C.c_double),
+                ("device", C.c_int32), ("reserved", C.c_int32)]
+
+
+class MrhState(C.Structure):
+    _fields_ = [("u", C.c_void_p), ("u_prev", C.c_void_p), ("u_stage", C.c_void_p), ("is_transient", C.c_int32),
+                ("nstages", C.c_int32), ("nsteps", C.c_int32), ("stage", C.c_int32), ("butcher_A", C.c_void_p),
+                ("butcher_b", C.c_void_p), ("bdf_wts", C.c_void_p), ("time", C.c_double), ("deltat", C.c_double),
+                ("stream", C.c_void_p)]
+
+
+SYMBOLS = ["mrh_default_config", "mrh_create", "mrh_destroy", "mrh_last_error", "mrh_build_brick", "mrh_set_mesh",
+           "mrh_set_dofmap", "mrh_set_crs", "mrh_add_side", "mrh_set_bc", "mrh_add_function", "mrh_finalize",
+           "mrh_finalize_host", "mrh_assemble_res", "mrh_assemble_jacres", "mrh_assemble_jacres_host",
+           "mrh_get_sizes", "mrh_get_mesh", "mrh_get_dofmap", "mrh_get_crs", "mrh_get_side", "mrh_get_bc",
+           "mrh_get_varname", "mrh_eval_function_host", "mrh_last_launch_count", "mrh_last_volume_kernel_ms",
+           "mrh_microbench"]
+
+
+def lib_path():
+    return os.path.join(_HERE, "libmrhyde_b200.so")
+
+
+def load_library(path=None):
+    path = path or lib_path()
+    if path in _LIBS:
+        return _LIBS[path]
+    if not os.path.exists(path):
+        raise MrhError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(there is no CPU fallback)")
+    L = C.CDLL(path)
+    L.mrh_last_error.restype = C.c_char_p
+    L.mrh_last_error.argtypes = [C.c_void_p]
+    L.mrh_get_varname.restype = C.c_char_p
+    L.mrh_get_varname.argtypes = [C.c_void_p, C.c_int32]
+    L.mrh_last_launch_count.restype = C.c_int64
+    L.mrh_last_launch_count.argtypes = [C.c_void_p]
+    L.mrh_last_volume_kernel_ms.restype = C.c_double
+    L.mrh_last_volume_kernel_ms.argtypes = [C.c_void_p]
+    L.mrh_create.argtypes = [C.POINTER(MrhConfig), C.POINTER(C.c_void_p)]
+    for n in ("mrh_destroy", "mrh_finalize", "mrh_finalize_host"):
+        getattr(L, n).argtypes = [C.c_void_p]
+    L.mrh_build_brick.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.mrh_set_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+    L.mrh_set_dofmap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    L.mrh_set_crs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    L.mrh_add_side.argtypes = [C.c_void_p, C.c_char_p, C.c_int32, C.c_void_p, C.c_int64]
+    L.mrh_set_bc.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_char_p]
+    L.mrh_add_function.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p]
+    L.mrh_assemble_res.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p]
+    L.mrh_assemble_jacres.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p]
+    L.mrh_assemble_jacres_host.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p]
+    L.mrh_get_sizes.argtypes = [C.c_void_p, C.c_void_p]
+    L.mrh_get_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.mrh_get_dofmap.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+    L.mrh_get_crs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.mrh_get_side.argtypes = [C.c_void_p, C.c_int32, C.c_char_p, C.c_int32, C.c_void_p, C.c_void_p]
+    L.mrh_get_bc.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+    L.mrh_eval_function_host.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_void_p, C.c_double,
+                                         C.c_void_p]
+    L.mrh_microbench.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+    _LIBS[path] = L
+    return L
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):      # torch tensor
+        return a.data_ptr()
+    return int(a)
+
+
+BC_CODES = {"dirichlet": 1, "weak_dirichlet": 2, "neumann": 3, "flux": 4}
+SIZE_NAMES = ["dim", "nelem", "nnode", "nvert", "nvar", "nb", "ndof_elem", "nlocal", "nnz", "nq", "nqs", "nsides",
+              "npatterns", "nfixed"]
+
+
+class Engine:
+    """One assembly engine handle (== one AssemblyManager on one GPU)."""
+
+    def __init__(self, physics, dim, order=1, lib=None, device=0, quadrature=-1, side_quadrature=-1,
+                 use_strong_dbc=True, fix_zero_rows=False, lump_mass=False, settings=None):
+        self.L = load_library(lib)
+        settings = settings or {}
+        cfg = MrhConfig()
+        self.L.mrh_default_config(C.byref(cfg))
+        self._physics = physics.encode()
+        cfg.dim, cfg.physics, cfg.order = dim, self._physics, order
+        cfg.quadrature, cfg.side_quadrature = quadrature, side_quadrature
+        cfg.use_strong_dbc, cfg.fix_zero_rows, cfg.lump_mass = int(use_strong_dbc), int(fix_zero_rows), int(lump_mass)
+        cfg.include_advection = int(bool(settings.get("include advection", False)))
+        cfg.use_supg = int(bool(settings.get("useSUPG", False)))
+        cfg.use_pspg = int(bool(settings.get("usePSPG", False)))
+        cfg.form_param = float(settings.get("form_param", 1.0))
+        cfg.le_penalty = float(settings.get("penalty", 10.0))
+        cfg.device = device
+        self.h = C.c_void_p()
+        rc = self.L.mrh_create(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            raise MrhError(f"mrh_create failed ({rc}): {self.L.mrh_last_error(None).decode()}")
+        self._keep = []
+
+    # -------------------------------------------------------------------------------------------------
+    def _ck(self, rc, what):
+        if rc < 0:
+            raise MrhError(f"{what} failed ({rc}): {self.L.mrh_last_error(self.h).decode()}")
+        return rc
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.mrh_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @classmethod
+    def from_problem(cls, p, lib=None, device=0, finalize=True, host_only=False):
+        """Build an engine from a tests/problems.py style dict (same dict drives the oracle)."""
+        extra = p.get("extra", {})
+        weak = bool(extra.get("use weak Dirichlet", False))
+        m = p["mesh"]
+        e = cls(p["physics"], m["dim"], p.get("order", 1), lib=lib, device=device,
+                quadrature=extra.get("quadrature", -1), side_quadrature=extra.get("side quadrature", -1),
+                use_strong_dbc=extra.get("use strong DBCs", True), fix_zero_rows=extra.get("fix zero rows", False),
+                lump_mass=extra.get("lump mass", False), settings=p.get("settings", {}))
+        n = [m["NX"], m["NY"], m.get("NZ", 1)]
+        lo = [m.get("xmin", 0.0), m.get("ymin", 0.0), m.get("zmin", 0.0)]
+        hi = [m.get("xmax", 1.0), m.get("ymax", 1.0), m.get("zmax", 1.0)]
+        e.build_brick(n, lo, hi)
+        for name, expr in p.get("functions", {}).items():       # physicsInterface.cpp:466-483: both locations
+            e.add_function(name, expr, "ip")
+            e.add_function(name, expr, "side ip")
+        for var, sides in p.get("dirichlet", {}).items():
+            for side, expr in sides.items():
+                e.set_bc(var, side, "weak_dirichlet" if weak else "dirichlet", expr)
+        for kind in ("neumann", "flux"):
+            for var, sides in p.get(kind, {}).items():
+                for side, expr in sides.items():
+                    e.set_bc(var, side, kind, expr)
+        if host_only:
+            e.finalize_host()
+        elif finalize:
+            e.finalize()
+        return e
+
+    # ---- set-up --------------------------------------------------------------------------------------
+    def build_brick(self, nxyz, lo=(0, 0, 0), hi=(1, 1, 1)):
+        n = np.asarray(list(nxyz) + [1] * (3 - len(nxyz)), dtype=np.int32)
+        lo = np.asarray(list(lo) + [0.0] * (3 - len(lo)), dtype=np.float64)
+        hi = np.asarray(list(hi) + [1.0] * (3 - len(hi)), dtype=np.float64)
+        self._ck(self.L.mrh_build_brick(self.h, _ptr(n), _ptr(lo), _ptr(hi)), "mrh_build_brick")
+
+    def set_mesh(self, nodes, elem2node):
+        nodes = np.ascontiguousarray(nodes, dtype=np.float64)
+        e2n = np.ascontiguousarray(elem2node, dtype=np.int32)
+        self._ck(self.L.mrh_set_mesh(self.h, _ptr(nodes), nodes.shape[0], _ptr(e2n), e2n.shape[0]), "mrh_set_mesh")
+
+    def set_dofmap(self, lids, offsets, nlocal):
+        lids = np.ascontiguousarray(lids, dtype=np.int32)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int32)
+        self._ck(self.L.mrh_set_dofmap(self.h, _ptr(lids), _ptr(offsets), nlocal), "mrh_set_dofmap")
+
+    def set_crs(self, rowptr, colind):
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+        colind = np.ascontiguousarray(colind, dtype=np.int32)
+        self._ck(self.L.mrh_set_crs(self.h, _ptr(rowptr), _ptr(colind), len(rowptr) - 1), "mrh_set_crs")
+
+    def add_side(self, name, local_side, elems):
+        elems = np.ascontiguousarray(elems, dtype=np.int32)
+        self._ck(self.L.mrh_add_side(self.h, name.encode(), local_side, _ptr(elems), len(elems)), "mrh_add_side")
+
+    def set_bc(self, var, side, kind, expr):
+        self._ck(self.L.mrh_set_bc(self.h, var.encode(), side.encode(), BC_CODES[kind], str(expr).encode()),
+                 "mrh_set_bc")
+
+    def add_function(self, name, expr, location="ip"):
+        self._ck(self.L.mrh_add_function(self.h, name.encode(), str(expr).encode(), location.encode()),
+                 "mrh_add_function")
+
+    def finalize(self):
+        self._ck(self.L.mrh_finalize(self.h), "mrh_finalize")
+
+    def finalize_host(self):
+        self._ck(self.L.mrh_finalize_host(self.h), "mrh_finalize_host")
+
+    # ---- introspection -------------------------------------------------------------------------------
+    def sizes(self):
+        s = np.zeros(16, dtype=np.int64)
+        self._ck(self.L.mrh_get_sizes(self.h, _ptr(s)), "mrh_get_sizes")
+        return dict(zip(SIZE_NAMES, (int(v) for v in s)))
+
+    def mesh(self):
+        s = self.sizes()
+        nodes = np.zeros((s["nnode"], s["dim"]))
+        e2n = np.zeros((s["nelem"], s["nvert"]), dtype=np.int32)
+        self._ck(self.L.mrh_get_mesh(self.h, _ptr(nodes), _ptr(e2n)), "mrh_get_mesh")
+        return nodes, e2n
+
+    def dofmap(self, fixed=True, coords=True):
+        s = self.sizes()
+        lids = np.zeros((s["nelem"], s["ndof_elem"]), dtype=np.int32)
+        offs = np.zeros((s["nvar"], s["nb"]), dtype=np.int32)
+        fx = np.zeros(s["nlocal"], dtype=np.uint8) if fixed else None
+        xyz = np.zeros((s["nlocal"], s["dim"])) if coords else None
+        var = np.zeros(s["nlocal"], dtype=np.int32) if coords else None
+        self._ck(self.L.mrh_get_dofmap(self.h, _ptr(lids), _ptr(offs), _ptr(fx), _ptr(xyz), _ptr(var)),
+                 "mrh_get_dofmap")
+        return lids, offs, fx, xyz, var
+
+    def dof_coords(self):
+        s = self.sizes()
+        xyz = np.zeros((s["nlocal"], s["dim"]))
+        var = np.zeros(s["nlocal"], dtype=np.int32)
+        self._ck(self.L.mrh_get_dofmap(self.h, None, None, None, _ptr(xyz), _ptr(var)), "mrh_get_dofmap")
+        return xyz, var
+
+    def crs(self):
+        s = self.sizes()
+        rowptr = np.zeros(s["nlocal"] + 1, dtype=np.int64)
+        colind = np.zeros(s["nnz"], dtype=np.int32)
+        self._ck(self.L.mrh_get_crs(self.h, _ptr(rowptr), _ptr(colind)), "mrh_get_crs")
+        return rowptr, colind
+
+    def sides(self):
+        out = []
+        for s in range(self.sizes()["nsides"]):
+            buf = C.create_string_buffer(64)
+            ls = C.c_int32(0)
+            n = self._ck(self.L.mrh_get_side(self.h, s, buf, 64, C.byref(ls), None), "mrh_get_side")
+            el = np.zeros(n, dtype=np.int32)
+            self.L.mrh_get_side(self.h, s, None, 0, None, _ptr(el))
+            out.append((buf.value.decode(), ls.value, el))
+        return out
+
+    def bc_codes(self):
+        s = self.sizes()
+        return np.array([[self.L.mrh_get_bc(self.h, v, k) for k in range(s["nsides"])] for v in range(s["nvar"])],
+                        dtype=np.int32)
+
+    def varnames(self):
+        return [self.L.mrh_get_varname(self.h, v).decode() for v in range(self.sizes()["nvar"])]
+
+    def eval_function(self, name, xyz, location="ip", time=0.0):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+        out = np.zeros(xyz.shape[0])
+        self._ck(self.L.mrh_eval_function_host(self.h, name.encode(), location.encode(), xyz.shape[0], _ptr(xyz),
+                                               time, _ptr(out)), "mrh_eval_function_host")
+        return out
+
+    # ---- hot path ------------------------------------------------------------------------------------
+    def _state(self, u, u_prev=None, u_stage=None, time_int=None, stream=None):
+        st = MrhState()
+        st.u, st.u_prev, st.u_stage = _ptr(u), _ptr(u_prev), _ptr(u_stage)
+        st.time, st.deltat = 0.0, 1.0
+        if time_int is not None:
+            A = np.ascontiguousarray(time_int["A"], dtype=np.float64)
+            b = np.ascontiguousarray(time_int["b"], dtype=np.float64)
+            bdf = np.ascontiguousarray(time_int["bdf"], dtype=np.float64)
+            self._keep = [A, b, bdf]
+            st.is_transient = 1
+            st.nstages, st.nsteps, st.stage = len(b), len(bdf) - 1, int(time_int.get("stage", 0))
+            st.butcher_A, st.butcher_b, st.bdf_wts = _ptr(A), _ptr(b), _ptr(bdf)
+            st.time, st.deltat = float(time_int.get("time", 0.0)), float(time_int["dt"])
+        st.stream = stream
+        return st
+
+    def assemble_res(self, u, res, **kw):
+        st = self._state(u, **kw)
+        self._ck(self.L.mrh_assemble_res(self.h, C.byref(st), _ptr(res)), "mrh_assemble_res")
+
+    def assemble_jacres(self, u, res, jac, **kw):
+        st = self._state(u, **kw)
+        self._ck(self.L.mrh_assemble_jacres(self.h, C.byref(st), _ptr(res), _ptr(jac)), "mrh_assemble_jacres")
+
+    def assemble_jacres_host(self, u, res, jac, **kw):
+        st = self._state(u, **kw)
+        self._ck(self.L.mrh_assemble_jacres_host(self.h, C.byref(st), _ptr(res), _ptr(jac)),
+                 "mrh_assemble_jacres_host")
+
+    def launch_count(self):
+        return int(self.L.mrh_last_launch_count(self.h))
+
+    def volume_kernel_ms(self):
+        return float(self.L.mrh_last_volume_kernel_ms(self.h))

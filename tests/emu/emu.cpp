@@ -1,0 +1,112 @@
+// TEST INFRASTRUCTURE (not product code): steps the product's __host__ __device__ kernel phases
+// (mrhyde_b200/csrc/assemble.h) on the CPU so the kernel arithmetic can be checked against the oracle in the
+// GPU-less build container.  Exports the same C ABI as libmrhyde_b200.so so tests drive both with one wrapper.
+// The product library never links or calls this file; without a GPU the product fails with MRH_ECUDA.
+#include "../../mrhyde_b200/csrc/capi_host.inl"
+#include "../../mrhyde_b200/csrc/dispatch.h"
+
+using namespace mrh;
+
+struct EmuImpl {
+  std::vector<uint16_t> pat; std::vector<int> pat_id;
+  int64_t launches = 0;
+};
+
+static int backend_create(mrh_engine* h) { h->impl = new EmuImpl(); return MRH_OK; }
+static void backend_destroy(mrh_engine* h) { delete (EmuImpl*)h->impl; }
+
+template <class C>
+static void run_launch(const KParams& kp) {
+  using G = GenPhases<C>;
+  const int EB = 3;
+  const bool jac = kp.compute_jac != 0;
+  GenSmem<C> L(EB, kp.tab.nq, jac, kp.tp.transient != 0);
+  std::vector<double> sm(L.total_doubles());
+  for (int64_t blk0 = 0; blk0 < kp.nwork; blk0 += EB) {
+    for (int it = 0; it < EB * C::N; ++it) G::gather_dof(kp, L, sm.data(), blk0, it);
+    for (int it = 0; it < EB * C::NV; ++it) G::gather_vertex(kp, L, sm.data(), blk0, it);
+    for (int it = 0; it < EB * L.nq; ++it) G::geometry(kp, L, sm.data(), blk0, it);
+    for (int it = 0; it < EB * L.nq; ++it) {
+      if (jac) G::template point<PAD<C::P>>(kp, L, sm.data(), blk0, it);
+      else G::template point<double>(kp, L, sm.data(), blk0, it);
+    }
+    for (int it = 0; it < EB * C::NB * C::NVAR; ++it) G::contract(kp, L, sm.data(), blk0, it);
+  }
+}
+
+static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac) {
+  auto& H = h->host; auto* E = (EmuImpl*)h->impl;
+  if (!H.host_final || E->pat_id.empty()) throw std::runtime_error("mrh_finalize has not been called");
+  BasePtrs bp;
+  bp.nodes = H.mesh.nodes.data(); bp.e2n = H.mesh.elem2node.data(); bp.lids = H.dofs.lids.data(); bp.fixed = H.isFixed.data();
+  bp.rowptr = H.crs.rowptr.data(); bp.pat = E->pat.data(); bp.pat_id = E->pat_id.data();
+  bp.code = H.ec.code.data(); bp.cpool = H.ec.cpool.data();
+  auto tab = [](const PointTables& T) { RefTab r{}; r.B = T.B.data(); r.G = T.G.data(); r.VB = T.VB.data(); r.VG = T.VG.data(); r.W = T.W.data(); r.nq = T.nq;
+    for (int c = 0; c < 3; ++c) { r.tanU[c] = T.tanU[c]; r.tanV[c] = T.tanV[c]; } return r; };
+  bp.vol_tab = tab(H.ref.vol);
+  for (int s = 0; s < H.ref.nsides; ++s) bp.side_tab[s] = tab(H.ref.side[s]);
+  E->launches = 0;
+  for (int side = -1; side < (int)H.side_launches.size(); ++side) {
+    if (side >= 0 && !H.side_launches[side].active) continue;
+    KParams kp;
+    H.fillParams(kp, bp, *st, res, jac, side, side >= 0 ? H.mesh.sides[side].elems.data() : nullptr);
+    if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_launch<decltype(c)>(kp); }))
+      throw std::runtime_error("configuration not supported");
+    E->launches++;
+  }
+  if (jac) {
+    auto diag = [&](int r) { for (int64_t p = H.crs.rowptr[r]; p < H.crs.rowptr[r + 1]; ++p) if (H.crs.colind[p] == r) return p; return (int64_t)-1; };
+    for (int d : H.dbc_dofs) { const int64_t p = diag(d); if (p >= 0) jac[p] = 1.0; }
+    if (H.cfg.fix_zero_rows)
+      for (int64_t r = 0; r < H.crs.nrows; ++r) {
+        double s = 0.0; for (int64_t p = H.crs.rowptr[r]; p < H.crs.rowptr[r + 1]; ++p) s += std::fabs(jac[p]);
+        if (s < 1.0e-14) { const int64_t p = diag((int)r); if (p >= 0) jac[p] = 1.0; }
+      }
+  }
+  return MRH_OK;
+}
+
+extern "C" {
+
+int mrh_finalize(mrh_handle h) {
+  if (!h) return MRH_EINVAL;
+  MRH_TRY(h)
+  auto& H = h->host; auto* E = (EmuImpl*)h->impl;
+  H.finalizeHost();
+  const int N = H.N;
+  E->pat.assign((size_t)H.mesh.nelem * N * N, 0); E->pat_id.resize((size_t)H.mesh.nelem);
+  for (int64_t e = 0; e < H.mesh.nelem; ++e) {
+    E->pat_id[e] = (int)e;
+    const int* l = &H.dofs.lids[(size_t)e * N];
+    for (int r = 0; r < N; ++r) {
+      const int64_t b = H.crs.rowptr[l[r]], en = H.crs.rowptr[l[r] + 1];
+      for (int c = 0; c < N; ++c) {
+        const int* it = std::lower_bound(&H.crs.colind[b], &H.crs.colind[0] + en, l[c]);
+        if (it == &H.crs.colind[0] + en || *it != l[c]) throw std::runtime_error("CRS graph misses an element coupling");
+        E->pat[((size_t)e * N + r) * N + c] = (uint16_t)(it - &H.crs.colind[b]);
+      }
+    }
+  }
+  return MRH_OK;
+  MRH_CATCH(h)
+}
+int mrh_assemble_res(mrh_handle h, const mrh_state* st, double* res) {
+  if (!h || !st || !res) return MRH_EINVAL;
+  MRH_TRY(h) return emu_assemble(h, st, res, nullptr); MRH_CATCH(h)
+}
+int mrh_assemble_jacres(mrh_handle h, const mrh_state* st, double* res, double* jac) {
+  if (!h || !st || !res || !jac) return MRH_EINVAL;
+  MRH_TRY(h) return emu_assemble(h, st, res, jac); MRH_CATCH(h)
+}
+int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st, double* res, double* jac) {
+  if (!h || !st || !res || !jac) return MRH_EINVAL;
+  MRH_TRY(h)
+  memset(res, 0, sizeof(double) * h->host.dofs.nlocal); memset(jac, 0, sizeof(double) * h->host.crs.colind.size());
+  return emu_assemble(h, st, res, jac);
+  MRH_CATCH(h)
+}
+int64_t mrh_last_launch_count(mrh_handle h) { return h ? ((EmuImpl*)h->impl)->launches : 0; }
+double mrh_last_volume_kernel_ms(mrh_handle) { return 0.0; }
+int mrh_microbench(int32_t, double*, double*, double*) { return MRH_EUNSUPPORTED; }
+
+}  // extern "C"
