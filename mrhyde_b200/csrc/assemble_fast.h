@@ -1,0 +1,215 @@
+// Specialised volume kernel for the headline configuration: thermal, HGRAD Q1 hexahedra, 2x2x2 Gauss rule,
+// coefficients that do not depend on the solution (BASELINE.json configs[1]).  One thread owns one element and
+// keeps everything — vertex coordinates, gathered DOFs, J / J^-1, the 8 physical gradients, the 8 residual
+// entries and the 8x8 element matrix — in registers; nothing goes through shared or global scratch.
+// It fuses what the reference runs as separate Kokkos launches per 100-element group:
+//   "assembly gather"                    /root/reference/src/managers/assemblyManager.cpp:3633-3641
+//   "wkset reset res" / seeding          /root/reference/src/tools/workset.cpp:430-459, :589-623, :836-857
+//   setJacobian/Inv/Det, HGRADtransformGRAD, computeCellMeasure
+//                                        /root/reference/src/interfaces/discretizationInterface.cpp:771-774, :923-971
+//   "wkset soln ip HGRAD" (e, grad e, e_t) workset.cpp:1044-1056
+//   "funcman evaluate <op>" (one launch per DAG node)   /root/reference/src/managers/functionManager.cpp:744-1900
+//   "Thermal volume resid 3D part 1"     /root/reference/src/physics/thermal.cpp:125-163
+//   "assembly insert Jac"                assemblyManager.cpp:4063-4144
+// Derivative lanes: with state-independent coefficients d r_i / d u_j = sum_q [rho cp alpha_t phi_i phi_j
+//   + kappa alpha_u grad phi_i . grad phi_j + alpha_u (b . grad phi_j) phi_i] w, written out explicitly; without
+// advection the element matrix is symmetric and only its 36 upper entries are accumulated.
+// For Q1 the field basis equals the vertex (geometry) basis, so everything is indexed by element slot
+// (= shards vertex) and the 2-point Gauss tables are compile-time constants of the unrolled point loop.
+#pragma once
+#include "assemble.h"
+
+namespace mrh {
+
+struct HexQ1 {
+  static constexpr double g = 0.57735026918962576451;   // 1/sqrt(3); 2-point Gauss, weights 1
+  // shards vertex s -> tensor bits
+  MRH_HD static constexpr int bx(int s) { return (s == 1 || s == 2 || s == 5 || s == 6) ? 1 : 0; }
+  MRH_HD static constexpr int by(int s) { return (s == 2 || s == 3 || s == 6 || s == 7) ? 1 : 0; }
+  MRH_HD static constexpr int bz(int s) { return s >> 2; }
+  // point q -> abscissa per direction (descending order: bit 0 -> +g), x fastest
+  MRH_HD static constexpr double xi(int qbit) { return qbit ? -g : g; }
+  MRH_HD static constexpr double l(int bit, int qbit) { return bit ? 0.5 * (1.0 + xi(qbit)) : 0.5 * (1.0 - xi(qbit)); }
+  MRH_HD static constexpr double dl(int bit) { return bit ? 0.5 : -0.5; }
+  MRH_HD static constexpr double N(int s, int q) { return l(bx(s), q & 1) * l(by(s), (q >> 1) & 1) * l(bz(s), q >> 2); }
+  MRH_HD static constexpr double dN(int s, int q, int c) {
+    return (c == 0) ? dl(bx(s)) * l(by(s), (q >> 1) & 1) * l(bz(s), q >> 2)
+         : (c == 1) ? l(bx(s), q & 1) * dl(by(s)) * l(bz(s), q >> 2)
+                    : l(bx(s), q & 1) * l(by(s), (q >> 1) & 1) * dl(bz(s));
+  }
+  MRH_HD static constexpr int tri(int i, int j) { return i * 8 - (i * (i - 1)) / 2 + (j - i); }   // i <= j, 36 entries
+};
+
+// eligibility of a volume launch for this kernel (checked on the host)
+inline bool thermal_hex_q1_eligible(int phys, int dim, int order, int nq, bool state_independent, int lump_mass) {
+  return phys == PHYS_THERMAL && dim == 3 && order == 1 && nq == 8 && state_independent && !lump_mass;
+}
+
+template <bool TRANSIENT, bool ADV, bool JAC>
+struct ThermalHexQ1 {
+  static constexpr int NK = ADV ? 64 : 36;
+
+  MRH_HDN static void element(const KParams& kp, int64_t e) {
+    // ---- gather: LIDs, vertex coordinates, DOFs ------------------------------------------------------
+    int lid[8];
+    {
+      const int4* lp = reinterpret_cast<const int4*>(kp.lids + e * 8);
+      const int4 a = lp[0], b = lp[1];
+      lid[0] = a.x; lid[1] = a.y; lid[2] = a.z; lid[3] = a.w; lid[4] = b.x; lid[5] = b.y; lid[6] = b.z; lid[7] = b.w;
+    }
+    double X[8][3];
+    {
+      const int4* np = reinterpret_cast<const int4*>(kp.e2n + e * 8);
+      const int4 a = np[0], b = np[1];
+      const int nd[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        const double* p = kp.nodes + (int64_t)nd[s] * 3;
+        X[s][0] = p[0]; X[s][1] = p[1]; X[s][2] = p[2];
+      }
+    }
+    double us[8], ud[8];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      const double uval = kp.u[lid[s]];
+      if (!TRANSIENT) { us[s] = uval; ud[s] = 0.0; }
+      else {
+        const TimeParams& tp = kp.tp;
+        const double prev0 = kp.u_prev[(size_t)lid[s] * tp.nsteps];
+        double beta_u = (1.0 - tp.alpha_u) * prev0;
+        for (int k = 0; k < tp.stage; ++k) beta_u += tp.a_over_b[k] * (kp.u_stage[(size_t)lid[s] * tp.nstages + k] - prev0);
+        double beta_t = 0.0;
+        for (int k = 1; k <= tp.nsteps; ++k) beta_t += tp.bdf[k] * kp.u_prev[(size_t)lid[s] * tp.nsteps + (k - 1)];
+        us[s] = tp.alpha_u * uval + beta_u;
+        ud[s] = tp.alpha_t * uval + beta_t * tp.timewt;
+      }
+    }
+    const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
+
+    // ---- coefficients at the 8 points (vector interpreter; constants cost nothing) --------------------
+    double px[8], py[8], pz[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      double x = 0.0, y = 0.0, z = 0.0;
+#pragma unroll
+      for (int s = 0; s < 8; ++s) { x += X[s][0] * HexQ1::N(s, q); y += X[s][1] * HexQ1::N(s, q); z += X[s][2] * HexQ1::N(s, q); }
+      px[q] = x; py[q] = y; pz[q] = z;
+    }
+    double src[8], kap[8], rcp[8];
+    eval_prog_vec<8>(kp.progs[TH_SOURCE], kp.code, kp.cpool, px, py, pz, kp.tp.time, src);
+    eval_prog_vec<8>(kp.progs[TH_DIFF], kp.code, kp.cpool, px, py, pz, kp.tp.time, kap);
+    if (TRANSIENT) {
+      double cp[8], rho[8];
+      eval_prog_vec<8>(kp.progs[TH_CP], kp.code, kp.cpool, px, py, pz, kp.tp.time, cp);
+      eval_prog_vec<8>(kp.progs[TH_RHO], kp.code, kp.cpool, px, py, pz, kp.tp.time, rho);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) rcp[q] = rho[q] * cp[q];
+    }
+    double bx[8], by[8], bz[8];
+    if (ADV) {
+      eval_prog_vec<8>(kp.progs[TH_BX], kp.code, kp.cpool, px, py, pz, kp.tp.time, bx);
+      eval_prog_vec<8>(kp.progs[TH_BY], kp.code, kp.cpool, px, py, pz, kp.tp.time, by);
+      eval_prog_vec<8>(kp.progs[TH_BZ], kp.code, kp.cpool, px, py, pz, kp.tp.time, bz);
+    }
+
+    // ---- point loop: geometry, gradients, residual, element matrix -----------------------------------
+    double r[8], K[NK];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) r[s] = 0.0;
+#pragma unroll
+    for (int k = 0; k < NK; ++k) K[k] = 0.0;
+
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      double J[3][3];
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          double s_ = 0.0;
+#pragma unroll
+          for (int s = 0; s < 8; ++s) s_ += X[s][i] * HexQ1::dN(s, q, j);
+          J[i][j] = s_;
+        }
+      double Ji[3][3];
+      const double det = det_inv<3>(J, Ji);
+      const double w = fabs(det);                       // reference weight 1
+      double gx[8], gy[8], gz[8];
+      double ex = 0.0, ey = 0.0, ez = 0.0, edot = 0.0;
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        gx[s] = Ji[0][0] * HexQ1::dN(s, q, 0) + Ji[1][0] * HexQ1::dN(s, q, 1) + Ji[2][0] * HexQ1::dN(s, q, 2);
+        gy[s] = Ji[0][1] * HexQ1::dN(s, q, 0) + Ji[1][1] * HexQ1::dN(s, q, 1) + Ji[2][1] * HexQ1::dN(s, q, 2);
+        gz[s] = Ji[0][2] * HexQ1::dN(s, q, 0) + Ji[1][2] * HexQ1::dN(s, q, 1) + Ji[2][2] * HexQ1::dN(s, q, 2);
+        ex += us[s] * gx[s]; ey += us[s] * gy[s]; ez += us[s] * gz[s];
+        if (TRANSIENT) edot += ud[s] * HexQ1::N(s, q);
+      }
+      const double kw = kap[q] * w;
+      double f0 = -src[q] * w;
+      if (TRANSIENT) f0 += rcp[q] * edot * w;
+      if (ADV) f0 += (bx[q] * ex + by[q] * ey + bz[q] * ez) * w;
+      const double fx = kw * ex, fy = kw * ey, fz = kw * ez;
+#pragma unroll
+      for (int s = 0; s < 8; ++s) r[s] += f0 * HexQ1::N(s, q) + fx * gx[s] + fy * gy[s] + fz * gz[s];
+      if (JAC) {
+        const double kwa = kw * au;
+        const double mw = TRANSIENT ? rcp[q] * at * w : 0.0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const double ax = kwa * gx[i], ay = kwa * gy[i], az = kwa * gz[i];
+          const double mi = TRANSIENT ? mw * HexQ1::N(i, q) : 0.0;
+          if (!ADV) {
+#pragma unroll
+            for (int j = i; j < 8; ++j) {
+              double v = K[HexQ1::tri(i, j)] + ax * gx[j] + ay * gy[j] + az * gz[j];
+              if (TRANSIENT) v += mi * HexQ1::N(j, q);
+              K[HexQ1::tri(i, j)] = v;
+            }
+          } else {
+            const double ci = au * w * HexQ1::N(i, q);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              double v = K[i * 8 + j] + ax * gx[j] + ay * gy[j] + az * gz[j];
+              v += ci * (bx[q] * gx[j] + by[q] * gy[j] + bz[q] * gz[j]);
+              if (TRANSIENT) v += mi * HexQ1::N(j, q);
+              K[i * 8 + j] = v;
+            }
+          }
+        }
+      }
+    }
+
+    // ---- scatter: residual subtracted, Jacobian added, fixed rows skipped ------------------------------
+    bool fx_[8];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      fx_[s] = kp.fixed[lid[s]] != 0;
+      if (!fx_[s]) atomic_add(kp.res + lid[s], -r[s]);
+    }
+    if (!JAC) return;
+    uint16_t pat[64];
+    {
+      const uint4* pp = reinterpret_cast<const uint4*>(kp.pat + (size_t)kp.pat_id[e] * 64);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint4 v = pp[k];
+        pat[k * 8 + 0] = (uint16_t)(v.x & 0xffff); pat[k * 8 + 1] = (uint16_t)(v.x >> 16);
+        pat[k * 8 + 2] = (uint16_t)(v.y & 0xffff); pat[k * 8 + 3] = (uint16_t)(v.y >> 16);
+        pat[k * 8 + 4] = (uint16_t)(v.z & 0xffff); pat[k * 8 + 5] = (uint16_t)(v.z >> 16);
+        pat[k * 8 + 6] = (uint16_t)(v.w & 0xffff); pat[k * 8 + 7] = (uint16_t)(v.w >> 16);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (fx_[i]) continue;
+      double* jrow = kp.jac + kp.rowptr[lid[i]];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const double v = ADV ? K[i * 8 + j] : (i <= j ? K[HexQ1::tri(i, j)] : K[HexQ1::tri(j, i)]);
+        atomic_add(jrow + pat[i * 8 + j], v);
+      }
+    }
+  }
+};
+
+}  // namespace mrh

@@ -9,6 +9,7 @@ struct mrh_engine {
   mrh::EngineHost host;
   std::string err;
   void* impl = nullptr;
+  int64_t npatterns = 0;
 };
 
 static thread_local std::string g_create_err;
@@ -130,7 +131,7 @@ int mrh_get_sizes(mrh_handle h, int64_t* out) {
   int64_t nfixed = 0; for (auto f : H.isFixed) nfixed += f;
   int64_t v[16] = {H.dim, H.mesh.nelem, H.mesh.nnode, H.nv, H.nvar, H.nb, H.N, H.dofs.nlocal,
                    (int64_t)H.crs.colind.size(), H.ref.vol.nq, H.ref.side.empty() ? 0 : H.ref.side[0].nq,
-                   (int64_t)H.mesh.sides.size(), 0, nfixed, 0, 0};
+                   (int64_t)H.mesh.sides.size(), h->npatterns, nfixed, 0, 0};
   memcpy(out, v, sizeof(v));
   return MRH_OK;
 }

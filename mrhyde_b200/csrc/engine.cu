@@ -1,0 +1,156 @@
+// Device side of the engine: sm_100a kernels wrapping the phase functions of assemble.h / assemble_fast.h,
+// slot-pattern dictionary construction, DBC fix-up kernels, and the C-ABI entry points that need the GPU.
+// There is NO CPU fallback: every entry point here returns MRH_ECUDA when the device is unavailable.
+#include <cuda_runtime.h>
+#include <thrust/device_ptr.h>
+#include <thrust/execution_policy.h>
+#include <thrust/sequence.h>
+#include <thrust/sort.h>
+#include <thrust/unique.h>
+
+#include "capi_host.inl"
+#include "dispatch.h"
+#include "assemble_fast.h"
+
+using namespace mrh;
+
+#define CUDA_CK(call)                                                                                   \
+  do { cudaError_t e_ = (call); if (e_ != cudaSuccess)                                                  \
+         throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #call); } while (0)
+
+namespace {
+
+template <class T>
+struct DevBuf {
+  T* p = nullptr; size_t n = 0;
+  DevBuf() {}
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { release(); }
+  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+  void alloc(size_t count) { release(); n = count; if (count) CUDA_CK(cudaMalloc((void**)&p, count * sizeof(T))); }
+  void upload(const T* h, size_t count) { alloc(count); if (count) CUDA_CK(cudaMemcpy(p, h, count * sizeof(T), cudaMemcpyHostToDevice)); }
+  void upload(const std::vector<T>& v) { upload(v.data(), v.size()); }
+};
+
+struct TabDev { DevBuf<double> B, G, VB, VG, W; };
+
+struct DeviceImpl {
+  int device = 0, num_sms = 148;
+  DevBuf<double> nodes; DevBuf<int> e2n, lids, pat_id, dbc, dbc_diag_dummy;
+  DevBuf<uint8_t> fixed; DevBuf<int64_t> rowptr, dbc_slots; DevBuf<int> colind; DevBuf<uint16_t> pat;
+  DevBuf<Instr> code; DevBuf<double> cpool;
+  TabDev vol_tab, side_tab[6];
+  std::vector<std::unique_ptr<DevBuf<int>>> side_elems;
+  BasePtrs bp;
+  int64_t npatterns = 0, launches = 0;
+  bool ready = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double vol_ms = 0.0;
+  // staging for the *_host entry point
+  DevBuf<double> h_u, h_res, h_jac;
+};
+
+// ------------------------------------------------------------------------------------------------ kernels
+template <class C, bool JAC>
+__global__ void __launch_bounds__(128) generic_assembly_kernel(const __grid_constant__ KParams kp) {
+  extern __shared__ double sm[];
+  using G = GenPhases<C>;
+  using S = typename std::conditional<JAC, PAD<C::P>, double>::type;
+  const int EB = kp.elems_per_block, tid = threadIdx.x, nt = blockDim.x;
+  const GenSmem<C> L(EB, kp.tab.nq, JAC, kp.tp.transient != 0);
+  for (int64_t blk0 = (int64_t)blockIdx.x * EB; blk0 < kp.nwork; blk0 += (int64_t)gridDim.x * EB) {
+    for (int it = tid; it < EB * C::N; it += nt) G::gather_dof(kp, L, sm, blk0, it);
+    for (int it = tid; it < EB * C::NV; it += nt) G::gather_vertex(kp, L, sm, blk0, it);
+    __syncthreads();
+    for (int it = tid; it < EB * L.nq; it += nt) G::geometry(kp, L, sm, blk0, it);
+    __syncthreads();
+    for (int it = tid; it < EB * L.nq; it += nt) G::template point<S>(kp, L, sm, blk0, it);
+    __syncthreads();
+    for (int it = tid; it < EB * C::NB * C::NVAR; it += nt) G::contract(kp, L, sm, blk0, it);
+    __syncthreads();
+  }
+}
+
+template <bool TRANSIENT, bool ADV, bool JAC>
+__global__ void __launch_bounds__(128) thermal_hex_q1_kernel(const __grid_constant__ KParams kp) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (int64_t)gridDim.x * blockDim.x)
+    ThermalHexQ1<TRANSIENT, ADV, JAC>::element(kp, e);
+}
+
+// row-relative CRS position of column `col` in row `row` (columns ascending)
+__device__ __forceinline__ int rel_slot(const int64_t* rowptr, const int* colind, int row, int col) {
+  const int64_t b = rowptr[row];
+  int lo = 0, hi = (int)(rowptr[row + 1] - b);
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (colind[b + mid] < col) lo = mid + 1; else hi = mid; }
+  return (lo < (int)(rowptr[row + 1] - b) && colind[b + lo] == col) ? lo : -1;
+}
+__device__ __forceinline__ uint64_t mix64(uint64_t h, uint64_t v) {
+  h ^= v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+  h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 29;
+  return h;
+}
+// pass 1: hash of each element's N x N slot pattern
+__global__ void pattern_hash_kernel(const int* lids, const int64_t* rowptr, const int* colind, int64_t nelem, int N,
+                                    uint64_t* hash, int* bad) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= nelem) return;
+  const int* l = lids + e * N;
+  uint64_t h = 0x1234567ull;
+  for (int r = 0; r < N; ++r)
+    for (int c = 0; c < N; ++c) {
+      const int s = rel_slot(rowptr, colind, l[r], l[c]);
+      if (s < 0) atomicExch(bad, 1);
+      h = mix64(h, (uint64_t)(s + 1));
+    }
+  hash[e] = h;
+}
+// pass 2: materialise the pattern of each representative element
+__global__ void pattern_fill_kernel(const int* lids, const int64_t* rowptr, const int* colind, const int* rep, int64_t npat,
+                                    int N, uint16_t* pat) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= npat * N) return;
+  const int64_t p = k / N; const int r = (int)(k % N);
+  const int* l = lids + (int64_t)rep[p] * N;
+  for (int c = 0; c < N; ++c) pat[(p * N + r) * N + c] = (uint16_t)rel_slot(rowptr, colind, l[r], l[c]);
+}
+// pass 3: pattern id of every element (binary search on the sorted unique hashes) and full verification
+__global__ void pattern_assign_kernel(const int* lids, const int64_t* rowptr, const int* colind, int64_t nelem, int N,
+                                      const uint64_t* hash, const uint64_t* uhash, int64_t npat, const uint16_t* pat,
+                                      int* pat_id, int* bad) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= nelem) return;
+  const uint64_t h = hash[e];
+  int64_t lo = 0, hi = npat;
+  while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (uhash[mid] < h) lo = mid + 1; else hi = mid; }
+  pat_id[e] = (int)lo;
+  const int* l = lids + e * N;
+  const uint16_t* P = pat + lo * N * N;
+  for (int r = 0; r < N; ++r)
+    for (int c = 0; c < N; ++c)
+      if ((int)P[r * N + c] != rel_slot(rowptr, colind, l[r], l[c])) atomicExch(bad, 2);
+}
+
+// updateJacDBC (assemblyManager.cpp:1167-1180): replaceLocalValues(dof, 1, 1.0, dof)
+__global__ void dbc_diag_kernel(const int64_t* slots, int64_t n, double* jac) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && slots[i] >= 0) jac[slots[i]] = 1.0;
+}
+__global__ void dbc_slot_kernel(const int* dbc, int64_t n, const int64_t* rowptr, const int* colind, int64_t* slots) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int s = rel_slot(rowptr, colind, dbc[i], dbc[i]);
+  slots[i] = s < 0 ? -1 : rowptr[dbc[i]] + s;
+}
+// fix zero rows (assemblyManager.cpp:2644-2663): rows whose |.|-sum is below 1e-14 get a unit diagonal
+__global__ void fix_zero_rows_kernel(const int64_t* rowptr, const int* colind, int64_t nrows, double* jac) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= nrows) return;
+  double s = 0.0;
+  for (int64_t p = rowptr[r]; p < rowptr[r + 1]; ++p) s += fabs(jac[p]);
+  if (s < 1.0e-14) { const int d = rel_slot(rowptr, colind, (int)r, (int)r); if (d >= 0) jac[rowptr[r] + d] = 1.0; }
+}
+
+}  // namespace
+
+#include "engine_launch.inl"

@@ -1,0 +1,298 @@
+// Part of engine.cu: device set-up, launch logic and the GPU-side C-ABI entry points.
+
+namespace {
+
+RefTab upload_tab(TabDev& D, const PointTables& T) {
+  D.B.upload(T.B); D.G.upload(T.G); D.VB.upload(T.VB); D.VG.upload(T.VG); D.W.upload(T.W);
+  RefTab r{};
+  r.B = D.B.p; r.G = D.G.p; r.VB = D.VB.p; r.VG = D.VG.p; r.W = D.W.p; r.nq = T.nq;
+  for (int c = 0; c < 3; ++c) { r.tanU[c] = T.tanU[c]; r.tanV[c] = T.tanV[c]; }
+  return r;
+}
+
+inline unsigned blocks_for(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
+
+void build_patterns(EngineHost& H, DeviceImpl& D) {
+  const int64_t ne = H.mesh.nelem; const int N = H.N;
+  DevBuf<uint64_t> hash, skey; DevBuf<int> idx, bad;
+  hash.alloc(ne); skey.alloc(ne); idx.alloc(ne); bad.alloc(1);
+  CUDA_CK(cudaMemset(bad.p, 0, sizeof(int)));
+  pattern_hash_kernel<<<blocks_for(ne, 128), 128>>>(D.lids.p, D.rowptr.p, D.colind.p, ne, N, hash.p, bad.p);
+  CUDA_CK(cudaGetLastError());
+  CUDA_CK(cudaMemcpy(skey.p, hash.p, ne * sizeof(uint64_t), cudaMemcpyDeviceToDevice));
+  thrust::device_ptr<uint64_t> kp(skey.p); thrust::device_ptr<int> ip(idx.p);
+  thrust::sequence(thrust::device, ip, ip + ne);
+  thrust::sort_by_key(thrust::device, kp, kp + ne, ip);
+  auto ends = thrust::unique_by_key(thrust::device, kp, kp + ne, ip);
+  const int64_t npat = ends.first - kp;
+  int hbad = 0; CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (hbad) throw std::runtime_error("CRS graph misses an element coupling (row/column of an element's LIDs not in the graph)");
+  D.pat.alloc((size_t)npat * N * N); D.pat_id.alloc(ne);
+  pattern_fill_kernel<<<blocks_for(npat * N, 128), 128>>>(D.lids.p, D.rowptr.p, D.colind.p, idx.p, npat, N, D.pat.p);
+  CUDA_CK(cudaGetLastError());
+  pattern_assign_kernel<<<blocks_for(ne, 128), 128>>>(D.lids.p, D.rowptr.p, D.colind.p, ne, N, hash.p, skey.p, npat, D.pat.p, D.pat_id.p, bad.p);
+  CUDA_CK(cudaGetLastError());
+  CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (hbad) throw std::runtime_error("slot-pattern dictionary verification failed (hash collision)");
+  D.npatterns = npat;
+}
+
+
+void device_finalize(mrh_engine* h) {
+  EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
+  CUDA_CK(cudaSetDevice(D.device));
+  H.finalizeHost();
+  D.ready = false;
+  D.nodes.upload(H.mesh.nodes); D.e2n.upload(H.mesh.elem2node); D.lids.upload(H.dofs.lids); D.fixed.upload(H.isFixed);
+  D.rowptr.upload(H.crs.rowptr); D.colind.upload(H.crs.colind);
+  D.code.upload(H.ec.code); D.cpool.upload(H.ec.cpool);
+  D.bp = BasePtrs();
+  D.bp.vol_tab = upload_tab(D.vol_tab, H.ref.vol);
+  for (int s = 0; s < H.ref.nsides; ++s) D.bp.side_tab[s] = upload_tab(D.side_tab[s], H.ref.side[s]);
+  D.side_elems.clear();
+  for (auto& S : H.mesh.sides) { D.side_elems.emplace_back(new DevBuf<int>()); D.side_elems.back()->upload(S.elems); }
+  build_patterns(H, D);
+  h->npatterns = D.npatterns;
+  D.dbc.upload(H.dbc_dofs); D.dbc_slots.alloc(H.dbc_dofs.size());
+  if (!H.dbc_dofs.empty()) {
+    dbc_slot_kernel<<<blocks_for((int64_t)H.dbc_dofs.size(), 128), 128>>>(D.dbc.p, (int64_t)H.dbc_dofs.size(), D.rowptr.p, D.colind.p, D.dbc_slots.p);
+    CUDA_CK(cudaGetLastError());
+  }
+  CUDA_CK(cudaDeviceSynchronize());
+  D.bp.nodes = D.nodes.p; D.bp.e2n = D.e2n.p; D.bp.lids = D.lids.p; D.bp.fixed = D.fixed.p; D.bp.rowptr = D.rowptr.p;
+  D.bp.pat = D.pat.p; D.bp.pat_id = D.pat_id.p; D.bp.code = D.code.p; D.bp.cpool = D.cpool.p;
+  if (!D.ev0) { CUDA_CK(cudaEventCreate(&D.ev0)); CUDA_CK(cudaEventCreate(&D.ev1)); }
+  D.ready = true;
+}
+
+template <class C, bool JAC>
+void launch_generic(const DeviceImpl& D, KParams& kp, cudaStream_t stream) {
+  const size_t per_elem = GenSmem<C>(1, kp.tab.nq, JAC, kp.tp.transient != 0).total_doubles() * sizeof(double);
+  int EB = (int)((100 * 1024) / per_elem);
+  if (EB < 1) EB = 1;
+  if (EB > 16) EB = 16;
+  const size_t smem = GenSmem<C>(EB, kp.tab.nq, JAC, kp.tp.transient != 0).total_doubles() * sizeof(double);
+  if (smem > 227 * 1024) throw std::runtime_error("element block does not fit in shared memory (quadrature too large)");
+  auto kern = generic_assembly_kernel<C, JAC>;
+  CUDA_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 1;
+  CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+  if (per_sm < 1) per_sm = 1;
+  kp.elems_per_block = EB;
+  const int64_t nblk = (kp.nwork + EB - 1) / EB;
+  const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * per_sm);
+  kern<<<grid, 128, smem, stream>>>(kp);
+  CUDA_CK(cudaGetLastError());
+}
+
+template <bool T, bool A, bool J>
+void launch_thermal_fast(const DeviceImpl& D, const KParams& kp, cudaStream_t stream) {
+  auto kern = thermal_hex_q1_kernel<T, A, J>;
+  int per_sm = 1;
+  CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, 0));
+  if (per_sm < 1) per_sm = 1;
+  const int64_t nblk = (kp.nwork + 127) / 128;
+  const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * per_sm * 4);
+  kern<<<grid, 128, 0, stream>>>(kp);
+  CUDA_CK(cudaGetLastError());
+}
+
+int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac) {
+  EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
+  if (!D.ready) throw std::runtime_error("mrh_finalize has not been called");
+  CUDA_CK(cudaSetDevice(D.device));
+  cudaStream_t stream = (cudaStream_t)st->stream;
+  D.launches = 0;
+  for (int side = -1; side < (int)H.side_launches.size(); ++side) {
+    if (side >= 0 && !H.side_launches[side].active) continue;
+    KParams kp;
+    H.fillParams(kp, D.bp, *st, res, jac, side, side >= 0 ? D.side_elems[side]->p : nullptr);
+    if (kp.tp.transient && (!st->u_prev || (kp.tp.stage > 0 && !st->u_stage))) throw std::runtime_error("transient assembly needs u_prev (and u_stage for stage > 0)");
+    if (side < 0) CUDA_CK(cudaEventRecord(D.ev0, stream));
+    const bool fast = side < 0 && !(H.cfg.flags & 1) &&
+        thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass);
+    if (fast) {
+      const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
+#define MRH_FAST(T, A, Jc) if (tr == T && adv == A && jc == Jc) launch_thermal_fast<T, A, Jc>(D, kp, stream);
+      MRH_FAST(false, false, false) MRH_FAST(false, false, true) MRH_FAST(false, true, false) MRH_FAST(false, true, true)
+      MRH_FAST(true, false, false) MRH_FAST(true, false, true) MRH_FAST(true, true, false) MRH_FAST(true, true, true)
+#undef MRH_FAST
+    } else {
+      const bool ok = dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) {
+        using C = decltype(c);
+        if (jac) launch_generic<C, true>(D, kp, stream); else launch_generic<C, false>(D, kp, stream);
+      });
+      if (!ok) throw std::runtime_error("configuration not supported: no kernel for this physics/dimension/order");
+    }
+    if (side < 0) CUDA_CK(cudaEventRecord(D.ev1, stream));
+    D.launches++;
+  }
+  if (jac) {
+    const int64_t nd = (int64_t)H.dbc_dofs.size();
+    if (nd > 0) { dbc_diag_kernel<<<blocks_for(nd, 256), 256, 0, stream>>>(D.dbc_slots.p, nd, jac); CUDA_CK(cudaGetLastError()); D.launches++; }
+    if (H.cfg.fix_zero_rows) {
+      fix_zero_rows_kernel<<<blocks_for(H.crs.nrows, 256), 256, 0, stream>>>(D.rowptr.p, D.colind.p, H.crs.nrows, jac);
+      CUDA_CK(cudaGetLastError()); D.launches++;
+    }
+  }
+  return MRH_OK;
+}
+
+// ---- micro-benchmarks (roofline denominators measured on the box itself) -------------------------------
+__global__ void dfma_kernel(double* out, int iters) {
+  double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double b = 1.0000001, c = 1e-9;
+  for (int i = 0; i < iters; ++i) {
+    a0 = a0 * b + c; a1 = a1 * b + c; a2 = a2 * b + c; a3 = a3 * b + c;
+    a4 = a4 * b + c; a5 = a5 * b + c; a6 = a6 * b + c; a7 = a7 * b + c;
+  }
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+// RED.F64 with the access pattern of the thermal scatter: consecutive threads hit consecutive 27-entry rows
+__global__ void red_kernel(double* buf, int64_t nrows, int reps) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nrows) return;
+  for (int r = 0; r < reps; ++r)
+    for (int k = 0; k < 8; ++k) atomicAdd(buf + ((t + (k >> 1)) % nrows) * 27 + ((k * 5 + r) % 27), 1.0);
+}
+__global__ void copy_kernel(const double2* __restrict__ a, double2* __restrict__ b, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) b[i] = a[i];
+}
+
+}  // namespace
+
+static int backend_create(mrh_engine* h) {
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    h->err = std::string("no CUDA device available (") + cudaGetErrorString(e) + "); this engine has no CPU fallback";
+    cudaGetLastError();
+    // the handle stays usable for host-only set-up/introspection; every GPU entry point fails with MRH_ECUDA
+    h->impl = nullptr;
+    return MRH_OK;
+  }
+  auto* D = new DeviceImpl();
+  D->device = h->host.cfg.device;
+  if (D->device < 0 || D->device >= ndev) { delete D; h->err = "CUDA device ordinal out of range"; return MRH_ECUDA; }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, D->device) != cudaSuccess) { delete D; h->err = "cudaGetDeviceProperties failed"; return MRH_ECUDA; }
+  D->num_sms = prop.multiProcessorCount;
+  h->impl = D;
+  return MRH_OK;
+}
+static void backend_destroy(mrh_engine* h) {
+  auto* D = (DeviceImpl*)h->impl;
+  if (!D) return;
+  cudaSetDevice(D->device);
+  if (D->ev0) { cudaEventDestroy(D->ev0); cudaEventDestroy(D->ev1); }
+  delete D;
+}
+
+#define MRH_NEED_GPU(h) if (!(h)->impl) { (h)->err = "no CUDA device available; this engine has no CPU fallback"; return MRH_ECUDA; }
+#define MRH_CATCH_CUDA(h)                                                                             \
+  } catch (const std::exception& e) {                                                                 \
+    (h)->err = e.what();                                                                              \
+    if ((h)->err.compare(0, 10, "CUDA error") == 0) return MRH_ECUDA;                                 \
+    if ((h)->err.find("not able to decompose") != std::string::npos || (h)->err.find("could not evaluate") != std::string::npos) return MRH_EPARSE; \
+    if ((h)->err.find("not supported") != std::string::npos) return MRH_EUNSUPPORTED;                 \
+    return MRH_EINVAL; }
+
+extern "C" {
+
+int mrh_finalize(mrh_handle h) {
+  if (!h) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h) device_finalize(h); return MRH_OK; MRH_CATCH_CUDA(h)
+}
+int mrh_assemble_res(mrh_handle h, const mrh_state* st, double* res) {
+  if (!h || !st || !st->u || !res) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h) return device_assemble(h, st, res, nullptr); MRH_CATCH_CUDA(h)
+}
+int mrh_assemble_jacres(mrh_handle h, const mrh_state* st, double* res, double* jac) {
+  if (!h || !st || !st->u || !res || !jac) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h) return device_assemble(h, st, res, jac); MRH_CATCH_CUDA(h)
+}
+int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res_host, double* jac_host) {
+  if (!h || !st_host || !st_host->u || !res_host || !jac_host) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h)
+  EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
+  if (st_host->is_transient) throw std::runtime_error("host-buffer entry point is steady-state only; not supported for transient states");
+  CUDA_CK(cudaSetDevice(D.device));
+  const size_t nl = (size_t)H.dofs.nlocal, nnz = H.crs.colind.size();
+  if (D.h_u.n != nl) { D.h_u.alloc(nl); D.h_res.alloc(nl); }
+  if (D.h_jac.n != nnz) D.h_jac.alloc(nnz);
+  cudaStream_t s = (cudaStream_t)st_host->stream;
+  CUDA_CK(cudaMemcpyAsync(D.h_u.p, st_host->u, nl * sizeof(double), cudaMemcpyHostToDevice, s));
+  CUDA_CK(cudaMemsetAsync(D.h_res.p, 0, nl * sizeof(double), s));
+  CUDA_CK(cudaMemsetAsync(D.h_jac.p, 0, nnz * sizeof(double), s));
+  mrh_state st = *st_host; st.u = D.h_u.p;
+  const int rc = device_assemble(h, &st, D.h_res.p, D.h_jac.p);
+  CUDA_CK(cudaMemcpyAsync(res_host, D.h_res.p, nl * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CUDA_CK(cudaMemcpyAsync(jac_host, D.h_jac.p, nnz * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CUDA_CK(cudaStreamSynchronize(s));
+  return rc;
+  MRH_CATCH_CUDA(h)
+}
+int64_t mrh_last_launch_count(mrh_handle h) { return (h && h->impl) ? ((DeviceImpl*)h->impl)->launches : 0; }
+double mrh_last_volume_kernel_ms(mrh_handle h) {
+  if (!h || !h->impl) return -1.0;
+  auto* D = (DeviceImpl*)h->impl;
+  if (!D->ev1 || cudaEventSynchronize(D->ev1) != cudaSuccess) return -1.0;
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, D->ev0, D->ev1) != cudaSuccess) return -1.0;
+  return (double)ms;
+}
+
+int mrh_microbench(int32_t device, double* dfma_tflops, double* red_gops, double* copy_gbs) {
+  try {
+    CUDA_CK(cudaSetDevice(device));
+    cudaDeviceProp prop; CUDA_CK(cudaGetDeviceProperties(&prop, device));
+    cudaEvent_t e0, e1; CUDA_CK(cudaEventCreate(&e0)); CUDA_CK(cudaEventCreate(&e1));
+    float ms = 0.f;
+    if (dfma_tflops) {
+      const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 15;
+      DevBuf<double> out; out.alloc((size_t)blocks * threads);
+      dfma_kernel<<<blocks, threads>>>(out.p, 1024);
+      double best = 0.0;
+      for (int rep = 0; rep < 3; ++rep) {
+        CUDA_CK(cudaEventRecord(e0)); dfma_kernel<<<blocks, threads>>>(out.p, iters); CUDA_CK(cudaEventRecord(e1));
+        CUDA_CK(cudaEventSynchronize(e1)); CUDA_CK(cudaEventElapsedTime(&ms, e0, e1));
+        best = std::max(best, 2.0 * 8.0 * iters * (double)blocks * threads / (ms * 1e-3) / 1e12);
+      }
+      *dfma_tflops = best;
+    }
+    if (red_gops) {
+      const int64_t nrows = 16 * 1024 * 1024; const int reps = 4;
+      DevBuf<double> buf; buf.alloc((size_t)nrows * 27);
+      CUDA_CK(cudaMemset(buf.p, 0, (size_t)nrows * 27 * sizeof(double)));
+      red_kernel<<<blocks_for(nrows, 128), 128>>>(buf.p, nrows, 1);
+      double best = 0.0;
+      for (int rep = 0; rep < 3; ++rep) {
+        CUDA_CK(cudaEventRecord(e0)); red_kernel<<<blocks_for(nrows, 128), 128>>>(buf.p, nrows, reps); CUDA_CK(cudaEventRecord(e1));
+        CUDA_CK(cudaEventSynchronize(e1)); CUDA_CK(cudaEventElapsedTime(&ms, e0, e1));
+        best = std::max(best, 8.0 * reps * (double)nrows / (ms * 1e-3) / 1e9);
+      }
+      *red_gops = best;
+    }
+    if (copy_gbs) {
+      const int64_t n = 256LL * 1024 * 1024;   // double2 elements: 4 GiB read + 4 GiB write
+      DevBuf<double2> a, b; a.alloc(n); b.alloc(n);
+      CUDA_CK(cudaMemset(a.p, 0, n * sizeof(double2)));
+      copy_kernel<<<prop.multiProcessorCount * 16, 512>>>(a.p, b.p, n);
+      double best = 0.0;
+      for (int rep = 0; rep < 3; ++rep) {
+        CUDA_CK(cudaEventRecord(e0)); copy_kernel<<<prop.multiProcessorCount * 16, 512>>>(a.p, b.p, n); CUDA_CK(cudaEventRecord(e1));
+        CUDA_CK(cudaEventSynchronize(e1)); CUDA_CK(cudaEventElapsedTime(&ms, e0, e1));
+        best = std::max(best, 2.0 * n * sizeof(double2) / (ms * 1e-3) / 1e9);
+      }
+      *copy_gbs = best;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return MRH_OK;
+  } catch (const std::exception&) { return MRH_ECUDA; }
+}
+
+}  // extern "C"

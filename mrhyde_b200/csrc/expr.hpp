@@ -58,8 +58,9 @@ class ExprCompiler {
     std::vector<Instr> out; bool state = false;
     emit(*T, T->fns[fi].second, out, state, 0);
     fold(out);
+    fuse(out);
     int depth = 0, sp = 0;
-    for (auto& in : out) { sp += delta(in.op); if (sp > depth) depth = sp; }
+    for (auto& in : out) { sp += (in.op >= OP_ADD && in.op <= OP_MEAN && in.arg != 0) ? 0 : delta(in.op); if (sp + 1 > depth) depth = sp + 1; }
     if (depth > MRH_MAXSTACK) throw std::runtime_error("expression too deep for the device evaluator: " + name);
     Prog p; p.pad_ = 0; p.cval = 0.0;
     if (out.size() == 1 && out[0].op == OP_CONST) { p.kind = 0; p.cval = cpool[out[0].cidx]; p.start = 0; p.len = 0; return p; }
@@ -235,6 +236,17 @@ class ExprCompiler {
     return true;
   }
 
+  // [leaf][binary] -> binary with fused right operand (bytecode.h); fields are not fused (arg holds the field id)
+  static void fuse(std::vector<Instr>& p) {
+    for (size_t i = 1; i < p.size(); ++i) {
+      const uint8_t op = p[i].op, lop = p[i - 1].op;
+      if (op >= OP_ADD && op <= OP_MEAN && p[i].arg == 0 && lop < OP_FIELD && i >= 2) {
+        // the leaf must be the right operand: the instruction before it must leave the left operand on the stack
+        p[i].arg = (uint8_t)(lop + 1); p[i].cidx = p[i - 1].cidx;
+        p.erase(p.begin() + i - 1); --i;
+      }
+    }
+  }
   // fold constant sub-programs exactly as the device would evaluate them (same operations, same order)
   void fold(std::vector<Instr>& p) {
     bool changed = true;

@@ -17,6 +17,11 @@
 #define MRH_HDN
 #endif
 
+#if !defined(__CUDACC__)
+struct int4 { int x, y, z, w; };
+struct uint4 { unsigned x, y, z, w; };
+#endif
+
 namespace mrh {
 
 template <int P>

@@ -17,7 +17,7 @@ class MrhConfig(C.Structure):
                 ("side_quadrature", C.c_int32), ("use_strong_dbc", C.c_int32), ("fix_zero_rows", C.c_int32),
                 ("lump_mass", C.c_int32), ("include_advection", C.c_int32), ("use_supg", C.c_int32),
                 ("use_pspg", C.c_int32), ("form_param", C.c_double), ("le_penalty", C.c_double),
-                ("device", C.c_int32), ("reserved", C.c_int32)]
+                ("device", C.c_int32), ("flags", C.c_int32)]
 
 
 class MrhState(C.Structure):
@@ -100,7 +100,7 @@ class Engine:
     """One assembly engine handle (== one AssemblyManager on one GPU)."""
 
     def __init__(self, physics, dim, order=1, lib=None, device=0, quadrature=-1, side_quadrature=-1,
-                 use_strong_dbc=True, fix_zero_rows=False, lump_mass=False, settings=None):
+                 use_strong_dbc=True, fix_zero_rows=False, lump_mass=False, settings=None, force_generic=False):
         self.L = load_library(lib)
         settings = settings or {}
         cfg = MrhConfig()
@@ -115,6 +115,7 @@ class Engine:
         cfg.form_param = float(settings.get("form_param", 1.0))
         cfg.le_penalty = float(settings.get("penalty", 10.0))
         cfg.device = device
+        cfg.flags = 1 if force_generic else 0
         self.h = C.c_void_p()
         rc = self.L.mrh_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:
@@ -139,7 +140,7 @@ class Engine:
             pass
 
     @classmethod
-    def from_problem(cls, p, lib=None, device=0, finalize=True, host_only=False):
+    def from_problem(cls, p, lib=None, device=0, finalize=True, host_only=False, force_generic=False):
         """Build an engine from a tests/problems.py style dict (same dict drives the oracle)."""
         extra = p.get("extra", {})
         weak = bool(extra.get("use weak Dirichlet", False))
@@ -147,7 +148,8 @@ class Engine:
         e = cls(p["physics"], m["dim"], p.get("order", 1), lib=lib, device=device,
                 quadrature=extra.get("quadrature", -1), side_quadrature=extra.get("side quadrature", -1),
                 use_strong_dbc=extra.get("use strong DBCs", True), fix_zero_rows=extra.get("fix zero rows", False),
-                lump_mass=extra.get("lump mass", False), settings=p.get("settings", {}))
+                lump_mass=extra.get("lump mass", False), settings=p.get("settings", {}),
+                force_generic=force_generic)
         n = [m["NX"], m["NY"], m.get("NZ", 1)]
         lo = [m.get("xmin", 0.0), m.get("ymin", 0.0), m.get("zmin", 0.0)]
         hi = [m.get("xmax", 1.0), m.get("ymax", 1.0), m.get("zmax", 1.0)]

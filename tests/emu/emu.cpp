@@ -4,12 +4,13 @@
 // The product library never links or calls this file; without a GPU the product fails with MRH_ECUDA.
 #include "../../mrhyde_b200/csrc/capi_host.inl"
 #include "../../mrhyde_b200/csrc/dispatch.h"
+#include "../../mrhyde_b200/csrc/assemble_fast.h"
 
 using namespace mrh;
 
 struct EmuImpl {
   std::vector<uint16_t> pat; std::vector<int> pat_id;
-  int64_t launches = 0;
+  int64_t launches = 0, fast_launches = 0;
 };
 
 static int backend_create(mrh_engine* h) { h->impl = new EmuImpl(); return MRH_OK; }
@@ -45,11 +46,23 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
     for (int c = 0; c < 3; ++c) { r.tanU[c] = T.tanU[c]; r.tanV[c] = T.tanV[c]; } return r; };
   bp.vol_tab = tab(H.ref.vol);
   for (int s = 0; s < H.ref.nsides; ++s) bp.side_tab[s] = tab(H.ref.side[s]);
-  E->launches = 0;
+  E->launches = 0; E->fast_launches = 0;
   for (int side = -1; side < (int)H.side_launches.size(); ++side) {
     if (side >= 0 && !H.side_launches[side].active) continue;
     KParams kp;
     H.fillParams(kp, bp, *st, res, jac, side, side >= 0 ? H.mesh.sides[side].elems.data() : nullptr);
+    if (side < 0 && !(H.cfg.flags & 1) &&
+        thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
+      const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
+      for (int64_t e = 0; e < kp.nwork; ++e) {
+#define MRH_FAST(T, A, Jc) if (tr == T && adv == A && jc == Jc) ThermalHexQ1<T, A, Jc>::element(kp, e);
+        MRH_FAST(false, false, false) MRH_FAST(false, false, true) MRH_FAST(false, true, false) MRH_FAST(false, true, true)
+        MRH_FAST(true, false, false) MRH_FAST(true, false, true) MRH_FAST(true, true, false) MRH_FAST(true, true, true)
+#undef MRH_FAST
+      }
+      E->launches++; E->fast_launches++;
+      continue;
+    }
     if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_launch<decltype(c)>(kp); }))
       throw std::runtime_error("configuration not supported");
     E->launches++;
@@ -106,7 +119,7 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st, double* res, dou
   MRH_CATCH(h)
 }
 int64_t mrh_last_launch_count(mrh_handle h) { return h ? ((EmuImpl*)h->impl)->launches : 0; }
-double mrh_last_volume_kernel_ms(mrh_handle) { return 0.0; }
+double mrh_last_volume_kernel_ms(mrh_handle h) { return h ? -(double)((EmuImpl*)h->impl)->fast_launches : 0.0; }  // emu: -#specialised launches
 int mrh_microbench(int32_t, double*, double*, double*) { return MRH_EUNSUPPORTED; }
 
 }  // extern "C"

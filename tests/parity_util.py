@@ -1,0 +1,175 @@
+"""Shared parity checker: one engine library (the CUDA product on a GPU box, or the CPU stepping harness of the
+kernels in tests/emu) against the oracle on the same seeded inputs.
+
+Bars: CRS rowptr/colind, element LIDs, offsets, fixed-DOF flags bit-exact; residual and Jacobian
+values <= 1e-12 relative, measured per vector/matrix as max|a-b|/max|b| and additionally per row.
+"""
+import copy
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+sys.path.insert(0, HERE)
+
+import problems  # noqa: E402
+from oracle.pyoracle import Oracle, config_text  # noqa: E402
+
+TOL = 1e-12
+EMU_LIB = os.path.join(HERE, "emu", "libmrhyde_emu.so")
+
+
+def build_emu():
+    src = os.path.join(HERE, "emu", "emu.cpp")
+    csrc = os.path.join(ROOT, "mrhyde_b200", "csrc")
+    deps = [src] + [os.path.join(csrc, f) for f in os.listdir(csrc)]
+    if (not os.path.exists(EMU_LIB)) or any(os.path.getmtime(d) > os.path.getmtime(EMU_LIB) for d in deps):
+        subprocess.check_call(["g++", "-O1", "-std=c++17", "-fPIC", "-shared", "-w", "-o", EMU_LIB, src])
+    return EMU_LIB
+
+
+def shrink(p, n3=4, n2=10):
+    p = copy.deepcopy(p)
+    m = p["mesh"]
+    if m["dim"] == 3:
+        m["NX"], m["NY"], m["NZ"] = n3, n3 + 1, n3 - 1
+    else:
+        m["NX"], m["NY"] = n2, n2 - 3
+    return p
+
+
+def cases():
+    """(id, problem, kwargs) — kwargs: transient=dict|None"""
+    P = problems
+    out = []
+    for mk in (P.regression_thermal_2d, P.regression_thermal_3d, P.regression_cdr_2d, P.regression_le_2d,
+               P.regression_le_3d, P.regression_ns_channel):
+        p = shrink(mk())
+        out.append((p["name"], p, {}))
+    out.append(("C3 cdr Q2 hex", shrink(P.config_c3(3), 3), {}))
+    out.append(("C5 ns supg pspg hex", shrink(P.config_c5(4)), {}))
+    # thermal Q2 quad, non-default quadrature
+    p = shrink(P.regression_thermal_2d()); p["order"] = 2; p["name"] = "thermal 2D Q2"
+    out.append((p["name"], p, {}))
+    # boundary terms: weak Dirichlet (Nitsche), Neumann, Flux
+    p = shrink(P.regression_thermal_3d()); p["extra"] = {"use weak Dirichlet": True}; p["name"] = "thermal 3D weak Dirichlet"
+    p["dirichlet"] = {"e": {"all boundaries": "0.1*x+y*z"}}
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_thermal_2d()); p["name"] = "thermal 2D Neumann+Flux+Dirichlet"
+    p["dirichlet"] = {"e": {"left": "0.0", "bottom": "sin(x)"}}
+    p["neumann"] = {"e": {"right": "1.0+y"}}
+    p["flux"] = {"e": {"top": "0.5*x"}}
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_le_3d()); p["extra"] = {"use weak Dirichlet": True}; p["name"] = "LE 3D weak Dirichlet + Neumann"
+    p["dirichlet"] = {v: {"bottom": "0.01*x", "left": "0.0"} for v in ("dx", "dy", "dz")}
+    p["neumann"] = {"dz": {"top": "0.3"}, "dx": {"right": "0.1*y"}}
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_le_2d()); p["extra"] = {"use weak Dirichlet": True}; p["name"] = "LE 2D weak Dirichlet"
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_ns_channel()); p["name"] = "NS 2D Neumann outflow + SUPG"
+    p["settings"] = {"usePSPG": True, "useSUPG": True}
+    p["neumann"] = {"ux": {"right": "0.2"}, "uy": {"right": "0.1*y"}}
+    out.append((p["name"], p, {}))
+    # state-dependent coefficient in thermal (forces the generic kernel) and advection
+    p = shrink(P.regression_thermal_3d()); p["name"] = "thermal 3D nonlinear diffusion + advection"
+    p["functions"] = dict(p["functions"]); p["functions"].update({"thermal diffusion": "1.0+e*e", "advection x": "1.0", "advection y": "x", "advection z": "0.5"})
+    p["settings"] = {"include advection": True}
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_thermal_3d()); p["name"] = "thermal 3D advection (specialised kernel)"
+    p["functions"] = dict(p["functions"]); p["functions"].update({"thermal diffusion": "1.0+x*y", "advection x": "1.0", "advection y": "x", "advection z": "0.5"})
+    p["settings"] = {"include advection": True}
+    out.append((p["name"], p, {}))
+    # transient (backward Euler and a 2-stage DIRK stage 1 with BDF2-like weights)
+    be = dict(A=[[1.0]], b=[1.0], bdf=[1.0, -1.0], dt=0.05, time=0.3, stage=0)
+    dirk = dict(A=[[0.25, 0.0], [0.5, 0.25]], b=[0.5, 0.5], bdf=[1.5, -2.0, 0.5], dt=0.02, time=0.1, stage=1)
+    for nm, ti in (("BE", be), ("DIRK2 stage1", dirk)):
+        p = shrink(P.regression_thermal_3d()); p["extra"] = {"transient": True}; p["name"] = "thermal 3D transient " + nm
+        p["functions"] = dict(p["functions"]); p["functions"].update({"density": "2.0", "specific heat": "1.0+x", "thermal source": "sin(t)*x"})
+        out.append((p["name"], p, {"transient": ti}))
+    p = shrink(P.config_c5(4)); p["extra"] = {"transient": True}; p["name"] = "NS 3D transient BE supg/pspg"
+    out.append((p["name"], p, {"transient": be}))
+    p = shrink(P.regression_cdr_2d()); p["extra"] = {"transient": True, "workset size": 40}; p["name"] = "cdr 2D transient DIRK2"
+    out.append((p["name"], p, {"transient": dirk}))
+    # lumped mass, fix-zero-rows
+    p = shrink(P.regression_thermal_2d()); p["extra"] = {"lump mass": True, "fix zero rows": True}; p["name"] = "thermal 2D lump mass"
+    out.append((p["name"], p, {}))
+    return out
+
+
+def oracle_problem(p):
+    """The oracle's config text does not know engine-only keys."""
+    q = copy.deepcopy(p)
+    q.pop("true", None)
+    q.pop("name", None)
+    return config_text(**q)
+
+
+def rel_errors(a, b, rowptr=None):
+    scale = np.abs(b).max()
+    g = np.abs(a - b).max() / (scale if scale > 0 else 1.0)
+    if rowptr is None:
+        return g, g
+    # per-row: ||d row||_inf / ||row||_inf
+    d = np.abs(a - b)
+    rows = np.repeat(np.arange(len(rowptr) - 1), np.diff(rowptr))
+    dmax = np.zeros(len(rowptr) - 1); bmax = np.zeros(len(rowptr) - 1)
+    np.maximum.at(dmax, rows, d); np.maximum.at(bmax, rows, np.abs(b))
+    ok = bmax > 0
+    return g, (dmax[ok] / bmax[ok]).max() if ok.any() else 0.0
+
+
+def check_case(p, kw, lib, on_gpu, force_generic=False, jacobian=True):
+    from mrhyde_b200 import Engine
+    o = Oracle(oracle_problem(p))
+    e = Engine.from_problem(p, lib=lib, force_generic=force_generic)
+    s = e.sizes()
+    assert (s["nlocal"], s["nnz"], s["nelem"]) == (o.nlocal, o.nnz, o.nelem)
+    lids, offs, fixed, xyz, var = e.dofmap()
+    ol, oo, of, oxyz, ovar = o.dofmap()
+    rp, ci = e.crs()
+    orp, oci = o.crs()
+    for a, b in ((lids, ol), (offs, oo), (fixed, of), (rp, orp), (ci, oci), (var, ovar), (xyz, oxyz)):
+        assert np.array_equal(a, b), "indexing is not bit-exact"
+    assert np.array_equal(e.bc_codes(), o.bc_codes())
+    u = problems.synthetic_state(xyz, var)
+    ti = kw.get("transient")
+    u_prev = u_stage = None
+    if ti is not None:
+        nsteps, nst = len(ti["bdf"]) - 1, len(ti["b"])
+        u_prev = np.stack([problems.synthetic_state(xyz, var, seed=77 + k) * 0.9 for k in range(nsteps)], axis=1).copy()
+        u_stage = np.stack([problems.synthetic_state(xyz, var, seed=99 + k) * 1.1 for k in range(nst)], axis=1).copy()
+        o.set_time(ti["A"], ti["b"], ti["bdf"], ti["dt"], ti["time"], ti["stage"])
+    ores, ojac = o.assemble(u, jacobian=jacobian, u_prev=u_prev, u_stage=u_stage)
+    if on_gpu:
+        import torch
+        dev = torch.device("cuda:0")
+        tu = torch.from_numpy(u).to(dev)
+        tp = torch.from_numpy(u_prev).to(dev) if u_prev is not None else None
+        ts = torch.from_numpy(u_stage).to(dev) if u_stage is not None else None
+        tres = torch.zeros(o.nlocal, dtype=torch.float64, device=dev)
+        tjac = torch.zeros(o.nnz, dtype=torch.float64, device=dev)
+        if jacobian:
+            e.assemble_jacres(tu, tres, tjac, u_prev=tp, u_stage=ts, time_int=ti)
+        else:
+            e.assemble_res(tu, tres, u_prev=tp, u_stage=ts, time_int=ti)
+        torch.cuda.synchronize()
+        res, jac = tres.cpu().numpy(), tjac.cpu().numpy()
+    else:
+        res, jac = np.zeros(o.nlocal), np.zeros(o.nnz)
+        if jacobian:
+            e.assemble_jacres(u, res, jac, u_prev=u_prev, u_stage=u_stage, time_int=ti)
+        else:
+            e.assemble_res(u, res, u_prev=u_prev, u_stage=u_stage, time_int=ti)
+    er, _ = rel_errors(res, ores)
+    assert er <= TOL, f"residual rel err {er:.3e}"
+    out = {"res": er, "launches": e.launch_count()}
+    if jacobian:
+        eg, erow = rel_errors(jac, ojac, rp)
+        assert eg <= TOL and erow <= 1e-10, f"jacobian rel err {eg:.3e} (per-row {erow:.3e})"
+        out.update(jac=eg, jac_row=erow)
+    e.close()
+    return out
