@@ -1,0 +1,95 @@
+"""GPU parity tests proper: the CUDA library through its C ABI against the oracle (run with -m gpu on a B200)."""
+import numpy as np
+import pytest
+
+import parity_util as U
+import problems
+
+pytestmark = pytest.mark.gpu
+CASES = U.cases()
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import torch
+    from mrhyde_b200 import lib_path
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return lib_path()
+
+
+@pytest.mark.parametrize("name,p,kw", CASES, ids=[c[0] for c in CASES])
+def test_cuda_matches_oracle(lib, name, p, kw):
+    U.check_case(p, kw, lib, on_gpu=True)
+    U.check_case(p, kw, lib, on_gpu=True, jacobian=False)
+
+
+@pytest.mark.parametrize("name,p,kw", [c for c in CASES if c[1]["physics"] == "thermal" and c[1]["mesh"]["dim"] == 3],
+                         ids=lambda v: v if isinstance(v, str) else "")
+def test_cuda_generic_kernel_on_specialised_cases(lib, name, p, kw):
+    U.check_case(p, kw, lib, on_gpu=True, force_generic=True)
+
+
+def test_mid_size_c2_against_oracle(lib):
+    """24^3 thermal Q1 (SURVEY.md 8d parity size) through the specialised kernel."""
+    r = U.check_case(problems.config_c2(24), {}, lib, on_gpu=True)
+    assert r["launches"] == 2          # one volume kernel + the DBC diagonal kernel
+
+
+def test_large_mesh_properties(lib):
+    """Size-independent properties at a size the oracle does not reach in seconds (96^3 thermal Q1):
+    Jacobian rows of non-fixed interior DOFs sum to ~0 (constants are in the Laplacian's kernel), J is symmetric in
+    its action (x.Jy == y.Jx on free DOFs), res(u) = -(J u - b) is affine in u (linearity), and repeated assembly
+    accumulates exactly twice the values up to atomics ordering."""
+    import torch
+    from mrhyde_b200 import Engine
+    p = problems.config_c2(96)
+    e = Engine.from_problem(p, lib=lib)
+    s = e.sizes()
+    rp, ci = e.crs()
+    xyz, var = e.dof_coords()
+    _, _, fixed, _, _ = e.dofmap()
+    dev = torch.device("cuda:0")
+    u = torch.from_numpy(problems.synthetic_state(xyz, var)).to(dev)
+    res = torch.zeros(s["nlocal"], dtype=torch.float64, device=dev)
+    jac = torch.zeros(s["nnz"], dtype=torch.float64, device=dev)
+    e.assemble_jacres(u, res, jac)
+    torch.cuda.synchronize()
+    J = torch.sparse_csr_tensor(torch.from_numpy(rp).to(dev), torch.from_numpy(ci.astype(np.int64)).to(dev), jac,
+                                size=(s["nlocal"], s["nlocal"]))
+    free = torch.from_numpy(fixed == 0).to(dev)
+    ones = torch.ones(s["nlocal"], dtype=torch.float64, device=dev)
+    rowsum = (J @ ones)
+    # rows whose whole stencil is free
+    touches_fixed = (J.abs() @ (~free).double()) > 0
+    interior = free & ~touches_fixed
+    assert rowsum[interior].abs().max().item() < 1e-12 * jac.abs().max().item() * 27
+    # fixed rows are identity rows
+    assert torch.allclose(rowsum[~free], torch.ones_like(rowsum[~free]))
+    # affine residual: res(u) - res(0) == -J u on free rows
+    res0 = torch.zeros_like(res)
+    e.assemble_res(torch.zeros_like(u), res0)
+    lin = -(J @ u)
+    d = (res - res0 - lin)[free].abs().max().item()
+    assert d < 1e-11 * max(res.abs().max().item(), 1.0)
+    # accumulate semantics
+    e.assemble_jacres(u, res, jac)
+    torch.cuda.synchronize()
+    rowsum2 = (torch.sparse_csr_tensor(torch.from_numpy(rp).to(dev), torch.from_numpy(ci.astype(np.int64)).to(dev), jac,
+                                       size=(s["nlocal"], s["nlocal"])) @ ones)
+    assert torch.allclose(rowsum2[interior], 2 * rowsum[interior], atol=1e-9)
+    assert s["npatterns"] >= 1 and s["npatterns"] < 4096
+
+
+def test_host_buffer_entry_point(lib):
+    from mrhyde_b200 import Engine
+    p = problems.config_c2(12)
+    e = Engine.from_problem(p, lib=lib)
+    s = e.sizes()
+    xyz, var = e.dof_coords()
+    u = problems.synthetic_state(xyz, var)
+    res = np.zeros(s["nlocal"]); jac = np.zeros(s["nnz"])
+    e.assemble_jacres_host(u, res, jac)
+    from oracle.pyoracle import Oracle
+    o = Oracle(U.oracle_problem(p))
+    ores, ojac = o.assemble(u)
+    assert U.rel_errors(res, ores)[0] < U.TOL and U.rel_errors(jac, ojac)[0] < U.TOL
