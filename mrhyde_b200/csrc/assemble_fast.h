@@ -48,8 +48,14 @@ inline bool thermal_hex_q1_eligible(int phys, int dim, int order, int nq, bool s
 template <bool TRANSIENT, bool ADV, bool JAC>
 struct ThermalHexQ1 {
   static constexpr int NK = ADV ? 64 : 36;
+  static constexpr int NSTAGE = 2 + (TRANSIENT ? 1 : 0) + (ADV ? 3 : 0);   // staged coefficient arrays (8 points each)
+  MRH_HD static constexpr int vtx(int a, int b, int c) {                   // tensor bits -> shards vertex
+    return (b ? (a ? 2 : 3) : (a ? 1 : 0)) + 4 * c;
+  }
 
-  MRH_HDN static void element(const KParams& kp, int64_t e) {
+  // stage: per-thread scratch for the coefficient values at the 8 points, element k of array m at
+  // stage[(m*8+k)*stride] (shared memory, stride = blockDim.x, on the device).
+  MRH_HDN static void element(const KParams& kp, int64_t e, double* stage, int stride) {
     // ---- gather: LIDs, vertex coordinates, DOFs ------------------------------------------------------
     int lid[8];
     {
@@ -86,92 +92,116 @@ struct ThermalHexQ1 {
     }
     const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
 
-    // ---- coefficients at the 8 points (vector interpreter; constants cost nothing) --------------------
-    double px[8], py[8], pz[8];
+    // ---- coefficients at the 8 points (vector interpreter), staged for the rolled point loop ------------
+    {
+      double px[8], py[8], pz[8], val[8];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      double x = 0.0, y = 0.0, z = 0.0;
+      for (int q = 0; q < 8; ++q) {
+        double x = 0.0, y = 0.0, z = 0.0;
 #pragma unroll
-      for (int s = 0; s < 8; ++s) { x += X[s][0] * HexQ1::N(s, q); y += X[s][1] * HexQ1::N(s, q); z += X[s][2] * HexQ1::N(s, q); }
-      px[q] = x; py[q] = y; pz[q] = z;
-    }
-    double src[8], kap[8], rcp[8];
-    eval_prog_vec<8>(kp.progs[TH_SOURCE], kp.code, kp.cpool, px, py, pz, kp.tp.time, src);
-    eval_prog_vec<8>(kp.progs[TH_DIFF], kp.code, kp.cpool, px, py, pz, kp.tp.time, kap);
-    if (TRANSIENT) {
-      double cp[8], rho[8];
-      eval_prog_vec<8>(kp.progs[TH_CP], kp.code, kp.cpool, px, py, pz, kp.tp.time, cp);
-      eval_prog_vec<8>(kp.progs[TH_RHO], kp.code, kp.cpool, px, py, pz, kp.tp.time, rho);
+        for (int s = 0; s < 8; ++s) { x += X[s][0] * HexQ1::N(s, q); y += X[s][1] * HexQ1::N(s, q); z += X[s][2] * HexQ1::N(s, q); }
+        px[q] = x; py[q] = y; pz[q] = z;
+      }
+      int m = 0;
+      auto put = [&](int slot) {
+        eval_prog_vec<8>(kp.progs[slot], kp.code, kp.cpool, px, py, pz, kp.tp.time, val);
 #pragma unroll
-      for (int q = 0; q < 8; ++q) rcp[q] = rho[q] * cp[q];
-    }
-    double bx[8], by[8], bz[8];
-    if (ADV) {
-      eval_prog_vec<8>(kp.progs[TH_BX], kp.code, kp.cpool, px, py, pz, kp.tp.time, bx);
-      eval_prog_vec<8>(kp.progs[TH_BY], kp.code, kp.cpool, px, py, pz, kp.tp.time, by);
-      eval_prog_vec<8>(kp.progs[TH_BZ], kp.code, kp.cpool, px, py, pz, kp.tp.time, bz);
+        for (int q = 0; q < 8; ++q) stage[(m * 8 + q) * stride] = val[q];
+        ++m;
+      };
+      put(TH_SOURCE); put(TH_DIFF);
+      if (TRANSIENT) {
+        double cp[8];
+        eval_prog_vec<8>(kp.progs[TH_CP], kp.code, kp.cpool, px, py, pz, kp.tp.time, cp);
+        eval_prog_vec<8>(kp.progs[TH_RHO], kp.code, kp.cpool, px, py, pz, kp.tp.time, val);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) stage[(m * 8 + q) * stride] = val[q] * cp[q];
+        ++m;
+      }
+      if (ADV) { put(TH_BX); put(TH_BY); put(TH_BZ); }
     }
 
-    // ---- point loop: geometry, gradients, residual, element matrix -----------------------------------
+    // ---- point loop (rolled: the body stays resident in the instruction cache) ------------------------
     double r[8], K[NK];
 #pragma unroll
     for (int s = 0; s < 8; ++s) r[s] = 0.0;
 #pragma unroll
     for (int k = 0; k < NK; ++k) K[k] = 0.0;
 
-#pragma unroll
+#pragma unroll 1
     for (int q = 0; q < 8; ++q) {
+      const double g = HexQ1::g;
+      const double sx = (q & 1) ? -g : g, sy = (q & 2) ? -g : g, sz = (q & 4) ? -g : g;
+      const double lx[2] = {0.5 - 0.5 * sx, 0.5 + 0.5 * sx}, ly[2] = {0.5 - 0.5 * sy, 0.5 + 0.5 * sy}, lz[2] = {0.5 - 0.5 * sz, 0.5 + 0.5 * sz};
+      double yz[2][2], xz[2][2], xy[2][2];
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b) { yz[a][b] = ly[a] * lz[b]; xz[a][b] = lx[a] * lz[b]; xy[a][b] = lx[a] * ly[b]; }
+      // J_ij = sum_s X_s,i dN_s/dxi_j written with edge differences (dN/dxi = +-1/2 * product of the other two)
       double J[3][3];
 #pragma unroll
-      for (int i = 0; i < 3; ++i)
+      for (int i = 0; i < 3; ++i) {
+        double c0 = 0.0, c1 = 0.0, c2 = 0.0;
 #pragma unroll
-        for (int j = 0; j < 3; ++j) {
-          double s_ = 0.0;
+        for (int a = 0; a < 2; ++a)
 #pragma unroll
-          for (int s = 0; s < 8; ++s) s_ += X[s][i] * HexQ1::dN(s, q, j);
-          J[i][j] = s_;
-        }
+          for (int b = 0; b < 2; ++b) {
+            c0 += yz[a][b] * (X[vtx(1, a, b)][i] - X[vtx(0, a, b)][i]);
+            c1 += xz[a][b] * (X[vtx(a, 1, b)][i] - X[vtx(a, 0, b)][i]);
+            c2 += xy[a][b] * (X[vtx(a, b, 1)][i] - X[vtx(a, b, 0)][i]);
+          }
+        J[i][0] = 0.5 * c0; J[i][1] = 0.5 * c1; J[i][2] = 0.5 * c2;
+      }
       double Ji[3][3];
       const double det = det_inv<3>(J, Ji);
       const double w = fabs(det);                       // reference weight 1
-      double gx[8], gy[8], gz[8];
+      double gx[8], gy[8], gz[8], Nq[8];
       double ex = 0.0, ey = 0.0, ez = 0.0, edot = 0.0;
 #pragma unroll
       for (int s = 0; s < 8; ++s) {
-        gx[s] = Ji[0][0] * HexQ1::dN(s, q, 0) + Ji[1][0] * HexQ1::dN(s, q, 1) + Ji[2][0] * HexQ1::dN(s, q, 2);
-        gy[s] = Ji[0][1] * HexQ1::dN(s, q, 0) + Ji[1][1] * HexQ1::dN(s, q, 1) + Ji[2][1] * HexQ1::dN(s, q, 2);
-        gz[s] = Ji[0][2] * HexQ1::dN(s, q, 0) + Ji[1][2] * HexQ1::dN(s, q, 1) + Ji[2][2] * HexQ1::dN(s, q, 2);
+        const int a = HexQ1::bx(s), b = HexQ1::by(s), c = HexQ1::bz(s);
+        const double d0 = (a ? 0.5 : -0.5) * yz[b][c], d1 = (b ? 0.5 : -0.5) * xz[a][c], d2 = (c ? 0.5 : -0.5) * xy[a][b];
+        Nq[s] = xy[a][b] * lz[c];
+        gx[s] = Ji[0][0] * d0 + Ji[1][0] * d1 + Ji[2][0] * d2;
+        gy[s] = Ji[0][1] * d0 + Ji[1][1] * d1 + Ji[2][1] * d2;
+        gz[s] = Ji[0][2] * d0 + Ji[1][2] * d1 + Ji[2][2] * d2;
         ex += us[s] * gx[s]; ey += us[s] * gy[s]; ez += us[s] * gz[s];
-        if (TRANSIENT) edot += ud[s] * HexQ1::N(s, q);
+        if (TRANSIENT) edot += ud[s] * Nq[s];
       }
-      const double kw = kap[q] * w;
-      double f0 = -src[q] * w;
-      if (TRANSIENT) f0 += rcp[q] * edot * w;
-      if (ADV) f0 += (bx[q] * ex + by[q] * ey + bz[q] * ez) * w;
+      const double srcq = stage[(0 * 8 + q) * stride], kapq = stage[(1 * 8 + q) * stride];
+      const double rcpq = TRANSIENT ? stage[(2 * 8 + q) * stride] : 0.0;
+      constexpr int AB = TRANSIENT ? 3 : 2;
+      const double bxq = ADV ? stage[((AB + 0) * 8 + q) * stride] : 0.0, byq = ADV ? stage[((AB + 1) * 8 + q) * stride] : 0.0,
+                   bzq = ADV ? stage[((AB + 2) * 8 + q) * stride] : 0.0;
+      const double kw = kapq * w;
+      double f0 = -srcq * w;
+      if (TRANSIENT) f0 += rcpq * edot * w;
+      if (ADV) f0 += (bxq * ex + byq * ey + bzq * ez) * w;
       const double fx = kw * ex, fy = kw * ey, fz = kw * ez;
 #pragma unroll
-      for (int s = 0; s < 8; ++s) r[s] += f0 * HexQ1::N(s, q) + fx * gx[s] + fy * gy[s] + fz * gz[s];
+      for (int s = 0; s < 8; ++s) r[s] += f0 * Nq[s] + fx * gx[s] + fy * gy[s] + fz * gz[s];
       if (JAC) {
         const double kwa = kw * au;
-        const double mw = TRANSIENT ? rcp[q] * at * w : 0.0;
+        const double mw = TRANSIENT ? rcpq * at * w : 0.0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const double ax = kwa * gx[i], ay = kwa * gy[i], az = kwa * gz[i];
-          const double mi = TRANSIENT ? mw * HexQ1::N(i, q) : 0.0;
+          const double mi = TRANSIENT ? mw * Nq[i] : 0.0;
           if (!ADV) {
 #pragma unroll
             for (int j = i; j < 8; ++j) {
               double v = K[HexQ1::tri(i, j)] + ax * gx[j] + ay * gy[j] + az * gz[j];
-              if (TRANSIENT) v += mi * HexQ1::N(j, q);
+              if (TRANSIENT) v += mi * Nq[j];
               K[HexQ1::tri(i, j)] = v;
             }
           } else {
-            const double ci = au * w * HexQ1::N(i, q);
+            const double ci = au * w * Nq[i];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               double v = K[i * 8 + j] + ax * gx[j] + ay * gy[j] + az * gz[j];
-              v += ci * (bx[q] * gx[j] + by[q] * gy[j] + bz[q] * gz[j]);
-              if (TRANSIENT) v += mi * HexQ1::N(j, q);
+              v += ci * (bxq * gx[j] + byq * gy[j] + bzq * gz[j]);
+              if (TRANSIENT) v += mi * Nq[j];
               K[i * 8 + j] = v;
             }
           }

@@ -74,8 +74,9 @@ __global__ void __launch_bounds__(128) generic_assembly_kernel(const __grid_cons
 
 template <bool TRANSIENT, bool ADV, bool JAC>
 __global__ void __launch_bounds__(128) thermal_hex_q1_kernel(const __grid_constant__ KParams kp) {
+  __shared__ double stage[ThermalHexQ1<TRANSIENT, ADV, JAC>::NSTAGE * 8 * 128];
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (int64_t)gridDim.x * blockDim.x)
-    ThermalHexQ1<TRANSIENT, ADV, JAC>::element(kp, e);
+    ThermalHexQ1<TRANSIENT, ADV, JAC>::element(kp, e, stage + threadIdx.x, 128);
 }
 
 // row-relative CRS position of column `col` in row `row` (columns ascending)

@@ -55,7 +55,7 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
         thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
       const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
       for (int64_t e = 0; e < kp.nwork; ++e) {
-#define MRH_FAST(T, A, Jc) if (tr == T && adv == A && jc == Jc) ThermalHexQ1<T, A, Jc>::element(kp, e);
+#define MRH_FAST(T, A, Jc) if (tr == T && adv == A && jc == Jc) { double stage[48]; ThermalHexQ1<T, A, Jc>::element(kp, e, stage, 1); }
         MRH_FAST(false, false, false) MRH_FAST(false, false, true) MRH_FAST(false, true, false) MRH_FAST(false, true, true)
         MRH_FAST(true, false, false) MRH_FAST(true, false, true) MRH_FAST(true, true, false) MRH_FAST(true, true, true)
 #undef MRH_FAST
