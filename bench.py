@@ -234,12 +234,12 @@ def run_gpu(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C2: 3D thermal, HGRAD Q1 hexes, structured brick, FP64 residual+Jacobian",
                        "mesh": f"{n}^3 per GPU" + (f", {world} z-slabs" if world > 1 else ""), "elements_per_gpu": s["nelem"],
-                       "dofs_per_gpu": s["nlocal"], "nnz_per_gpu": s["nnz"], "slot_patterns": s["npatterns"],
+                       "dofs_per_gpu": s["nlocal"], "nnz_per_gpu": s["nnz"], "slot_patterns": s["npatterns"], "volume_kernel": e.kernel_path(),
                        "l2": "inputs+outputs (4.6 GB/step) exceed the 126 MB L2; no flush needed",
                        "timing": "CUDA events on the launch stream, K steps, max over ranks", "setup_s": round(t_setup, 1)},
             "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
                          "traffic": None, "peak_source": "MEASURED_PEAKS.json (of measured)" if pk else "fallback 6650 (of fallback)",
-                         "kernel": "thermal_hex_q1_kernel<false,false,true>", "kernel_ms": vk * 1e3,
+                         "kernel": "thermal Q1 hex specialised kernel (" + e.kernel_path() + ")", "kernel_ms": vk * 1e3,
                          "bytes_per_elem": BYTES_PER_ELEM, "binding_roof": "fp64 (see roofline_fp64)"},
             "roofline_fp64": {"bound": "fp64", "achieved": ach_tf, "peak": dfma.value, "unit": "TFLOP/s",
                               "frac": ach_tf / dfma.value if dfma.value > 0 else None, "flops_per_elem": FLOPS_PER_ELEM,

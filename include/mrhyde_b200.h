@@ -57,7 +57,7 @@ typedef struct mrh_config {
   double form_param;          /* thermal / LE "form_param" (default 1.0) */
   double le_penalty;          /* LE "penalty" (default 10.0) */
   int32_t device;             /* CUDA device ordinal */
-  int32_t flags;              /* bit 0: force the generic kernel even where a specialised one applies (tests) */
+  int32_t flags;              /* bit 0: force the generic kernel; bit 1: no NVRTC specialisation (tests) */
 } mrh_config;
 
 /* Workset time data: Workset::{time,deltat,isTransient,current_stage,butcher_A,butcher_b,BDF_wts}
@@ -133,6 +133,9 @@ const char* mrh_get_varname(mrh_handle h, int32_t var);
 /* evaluate a registered "ip" function on host doubles at given points (parser known-answer tests) */
 int mrh_eval_function_host(mrh_handle h, const char* name, const char* location, int64_t npts, const double* xyz,
                            double time, double* out);
+/* which volume kernel the last assemble call used: "nvrtc-specialised", "specialised" (in-kernel bytecode
+ * interpreter) or "generic" */
+const char* mrh_last_kernel_path(mrh_handle h);
 /* number of kernels launched by the last assemble call (bench.py "gpu_launches") */
 int64_t mrh_last_launch_count(mrh_handle h);
 /* device time of the dominant (volume) kernel of the last assemble call, ms (CUDA events on the caller's stream) */

@@ -40,12 +40,19 @@ struct HexQ1 {
   MRH_HD static constexpr int tri(int i, int j) { return i * 8 - (i * (i - 1)) / 2 + (j - i); }   // i <= j, 36 entries
 };
 
+#if !defined(__CUDACC_RTC__)
 // eligibility of a volume launch for this kernel (checked on the host)
 inline bool thermal_hex_q1_eligible(int phys, int dim, int order, int nq, bool state_independent, int lump_mass) {
   return phys == PHYS_THERMAL && dim == 3 && order == 1 && nq == 8 && state_independent && !lump_mass;
 }
+#endif
 
-template <bool TRANSIENT, bool ADV, bool JAC>
+// Coefficient policy.  InterpCoefs: the bytecode programs are run by the vector interpreter before the point loop
+// and their values staged in shared memory.  The NVRTC build (jit.hpp) supplies a policy with staged = false whose
+// source()/diff()/rhocp()/bx()/by()/bz() are the expressions themselves, compiled inline into the point loop.
+struct InterpCoefs { static constexpr bool staged = true; };
+
+template <bool TRANSIENT, bool ADV, bool JAC, class CF = InterpCoefs>
 struct ThermalHexQ1 {
   static constexpr int NK = ADV ? 64 : 36;
   static constexpr int NSTAGE = 2 + (TRANSIENT ? 1 : 0) + (ADV ? 3 : 0);   // staged coefficient arrays (8 points each)
@@ -93,7 +100,7 @@ struct ThermalHexQ1 {
     const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
 
     // ---- coefficients at the 8 points (vector interpreter), staged for the rolled point loop ------------
-    {
+    if constexpr (CF::staged) {
       double px[8], py[8], pz[8], val[8];
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
@@ -169,11 +176,21 @@ struct ThermalHexQ1 {
         ex += us[s] * gx[s]; ey += us[s] * gy[s]; ez += us[s] * gz[s];
         if (TRANSIENT) edot += ud[s] * Nq[s];
       }
-      const double srcq = stage[(0 * 8 + q) * stride], kapq = stage[(1 * 8 + q) * stride];
-      const double rcpq = TRANSIENT ? stage[(2 * 8 + q) * stride] : 0.0;
-      constexpr int AB = TRANSIENT ? 3 : 2;
-      const double bxq = ADV ? stage[((AB + 0) * 8 + q) * stride] : 0.0, byq = ADV ? stage[((AB + 1) * 8 + q) * stride] : 0.0,
-                   bzq = ADV ? stage[((AB + 2) * 8 + q) * stride] : 0.0;
+      double srcq, kapq, rcpq = 0.0, bxq = 0.0, byq = 0.0, bzq = 0.0;
+      if constexpr (CF::staged) {
+        constexpr int AB = TRANSIENT ? 3 : 2;
+        srcq = stage[(0 * 8 + q) * stride]; kapq = stage[(1 * 8 + q) * stride];
+        if (TRANSIENT) rcpq = stage[(2 * 8 + q) * stride];
+        if (ADV) { bxq = stage[((AB + 0) * 8 + q) * stride]; byq = stage[((AB + 1) * 8 + q) * stride]; bzq = stage[((AB + 2) * 8 + q) * stride]; }
+      } else {
+        double x = 0.0, y = 0.0, z = 0.0;
+#pragma unroll
+        for (int s = 0; s < 8; ++s) { x += X[s][0] * Nq[s]; y += X[s][1] * Nq[s]; z += X[s][2] * Nq[s]; }
+        const double t = kp.tp.time;
+        srcq = CF::source(x, y, z, t); kapq = CF::diff(x, y, z, t);
+        if (TRANSIENT) rcpq = CF::rhocp(x, y, z, t);
+        if (ADV) { bxq = CF::bx(x, y, z, t); byq = CF::by(x, y, z, t); bzq = CF::bz(x, y, z, t); }
+      }
       const double kw = kapq * w;
       double f0 = -srcq * w;
       if (TRANSIENT) f0 += rcpq * edot * w;

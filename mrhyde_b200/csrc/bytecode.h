@@ -3,7 +3,9 @@
 // :762-1900).  Here each expression is compiled once on the host (expr.hpp) into a postfix program that a
 // thread evaluates per quadrature point inside the fused assembly kernel, on doubles or on PAD<P> lanes.
 #pragma once
+#if !defined(__CUDACC_RTC__)
 #include <cstdint>
+#endif
 #include "pad.h"
 
 namespace mrh {

@@ -9,8 +9,9 @@
 #include <thrust/unique.h>
 
 #include "capi_host.inl"
-#include "dispatch.h"
 #include "assemble_fast.h"
+#include "generic_kernels.h"
+#include "jit.hpp"
 
 using namespace mrh;
 
@@ -49,29 +50,12 @@ struct DeviceImpl {
   double vol_ms = 0.0;
   // staging for the *_host entry point
   DevBuf<double> h_u, h_res, h_jac;
+  JitCache jit;
+  bool jit_used = false;
+  const char* last_path = "none";
 };
 
 // ------------------------------------------------------------------------------------------------ kernels
-template <class C, bool JAC>
-__global__ void __launch_bounds__(128) generic_assembly_kernel(const __grid_constant__ KParams kp) {
-  extern __shared__ double sm[];
-  using G = GenPhases<C>;
-  using S = typename std::conditional<JAC, PAD<C::P>, double>::type;
-  const int EB = kp.elems_per_block, tid = threadIdx.x, nt = blockDim.x;
-  const GenSmem<C> L(EB, kp.tab.nq, JAC, kp.tp.transient != 0);
-  for (int64_t blk0 = (int64_t)blockIdx.x * EB; blk0 < kp.nwork; blk0 += (int64_t)gridDim.x * EB) {
-    for (int it = tid; it < EB * C::N; it += nt) G::gather_dof(kp, L, sm, blk0, it);
-    for (int it = tid; it < EB * C::NV; it += nt) G::gather_vertex(kp, L, sm, blk0, it);
-    __syncthreads();
-    for (int it = tid; it < EB * L.nq; it += nt) G::geometry(kp, L, sm, blk0, it);
-    __syncthreads();
-    for (int it = tid; it < EB * L.nq; it += nt) G::template point<S>(kp, L, sm, blk0, it);
-    __syncthreads();
-    for (int it = tid; it < EB * C::NB * C::NVAR; it += nt) G::contract(kp, L, sm, blk0, it);
-    __syncthreads();
-  }
-}
-
 template <bool TRANSIENT, bool ADV, bool JAC>
 __global__ void __launch_bounds__(128) thermal_hex_q1_kernel(const __grid_constant__ KParams kp) {
   __shared__ double stage[ThermalHexQ1<TRANSIENT, ADV, JAC>::NSTAGE * 8 * 128];

@@ -53,6 +53,24 @@ void device_finalize(mrh_engine* h) {
   for (auto& S : H.mesh.sides) { D.side_elems.emplace_back(new DevBuf<int>()); D.side_elems.back()->upload(S.elems); }
   build_patterns(H, D);
   h->npatterns = D.npatterns;
+  // NVRTC specialisation of the coefficient expressions for the specialised thermal kernel (jit.hpp)
+  D.jit.clear();
+  if (!(H.cfg.flags & 3) && thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
+    try {
+      std::string src;
+      src += jit_function_source("source", H.vol_progs[TH_SOURCE], H.ec.code, H.ec.cpool);
+      src += jit_function_source("diff", H.vol_progs[TH_DIFF], H.ec.code, H.ec.cpool);
+      src += jit_function_source("rho_", H.vol_progs[TH_RHO], H.ec.code, H.ec.cpool);
+      src += jit_function_source("cp_", H.vol_progs[TH_CP], H.ec.code, H.ec.cpool);
+      src += "  static __device__ __forceinline__ double rhocp(double x, double y, double z, double t) { return rho_(x, y, z, t) * cp_(x, y, z, t); }\n";
+      src += jit_function_source("bx", H.vol_progs[TH_BX], H.ec.code, H.ec.cpool);
+      src += jit_function_source("by", H.vol_progs[TH_BY], H.ec.code, H.ec.cpool);
+      src += jit_function_source("bz", H.vol_progs[TH_BZ], H.ec.code, H.ec.cpool);
+      D.jit.setCoefficientSource(src);
+      const bool adv = H.cfg.include_advection != 0;
+      if (!D.jit.thermal(false, adv, true) || !D.jit.thermal(false, adv, false)) h->err = "NVRTC specialisation unavailable, using the in-kernel interpreter: " + D.jit.last_error;
+    } catch (const std::exception& ex) { D.jit.clear(); h->err = std::string("NVRTC specialisation skipped: ") + ex.what(); }
+  }
   D.dbc.upload(H.dbc_dofs); D.dbc_slots.alloc(H.dbc_dofs.size());
   if (!H.dbc_dofs.empty()) {
     dbc_slot_kernel<<<blocks_for((int64_t)H.dbc_dofs.size(), 128), 128>>>(D.dbc.p, (int64_t)H.dbc_dofs.size(), D.rowptr.p, D.colind.p, D.dbc_slots.p);
@@ -63,26 +81,6 @@ void device_finalize(mrh_engine* h) {
   D.bp.pat = D.pat.p; D.bp.pat_id = D.pat_id.p; D.bp.code = D.code.p; D.bp.cpool = D.cpool.p;
   if (!D.ev0) { CUDA_CK(cudaEventCreate(&D.ev0)); CUDA_CK(cudaEventCreate(&D.ev1)); }
   D.ready = true;
-}
-
-template <class C, bool JAC>
-void launch_generic(const DeviceImpl& D, KParams& kp, cudaStream_t stream) {
-  const size_t per_elem = GenSmem<C>(1, kp.tab.nq, JAC, kp.tp.transient != 0).total_doubles() * sizeof(double);
-  int EB = (int)((100 * 1024) / per_elem);
-  if (EB < 1) EB = 1;
-  if (EB > 16) EB = 16;
-  const size_t smem = GenSmem<C>(EB, kp.tab.nq, JAC, kp.tp.transient != 0).total_doubles() * sizeof(double);
-  if (smem > 227 * 1024) throw std::runtime_error("element block does not fit in shared memory (quadrature too large)");
-  auto kern = generic_assembly_kernel<C, JAC>;
-  CUDA_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 1;
-  CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
-  if (per_sm < 1) per_sm = 1;
-  kp.elems_per_block = EB;
-  const int64_t nblk = (kp.nwork + EB - 1) / EB;
-  const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * per_sm);
-  kern<<<grid, 128, smem, stream>>>(kp);
-  CUDA_CK(cudaGetLastError());
 }
 
 template <bool T, bool A, bool J>
@@ -113,15 +111,23 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
         thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass);
     if (fast) {
       const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
+      JitKernel* jk = (H.cfg.flags & 2) ? nullptr : D.jit.thermal(tr, adv, jc);
+      D.jit_used = jk != nullptr;
+      D.last_path = jk ? "nvrtc-specialised" : "specialised";
+      if (jk) {
+        const int64_t nblk = (kp.nwork + 127) / 128;
+        const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * jk->blocks_per_sm * 4);
+        void* args[] = {(void*)&kp};
+        if (JitApi::get().LaunchKernel(jk->fn, grid, 1, 1, 128, 1, 1, 0, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+          throw std::runtime_error("CUDA error: cuLaunchKernel failed for the NVRTC-specialised kernel");
+      } else
 #define MRH_FAST(T, A, Jc) if (tr == T && adv == A && jc == Jc) launch_thermal_fast<T, A, Jc>(D, kp, stream);
       MRH_FAST(false, false, false) MRH_FAST(false, false, true) MRH_FAST(false, true, false) MRH_FAST(false, true, true)
       MRH_FAST(true, false, false) MRH_FAST(true, false, true) MRH_FAST(true, true, false) MRH_FAST(true, true, true)
 #undef MRH_FAST
     } else {
-      const bool ok = dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) {
-        using C = decltype(c);
-        if (jac) launch_generic<C, true>(D, kp, stream); else launch_generic<C, false>(D, kp, stream);
-      });
+      if (side < 0) D.last_path = "generic";
+      const bool ok = launch_generic_assembly(H.phys, H.dim, H.order, jac != nullptr, D.num_sms, kp, (void*)stream);
       if (!ok) throw std::runtime_error("configuration not supported: no kernel for this physics/dimension/order");
     }
     if (side < 0) CUDA_CK(cudaEventRecord(D.ev1, stream));
@@ -235,6 +241,11 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res
   CUDA_CK(cudaStreamSynchronize(s));
   return rc;
   MRH_CATCH_CUDA(h)
+}
+const char* mrh_last_kernel_path(mrh_handle h) {
+  if (!h || !h->impl) return "none";
+  auto* D = (DeviceImpl*)h->impl;
+  return D->last_path;
 }
 int64_t mrh_last_launch_count(mrh_handle h) { return (h && h->impl) ? ((DeviceImpl*)h->impl)->launches : 0; }
 double mrh_last_volume_kernel_ms(mrh_handle h) {

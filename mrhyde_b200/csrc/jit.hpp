@@ -1,0 +1,177 @@
+// Run-time specialisation of the coefficient expressions (host side).
+// The reference interprets every coefficient string with one Kokkos launch per DAG node, per 100-element group
+// (/root/reference/src/managers/functionManager.cpp:588-760).  Here the postfix programs produced by expr.hpp are
+// printed back as straight-line CUDA C++ and compiled with NVRTC for sm_100a together with the hand-written
+// specialised kernel (assemble_fast.h), so the expressions are inlined into the element's point loop.
+// libnvrtc and libcuda are opened lazily with dlopen: the library still loads on a machine without a driver, and
+// when NVRTC is unavailable the engine keeps using the in-kernel bytecode interpreter (still on the GPU).
+#pragma once
+#include <cuda.h>
+#include <dlfcn.h>
+#include <nvrtc.h>
+
+#include <cstdio>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "bytecode.h"
+#include "embedded_headers.inc"
+
+namespace mrh {
+
+struct JitApi {
+  bool ok = false; std::string why;
+  nvrtcResult (*CreateProgram)(nvrtcProgram*, const char*, const char*, int, const char* const*, const char* const*) = nullptr;
+  nvrtcResult (*CompileProgram)(nvrtcProgram, int, const char* const*) = nullptr;
+  nvrtcResult (*GetCUBINSize)(nvrtcProgram, size_t*) = nullptr;
+  nvrtcResult (*GetCUBIN)(nvrtcProgram, char*) = nullptr;
+  nvrtcResult (*GetProgramLogSize)(nvrtcProgram, size_t*) = nullptr;
+  nvrtcResult (*GetProgramLog)(nvrtcProgram, char*) = nullptr;
+  nvrtcResult (*DestroyProgram)(nvrtcProgram*) = nullptr;
+  CUresult (*ModuleLoadData)(CUmodule*, const void*) = nullptr;
+  CUresult (*ModuleUnload)(CUmodule) = nullptr;
+  CUresult (*ModuleGetFunction)(CUfunction*, CUmodule, const char*) = nullptr;
+  CUresult (*LaunchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream, void**, void**) = nullptr;
+  CUresult (*OccupancyMaxActiveBlocks)(int*, CUfunction, int, size_t) = nullptr;
+
+  static JitApi& get() {
+    static JitApi a;
+    static bool tried = false;
+    if (tried) return a;
+    tried = true;
+    void* hn = nullptr;
+    for (const char* n : {"libnvrtc.so.12", "libnvrtc.so", "/usr/local/cuda/lib64/libnvrtc.so.12"}) if (!hn) hn = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    void* hc = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+    if (!hn) { a.why = "libnvrtc not found"; return a; }
+    if (!hc) { a.why = "libcuda not found"; return a; }
+#define MRH_SYM(h, field, name) a.field = reinterpret_cast<decltype(a.field)>(dlsym(h, name)); if (!a.field) { a.why = std::string("missing symbol ") + name; return a; }
+    MRH_SYM(hn, CreateProgram, "nvrtcCreateProgram") MRH_SYM(hn, CompileProgram, "nvrtcCompileProgram")
+    MRH_SYM(hn, GetCUBINSize, "nvrtcGetCUBINSize") MRH_SYM(hn, GetCUBIN, "nvrtcGetCUBIN")
+    MRH_SYM(hn, GetProgramLogSize, "nvrtcGetProgramLogSize") MRH_SYM(hn, GetProgramLog, "nvrtcGetProgramLog")
+    MRH_SYM(hn, DestroyProgram, "nvrtcDestroyProgram")
+    MRH_SYM(hc, ModuleLoadData, "cuModuleLoadData") MRH_SYM(hc, ModuleUnload, "cuModuleUnload")
+    MRH_SYM(hc, ModuleGetFunction, "cuModuleGetFunction") MRH_SYM(hc, LaunchKernel, "cuLaunchKernel")
+    MRH_SYM(hc, OccupancyMaxActiveBlocks, "cuOccupancyMaxActiveBlocksPerMultiprocessor")
+#undef MRH_SYM
+    a.ok = true;
+    return a;
+  }
+};
+
+// ---- postfix program -> C++ source of   static __device__ double name(double x, double y, double z, double t) ----
+inline std::string jit_literal(double v) {
+  char buf[64]; snprintf(buf, sizeof buf, "%.17g", v);
+  std::string s(buf);
+  if (s.find_first_of(".en") == std::string::npos) s += ".0";       // 'n' covers inf/nan (not valid literals anyway)
+  return "(" + s + ")";
+}
+
+inline std::string jit_function_source(const std::string& name, const Prog& pr, const std::vector<Instr>& code,
+                                       const std::vector<double>& cpool) {
+  std::string out = "  static __device__ __forceinline__ double " + name + "(double x, double y, double z, double t) {\n";
+  if (pr.kind == 0) return out + "    return " + jit_literal(pr.cval) + ";\n  }\n";
+  if (pr.kind == 2) throw std::runtime_error("state-dependent coefficient cannot be specialised");
+  std::vector<std::string> st;
+  int ntmp = 0;
+  auto leaf = [&](uint8_t op, uint16_t cidx) -> std::string {
+    switch (op) {
+      case OP_CONST: return jit_literal(cpool[cidx]);
+      case OP_X: return "x"; case OP_Y: return "y"; case OP_Z: return "z"; case OP_TIME: return "t";
+      default: return "(0.0)";       // normals / tangents do not exist at volume points
+    }
+  };
+  auto emit = [&](const std::string& rhs) { const std::string v = "v" + std::to_string(ntmp++); out += "    const double " + v + " = " + rhs + ";\n"; st.push_back(v); };
+  for (int pc = pr.start; pc < pr.start + pr.len; ++pc) {
+    const Instr in = code[pc];
+    if (in.op == OP_FIELD) throw std::runtime_error("state-dependent coefficient cannot be specialised");
+    if (in.op < OP_FIELD) { st.push_back(leaf(in.op, in.cidx)); continue; }
+    if (in.op <= OP_MEAN) {
+      std::string b;
+      if (in.arg != 0) b = leaf(in.arg - 1, in.cidx); else { b = st.back(); st.pop_back(); }
+      const std::string a = st.back(); st.pop_back();
+      switch (in.op) {
+        case OP_ADD: emit(a + " + " + b); break;
+        case OP_SUB: emit(a + " + (-" + b + ")"); break;
+        case OP_MUL: emit(a + " * " + b); break;
+        case OP_DIV: emit(a + " / " + b); break;
+        case OP_POW: emit("pow(" + a + ", " + b + ")"); break;
+        case OP_LT: emit("(" + a + " < " + b + ") ? 1.0 : 0.0"); break;
+        case OP_LTE: emit("(" + a + " <= " + b + ") ? 1.0 : 0.0"); break;
+        case OP_GT: emit("(" + a + " > " + b + ") ? 1.0 : 0.0"); break;
+        case OP_GTE: emit("(" + a + " >= " + b + ") ? 1.0 : 0.0"); break;
+        case OP_MAX: emit("(" + a + " < " + b + ") ? " + b + " : " + a); break;
+        case OP_MIN: emit("(" + a + " > " + b + ") ? " + b + " : " + a); break;
+        default: emit("0.5 * " + a + " + 0.5 * " + b); break;
+      }
+      continue;
+    }
+    if (in.op == OP_NIP) { const std::string top = st.back(); st.pop_back(); st.pop_back(); st.push_back(top); continue; }
+    const std::string a = st.back(); st.pop_back();
+    switch (in.op) {
+      case OP_SIN: emit("sin(" + a + ")"); break;
+      case OP_COS: emit("cos(" + a + ")"); break;
+      case OP_TAN: emit("tan(" + a + ")"); break;
+      case OP_EXP: emit("exp(" + a + ")"); break;
+      case OP_LOG: emit("log(" + a + ")"); break;
+      case OP_SQRT: emit("sqrt(" + a + ")"); break;
+      case OP_SINH: emit("sinh(" + a + ")"); break;
+      case OP_COSH: emit("cosh(" + a + ")"); break;
+      default: emit("(" + a + " < 0.0) ? -" + a + " : " + a); break;
+    }
+  }
+  return out + "    return " + st.back() + ";\n  }\n";
+}
+
+// One NVRTC-compiled module holding the specialised thermal kernel for one (TRANSIENT, ADV, JAC) variant.
+struct JitKernel {
+  CUmodule mod = nullptr; CUfunction fn = nullptr; int blocks_per_sm = 1; std::string source, log;
+};
+
+class JitCache {
+ public:
+  std::string last_error;
+  ~JitCache() { for (auto& kv : kernels_) if (kv.second.mod && JitApi::get().ok) JitApi::get().ModuleUnload(kv.second.mod); }
+  void clear() { for (auto& kv : kernels_) if (kv.second.mod && JitApi::get().ok) JitApi::get().ModuleUnload(kv.second.mod); kernels_.clear(); coef_src_.clear(); }
+  void setCoefficientSource(const std::string& s) { clear(); coef_src_ = s; }
+  bool hasSource() const { return !coef_src_.empty(); }
+
+  // returns nullptr (and sets last_error) when the variant cannot be built
+  JitKernel* thermal(bool transient, bool adv, bool jac) {
+    const int key = (transient ? 4 : 0) | (adv ? 2 : 0) | (jac ? 1 : 0);
+    auto it = kernels_.find(key);
+    if (it != kernels_.end()) return it->second.fn ? &it->second : nullptr;
+    JitKernel& K = kernels_[key];
+    JitApi& api = JitApi::get();
+    if (!api.ok) { last_error = api.why; return nullptr; }
+    if (coef_src_.empty()) { last_error = "no coefficient source"; return nullptr; }
+    auto B = [](bool b) { return b ? "true" : "false"; };
+    K.source = std::string("#include \"assemble_fast.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
+        "};\n}\nextern \"C\" __global__ void __launch_bounds__(128) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
+        "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
+        "    mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs>::element(kp, e, nullptr, 0);\n}\n";
+    std::vector<const char*> hdr_src, hdr_name;
+    for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
+    nvrtcProgram prog;
+    if (api.CreateProgram(&prog, K.source.c_str(), "mrh_jit_thermal.cu", (int)hdr_src.size(), hdr_src.data(), hdr_name.data()) != NVRTC_SUCCESS) { last_error = "nvrtcCreateProgram failed"; return nullptr; }
+    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1"};
+    const nvrtcResult rc = api.CompileProgram(prog, 4, opts);
+    size_t ls = 0; api.GetProgramLogSize(prog, &ls);
+    if (ls > 1) { K.log.resize(ls); api.GetProgramLog(prog, &K.log[0]); }
+    if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + K.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }
+    size_t cs = 0; api.GetCUBINSize(prog, &cs);
+    std::vector<char> cubin(cs);
+    api.GetCUBIN(prog, cubin.data());
+    api.DestroyProgram(&prog);
+    if (api.ModuleLoadData(&K.mod, cubin.data()) != CUDA_SUCCESS) { last_error = "cuModuleLoadData failed"; K.mod = nullptr; return nullptr; }
+    if (api.ModuleGetFunction(&K.fn, K.mod, "mrh_jit_thermal_hex_q1") != CUDA_SUCCESS) { last_error = "kernel symbol not found"; K.fn = nullptr; return nullptr; }
+    if (api.OccupancyMaxActiveBlocks(&K.blocks_per_sm, K.fn, 128, 0) != CUDA_SUCCESS || K.blocks_per_sm < 1) K.blocks_per_sm = 1;
+    return &K;
+  }
+
+ private:
+  std::map<int, JitKernel> kernels_;
+  std::string coef_src_;
+};
+
+}  // namespace mrh

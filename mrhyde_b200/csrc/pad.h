@@ -7,7 +7,13 @@
 // with respect to that point state.  The element Jacobian is then the dense contraction
 //   K_(v,i),(m,j) = sum_q sum_a sum_b T_ia(q) dF_(v,a)/d(m,b) T_jb(q)            (assemble.h, phase 2).
 #pragma once
+#if defined(__CUDACC_RTC__)
+// NVRTC build of the specialised kernels (jit.hpp): no host headers; the fixed-width types are spelled out
+typedef unsigned char uint8_t; typedef unsigned short uint16_t; typedef int int32_t; typedef unsigned int uint32_t;
+typedef long long int64_t; typedef unsigned long long uint64_t; typedef unsigned long size_t;
+#else
 #include <cmath>
+#endif
 
 #if defined(__CUDACC__)
 #define MRH_HD __host__ __device__ __forceinline__

@@ -1,6 +1,8 @@
 // Launch parameter block shared by every assembly kernel (plain data, passed by value).
 #pragma once
+#if !defined(__CUDACC_RTC__)
 #include <cstdint>
+#endif
 #include "bytecode.h"
 
 namespace mrh {

@@ -32,7 +32,7 @@ SYMBOLS = ["mrh_default_config", "mrh_create", "mrh_destroy", "mrh_last_error", 
            "mrh_finalize_host", "mrh_assemble_res", "mrh_assemble_jacres", "mrh_assemble_jacres_host",
            "mrh_get_sizes", "mrh_get_mesh", "mrh_get_dofmap", "mrh_get_crs", "mrh_get_side", "mrh_get_bc",
            "mrh_get_varname", "mrh_eval_function_host", "mrh_last_launch_count", "mrh_last_volume_kernel_ms",
-           "mrh_microbench"]
+           "mrh_microbench", "mrh_last_kernel_path"]
 
 
 def lib_path():
@@ -51,6 +51,8 @@ def load_library(path=None):
     L.mrh_last_error.argtypes = [C.c_void_p]
     L.mrh_get_varname.restype = C.c_char_p
     L.mrh_get_varname.argtypes = [C.c_void_p, C.c_int32]
+    L.mrh_last_kernel_path.restype = C.c_char_p
+    L.mrh_last_kernel_path.argtypes = [C.c_void_p]
     L.mrh_last_launch_count.restype = C.c_int64
     L.mrh_last_launch_count.argtypes = [C.c_void_p]
     L.mrh_last_volume_kernel_ms.restype = C.c_double
@@ -100,7 +102,7 @@ class Engine:
     """One assembly engine handle (== one AssemblyManager on one GPU)."""
 
     def __init__(self, physics, dim, order=1, lib=None, device=0, quadrature=-1, side_quadrature=-1,
-                 use_strong_dbc=True, fix_zero_rows=False, lump_mass=False, settings=None, force_generic=False):
+                 use_strong_dbc=True, fix_zero_rows=False, lump_mass=False, settings=None, force_generic=False, no_jit=False):
         self.L = load_library(lib)
         settings = settings or {}
         cfg = MrhConfig()
@@ -115,7 +117,7 @@ class Engine:
         cfg.form_param = float(settings.get("form_param", 1.0))
         cfg.le_penalty = float(settings.get("penalty", 10.0))
         cfg.device = device
-        cfg.flags = 1 if force_generic else 0
+        cfg.flags = (1 if force_generic else 0) | (2 if no_jit else 0)
         self.h = C.c_void_p()
         rc = self.L.mrh_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:
@@ -140,7 +142,7 @@ class Engine:
             pass
 
     @classmethod
-    def from_problem(cls, p, lib=None, device=0, finalize=True, host_only=False, force_generic=False):
+    def from_problem(cls, p, lib=None, device=0, finalize=True, host_only=False, force_generic=False, no_jit=False):
         """Build an engine from a tests/problems.py style dict (same dict drives the oracle)."""
         extra = p.get("extra", {})
         weak = bool(extra.get("use weak Dirichlet", False))
@@ -149,7 +151,7 @@ class Engine:
                 quadrature=extra.get("quadrature", -1), side_quadrature=extra.get("side quadrature", -1),
                 use_strong_dbc=extra.get("use strong DBCs", True), fix_zero_rows=extra.get("fix zero rows", False),
                 lump_mass=extra.get("lump mass", False), settings=p.get("settings", {}),
-                force_generic=force_generic)
+                force_generic=force_generic, no_jit=no_jit)
         n = [m["NX"], m["NY"], m.get("NZ", 1)]
         lo = [m.get("xmin", 0.0), m.get("ymin", 0.0), m.get("zmin", 0.0)]
         hi = [m.get("xmax", 1.0), m.get("ymax", 1.0), m.get("zmax", 1.0)]
@@ -303,6 +305,9 @@ class Engine:
         st = self._state(u, **kw)
         self._ck(self.L.mrh_assemble_jacres_host(self.h, C.byref(st), _ptr(res), _ptr(jac)),
                  "mrh_assemble_jacres_host")
+
+    def kernel_path(self):
+        return self.L.mrh_last_kernel_path(self.h).decode()
 
     def launch_count(self):
         return int(self.L.mrh_last_launch_count(self.h))

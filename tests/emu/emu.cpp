@@ -118,6 +118,7 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st, double* res, dou
   return emu_assemble(h, st, res, jac);
   MRH_CATCH(h)
 }
+const char* mrh_last_kernel_path(mrh_handle h) { return (h && ((EmuImpl*)h->impl)->fast_launches) ? "specialised" : "generic"; }
 int64_t mrh_last_launch_count(mrh_handle h) { return h ? ((EmuImpl*)h->impl)->launches : 0; }
 double mrh_last_volume_kernel_ms(mrh_handle h) { return h ? -(double)((EmuImpl*)h->impl)->fast_launches : 0.0; }  // emu: -#specialised launches
 int mrh_microbench(int32_t, double*, double*, double*) { return MRH_EUNSUPPORTED; }

@@ -122,10 +122,10 @@ def rel_errors(a, b, rowptr=None):
     return g, (dmax[ok] / bmax[ok]).max() if ok.any() else 0.0
 
 
-def check_case(p, kw, lib, on_gpu, force_generic=False, jacobian=True):
+def check_case(p, kw, lib, on_gpu, force_generic=False, jacobian=True, no_jit=False):
     from mrhyde_b200 import Engine
     o = Oracle(oracle_problem(p))
-    e = Engine.from_problem(p, lib=lib, force_generic=force_generic)
+    e = Engine.from_problem(p, lib=lib, force_generic=force_generic, no_jit=no_jit)
     s = e.sizes()
     assert (s["nlocal"], s["nnz"], s["nelem"]) == (o.nlocal, o.nnz, o.nelem)
     lids, offs, fixed, xyz, var = e.dofmap()
@@ -166,7 +166,7 @@ def check_case(p, kw, lib, on_gpu, force_generic=False, jacobian=True):
             e.assemble_res(u, res, u_prev=u_prev, u_stage=u_stage, time_int=ti)
     er, _ = rel_errors(res, ores)
     assert er <= TOL, f"residual rel err {er:.3e}"
-    out = {"res": er, "launches": e.launch_count()}
+    out = {"res": er, "launches": e.launch_count(), "path": e.kernel_path()}
     if jacobian:
         eg, erow = rel_errors(jac, ojac, rp)
         assert eg <= TOL and erow <= 1e-10, f"jacobian rel err {eg:.3e} (per-row {erow:.3e})"

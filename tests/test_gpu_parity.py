@@ -29,6 +29,19 @@ def test_cuda_generic_kernel_on_specialised_cases(lib, name, p, kw):
     U.check_case(p, kw, lib, on_gpu=True, force_generic=True)
 
 
+@pytest.mark.parametrize("name,p,kw", [c for c in CASES if c[1]["physics"] == "thermal" and c[1]["mesh"]["dim"] == 3],
+                         ids=lambda v: v if isinstance(v, str) else "")
+def test_cuda_specialised_kernel_with_interpreter(lib, name, p, kw):
+    """the specialised kernel without the NVRTC step (bytecode interpreter inside the kernel)"""
+    r = U.check_case(p, kw, lib, on_gpu=True, no_jit=True)
+    assert r["path"] != "nvrtc-specialised"
+
+
+def test_nvrtc_path_is_taken(lib):
+    r = U.check_case(problems.config_c2(6), {}, lib, on_gpu=True)
+    assert r["path"] == "nvrtc-specialised", r
+
+
 def test_mid_size_c2_against_oracle(lib):
     """24^3 thermal Q1 (SURVEY.md 8d parity size) through the specialised kernel."""
     r = U.check_case(problems.config_c2(24), {}, lib, on_gpu=True)
