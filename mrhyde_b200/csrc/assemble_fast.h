@@ -63,8 +63,15 @@ struct ThermalHexQ1 {
   // stage: per-thread scratch for the coefficient values at the 8 points, element k of array m at
   // stage[(m*8+k)*stride] (shared memory, stride = blockDim.x, on the device).
   MRH_HDN static void element(const KParams& kp, int64_t e, double* stage, int stride) {
+    int lid[8]; double r[8], K[NK];
+    compute(kp, e, stage, stride, lid, r, K);
+    scatter(kp, e, lid, r, K);
+  }
+
+  // gather + geometry + point loop of one element: r = element residual, K = element matrix (36 upper entries
+  // when symmetric, else 8x8 row-major)
+  MRH_HDN static void compute(const KParams& kp, int64_t e, double* stage, int stride, int (&lid)[8], double (&r)[8], double (&K)[NK]) {
     // ---- gather: LIDs, vertex coordinates, DOFs ------------------------------------------------------
-    int lid[8];
     {
       const int4* lp = reinterpret_cast<const int4*>(kp.lids + e * 8);
       const int4 a = lp[0], b = lp[1];
@@ -129,7 +136,6 @@ struct ThermalHexQ1 {
     }
 
     // ---- point loop (rolled: the body stays resident in the instruction cache) ------------------------
-    double r[8], K[NK];
 #pragma unroll
     for (int s = 0; s < 8; ++s) r[s] = 0.0;
 #pragma unroll
@@ -226,7 +232,14 @@ struct ThermalHexQ1 {
       }
     }
 
-    // ---- scatter: residual subtracted, Jacobian added, fixed rows skipped ------------------------------
+  }
+
+  MRH_HD static double kval(const double (&K)[NK], int i, int j) {
+    return ADV ? K[i * 8 + j] : (i <= j ? K[HexQ1::tri(i, j)] : K[HexQ1::tri(j, i)]);
+  }
+
+  // ---- direct scatter: residual subtracted, Jacobian added, fixed rows skipped (one RED per entry) --------
+  MRH_HDN static void scatter(const KParams& kp, int64_t e, const int (&lid)[8], const double (&r)[8], const double (&K)[NK]) {
     bool fx_[8];
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
@@ -252,11 +265,65 @@ struct ThermalHexQ1 {
       double* jrow = kp.jac + kp.rowptr[lid[i]];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const double v = ADV ? K[i * 8 + j] : (i <= j ? K[HexQ1::tri(i, j)] : K[HexQ1::tri(j, i)]);
-        atomic_add(jrow + pat[i * 8 + j], v);
+        atomic_add(jrow + pat[i * 8 + j], kval(K, i, j));
       }
     }
   }
+#if defined(__CUDACC__)
+  // ---- tile-staged scatter (device only) ------------------------------------------------------------------
+  // One CTA owns a tile of 128 elements (kp.tile, built at finalize): every thread adds its element's entries
+  // into the tile's accumulation array in shared memory (each distinct CRS slot / residual row of the tile once),
+  // then the CTA flushes the array with REDs whose lanes walk consecutive CRS slots.  Against one RED per
+  // element entry this halves the number of REDs and lets several lanes share a 32-byte sector, which is what
+  // bounds RED.F64 throughput on B200 (profiles/r1_red_microbench.txt).
+  __device__ static void tiled(const KParams& kp, double* stage, int stride, double* acc) {
+    const TilePlan& tp = kp.tile;
+    const int tid = threadIdx.x;
+    for (int k = tid; k < tp.max_acc; k += 128) acc[k] = 0.0;
+    __syncthreads();
+    for (int64_t t = blockIdx.x; t < tp.ntiles; t += gridDim.x) {
+      const int64_t e0 = t * 128 + tid;
+      const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
+      const int E = JAC ? (int)(tp.eptr[t + 1] - eb) : 0, R = (int)(tp.rptr[t + 1] - rb);
+      if (e0 < kp.nwork) {
+        const int64_t e = tp.perm[e0];
+        int lid[8]; double r[8], K[NK];
+        compute(kp, e, stage, stride, lid, r, K);
+        const uint4* pp = reinterpret_cast<const uint4*>(tp.tpat + (size_t)tp.tpat_id[e] * 72);
+        {
+          const uint4 v = pp[8];                                   // residual rows: entries 64..71
+          const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int s = 0; s < 8; ++s) {
+            const unsigned loc = (w[s >> 1] >> ((s & 1) * 16)) & 0xffffu;
+            if (loc != 0xffffu) atomicAdd(acc + E + loc, -r[s]);
+          }
+        }
+        if (JAC) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint4 v = pp[i];
+            const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const unsigned loc = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+              if (loc != 0xffffu) atomicAdd(acc + loc, kval(K, i, j));
+            }
+          }
+        }
+      }
+      __syncthreads();
+      if (JAC) {
+        double* jb = kp.jac + tp.base[t];
+        const unsigned* off = tp.off + eb;
+        for (int k = tid; k < E; k += 128) { atomicAdd(jb + off[k], acc[k]); acc[k] = 0.0; }
+      }
+      const int* rows = tp.rows + rb;
+      for (int k = tid; k < R; k += 128) { atomicAdd(kp.res + rows[k], acc[E + k]); acc[E + k] = 0.0; }
+      __syncthreads();
+    }
+  }
+#endif
 };
 
 }  // namespace mrh

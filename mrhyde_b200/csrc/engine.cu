@@ -51,6 +51,7 @@ struct DeviceImpl {
   // staging for the *_host entry point
   DevBuf<double> h_u, h_res, h_jac;
   JitCache jit;
+  struct TileDev* tiles = nullptr;     // engine_tiles.inl
   bool jit_used = false;
   const char* last_path = "none";
 };
@@ -61,6 +62,13 @@ __global__ void __launch_bounds__(128) thermal_hex_q1_kernel(const __grid_consta
   __shared__ double stage[ThermalHexQ1<TRANSIENT, ADV, JAC>::NSTAGE * 8 * 128];
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (int64_t)gridDim.x * blockDim.x)
     ThermalHexQ1<TRANSIENT, ADV, JAC>::element(kp, e, stage + threadIdx.x, 128);
+}
+
+template <bool TRANSIENT, bool ADV, bool JAC>
+__global__ void __launch_bounds__(128) thermal_hex_q1_tiled_kernel(const __grid_constant__ KParams kp) {
+  __shared__ double stage[ThermalHexQ1<TRANSIENT, ADV, JAC>::NSTAGE * 8 * 128];
+  extern __shared__ double acc[];
+  ThermalHexQ1<TRANSIENT, ADV, JAC>::tiled(kp, stage + threadIdx.x, 128, acc);
 }
 
 // row-relative CRS position of column `col` in row `row` (columns ascending)
@@ -136,6 +144,9 @@ __global__ void fix_zero_rows_kernel(const int64_t* rowptr, const int* colind, i
   if (s < 1.0e-14) { const int d = rel_slot(rowptr, colind, (int)r, (int)r); if (d >= 0) jac[rowptr[r] + d] = 1.0; }
 }
 
+inline unsigned blocks_for(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
+
 }  // namespace
 
+#include "engine_tiles.inl"
 #include "engine_launch.inl"

@@ -195,6 +195,19 @@ class EngineHost {
     }
   }
 
+  // element order of the tile-staged scatter: 8x4x4-element bricks on the structured mesh, identity otherwise
+  std::vector<int> tileOrder() const {
+    std::vector<int> perm; perm.reserve((size_t)mesh.nelem);
+    const int nx = mesh.NXYZ[0], ny = mesh.NXYZ[1], nz = mesh.NXYZ[2];
+    if (dim == 3 && nx > 0 && (int64_t)nx * ny * nz == mesh.nelem) {
+      const int bx = 8, by = 4, bz = 4;
+      for (int K = 0; K < nz; K += bz) for (int J = 0; J < ny; J += by) for (int I = 0; I < nx; I += bx)
+        for (int k = K; k < std::min(K + bz, nz); ++k) for (int j = J; j < std::min(J + by, ny); ++j) for (int i = I; i < std::min(I + bx, nx); ++i)
+          perm.push_back((int)(i + (int64_t)nx * (j + (int64_t)ny * k)));
+    } else for (int64_t e = 0; e < mesh.nelem; ++e) perm.push_back((int)e);
+    return perm;
+  }
+
   // true when no coefficient of the volume launch depends on the solution (enables the specialised kernels)
   bool volumeStateIndependent() const { for (auto& p : vol_progs) if (p.kind == 2) return false; return true; }
 

@@ -10,8 +10,6 @@ RefTab upload_tab(TabDev& D, const PointTables& T) {
   return r;
 }
 
-inline unsigned blocks_for(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
-
 void build_patterns(EngineHost& H, DeviceImpl& D) {
   const int64_t ne = H.mesh.nelem; const int N = H.N;
   DevBuf<uint64_t> hash, skey; DevBuf<int> idx, bad;
@@ -53,6 +51,13 @@ void device_finalize(mrh_engine* h) {
   for (auto& S : H.mesh.sides) { D.side_elems.emplace_back(new DevBuf<int>()); D.side_elems.back()->upload(S.elems); }
   build_patterns(H, D);
   h->npatterns = D.npatterns;
+  // tile plan of the tile-staged scatter (engine_tiles.inl)
+  if (!D.tiles) D.tiles = new TileDev();
+  D.tiles->release();
+  if (!(H.cfg.flags & 5) && thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
+    const std::string why = build_tile_plan(H.tileOrder(), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p, *D.tiles);
+    if (!D.tiles->ok) h->err = "tile-staged scatter unavailable (" + why + "), using direct scatter";
+  }
   // NVRTC specialisation of the coefficient expressions for the specialised thermal kernel (jit.hpp)
   D.jit.clear();
   if (!(H.cfg.flags & 3) && thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
@@ -95,6 +100,18 @@ void launch_thermal_fast(const DeviceImpl& D, const KParams& kp, cudaStream_t st
   CUDA_CK(cudaGetLastError());
 }
 
+template <bool T, bool A, bool J>
+void launch_thermal_tiled(const DeviceImpl& D, const KParams& kp, size_t acc_bytes, cudaStream_t stream) {
+  auto kern = thermal_hex_q1_tiled_kernel<T, A, J>;
+  CUDA_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)acc_bytes));
+  int per_sm = 1;
+  CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, acc_bytes));
+  if (per_sm < 1) per_sm = 1;
+  const unsigned grid = (unsigned)std::min<int64_t>(kp.tile.ntiles, (int64_t)D.num_sms * per_sm);
+  kern<<<grid, 128, acc_bytes, stream>>>(kp);
+  CUDA_CK(cudaGetLastError());
+}
+
 int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac) {
   EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
   if (!D.ready) throw std::runtime_error("mrh_finalize has not been called");
@@ -113,18 +130,32 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
       const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
       JitKernel* jk = (H.cfg.flags & 2) ? nullptr : D.jit.thermal(tr, adv, jc);
       D.jit_used = jk != nullptr;
-      D.last_path = jk ? "nvrtc-specialised" : "specialised";
+      const bool tiled = D.tiles && D.tiles->ok;
+      if (tiled) fill_tile_params(*D.tiles, kp.tile);
+      const size_t acc_bytes = tiled ? (size_t)D.tiles->max_acc * sizeof(double) : 0;
+      D.last_path = jk ? (tiled ? "nvrtc-specialised+tiled" : "nvrtc-specialised") : (tiled ? "specialised+tiled" : "specialised");
       if (jk) {
         const int64_t nblk = (kp.nwork + 127) / 128;
-        const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * jk->blocks_per_sm * 4);
+        unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * jk->blocks_per_sm * 4);
+        if (tiled) {
+          if (jk->smem_set != acc_bytes) {
+            JitApi& api = JitApi::get();
+            if (acc_bytes > 48 * 1024 && api.FuncSetAttribute(jk->fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)acc_bytes) != CUDA_SUCCESS)
+              throw std::runtime_error("CUDA error: cuFuncSetAttribute(shared memory) failed");
+            if (api.OccupancyMaxActiveBlocks(&jk->tiled_blocks_per_sm, jk->fn, 128, acc_bytes) != CUDA_SUCCESS || jk->tiled_blocks_per_sm < 1) jk->tiled_blocks_per_sm = 1;
+            jk->smem_set = acc_bytes;
+          }
+          grid = (unsigned)std::min<int64_t>(D.tiles->ntiles, (int64_t)D.num_sms * jk->tiled_blocks_per_sm);
+        }
         void* args[] = {(void*)&kp};
-        if (JitApi::get().LaunchKernel(jk->fn, grid, 1, 1, 128, 1, 1, 0, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+        if (JitApi::get().LaunchKernel(jk->fn, grid, 1, 1, 128, 1, 1, (unsigned)acc_bytes, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
           throw std::runtime_error("CUDA error: cuLaunchKernel failed for the NVRTC-specialised kernel");
-      } else
-#define MRH_FAST(T, A, Jc) if (tr == T && adv == A && jc == Jc) launch_thermal_fast<T, A, Jc>(D, kp, stream);
+      } else {
+#define MRH_FAST(T, A, Jc) if (tr == T && adv == A && jc == Jc) { if (tiled) launch_thermal_tiled<T, A, Jc>(D, kp, acc_bytes, stream); else launch_thermal_fast<T, A, Jc>(D, kp, stream); }
       MRH_FAST(false, false, false) MRH_FAST(false, false, true) MRH_FAST(false, true, false) MRH_FAST(false, true, true)
       MRH_FAST(true, false, false) MRH_FAST(true, false, true) MRH_FAST(true, true, false) MRH_FAST(true, true, true)
 #undef MRH_FAST
+      }
     } else {
       if (side < 0) D.last_path = "generic";
       const bool ok = launch_generic_assembly(H.phys, H.dim, H.order, jac != nullptr, D.num_sms, kp, (void*)stream);
@@ -191,6 +222,7 @@ static void backend_destroy(mrh_engine* h) {
   if (!D) return;
   cudaSetDevice(D->device);
   if (D->ev0) { cudaEventDestroy(D->ev0); cudaEventDestroy(D->ev1); }
+  delete D->tiles;
   delete D;
 }
 

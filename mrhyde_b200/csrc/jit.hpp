@@ -34,6 +34,7 @@ struct JitApi {
   CUresult (*ModuleGetFunction)(CUfunction*, CUmodule, const char*) = nullptr;
   CUresult (*LaunchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream, void**, void**) = nullptr;
   CUresult (*OccupancyMaxActiveBlocks)(int*, CUfunction, int, size_t) = nullptr;
+  CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
 
   static JitApi& get() {
     static JitApi a;
@@ -53,6 +54,7 @@ struct JitApi {
     MRH_SYM(hc, ModuleLoadData, "cuModuleLoadData") MRH_SYM(hc, ModuleUnload, "cuModuleUnload")
     MRH_SYM(hc, ModuleGetFunction, "cuModuleGetFunction") MRH_SYM(hc, LaunchKernel, "cuLaunchKernel")
     MRH_SYM(hc, OccupancyMaxActiveBlocks, "cuOccupancyMaxActiveBlocksPerMultiprocessor")
+    MRH_SYM(hc, FuncSetAttribute, "cuFuncSetAttribute")
 #undef MRH_SYM
     a.ok = true;
     return a;
@@ -125,7 +127,7 @@ inline std::string jit_function_source(const std::string& name, const Prog& pr, 
 
 // One NVRTC-compiled module holding the specialised thermal kernel for one (TRANSIENT, ADV, JAC) variant.
 struct JitKernel {
-  CUmodule mod = nullptr; CUfunction fn = nullptr; int blocks_per_sm = 1; std::string source, log;
+  CUmodule mod = nullptr; CUfunction fn = nullptr; int blocks_per_sm = 1, tiled_blocks_per_sm = 1; size_t smem_set = 0; std::string source, log;
 };
 
 class JitCache {
@@ -148,8 +150,11 @@ class JitCache {
     auto B = [](bool b) { return b ? "true" : "false"; };
     K.source = std::string("#include \"assemble_fast.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
         "};\n}\nextern \"C\" __global__ void __launch_bounds__(128) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
+        "  typedef mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n"
+        "  extern __shared__ double acc[];\n"
+        "  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, acc); return; }\n"
         "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
-        "    mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs>::element(kp, e, nullptr, 0);\n}\n";
+        "    Kern::element(kp, e, nullptr, 0);\n}\n";
     std::vector<const char*> hdr_src, hdr_name;
     for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
     nvrtcProgram prog;

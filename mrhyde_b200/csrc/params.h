@@ -43,6 +43,20 @@ struct PhysParams {
   double le_penalty;     // LE "penalty"
 };
 
+struct TilePlan {          // tile-staged scatter of the specialised kernels (built at finalize, engine_tiles.inl)
+  const int* perm;           // (nelem)   element order: tile t = perm[128 t .. 128 t + 127]
+  const int64_t* eptr;       // (ntiles+1) first accumulation entry of each tile
+  const int64_t* rptr;       // (ntiles+1) first residual row of each tile
+  const int64_t* base;       // (ntiles)  smallest CRS slot of the tile
+  const uint32_t* off;       // (sum E_t) CRS slot of each tile entry relative to base, ascending
+  const int* rows;           // (sum R_t) residual rows (LIDs) of each tile, ascending
+  const uint16_t* tpat;      // (npattern, 72) per element: tile entry of K(i,j) at [8 i + j], tile row of r_s at [64 + s]; 0xFFFF = fixed row
+  const int* tpat_id;        // (nelem)
+  int64_t ntiles;
+  int max_acc;               // largest E_t + R_t: doubles of shared memory per CTA
+  int pad_;
+};
+
 struct KParams {
   const double* nodes;       // (nnode, DIM)
   const int* e2n;            // (nelem, NV)
@@ -66,6 +80,7 @@ struct KParams {
   Prog progs[MRH_MAXPROG];
   int offsets[4 * 27];       // offsets(var, basis dof) -> element slot
   int is_side, lump_mass, compute_jac, elems_per_block;
+  TilePlan tile;
 };
 
 }  // namespace mrh

@@ -31,15 +31,26 @@ def test_cuda_generic_kernel_on_specialised_cases(lib, name, p, kw):
 
 @pytest.mark.parametrize("name,p,kw", [c for c in CASES if c[1]["physics"] == "thermal" and c[1]["mesh"]["dim"] == 3],
                          ids=lambda v: v if isinstance(v, str) else "")
-def test_cuda_specialised_kernel_with_interpreter(lib, name, p, kw):
-    """the specialised kernel without the NVRTC step (bytecode interpreter inside the kernel)"""
-    r = U.check_case(p, kw, lib, on_gpu=True, no_jit=True)
-    assert r["path"] != "nvrtc-specialised"
+@pytest.mark.parametrize("no_jit,no_tiles", [(True, False), (False, True), (True, True)])
+def test_cuda_specialised_kernel_variants(lib, name, p, kw, no_jit, no_tiles):
+    """the specialised kernel without the NVRTC step (bytecode interpreter inside the kernel) and / or with the
+    direct instead of the tile-staged scatter"""
+    r = U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles)
+    assert ("nvrtc" in r["path"]) == (not no_jit) and ("tiled" in r["path"]) == (not no_tiles), r
+    U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles, jacobian=False)
 
 
-def test_nvrtc_path_is_taken(lib):
+def test_default_path_is_nvrtc_and_tiled(lib):
     r = U.check_case(problems.config_c2(6), {}, lib, on_gpu=True)
-    assert r["path"] == "nvrtc-specialised", r
+    assert r["path"] == "nvrtc-specialised+tiled", r
+
+
+@pytest.mark.parametrize("n", [(5, 3, 7), (8, 4, 4), (17, 9, 6)])
+def test_tiled_scatter_on_ragged_meshes(lib, n):
+    """mesh sizes that do not divide the 8x4x4 tile, and one that is exactly one tile"""
+    p = problems.config_c2(4)
+    p["mesh"]["NX"], p["mesh"]["NY"], p["mesh"]["NZ"] = n
+    U.check_case(p, {}, lib, on_gpu=True)
 
 
 def test_mid_size_c2_against_oracle(lib):
