@@ -70,16 +70,24 @@ struct ThermalHexQ1 {
 
   // gather + geometry + point loop of one element: r = element residual, K = element matrix (36 upper entries
   // when symmetric, else 8x8 row-major)
+  struct NoHook { MRH_HD void operator()() const {} };
   MRH_HDN static void compute(const KParams& kp, int64_t e, double* stage, int stride, int (&lid)[8], double (&r)[8], double (&K)[NK]) {
+    compute(kp, kp.lids + e * 8, kp.e2n + e * 8, stage, stride, lid, r, K, NoHook());
+  }
+  // lrow / nrow: the element's 8 LIDs / 8 node ids (16-byte aligned; global or shared memory).  after_gather() runs
+  // once the gather loads have been issued (the tiled kernel starts its asynchronous copies there).
+  template <class Hook>
+  MRH_HDN static void compute(const KParams& kp, const int* lrow, const int* nrow, double* stage, int stride, int (&lid)[8], double (&r)[8],
+                              double (&K)[NK], Hook&& after_gather) {
     // ---- gather: LIDs, vertex coordinates, DOFs ------------------------------------------------------
     {
-      const int4* lp = reinterpret_cast<const int4*>(kp.lids + e * 8);
+      const int4* lp = reinterpret_cast<const int4*>(lrow);
       const int4 a = lp[0], b = lp[1];
       lid[0] = a.x; lid[1] = a.y; lid[2] = a.z; lid[3] = a.w; lid[4] = b.x; lid[5] = b.y; lid[6] = b.z; lid[7] = b.w;
     }
     double X[8][3];
     {
-      const int4* np = reinterpret_cast<const int4*>(kp.e2n + e * 8);
+      const int4* np = reinterpret_cast<const int4*>(nrow);
       const int4 a = np[0], b = np[1];
       const int nd[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 #pragma unroll
@@ -104,6 +112,7 @@ struct ThermalHexQ1 {
         ud[s] = tp.alpha_t * uval + beta_t * tp.timewt;
       }
     }
+    after_gather();
     const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
 
     // ---- coefficients at the 8 points (vector interpreter), staged for the rolled point loop ------------
@@ -271,56 +280,131 @@ struct ThermalHexQ1 {
   }
 #if defined(__CUDACC__)
   // ---- tile-staged scatter (device only) ------------------------------------------------------------------
-  // One CTA owns a tile of 128 elements (kp.tile, built at finalize): every thread adds its element's entries
-  // into the tile's accumulation array in shared memory (each distinct CRS slot / residual row of the tile once),
-  // then the CTA flushes the array with REDs whose lanes walk consecutive CRS slots.  Against one RED per
-  // element entry this halves the number of REDs and lets several lanes share a 32-byte sector, which is what
-  // bounds RED.F64 throughput on B200 (profiles/r1_red_microbench.txt).
-  __device__ static void tiled(const KParams& kp, double* stage, int stride, double* acc) {
+  // One CTA owns a tile of 128 elements (kp.tile, built at finalize).  Every thread parks its element matrix and
+  // residual in shared memory (entry-major, conflict free).  The tile's 128 x 72 contributions were sorted by
+  // destination (CRS slot, then residual row) at plan time; thread t walks sorted positions [72 t, 72 t + 72),
+  // sums each run of equal destinations in a register and stores the run total into the tile's accumulation
+  // array - no shared-memory atomics except for the one run per thread that started in the previous thread's
+  // chunk.  The CTA then flushes the array with REDs whose lanes walk consecutive CRS slots: against one RED
+  // per element entry this halves the REDs and lets several lanes share a 32-byte sector, which is what bounds
+  // RED.F64 throughput on B200 (profiles/r1_red_microbench.txt).
+  // While an element is computed, LDGSTS copies bring the tile's slot / row lists and the NEXT tile's LID / node
+  // rows into shared memory, and L2 prefetches are issued for the next tile's vertices and DOFs, so that neither
+  // the flush nor the next gather waits on DRAM.
+  // dynamic shared memory: Ks[(NK + 8) * 128] | zero cell | pad | acc[max_acc + 1] | carry[128] | rowbuf[128][16] int
+  //                        | off[max_e] uint32 | rows[max_r] int
+  static constexpr int NE = NK + 8;
+  __host__ __device__ static constexpr size_t tiled_smem_bytes(int max_acc, int max_e, int max_r) {
+    return ((size_t)NE * 128 + 2 + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+  }
+  __device__ __forceinline__ static void cp_async4(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+  }
+  __device__ __forceinline__ static void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+  }
+  __device__ __forceinline__ static void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(__cvta_generic_to_global(p))); }
+  __device__ static void tiled(const KParams& kp, double* stage, int stride, double* sm) {
+    static_assert(JAC, "the tile-staged scatter is used for Jacobian assembly only");
     const TilePlan& tp = kp.tile;
     const int tid = threadIdx.x;
-    for (int k = tid; k < tp.max_acc; k += 128) acc[k] = 0.0;
-    __syncthreads();
-    for (int64_t t = blockIdx.x; t < tp.ntiles; t += gridDim.x) {
-      const int64_t e0 = t * 128 + tid;
+    double* Ks = sm;
+    double* acc = sm + NE * 128 + 2;
+    double* carry = acc + ((tp.max_acc + 2) & ~1);        // keeps the row buffer 16-byte aligned
+    int* rowbuf = reinterpret_cast<int*>(carry + 128) + tid * 16;          // my element's 8 LIDs | 8 node ids
+    unsigned* s_off = reinterpret_cast<unsigned*>(carry + 128) + 128 * 16;
+    int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
+    if (tid == 0) Ks[NE * 128] = 0.0;                     // masked contributions read this cell
+    const int64_t tstep = gridDim.x;
+    auto element_of = [&](int64_t t) -> int { const int64_t e0 = t * 128 + tid; return (t < tp.ntiles && e0 < kp.nwork) ? tp.perm[e0] : -1; };
+    auto fetch_rows = [&](int e) {
+      if (e < 0) return;
+      cp_async16(rowbuf, kp.lids + (int64_t)e * 8); cp_async16(rowbuf + 4, kp.lids + (int64_t)e * 8 + 4);
+      cp_async16(rowbuf + 8, kp.e2n + (int64_t)e * 8); cp_async16(rowbuf + 12, kp.e2n + (int64_t)e * 8 + 4);
+    };
+    int e_cur = element_of(blockIdx.x), e_next = element_of(blockIdx.x + tstep);
+    fetch_rows(e_cur);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (int64_t t = blockIdx.x; t < tp.ntiles; t += tstep) {
       const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
-      const int E = JAC ? (int)(tp.eptr[t + 1] - eb) : 0, R = (int)(tp.rptr[t + 1] - rb);
-      if (e0 < kp.nwork) {
-        const int64_t e = tp.perm[e0];
+      const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
+      int e_next2 = -1;
+      asm volatile("cp.async.wait_group 0;" ::: "memory");                 // my rows have arrived (no other thread reads them)
+      auto start_copies = [&]() {
+        for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + eb + k);
+        for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + rb + k);
+        fetch_rows(e_next);                                                // rowbuf has been read into registers by now
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        e_next2 = element_of(t + 2 * tstep);
+      };
+      if (e_cur >= 0) {
         int lid[8]; double r[8], K[NK];
-        compute(kp, e, stage, stride, lid, r, K);
-        const uint4* pp = reinterpret_cast<const uint4*>(tp.tpat + (size_t)tp.tpat_id[e] * 72);
-        {
-          const uint4 v = pp[8];                                   // residual rows: entries 64..71
-          const unsigned w[4] = {v.x, v.y, v.z, v.w};
+        compute(kp, rowbuf, rowbuf + 8, stage, stride, lid, r, K, start_copies);
 #pragma unroll
-          for (int s = 0; s < 8; ++s) {
-            const unsigned loc = (w[s >> 1] >> ((s & 1) * 16)) & 0xffffu;
-            if (loc != 0xffffu) atomicAdd(acc + E + loc, -r[s]);
-          }
-        }
-        if (JAC) {
+        for (int k = 0; k < NK; ++k) Ks[k * 128 + tid] = K[k];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const uint4 v = pp[i];
-            const unsigned w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const unsigned loc = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-              if (loc != 0xffffu) atomicAdd(acc + loc, kval(K, i, j));
-            }
-          }
-        }
-      }
+        for (int s = 0; s < 8; ++s) Ks[(NK + s) * 128 + tid] = -r[s];
+      } else start_copies();
+#if defined(MRH_DEBUG_SKIP_SCATTER)                         // tuning experiment: element computation only (results are NOT assembled)
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
       __syncthreads();
-      if (JAC) {
+      e_cur = e_next; e_next = e_next2;
+      continue;
+#endif
+      const size_t cid = (size_t)tp.cl_id[t] * 128 + tid;
+      unsigned w[36];
+      {
+        const uint4* cl = reinterpret_cast<const uint4*>(tp.clist + cid * 72);
+#pragma unroll
+        for (int i = 0; i < 9; ++i) { const uint4 v = __ldg(cl + i); w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w; }
+      }
+      const int loc0 = tp.cbase[cid];
+      const bool cont = (w[0] & 0x8000u) == 0;            // my first run started in the previous thread's chunk
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      if (e_next >= 0) {                                  // next tile's vertices and DOFs on their way to L2
+#pragma unroll
+        for (int s = 0; s < 8; ++s) { prefetch_l2(kp.u + rowbuf[s]); prefetch_l2(kp.nodes + (int64_t)rowbuf[8 + s] * 3); }
+      }
+      __syncthreads();                                    // element store and list copies complete
+      {
+        double sum = 0.0;
+        int loc = loc0;
+        double* dst = cont ? carry + tid : acc + loc;
+#pragma unroll
+        for (int g = 0; g < 72; g += 8) {                 // loads of a group are issued ahead of its (possibly aliasing) stores
+          double v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int k = g + u;
+            const unsigned c = (k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffffu);
+            v[u] = Ks[c & 0x7fffu];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int k = g + u;
+            const unsigned c = (k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffffu);
+            if (k > 0 && (c & 0x8000u)) { *dst = sum; ++loc; dst = acc + loc; sum = 0.0; }
+            sum += v[u];
+          }
+        }
+        *dst = sum;
+      }
+      __syncthreads();                                    // run totals stored
+      if (cont) atomicAdd(acc + loc0, carry[tid]);
+      __syncthreads();
+      {
         double* jb = kp.jac + tp.base[t];
-        const unsigned* off = tp.off + eb;
-        for (int k = tid; k < E; k += 128) { atomicAdd(jb + off[k], acc[k]); acc[k] = 0.0; }
+        for (int k0 = tid; k0 < E; k0 += 512) {
+          unsigned o[4]; double v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) { o[u] = s_off[k]; v[u] = acc[k]; } }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) atomicAdd(jb + o[u], v[u]); }
+        }
+        for (int k = tid; k < R; k += 128) atomicAdd(kp.res + s_rows[k], acc[E + k]);
       }
-      const int* rows = tp.rows + rb;
-      for (int k = tid; k < R; k += 128) { atomicAdd(kp.res + rows[k], acc[E + k]); acc[E + k] = 0.0; }
-      __syncthreads();
+      __syncthreads();                                    // s_off / s_rows / acc free for the next tile's copies
+      e_cur = e_next; e_next = e_next2;
     }
   }
 #endif

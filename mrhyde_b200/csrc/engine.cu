@@ -64,11 +64,11 @@ __global__ void __launch_bounds__(128) thermal_hex_q1_kernel(const __grid_consta
     ThermalHexQ1<TRANSIENT, ADV, JAC>::element(kp, e, stage + threadIdx.x, 128);
 }
 
-template <bool TRANSIENT, bool ADV, bool JAC>
+template <bool TRANSIENT, bool ADV>
 __global__ void __launch_bounds__(128) thermal_hex_q1_tiled_kernel(const __grid_constant__ KParams kp) {
-  __shared__ double stage[ThermalHexQ1<TRANSIENT, ADV, JAC>::NSTAGE * 8 * 128];
-  extern __shared__ double acc[];
-  ThermalHexQ1<TRANSIENT, ADV, JAC>::tiled(kp, stage + threadIdx.x, 128, acc);
+  __shared__ double stage[ThermalHexQ1<TRANSIENT, ADV, true>::NSTAGE * 8 * 128];
+  extern __shared__ double dsm[];
+  ThermalHexQ1<TRANSIENT, ADV, true>::tiled(kp, stage + threadIdx.x, 128, dsm);
 }
 
 // row-relative CRS position of column `col` in row `row` (columns ascending)

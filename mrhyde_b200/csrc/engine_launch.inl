@@ -55,7 +55,8 @@ void device_finalize(mrh_engine* h) {
   if (!D.tiles) D.tiles = new TileDev();
   D.tiles->release();
   if (!(H.cfg.flags & 5) && thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
-    const std::string why = build_tile_plan(H.tileOrder(), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p, *D.tiles);
+    const std::string why = build_tile_plan(H.tileOrder(), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p,
+                                            H.cfg.include_advection ? 64 : 36, *D.tiles);
     if (!D.tiles->ok) h->err = "tile-staged scatter unavailable (" + why + "), using direct scatter";
   }
   // NVRTC specialisation of the coefficient expressions for the specialised thermal kernel (jit.hpp)
@@ -102,7 +103,8 @@ void launch_thermal_fast(const DeviceImpl& D, const KParams& kp, cudaStream_t st
 
 template <bool T, bool A, bool J>
 void launch_thermal_tiled(const DeviceImpl& D, const KParams& kp, size_t acc_bytes, cudaStream_t stream) {
-  auto kern = thermal_hex_q1_tiled_kernel<T, A, J>;
+  if constexpr (!J) { (void)D; (void)kp; (void)acc_bytes; (void)stream; throw std::runtime_error("internal: tiled scatter requested for a residual-only pass"); } else {
+  auto kern = thermal_hex_q1_tiled_kernel<T, A>;
   CUDA_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)acc_bytes));
   int per_sm = 1;
   CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, acc_bytes));
@@ -110,6 +112,7 @@ void launch_thermal_tiled(const DeviceImpl& D, const KParams& kp, size_t acc_byt
   const unsigned grid = (unsigned)std::min<int64_t>(kp.tile.ntiles, (int64_t)D.num_sms * per_sm);
   kern<<<grid, 128, acc_bytes, stream>>>(kp);
   CUDA_CK(cudaGetLastError());
+  }
 }
 
 int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac) {
@@ -130,9 +133,10 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
       const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
       JitKernel* jk = (H.cfg.flags & 2) ? nullptr : D.jit.thermal(tr, adv, jc);
       D.jit_used = jk != nullptr;
-      const bool tiled = D.tiles && D.tiles->ok;
+      const bool tiled = jc && D.tiles && D.tiles->ok && D.tiles->nk == (adv ? 64 : 36);       // residual-only passes scatter directly
       if (tiled) fill_tile_params(*D.tiles, kp.tile);
-      const size_t acc_bytes = tiled ? (size_t)D.tiles->max_acc * sizeof(double) : 0;
+      const size_t acc_bytes = !tiled ? 0 : adv ? ThermalHexQ1<false, true, true>::tiled_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r)
+                                                : ThermalHexQ1<false, false, true>::tiled_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r);
       D.last_path = jk ? (tiled ? "nvrtc-specialised+tiled" : "nvrtc-specialised") : (tiled ? "specialised+tiled" : "specialised");
       if (jk) {
         const int64_t nblk = (kp.nwork + 127) / 128;

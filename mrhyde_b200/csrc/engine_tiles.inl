@@ -1,208 +1,202 @@
 // Part of engine.cu: construction of the tile plan used by the tile-staged scatter (params.h TilePlan).
-// Elements are taken in tiles of 128 (host-chosen order, brick-blocked on structured meshes); for each tile the
-// distinct CRS slots and residual rows its elements touch are found with a block-wide radix sort, and every element
-// gets the position of its 64 + 8 contributions in those lists.  The per-element position vectors are
-// de-duplicated into a dictionary like the slot patterns (structured meshes collapse to a few hundred vectors).
+// Elements are taken in tiles of 128 (host-chosen order, brick-blocked on structured meshes).  The 128 x 72
+// contributions of a tile (64 element-matrix entries + 8 residual entries per element) are sorted by destination
+// (CRS slot, then residual row; contributions of fixed rows last) with a block-wide radix sort.  The sorted order
+// is the tile's contribution list: thread t of the assembly kernel sums positions [72 t, 72 t + 72).  The distinct
+// destinations give the tile's slot / row lists for the flush.  Contribution lists are de-duplicated into a
+// dictionary (structured meshes collapse to a few dozen lists).
 #include <cub/block/block_radix_sort.cuh>
 #include <cub/block/block_scan.cuh>
 
 namespace {
 
 constexpr int TILE_ELEMS = 128;
-constexpr unsigned long long SLOT_SENTINEL = ~0ull;
-constexpr unsigned ROW_SENTINEL = ~0u;
+constexpr int TILE_NC = 72;                                // contributions per element
+constexpr int SRC_BITS = 14;                               // entry * 128 + thread < 72 * 128 + 1
+constexpr unsigned long long KEY_SENTINEL = ~0ull;
+constexpr unsigned long long ROW_SPACE = 1ull << 45;       // destination keys: CRS slot | ROW_SPACE + row | masked
+constexpr unsigned long long MASKED_DEST = KEY_SENTINEL >> SRC_BITS;
 
 struct TileDev {
-  DevBuf<int> perm, rows, tpat_id;
+  DevBuf<int> perm, rows, cl_id;
   DevBuf<int64_t> eptr, rptr, base;
   DevBuf<uint32_t> off;
-  DevBuf<uint16_t> tpat;
+  DevBuf<uint16_t> clist, cbase;
   int64_t ntiles = 0, npatterns = 0;
-  int max_acc = 0;
+  int max_acc = 0, nk = 0, max_e = 0, max_r = 0;
   bool ok = false;
-  void release() { perm.release(); rows.release(); tpat_id.release(); eptr.release(); rptr.release(); base.release(); off.release(); tpat.release(); ok = false; }
+  void release() { perm.release(); rows.release(); cl_id.release(); eptr.release(); rptr.release(); base.release(); off.release();
+                   clist.release(); cbase.release(); ok = false; }
 };
 
 struct TileSmem {
-  typedef cub::BlockRadixSort<unsigned long long, TILE_ELEMS, 64> Sort64;
-  typedef cub::BlockRadixSort<unsigned, TILE_ELEMS, 8> Sort8;
-  typedef cub::BlockScan<int, TILE_ELEMS> Scan;
-  union Temp { typename Sort64::TempStorage s64; typename Sort8::TempStorage s8; typename Scan::TempStorage scan; };
+  typedef cub::BlockRadixSort<unsigned long long, TILE_ELEMS, TILE_NC> Sort;
+  typedef cub::BlockScan<long long, TILE_ELEMS> Scan;
+  union Temp { typename Sort::TempStorage sort; typename Scan::TempStorage scan; };
   Temp temp;
-  unsigned long long uniq[TILE_ELEMS * 64];
-  unsigned urow[TILE_ELEMS * 8];
-  unsigned long long last64[TILE_ELEMS];
-  unsigned last8[TILE_ELEMS];
-  int total;
+  unsigned long long last[TILE_ELEMS];
+  unsigned long long hash[TILE_ELEMS];
+  unsigned long long first_dest;
 };
 
-// N = 8 (Q1 hex, one variable): slots of element e, fixed rows masked out
-__device__ __forceinline__ void element_slots(const int* lids, const uint8_t* fixed, const int64_t* rowptr, const int* colind,
-                                              int64_t e, unsigned long long (&key)[64], unsigned (&row)[8]) {
+// destination keys of the 72 contributions of element e held by thread `tid` (N = 8: Q1 hex, one variable)
+__device__ __forceinline__ void element_keys(const int* lids, const uint8_t* fixed, const int64_t* rowptr, const int* colind,
+                                             int64_t e, int tid, int nk, unsigned long long (&key)[TILE_NC], int* bad) {
   const int* l = lids + e * 8;
   for (int i = 0; i < 8; ++i) {
     const int li = l[i];
     const bool fx = fixed[li] != 0;
-    row[i] = fx ? ROW_SENTINEL : (unsigned)li;
     for (int j = 0; j < 8; ++j) {
       const int s = fx ? -1 : rel_slot(rowptr, colind, li, l[j]);
-      key[i * 8 + j] = (s < 0) ? SLOT_SENTINEL : (unsigned long long)(rowptr[li] + s);
+      if (!fx && s < 0) atomicExch(bad, 1);
+      const int entry = (nk == 64) ? i * 8 + j : (i <= j ? HexQ1::tri(i, j) : HexQ1::tri(j, i));
+      key[i * 8 + j] = (s < 0) ? KEY_SENTINEL : (((unsigned long long)(rowptr[li] + s) << SRC_BITS) | (unsigned)(entry * TILE_ELEMS + tid));
     }
+    key[64 + i] = fx ? KEY_SENTINEL : (((ROW_SPACE + (unsigned long long)li) << SRC_BITS) | (unsigned)((nk + i) * TILE_ELEMS + tid));
   }
 }
 
 template <bool WRITE>
 __global__ void __launch_bounds__(TILE_ELEMS) tile_plan_kernel(const int* perm, int64_t nelem, const int* lids, const uint8_t* fixed,
-                                                               const int64_t* rowptr, const int* colind, int* E_count, int* R_count,
+                                                               const int64_t* rowptr, const int* colind, int nk, int* E_count, int* R_count,
                                                                const int64_t* eptr, const int64_t* rptr, int64_t* tile_base,
-                                                               uint32_t* tile_off, int* tile_rows, uint16_t* loc_all, uint64_t* hash, int* bad) {
+                                                               uint32_t* tile_off, int* tile_rows, uint16_t* cl_all, uint16_t* cbase_all,
+                                                               uint64_t* tile_hash, int* bad) {
   extern __shared__ __align__(16) unsigned char smraw[];
   TileSmem& S = *reinterpret_cast<TileSmem*>(smraw);
   const int tid = threadIdx.x;
   const int64_t t = blockIdx.x, e0 = t * TILE_ELEMS + tid;
-  const int64_t e = (e0 < nelem) ? (int64_t)perm[e0] : -1;
-  unsigned long long key[64]; unsigned row[8];
-  if (e >= 0) element_slots(lids, fixed, rowptr, colind, e, key, row);
-  else { for (int k = 0; k < 64; ++k) key[k] = SLOT_SENTINEL; for (int k = 0; k < 8; ++k) row[k] = ROW_SENTINEL; }
+  unsigned long long key[TILE_NC];
+  if (e0 < nelem) element_keys(lids, fixed, rowptr, colind, (int64_t)perm[e0], tid, nk, key, bad);
+  else for (int k = 0; k < TILE_NC; ++k) key[k] = KEY_SENTINEL;
 
-  // ---- distinct CRS slots of the tile ------------------------------------------------------------------
-  TileSmem::Sort64(S.temp.s64).Sort(key);
-  S.last64[tid] = key[63];
+  TileSmem::Sort(S.temp.sort).Sort(key);                   // blocked arrangement: thread t holds positions [72 t, 72 t + 72)
+  S.last[tid] = key[TILE_NC - 1] >> SRC_BITS;
+  if (tid == 0) S.first_dest = key[0] >> SRC_BITS;
   __syncthreads();
-  unsigned long long prev = (tid == 0) ? SLOT_SENTINEL : S.last64[tid - 1];
-  int cnt = 0;
-  for (int k = 0; k < 64; ++k) { if (key[k] != SLOT_SENTINEL && (key[k] != prev || (tid == 0 && k == 0))) ++cnt; prev = key[k]; }
-  int offs = 0, total = 0;
-  TileSmem::Scan(S.temp.scan).ExclusiveSum(cnt, offs, total);
-  __syncthreads();
-  const int E = total;
-  if (WRITE) {
-    prev = (tid == 0) ? SLOT_SENTINEL : S.last64[tid - 1];
-    for (int k = 0; k < 64; ++k) { if (key[k] != SLOT_SENTINEL && (key[k] != prev || (tid == 0 && k == 0))) S.uniq[offs++] = key[k]; prev = key[k]; }
-  } else if (tid == 0) E_count[t] = E;
-  __syncthreads();
+  // a contribution starts a run when its destination differs from its predecessor's
+  unsigned long long prev = (tid == 0) ? 0ull : S.last[tid - 1];
+  long long cnt = 0;                                        // packed counts: slots | rows << 20 | masked << 40
+  bool starts0 = false;
+  for (int k = 0; k < TILE_NC; ++k) {
+    const unsigned long long d = key[k] >> SRC_BITS;
+    const bool st = (tid == 0 && k == 0) || d != prev;
+    if (k == 0) starts0 = st;
+    if (st) cnt += (d < ROW_SPACE) ? 1ll : (d != MASKED_DEST ? (1ll << 20) : (1ll << 40));
+    prev = d;
+  }
+  long long before = 0, total = 0;
+  TileSmem::Scan(S.temp.scan).ExclusiveSum(cnt, before, total);
+  const int E = (int)(total & 0xfffff), R = (int)((total >> 20) & 0xfffff);
+  if (!WRITE) { if (tid == 0) { E_count[t] = E; R_count[t] = R; } return; }
 
-  // ---- distinct residual rows -----------------------------------------------------------------------------
-  TileSmem::Sort8(S.temp.s8).Sort(row);
-  S.last8[tid] = row[7];
-  __syncthreads();
-  unsigned prow = (tid == 0) ? ROW_SENTINEL : S.last8[tid - 1];
-  cnt = 0;
-  for (int k = 0; k < 8; ++k) { if (row[k] != ROW_SENTINEL && (row[k] != prow || (tid == 0 && k == 0))) ++cnt; prow = row[k]; }
-  TileSmem::Scan(S.temp.scan).ExclusiveSum(cnt, offs, total);
-  __syncthreads();
-  const int R = total;
-  if (!WRITE) { if (tid == 0) R_count[t] = R; return; }
-  prow = (tid == 0) ? ROW_SENTINEL : S.last8[tid - 1];
-  for (int k = 0; k < 8; ++k) { if (row[k] != ROW_SENTINEL && (row[k] != prow || (tid == 0 && k == 0))) S.urow[offs++] = row[k]; prow = row[k]; }
-  __syncthreads();
-
-  // ---- write the tile lists ---------------------------------------------------------------------------------
-  const unsigned long long base = (E > 0) ? S.uniq[0] : 0ull;
+  int run = (int)((before & 0xfffff) + ((before >> 20) & 0xfffff) + (before >> 40));     // runs that start before my chunk
+  const unsigned long long base = (E > 0) ? S.first_dest : 0ull;
   if (tid == 0) tile_base[t] = (int64_t)base;
-  for (int k = tid; k < E; k += TILE_ELEMS) {
-    const unsigned long long d = S.uniq[k] - base;
-    if (d > 0xffffffffull) atomicExch(bad, 3);
-    tile_off[eptr[t] + k] = (uint32_t)d;
-  }
-  for (int k = tid; k < R; k += TILE_ELEMS) tile_rows[rptr[t] + k] = (int)S.urow[k];
-  if (E > 65534 || R > 65534) atomicExch(bad, 4);
-  if (e < 0) return;
-
-  // ---- position of this element's contributions in the lists --------------------------------------------------
-  element_slots(lids, fixed, rowptr, colind, e, key, row);
+  if (E + R > 32000) atomicExch(bad, 4);
+  const int zero_src = (nk + 8) * TILE_ELEMS;
+  uint16_t* out = cl_all + ((size_t)t * TILE_ELEMS + tid) * TILE_NC;
   uint64_t h = 0x51ed27ull;
-  uint16_t* out = loc_all + e * 72;
-  for (int k = 0; k < 64; ++k) {
-    unsigned loc = 0xffffu;
-    if (key[k] != SLOT_SENTINEL) {
-      int lo = 0, hi = E;
-      while (lo < hi) { const int mid = (lo + hi) >> 1; if (S.uniq[mid] < key[k]) lo = mid + 1; else hi = mid; }
-      loc = (unsigned)lo;
+  const int loc0 = starts0 ? run : run - 1;
+  cbase_all[(size_t)t * TILE_ELEMS + tid] = (uint16_t)loc0;
+  h = mix64(h, (uint64_t)loc0);
+  prev = (tid == 0) ? 0ull : S.last[tid - 1];
+  for (int k = 0; k < TILE_NC; ++k) {
+    const unsigned long long d = key[k] >> SRC_BITS;
+    const bool st = (tid == 0 && k == 0) || d != prev;
+    if (st) {
+      if (d < ROW_SPACE) {
+        const unsigned long long rel = d - base;
+        if (rel > 0xffffffffull) atomicExch(bad, 3);
+        tile_off[eptr[t] + run] = (uint32_t)rel;
+      } else if (d != MASKED_DEST) tile_rows[rptr[t] + (run - E)] = (int)(d - ROW_SPACE);
+      ++run;
     }
-    out[k] = (uint16_t)loc; h = mix64(h, loc);
+    const unsigned src = (d == MASKED_DEST) ? (unsigned)zero_src : (unsigned)(key[k] & ((1u << SRC_BITS) - 1));
+    const unsigned c = src | (st ? 0x8000u : 0u);
+    out[k] = (uint16_t)c; h = mix64(h, c);
+    prev = d;
   }
-  for (int k = 0; k < 8; ++k) {
-    unsigned loc = 0xffffu;
-    if (row[k] != ROW_SENTINEL) {
-      int lo = 0, hi = R;
-      while (lo < hi) { const int mid = (lo + hi) >> 1; if (S.urow[mid] < row[k]) lo = mid + 1; else hi = mid; }
-      loc = (unsigned)lo;
-    }
-    out[64 + k] = (uint16_t)loc; h = mix64(h, loc);
-  }
-  hash[e] = h;
+  S.hash[tid] = h;
+  __syncthreads();
+  if (tid == 0) { uint64_t g = 0x9d2cull; for (int k = 0; k < TILE_ELEMS; ++k) g = mix64(g, S.hash[k]); tile_hash[t] = g; }
 }
 
-__global__ void tpat_fill_kernel(const uint16_t* loc_all, const int* rep, int64_t npat, uint16_t* tpat) {
+__global__ void clist_fill_kernel(const uint16_t* cl_all, const uint16_t* cbase_all, const int* rep, int64_t npat, uint16_t* clist, uint16_t* cbase) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= npat * 72) return;
-  tpat[k] = loc_all[(int64_t)rep[k / 72] * 72 + (k % 72)];
+  constexpr int64_t L = (int64_t)TILE_ELEMS * TILE_NC;
+  if (k < npat * L) clist[k] = cl_all[(int64_t)rep[k / L] * L + (k % L)];
+  if (k < npat * TILE_ELEMS) cbase[k] = cbase_all[(int64_t)rep[k / TILE_ELEMS] * TILE_ELEMS + (k % TILE_ELEMS)];
 }
-__global__ void tpat_assign_kernel(const uint16_t* loc_all, int64_t nelem, const uint64_t* hash, const uint64_t* uhash, int64_t npat,
-                                   const uint16_t* tpat, int* tpat_id, int* bad) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= nelem) return;
-  const uint64_t h = hash[e];
+// list id of every tile (binary search on the sorted unique hashes) and full verification against the dictionary
+__global__ void clist_assign_kernel(const uint16_t* cl_all, const uint16_t* cbase_all, int64_t ntiles, const uint64_t* hash, const uint64_t* uhash,
+                                    int64_t npat, const uint16_t* clist, const uint16_t* cbase, int* cl_id, int* bad) {
+  const int64_t t = blockIdx.x;
+  const uint64_t h = hash[t];
   int64_t lo = 0, hi = npat;
   while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (uhash[mid] < h) lo = mid + 1; else hi = mid; }
-  tpat_id[e] = (int)lo;
   if (lo >= npat) { atomicExch(bad, 5); return; }
-  for (int k = 0; k < 72; ++k) if (tpat[lo * 72 + k] != loc_all[e * 72 + k]) atomicExch(bad, 5);
+  if (threadIdx.x == 0) cl_id[t] = (int)lo;
+  constexpr int L = TILE_ELEMS * TILE_NC;
+  for (int k = threadIdx.x; k < L; k += blockDim.x) if (clist[lo * L + k] != cl_all[t * L + k]) atomicExch(bad, 5);
+  for (int k = threadIdx.x; k < TILE_ELEMS; k += blockDim.x) if (cbase[lo * TILE_ELEMS + k] != cbase_all[t * TILE_ELEMS + k]) atomicExch(bad, 5);
 }
 
 // throws on CUDA errors; leaves T.ok = false (with a reason) when the plan cannot be used
 std::string build_tile_plan(const std::vector<int>& perm_host, int64_t nelem, const int* d_lids, const uint8_t* d_fixed,
-                            const int64_t* d_rowptr, const int* d_colind, TileDev& T) {
+                            const int64_t* d_rowptr, const int* d_colind, int nk, TileDev& T) {
   T.release();
   const int64_t nt = (nelem + TILE_ELEMS - 1) / TILE_ELEMS;
-  T.ntiles = nt;
+  T.ntiles = nt; T.nk = nk; T.max_e = T.max_r = 0;
   T.perm.upload(perm_host);
   DevBuf<int> Ec, Rc, bad, idx; Ec.alloc(nt); Rc.alloc(nt); bad.alloc(1);
   CUDA_CK(cudaMemset(bad.p, 0, sizeof(int)));
   const size_t smem = sizeof(TileSmem);
   CUDA_CK(cudaFuncSetAttribute(tile_plan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   CUDA_CK(cudaFuncSetAttribute(tile_plan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  tile_plan_kernel<false><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, Ec.p, Rc.p,
-                                                             nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, bad.p);
+  tile_plan_kernel<false><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, nk, Ec.p, Rc.p,
+                                                             nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, bad.p);
   CUDA_CK(cudaGetLastError());
   std::vector<int> hE(nt), hR(nt);
   CUDA_CK(cudaMemcpy(hE.data(), Ec.p, nt * sizeof(int), cudaMemcpyDeviceToHost));
   CUDA_CK(cudaMemcpy(hR.data(), Rc.p, nt * sizeof(int), cudaMemcpyDeviceToHost));
+  int hbad = 0; CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (hbad) { T.release(); return "an element entry has no CRS slot"; }
   std::vector<int64_t> eptr(nt + 1, 0), rptr(nt + 1, 0);
   int max_acc = 0;
-  for (int64_t t = 0; t < nt; ++t) { eptr[t + 1] = eptr[t] + hE[t]; rptr[t + 1] = rptr[t] + hR[t]; max_acc = std::max(max_acc, hE[t] + hR[t]); }
+  for (int64_t t = 0; t < nt; ++t) { eptr[t + 1] = eptr[t] + hE[t]; rptr[t + 1] = rptr[t] + hR[t]; max_acc = std::max(max_acc, hE[t] + hR[t]); T.max_e = std::max(T.max_e, hE[t]); T.max_r = std::max(T.max_r, hR[t]); }
   T.max_acc = max_acc;
   T.eptr.upload(eptr); T.rptr.upload(rptr); T.base.alloc(nt);
   T.off.alloc((size_t)std::max<int64_t>(eptr[nt], 1)); T.rows.alloc((size_t)std::max<int64_t>(rptr[nt], 1));
-  DevBuf<uint16_t> loc_all; loc_all.alloc((size_t)nelem * 72);
-  DevBuf<uint64_t> hash, skey; hash.alloc(nelem); skey.alloc(nelem); idx.alloc(nelem);
-  tile_plan_kernel<true><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, nullptr, nullptr,
-                                                            T.eptr.p, T.rptr.p, T.base.p, T.off.p, T.rows.p, loc_all.p, hash.p, bad.p);
-  CUDA_CK(cudaGetLastError());
-  int hbad = 0; CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
-  if (hbad) { T.release(); return hbad == 3 ? "a tile spans more than 2^32 CRS slots" : "a tile has more than 65534 entries"; }
-  CUDA_CK(cudaMemcpy(skey.p, hash.p, nelem * sizeof(uint64_t), cudaMemcpyDeviceToDevice));
-  thrust::device_ptr<uint64_t> kp(skey.p); thrust::device_ptr<int> ip(idx.p);
-  thrust::sequence(thrust::device, ip, ip + nelem);
-  thrust::sort_by_key(thrust::device, kp, kp + nelem, ip);
-  auto ends = thrust::unique_by_key(thrust::device, kp, kp + nelem, ip);
-  const int64_t npat = ends.first - kp;
-  T.npatterns = npat;
-  T.tpat.alloc((size_t)npat * 72); T.tpat_id.alloc(nelem);
-  tpat_fill_kernel<<<blocks_for(npat * 72, 256), 256>>>(loc_all.p, idx.p, npat, T.tpat.p);
-  CUDA_CK(cudaGetLastError());
-  tpat_assign_kernel<<<blocks_for(nelem, 128), 128>>>(loc_all.p, nelem, hash.p, skey.p, npat, T.tpat.p, T.tpat_id.p, bad.p);
+  constexpr size_t L = (size_t)TILE_ELEMS * TILE_NC;
+  DevBuf<uint16_t> cl_all, cbase_all; cl_all.alloc((size_t)nt * L); cbase_all.alloc((size_t)nt * TILE_ELEMS);
+  DevBuf<uint64_t> hash, skey; hash.alloc(nt); skey.alloc(nt); idx.alloc(nt);
+  tile_plan_kernel<true><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, nk, nullptr, nullptr,
+                                                            T.eptr.p, T.rptr.p, T.base.p, T.off.p, T.rows.p, cl_all.p, cbase_all.p, hash.p, bad.p);
   CUDA_CK(cudaGetLastError());
   CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
-  if (hbad) { T.release(); return "tile pattern dictionary verification failed (hash collision)"; }
+  if (hbad) { T.release(); return hbad == 3 ? "a tile spans more than 2^32 CRS slots" : "a tile has more than 32000 destinations"; }
+  CUDA_CK(cudaMemcpy(skey.p, hash.p, nt * sizeof(uint64_t), cudaMemcpyDeviceToDevice));
+  thrust::device_ptr<uint64_t> kp(skey.p); thrust::device_ptr<int> ip(idx.p);
+  thrust::sequence(thrust::device, ip, ip + nt);
+  thrust::sort_by_key(thrust::device, kp, kp + nt, ip);
+  auto ends = thrust::unique_by_key(thrust::device, kp, kp + nt, ip);
+  const int64_t npat = ends.first - kp;
+  T.npatterns = npat;
+  T.clist.alloc((size_t)npat * L); T.cbase.alloc((size_t)npat * TILE_ELEMS); T.cl_id.alloc(nt);
+  clist_fill_kernel<<<blocks_for(npat * (int64_t)L, 256), 256>>>(cl_all.p, cbase_all.p, idx.p, npat, T.clist.p, T.cbase.p);
+  CUDA_CK(cudaGetLastError());
+  clist_assign_kernel<<<(unsigned)nt, 256>>>(cl_all.p, cbase_all.p, nt, hash.p, skey.p, npat, T.clist.p, T.cbase.p, T.cl_id.p, bad.p);
+  CUDA_CK(cudaGetLastError());
+  CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (hbad) { T.release(); return "contribution list dictionary verification failed (hash collision)"; }
   T.ok = true;
   return "";
 }
 
 void fill_tile_params(const TileDev& T, TilePlan& tp) {
   tp.perm = T.perm.p; tp.eptr = T.eptr.p; tp.rptr = T.rptr.p; tp.base = T.base.p; tp.off = T.off.p; tp.rows = T.rows.p;
-  tp.tpat = T.tpat.p; tp.tpat_id = T.tpat_id.p; tp.ntiles = T.ntiles; tp.max_acc = T.max_acc; tp.pad_ = 0;
+  tp.clist = T.clist.p; tp.cbase = T.cbase.p; tp.cl_id = T.cl_id.p; tp.ntiles = T.ntiles; tp.max_acc = T.max_acc; tp.nk = T.nk; tp.max_e = T.max_e; tp.max_r = T.max_r;
 }
 
 }  // namespace

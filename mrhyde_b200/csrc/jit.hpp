@@ -11,6 +11,7 @@
 #include <nvrtc.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <map>
 #include <string>
 #include <vector>
@@ -149,18 +150,22 @@ class JitCache {
     if (coef_src_.empty()) { last_error = "no coefficient source"; return nullptr; }
     auto B = [](bool b) { return b ? "true" : "false"; };
     K.source = std::string("#include \"assemble_fast.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
-        "};\n}\nextern \"C\" __global__ void __launch_bounds__(128) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
+        "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
         "  typedef mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n"
-        "  extern __shared__ double acc[];\n"
-        "  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, acc); return; }\n"
+        "  extern __shared__ double dsm[];\n" +
+        (jac ? "  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, dsm); return; }\n" : "") +
         "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
         "    Kern::element(kp, e, nullptr, 0);\n}\n";
     std::vector<const char*> hdr_src, hdr_name;
     for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
     nvrtcProgram prog;
     if (api.CreateProgram(&prog, K.source.c_str(), "mrh_jit_thermal.cu", (int)hdr_src.size(), hdr_src.data(), hdr_name.data()) != NVRTC_SUCCESS) { last_error = "nvrtcCreateProgram failed"; return nullptr; }
-    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1"};
-    const nvrtcResult rc = api.CompileProgram(prog, 4, opts);
+    std::string minb = "-DMRH_JIT_MINB=2";                                                          // CTAs of 128 threads per SM the register allocation targets
+    if (const char* ev = getenv("MRH_JIT_MINB")) minb = std::string("-DMRH_JIT_MINB=") + ev;          // tuning experiments
+    std::string extra = "-DMRH_JIT_EXTRA=0";
+    if (const char* ev = getenv("MRH_JIT_DEFINE")) extra = std::string("-D") + ev;                    // tuning experiments
+    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", minb.c_str(), extra.c_str()};
+    const nvrtcResult rc = api.CompileProgram(prog, 6, opts);
     size_t ls = 0; api.GetProgramLogSize(prog, &ls);
     if (ls > 1) { K.log.resize(ls); api.GetProgramLog(prog, &K.log[0]); }
     if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + K.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }

@@ -45,16 +45,19 @@ struct PhysParams {
 
 struct TilePlan {          // tile-staged scatter of the specialised kernels (built at finalize, engine_tiles.inl)
   const int* perm;           // (nelem)   element order: tile t = perm[128 t .. 128 t + 127]
-  const int64_t* eptr;       // (ntiles+1) first accumulation entry of each tile
-  const int64_t* rptr;       // (ntiles+1) first residual row of each tile
+  const int64_t* eptr;       // (ntiles+1) first CRS-slot entry of each tile in `off`
+  const int64_t* rptr;       // (ntiles+1) first residual row of each tile in `rows`
   const int64_t* base;       // (ntiles)  smallest CRS slot of the tile
-  const uint32_t* off;       // (sum E_t) CRS slot of each tile entry relative to base, ascending
-  const int* rows;           // (sum R_t) residual rows (LIDs) of each tile, ascending
-  const uint16_t* tpat;      // (npattern, 72) per element: tile entry of K(i,j) at [8 i + j], tile row of r_s at [64 + s]; 0xFFFF = fixed row
-  const int* tpat_id;        // (nelem)
+  const uint32_t* off;       // (sum E_t) distinct CRS slots of each tile relative to base, ascending
+  const int* rows;           // (sum R_t) distinct residual rows (LIDs) of each tile, ascending
+  const uint16_t* clist;     // (nlist, 128, 72) the tile's contributions sorted by destination; thread t reads row t:
+                             //   bits 0..14 = entry * 128 + thread in the shared element store, bit 15 = first of its destination
+  const uint16_t* cbase;     // (nlist, 128) index in [slots | rows | masked] of the destination of thread t's first contribution
+  const int* cl_id;          // (ntiles)  contribution list of each tile (lists are de-duplicated)
   int64_t ntiles;
-  int max_acc;               // largest E_t + R_t: doubles of shared memory per CTA
-  int pad_;
+  int max_acc;               // largest E_t + R_t: accumulation doubles per CTA (+1 cell for masked contributions)
+  int nk;                    // 36 (symmetric element matrix) or 64: entry numbering the lists were built for
+  int max_e, max_r;          // largest E_t, largest R_t (staged slot / row lists)
 };
 
 struct KParams {

@@ -1,6 +1,7 @@
 // compile-only check (no GPU needed): the NVRTC translation unit of the specialised thermal kernel builds for sm_100a
 #include <nvrtc.h>
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include "../mrhyde_b200/csrc/expr.hpp"
@@ -18,15 +19,20 @@ int main() {
   src += "  static __device__ __forceinline__ double rhocp(double x, double y, double z, double t) { return rho_(x, y, z, t) * cp_(x, y, z, t); }\n";
   for (const char* n : {"bx", "by", "bz"}) src += jit_function_source(n, ec.compile("one", "ip"), ec.code, ec.cpool);
   printf("%s\n", src.c_str());
+  const char* minb_env = getenv("MRH_JIT_MINB");
+  const std::string minb = std::string("-DMRH_JIT_MINB=") + (minb_env ? minb_env : "2");
   std::string full = std::string("#include \"assemble_fast.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + src +
-      "};\n}\nextern \"C\" __global__ void __launch_bounds__(128) k(const __grid_constant__ mrh::KParams kp) {\n"
+      "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) k(const __grid_constant__ mrh::KParams kp) {\n"
+      "  typedef mrh::ThermalHexQ1<false, false, true, mrh::JitCoefs> Kern;\n"
+      "  extern __shared__ double dsm[];\n"
+      "  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, dsm); return; }\n"
       "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
-      "    mrh::ThermalHexQ1<false, false, true, mrh::JitCoefs>::element(kp, e, nullptr, 0);\n}\n";
+      "    Kern::element(kp, e, nullptr, 0);\n}\n";
   std::vector<const char*> hs, hn;
   for (int i = 0; i < k_num_embedded_headers; ++i) { hn.push_back(k_embedded_headers[i].name); hs.push_back(k_embedded_headers[i].text); }
   nvrtcProgram p; nvrtcCreateProgram(&p, full.c_str(), "probe.cu", (int)hs.size(), hs.data(), hn.data());
-  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", "--ptxas-options=-v"};
-  nvrtcResult rc = nvrtcCompileProgram(p, 5, opts);
+  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", "--ptxas-options=-v", minb.c_str()};
+  nvrtcResult rc = nvrtcCompileProgram(p, 6, opts);
   size_t ls; nvrtcGetProgramLogSize(p, &ls); std::string log(ls, ' '); nvrtcGetProgramLog(p, &log[0]);
   printf("rc=%d\n%s\n", (int)rc, log.c_str());
   if (rc == NVRTC_SUCCESS) { size_t cs; nvrtcGetCUBINSize(p, &cs); std::vector<char> c(cs); nvrtcGetCUBIN(p, c.data()); FILE* f = fopen("/tmp/jit_probe.cubin", "wb"); fwrite(c.data(), 1, cs, f); fclose(f); printf("cubin %zu bytes\n", cs); }
