@@ -70,22 +70,19 @@ struct ThermalHexQ1 {
 
   // gather + geometry + point loop of one element: r = element residual, K = element matrix (36 upper entries
   // when symmetric, else 8x8 row-major)
-  struct NoHook { MRH_HD void operator()() const {} };
   MRH_HDN static void compute(const KParams& kp, int64_t e, double* stage, int stride, int (&lid)[8], double (&r)[8], double (&K)[NK]) {
-    compute(kp, kp.lids + e * 8, kp.e2n + e * 8, stage, stride, lid, r, K, NoHook());
+    double X[8][3], us[8], ud[8];
+    gather(kp, kp.lids + e * 8, kp.e2n + e * 8, lid, X, us, ud);
+    work(kp, X, us, ud, stage, stride, r, K);
   }
-  // lrow / nrow: the element's 8 LIDs / 8 node ids (16-byte aligned; global or shared memory).  after_gather() runs
-  // once the gather loads have been issued (the tiled kernel starts its asynchronous copies there).
-  template <class Hook>
-  MRH_HDN static void compute(const KParams& kp, const int* lrow, const int* nrow, double* stage, int stride, int (&lid)[8], double (&r)[8],
-                              double (&K)[NK], Hook&& after_gather) {
-    // ---- gather: LIDs, vertex coordinates, DOFs ------------------------------------------------------
+  // ---- gather: LIDs, vertex coordinates, DOFs (time-stage combination for transient runs) ----------------
+  // lrow / nrow: the element's 8 LIDs / 8 node ids (16-byte aligned; global or shared memory)
+  MRH_HDN static void gather(const KParams& kp, const int* lrow, const int* nrow, int (&lid)[8], double (&X)[8][3], double (&us)[8], double (&ud)[8]) {
     {
       const int4* lp = reinterpret_cast<const int4*>(lrow);
       const int4 a = lp[0], b = lp[1];
       lid[0] = a.x; lid[1] = a.y; lid[2] = a.z; lid[3] = a.w; lid[4] = b.x; lid[5] = b.y; lid[6] = b.z; lid[7] = b.w;
     }
-    double X[8][3];
     {
       const int4* np = reinterpret_cast<const int4*>(nrow);
       const int4 a = np[0], b = np[1];
@@ -96,7 +93,6 @@ struct ThermalHexQ1 {
         X[s][0] = p[0]; X[s][1] = p[1]; X[s][2] = p[2];
       }
     }
-    double us[8], ud[8];
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
       const double uval = kp.u[lid[s]];
@@ -112,7 +108,10 @@ struct ThermalHexQ1 {
         ud[s] = tp.alpha_t * uval + beta_t * tp.timewt;
       }
     }
-    after_gather();
+  }
+  // ---- geometry + point loop of one element: r = element residual, K = element matrix -----------------------
+  MRH_HDN static void work(const KParams& kp, const double (&X)[8][3], const double (&us)[8], const double (&ud)[8], double* stage, int stride,
+                           double (&r)[8], double (&K)[NK]) {
     const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
 
     // ---- coefficients at the 8 points (vector interpreter), staged for the rolled point loop ------------
@@ -288,9 +287,9 @@ struct ThermalHexQ1 {
   // chunk.  The CTA then flushes the array with REDs whose lanes walk consecutive CRS slots: against one RED
   // per element entry this halves the REDs and lets several lanes share a 32-byte sector, which is what bounds
   // RED.F64 throughput on B200 (profiles/r1_red_microbench.txt).
-  // While an element is computed, LDGSTS copies bring the tile's slot / row lists and the NEXT tile's LID / node
-  // rows into shared memory, and L2 prefetches are issued for the next tile's vertices and DOFs, so that neither
-  // the flush nor the next gather waits on DRAM.
+  // While an element is computed, LDGSTS copies bring the tile's slot / row lists into shared memory; the gather
+  // loads of the NEXT tile are issued before this tile's scatter and the LID / node rows of the tile after that are
+  // copied asynchronously, so that neither the flush nor the next element computation waits on DRAM.
   // dynamic shared memory: Ks[(NK + 8) * 128] | zero cell | pad | acc[max_acc + 1] | carry[128] | rowbuf[128][16] int
   //                        | off[max_e] uint32 | rows[max_r] int
   static constexpr int NE = NK + 8;
@@ -303,7 +302,6 @@ struct ThermalHexQ1 {
   __device__ __forceinline__ static void cp_async16(void* smem_dst, const void* gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
   }
-  __device__ __forceinline__ static void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(__cvta_generic_to_global(p))); }
   __device__ static void tiled(const KParams& kp, double* stage, int stride, double* sm) {
     static_assert(JAC, "the tile-staged scatter is used for Jacobian assembly only");
     const TilePlan& tp = kp.tile;
@@ -322,33 +320,41 @@ struct ThermalHexQ1 {
       cp_async16(rowbuf, kp.lids + (int64_t)e * 8); cp_async16(rowbuf + 4, kp.lids + (int64_t)e * 8 + 4);
       cp_async16(rowbuf + 8, kp.e2n + (int64_t)e * 8); cp_async16(rowbuf + 12, kp.e2n + (int64_t)e * 8 + 4);
     };
-    int e_cur = element_of(blockIdx.x), e_next = element_of(blockIdx.x + tstep);
-    fetch_rows(e_cur);
+    // software pipeline over the CTA's tiles: while tile t is scattered, the gather loads of tile t + 1 are in
+    // flight and the LID / node rows of tile t + 2 are being copied into rowbuf
+    int e_cur = element_of(blockIdx.x), e_next = element_of(blockIdx.x + tstep), e_next2 = element_of(blockIdx.x + 2 * tstep);
+    double X[8][3], us[8], ud[8];
+    {
+      int lid[8];
+      if (e_cur >= 0) gather(kp, kp.lids + (int64_t)e_cur * 8, kp.e2n + (int64_t)e_cur * 8, lid, X, us, ud);
+    }
+    fetch_rows(e_next);
     asm volatile("cp.async.commit_group;" ::: "memory");
     for (int64_t t = blockIdx.x; t < tp.ntiles; t += tstep) {
       const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
       const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
-      int e_next2 = -1;
-      asm volatile("cp.async.wait_group 0;" ::: "memory");                 // my rows have arrived (no other thread reads them)
-      auto start_copies = [&]() {
-        for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + eb + k);
-        for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + rb + k);
-        fetch_rows(e_next);                                                // rowbuf has been read into registers by now
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        e_next2 = element_of(t + 2 * tstep);
-      };
+      for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + eb + k);
+      for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + rb + k);
+      asm volatile("cp.async.commit_group;" ::: "memory");
       if (e_cur >= 0) {
-        int lid[8]; double r[8], K[NK];
-        compute(kp, rowbuf, rowbuf + 8, stage, stride, lid, r, K, start_copies);
+        double r[8], K[NK];
+        work(kp, X, us, ud, stage, stride, r, K);
 #pragma unroll
         for (int k = 0; k < NK; ++k) Ks[k * 128 + tid] = K[k];
 #pragma unroll
         for (int s = 0; s < 8; ++s) Ks[(NK + s) * 128 + tid] = -r[s];
-      } else start_copies();
+      }
+      asm volatile("cp.async.wait_group 0;" ::: "memory");                 // slot / row lists of this tile, my rows of the next
+      if (e_next >= 0) {
+        int lid[8];
+        gather(kp, rowbuf, rowbuf + 8, lid, X, us, ud);                    // consumed after this tile's scatter
+      }
+      const int e_next3 = element_of(t + 3 * tstep);
 #if defined(MRH_DEBUG_SKIP_SCATTER)                         // tuning experiment: element computation only (results are NOT assembled)
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
       __syncthreads();
-      e_cur = e_next; e_next = e_next2;
+      fetch_rows(e_next2);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      e_cur = e_next; e_next = e_next2; e_next2 = e_next3;
       continue;
 #endif
       const size_t cid = (size_t)tp.cl_id[t] * 128 + tid;
@@ -360,11 +366,6 @@ struct ThermalHexQ1 {
       }
       const int loc0 = tp.cbase[cid];
       const bool cont = (w[0] & 0x8000u) == 0;            // my first run started in the previous thread's chunk
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-      if (e_next >= 0) {                                  // next tile's vertices and DOFs on their way to L2
-#pragma unroll
-        for (int s = 0; s < 8; ++s) { prefetch_l2(kp.u + rowbuf[s]); prefetch_l2(kp.nodes + (int64_t)rowbuf[8 + s] * 3); }
-      }
       __syncthreads();                                    // element store and list copies complete
       {
         double sum = 0.0;
@@ -404,7 +405,9 @@ struct ThermalHexQ1 {
         for (int k = tid; k < R; k += 128) atomicAdd(kp.res + s_rows[k], acc[E + k]);
       }
       __syncthreads();                                    // s_off / s_rows / acc free for the next tile's copies
-      e_cur = e_next; e_next = e_next2;
+      fetch_rows(e_next2);                                // rowbuf was consumed by the gather above
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      e_cur = e_next; e_next = e_next2; e_next2 = e_next3;
     }
   }
 #endif

@@ -70,11 +70,9 @@ inline std::string jit_literal(double v) {
   return "(" + s + ")";
 }
 
-inline std::string jit_function_source(const std::string& name, const Prog& pr, const std::vector<Instr>& code,
-                                       const std::vector<double>& cpool) {
-  std::string out = "  static __device__ __forceinline__ double " + name + "(double x, double y, double z, double t) {\n";
-  if (pr.kind == 0) return out + "    return " + jit_literal(pr.cval) + ";\n  }\n";
-  if (pr.kind == 2) throw std::runtime_error("state-dependent coefficient cannot be specialised");
+// fast = true: sin / cos go through mrh::trig_fast (pad.h), which clears `ok` for arguments outside its range
+inline std::string jit_function_body(const Prog& pr, const std::vector<Instr>& code, const std::vector<double>& cpool, bool fast, bool* uses_trig) {
+  std::string out;
   std::vector<std::string> st;
   int ntmp = 0;
   auto leaf = [&](uint8_t op, uint16_t cidx) -> std::string {
@@ -112,8 +110,8 @@ inline std::string jit_function_source(const std::string& name, const Prog& pr, 
     if (in.op == OP_NIP) { const std::string top = st.back(); st.pop_back(); st.pop_back(); st.push_back(top); continue; }
     const std::string a = st.back(); st.pop_back();
     switch (in.op) {
-      case OP_SIN: emit("sin(" + a + ")"); break;
-      case OP_COS: emit("cos(" + a + ")"); break;
+      case OP_SIN: *uses_trig = true; emit(fast ? "mrh::trig_fast(" + a + ", 0, ok)" : "sin(" + a + ")"); break;
+      case OP_COS: *uses_trig = true; emit(fast ? "mrh::trig_fast(" + a + ", 1, ok)" : "cos(" + a + ")"); break;
       case OP_TAN: emit("tan(" + a + ")"); break;
       case OP_EXP: emit("exp(" + a + ")"); break;
       case OP_LOG: emit("log(" + a + ")"); break;
@@ -123,7 +121,24 @@ inline std::string jit_function_source(const std::string& name, const Prog& pr, 
       default: emit("(" + a + " < 0.0) ? -" + a + " : " + a); break;
     }
   }
-  return out + "    return " + st.back() + ";\n  }\n";
+  return out + "    const double result = " + st.back() + ";\n";
+}
+
+// Expressions with sin / cos are emitted twice: a branch-free version on the fast range reduction (so that the
+// compiler can interleave the polynomial chains of several calls) and an exact out-of-line version taken by the
+// whole expression when any argument was outside the fast range.
+inline std::string jit_function_source(const std::string& name, const Prog& pr, const std::vector<Instr>& code,
+                                       const std::vector<double>& cpool) {
+  const std::string sig = "(double x, double y, double z, double t) {\n";
+  const std::string head = "  static __device__ __forceinline__ double " + name + sig;
+  if (pr.kind == 0) return head + "    return " + jit_literal(pr.cval) + ";\n  }\n";
+  if (pr.kind == 2) throw std::runtime_error("state-dependent coefficient cannot be specialised");
+  bool trig = false;
+  const std::string exact = jit_function_body(pr, code, cpool, false, &trig);
+  if (!trig) return head + exact + "    return result;\n  }\n";
+  const std::string fast = jit_function_body(pr, code, cpool, true, &trig);
+  return "  static __device__ __noinline__ double " + name + "_exact" + sig + exact + "    return result;\n  }\n" +
+         head + "    bool ok = true;\n" + fast + "    return ok ? result : " + name + "_exact(x, y, z, t);\n  }\n";
 }
 
 // One NVRTC-compiled module holding the specialised thermal kernel for one (TRANSIENT, ADV, JAC) variant.

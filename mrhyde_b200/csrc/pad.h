@@ -95,6 +95,33 @@ template <int P> MRH_HD PAD<P> chain(const PAD<P>& a, double f, double g) { PAD<
 #pragma unroll
   MRH_LANES r.d[i] = g * a.d[i]; return r; }
 
+#if defined(__CUDACC__)
+// sin(x) (shift 0) or cos(x) (shift 1) for |x| < 105615: three-term Cody-Waite reduction by pi/2 with FMAs and the
+// fdlibm kernel polynomials (error below 1 ulp on the reduced range); straight-line code with immediate
+// coefficients, unlike the library routine whose table loads and slow-path branch serialise neighbouring calls.
+// `ok` is cleared for arguments outside the range (and NaN); the caller then re-evaluates with sin() / cos().
+__device__ __forceinline__ double trig_fast(double x, int shift, bool& ok) {
+  ok = ok && (fabs(x) < 105615.0);
+  const double t = fma(x, 6.3661977236758138e-01, 6755399441055744.0);
+  const int k = __double2loint(t) + shift;
+  const double q = t - 6755399441055744.0;
+  double r = fma(-q, 1.5707963267948966e+00, x);
+  r = fma(-q, 6.1232339957367574e-17, r);
+  r = fma(-q, 8.4784276603688985e-32, r);
+  const double z = r * r;
+  const bool c = (k & 1) != 0;
+  double p = c ? -1.13596475577881948265e-11 : 1.58969099521155010221e-10;
+  p = fma(p, z, c ? 2.08757232129817482790e-09 : -2.50507602534068634195e-08);
+  p = fma(p, z, c ? -2.75573143513906633035e-07 : 2.75573137070700676789e-06);
+  p = fma(p, z, c ? 2.48015872894767294178e-05 : -1.98412698298579493134e-04);
+  p = fma(p, z, c ? -1.38888888888741095749e-03 : 8.33333333332248946124e-03);
+  p = fma(p, z, c ? 4.16666666666666019037e-02 : -1.66666666666666324348e-01);
+  const double base = c ? fma(-0.5, z, 1.0) : r;
+  const double m = c ? z * z : r * z;
+  const double v = fma(m, p, base);
+  return (k & 2) ? -v : v;
+}
+#endif
 MRH_HD double f_sin(double x) { return sin(x); }
 MRH_HD double f_cos(double x) { return cos(x); }
 MRH_HD double f_tan(double x) { return tan(x); }

@@ -7,7 +7,7 @@ import problems
 from mrhyde_b200 import Engine
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
-variants = [dict(no_tiles=False, minb="2", define="MRH_JIT_EXTRA=0"), dict(no_tiles=False, minb="2", define="MRH_DEBUG_SKIP_SCATTER=1")]
+variants = [dict(no_tiles=False, minb="2", define="MRH_JIT_EXTRA=0"), dict(no_tiles=False, minb="2", define="MRH_DEBUG_SKIP_SCATTER=1"), dict(no_tiles=True, minb="2", define="MRH_JIT_EXTRA=0")]
 dev = torch.device("cuda", 0)
 for v in variants:
     os.environ["MRH_JIT_MINB"] = v["minb"]; os.environ["MRH_JIT_DEFINE"] = v["define"]
