@@ -410,6 +410,144 @@ struct ThermalHexQ1 {
       e_cur = e_next; e_next = e_next2; e_next2 = e_next3;
     }
   }
+  // ---- warp-specialised tile-staged assembly (device only; NVRTC kernel) ---------------------------------------
+  // One CTA of 384 threads per SM: warpgroups 1 and 2 (MRH_WS_CREG registers per thread after setmaxnreg) only compute
+  // elements - each owns a stream of tiles, parks K and r in its own shared element store and signals a named
+  // barrier; warpgroup 0 (MRH_WS_SREG registers) does everything else for both streams: contribution-list run sums, carry
+  // adds, RED flush, list copies.  The FP64 pipe therefore always sees two computing warps per scheduler instead of
+  // alternating with the scatter phases of the same warps.
+  // dynamic shared memory: Ks[2][NE * 128 + 2] | acc[(max_acc + 2) & ~1] | carry[128] | rowbuf[2][128][16] int
+  //                        | off[max_e] uint32 | rows[max_r] int
+  __host__ __device__ static constexpr size_t ws_smem_bytes(int max_acc, int max_e, int max_r) {
+    return (2 * ((size_t)NE * 128 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 2 * 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+  }
+#if defined(MRH_WS_CREG)
+  __device__ __forceinline__ static void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+  __device__ __forceinline__ static void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+  __device__ static void tiled_ws(const KParams& kp, double* sm) {
+    static_assert(JAC, "the tile-staged scatter is used for Jacobian assembly only");
+    static_assert(!CF::staged, "the warp-specialised kernel is built with NVRTC-printed coefficients");
+    const TilePlan& tp = kp.tile;
+    const int wg = threadIdx.x >> 7, tid = threadIdx.x & 127;
+    constexpr int KSZ = NE * 128 + 2;
+    double* acc = sm + 2 * KSZ;
+    double* carry = acc + ((tp.max_acc + 2) & ~1);
+    int* rowbase = reinterpret_cast<int*>(carry + 128);
+    unsigned* s_off = reinterpret_cast<unsigned*>(rowbase + 2 * 128 * 16);
+    int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
+    const int64_t tstep = 2 * (int64_t)gridDim.x;
+    constexpr int BAR_FULL = 1, BAR_EMPTY = 3, BAR_SCATTER = 5;        // named barriers (0 is __syncthreads)
+    if (wg == 0) {
+      // ================================= scatter warpgroup =================================
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MRH_WS_SREG));
+      if (tid < 2) sm[tid * KSZ + NE * 128] = 0.0;          // masked contributions read these cells
+      for (int64_t t0 = 2 * (int64_t)blockIdx.x; t0 < tp.ntiles; t0 += tstep) {
+#pragma unroll 1
+        for (int g = 0; g < 2; ++g) {
+          const int64_t t = t0 + g;
+          if (t >= tp.ntiles) break;
+          const double* Ks = sm + g * KSZ;
+          const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
+          const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
+          for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + eb + k);
+          for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + rb + k);
+          asm volatile("cp.async.commit_group;" ::: "memory");
+          const size_t cid = (size_t)tp.cl_id[t] * 128 + tid;
+          const uint4* cl = reinterpret_cast<const uint4*>(tp.clist + cid * 72);
+          uint4 wv = __ldg(cl);
+          const int loc0 = tp.cbase[cid];
+          const bool cont = (wv.x & 0x8000u) == 0;          // my first run started in the previous thread's chunk
+          bar_sync(BAR_FULL + g, 256);                      // element store of stream g complete
+          {
+            double sum = 0.0;
+            int loc = loc0;
+            double* dst = cont ? carry + tid : acc + loc;
+#pragma unroll
+            for (int c = 0; c < 9; ++c) {
+              const unsigned w[4] = {wv.x, wv.y, wv.z, wv.w};
+              if (c < 8) wv = __ldg(cl + c + 1);
+              double v[8];
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
+                v[u] = Ks[cc & 0x7fffu];
+              }
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
+                if ((c > 0 || u > 0) && (cc & 0x8000u)) { *dst = sum; ++loc; dst = acc + loc; sum = 0.0; }
+                sum += v[u];
+              }
+            }
+            *dst = sum;
+          }
+          bar_sync(BAR_SCATTER, 128);                       // run totals stored, element store no longer read
+          bar_arrive(BAR_EMPTY + g, 256);
+          if (cont) atomicAdd(acc + loc0, carry[tid]);
+          asm volatile("cp.async.wait_group 0;" ::: "memory");
+          bar_sync(BAR_SCATTER, 128);
+          {
+            double* jb = kp.jac + tp.base[t];
+            for (int k0 = tid; k0 < E; k0 += 512) {
+              unsigned o[4]; double v[4];
+#pragma unroll
+              for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) { o[u] = s_off[k]; v[u] = acc[k]; } }
+#pragma unroll
+              for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) atomicAdd(jb + o[u], v[u]); }
+            }
+            for (int k = tid; k < R; k += 128) atomicAdd(kp.res + s_rows[k], acc[E + k]);
+          }
+          bar_sync(BAR_SCATTER, 128);                       // lists and accumulation array free again
+        }
+      }
+    } else {
+      // ================================= compute warpgroups =================================
+      asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MRH_WS_CREG));
+      const int g = wg - 1;
+      double* Ks = sm + g * KSZ;
+      int* rowbuf = rowbase + (g * 128 + tid) * 16;         // my next element's 8 LIDs | 8 node ids
+      auto element_of = [&](int64_t t) -> int { const int64_t e0 = t * 128 + tid; return (t < tp.ntiles && e0 < kp.nwork) ? tp.perm[e0] : -1; };
+      auto fetch_rows = [&](int e) {
+        if (e < 0) return;
+        cp_async16(rowbuf, kp.lids + (int64_t)e * 8); cp_async16(rowbuf + 4, kp.lids + (int64_t)e * 8 + 4);
+        cp_async16(rowbuf + 8, kp.e2n + (int64_t)e * 8); cp_async16(rowbuf + 12, kp.e2n + (int64_t)e * 8 + 4);
+      };
+      const int64_t tfirst = 2 * (int64_t)blockIdx.x + g;
+      int e_cur = element_of(tfirst), e_next = element_of(tfirst + tstep), e_next2 = element_of(tfirst + 2 * tstep);
+      double X[8][3], us[8], ud[8];
+      {
+        int lid[8];
+        if (e_cur >= 0) gather(kp, kp.lids + (int64_t)e_cur * 8, kp.e2n + (int64_t)e_cur * 8, lid, X, us, ud);
+      }
+      fetch_rows(e_next);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      bool first = true;
+      for (int64_t t = tfirst; t < tp.ntiles; t += tstep) {
+        double r[8], K[NK];
+        if (e_cur >= 0) work(kp, X, us, ud, nullptr, 0, r, K);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");             // my rows of the next tile
+        if (e_next >= 0) {
+          int lid[8];
+          gather(kp, rowbuf, rowbuf + 8, lid, X, us, ud);                // in flight while K is parked
+        }
+        const int e_next3 = element_of(t + 3 * tstep);
+        if (!first) bar_sync(BAR_EMPTY + g, 256);                        // the scatter group has consumed my previous tile
+        first = false;
+        if (e_cur >= 0) {
+#pragma unroll
+          for (int k = 0; k < NK; ++k) Ks[k * 128 + tid] = K[k];
+#pragma unroll
+          for (int s = 0; s < 8; ++s) Ks[(NK + s) * 128 + tid] = -r[s];
+        }
+        bar_arrive(BAR_FULL + g, 256);
+        fetch_rows(e_next2);                                             // rowbuf was consumed by the gather above
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        e_cur = e_next; e_next = e_next2; e_next2 = e_next3;
+      }
+      if (!first) bar_sync(BAR_EMPTY + g, 256);                          // pairs with the scatter group's last arrive
+    }
+  }
+#endif  // MRH_WS_CREG
 #endif
 };
 

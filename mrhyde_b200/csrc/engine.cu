@@ -37,7 +37,7 @@ struct DevBuf {
 struct TabDev { DevBuf<double> B, G, VB, VG, W; };
 
 struct DeviceImpl {
-  int device = 0, num_sms = 148;
+  int device = 0, num_sms = 148, max_smem_optin = 48 * 1024;
   DevBuf<double> nodes; DevBuf<int> e2n, lids, pat_id, dbc, dbc_diag_dummy;
   DevBuf<uint8_t> fixed; DevBuf<int64_t> rowptr, dbc_slots; DevBuf<int> colind; DevBuf<uint16_t> pat;
   DevBuf<Instr> code; DevBuf<double> cpool;

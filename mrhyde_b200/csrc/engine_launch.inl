@@ -138,7 +138,23 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
       const size_t acc_bytes = !tiled ? 0 : adv ? ThermalHexQ1<false, true, true>::tiled_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r)
                                                 : ThermalHexQ1<false, false, true>::tiled_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r);
       D.last_path = jk ? (tiled ? "nvrtc-specialised+tiled" : "nvrtc-specialised") : (tiled ? "specialised+tiled" : "specialised");
-      if (jk) {
+      // warp-specialised variant of the tiled kernel (384 threads, one CTA per SM) when its shared memory fits
+      const size_t ws_bytes = !tiled ? 0 : adv ? ThermalHexQ1<false, true, true>::ws_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r)
+                                               : ThermalHexQ1<false, false, true>::ws_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r);
+      const bool ws = tiled && jk && jk->fn_ws && !(H.cfg.flags & 8) && ws_bytes <= (size_t)D.max_smem_optin;
+      if (ws) {
+        JitApi& api = JitApi::get();
+        if (jk->ws_smem_set != ws_bytes) {
+          if (api.FuncSetAttribute(jk->fn_ws, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)ws_bytes) != CUDA_SUCCESS)
+            throw std::runtime_error("CUDA error: cuFuncSetAttribute(shared memory) failed");
+          jk->ws_smem_set = ws_bytes;
+        }
+        D.last_path = "nvrtc-specialised+tiled-ws";
+        const unsigned grid = (unsigned)std::min<int64_t>((D.tiles->ntiles + 1) / 2, (int64_t)D.num_sms);
+        void* args[] = {(void*)&kp};
+        if (api.LaunchKernel(jk->fn_ws, grid, 1, 1, 384, 1, 1, (unsigned)ws_bytes, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+          throw std::runtime_error("CUDA error: cuLaunchKernel failed for the warp-specialised NVRTC kernel");
+      } else if (jk) {
         const int64_t nblk = (kp.nwork + 127) / 128;
         unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * jk->blocks_per_sm * 4);
         if (tiled) {
@@ -218,6 +234,7 @@ static int backend_create(mrh_engine* h) {
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, D->device) != cudaSuccess) { delete D; h->err = "cudaGetDeviceProperties failed"; return MRH_ECUDA; }
   D->num_sms = prop.multiProcessorCount;
+  D->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
   h->impl = D;
   return MRH_OK;
 }

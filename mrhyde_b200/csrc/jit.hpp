@@ -143,7 +143,7 @@ inline std::string jit_function_source(const std::string& name, const Prog& pr, 
 
 // One NVRTC-compiled module holding the specialised thermal kernel for one (TRANSIENT, ADV, JAC) variant.
 struct JitKernel {
-  CUmodule mod = nullptr; CUfunction fn = nullptr; int blocks_per_sm = 1, tiled_blocks_per_sm = 1; size_t smem_set = 0; std::string source, log;
+  CUmodule mod = nullptr; CUfunction fn = nullptr, fn_ws = nullptr; size_t ws_smem_set = 0; int blocks_per_sm = 1, tiled_blocks_per_sm = 1; size_t smem_set = 0; std::string source, log;
 };
 
 class JitCache {
@@ -171,6 +171,10 @@ class JitCache {
         (jac ? "  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, dsm); return; }\n" : "") +
         "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
         "    Kern::element(kp, e, nullptr, 0);\n}\n";
+    if (jac)          // warp-specialised variant: 384 threads, one CTA per SM (assemble_fast.h tiled_ws)
+      K.source += std::string("extern \"C\" __global__ void __launch_bounds__(384, 1) mrh_jit_thermal_hex_q1_ws(const __grid_constant__ mrh::KParams kp) {\n") +
+          "  typedef mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", true, mrh::JitCoefs> Kern;\n"
+          "  extern __shared__ double dsm[];\n  Kern::tiled_ws(kp, dsm);\n}\n";
     std::vector<const char*> hdr_src, hdr_name;
     for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
     nvrtcProgram prog;
@@ -179,8 +183,11 @@ class JitCache {
     if (const char* ev = getenv("MRH_JIT_MINB")) minb = std::string("-DMRH_JIT_MINB=") + ev;          // tuning experiments
     std::string extra = "-DMRH_JIT_EXTRA=0";
     if (const char* ev = getenv("MRH_JIT_DEFINE")) extra = std::string("-D") + ev;                    // tuning experiments
-    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", minb.c_str(), extra.c_str()};
-    const nvrtcResult rc = api.CompileProgram(prog, 6, opts);
+    std::string creg = "-DMRH_WS_CREG=232", sreg = "-DMRH_WS_SREG=40";                              // 256 * CREG + 128 * SREG <= 384 * 168
+    if (const char* ev = getenv("MRH_WS_CREG")) creg = std::string("-DMRH_WS_CREG=") + ev;
+    if (const char* ev = getenv("MRH_WS_SREG")) sreg = std::string("-DMRH_WS_SREG=") + ev;
+    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", minb.c_str(), extra.c_str(), creg.c_str(), sreg.c_str()};
+    const nvrtcResult rc = api.CompileProgram(prog, 8, opts);
     size_t ls = 0; api.GetProgramLogSize(prog, &ls);
     if (ls > 1) { K.log.resize(ls); api.GetProgramLog(prog, &K.log[0]); }
     if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + K.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }
@@ -191,6 +198,7 @@ class JitCache {
     if (api.ModuleLoadData(&K.mod, cubin.data()) != CUDA_SUCCESS) { last_error = "cuModuleLoadData failed"; K.mod = nullptr; return nullptr; }
     if (api.ModuleGetFunction(&K.fn, K.mod, "mrh_jit_thermal_hex_q1") != CUDA_SUCCESS) { last_error = "kernel symbol not found"; K.fn = nullptr; return nullptr; }
     if (api.OccupancyMaxActiveBlocks(&K.blocks_per_sm, K.fn, 128, 0) != CUDA_SUCCESS || K.blocks_per_sm < 1) K.blocks_per_sm = 1;
+    if (!jac || api.ModuleGetFunction(&K.fn_ws, K.mod, "mrh_jit_thermal_hex_q1_ws") != CUDA_SUCCESS) K.fn_ws = nullptr;
     return &K;
   }
 

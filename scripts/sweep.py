@@ -7,11 +7,11 @@ import problems
 from mrhyde_b200 import Engine
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
-variants = [dict(no_tiles=False, minb="2", define="MRH_JIT_EXTRA=0"), dict(no_tiles=False, minb="2", define="MRH_DEBUG_SKIP_SCATTER=1"), dict(no_tiles=True, minb="2", define="MRH_JIT_EXTRA=0")]
+variants = [dict(no_ws=False, creg="232", sreg="40"), dict(no_ws=False, creg="240", sreg="24")]
 dev = torch.device("cuda", 0)
 for v in variants:
-    os.environ["MRH_JIT_MINB"] = v["minb"]; os.environ["MRH_JIT_DEFINE"] = v["define"]
-    e = Engine.from_problem(problems.config_c2(n), device=0, no_tiles=v["no_tiles"])
+    os.environ["MRH_WS_CREG"] = v["creg"]; os.environ["MRH_WS_SREG"] = v["sreg"]
+    e = Engine.from_problem(problems.config_c2(n), device=0, no_ws=v["no_ws"])
     s = e.sizes()
     xyz, var = e.dof_coords()
     u = torch.from_numpy(problems.synthetic_state(xyz, var)).to(dev)

@@ -31,19 +31,20 @@ def test_cuda_generic_kernel_on_specialised_cases(lib, name, p, kw):
 
 @pytest.mark.parametrize("name,p,kw", [c for c in CASES if c[1]["physics"] == "thermal" and c[1]["mesh"]["dim"] == 3],
                          ids=lambda v: v if isinstance(v, str) else "")
-@pytest.mark.parametrize("no_jit,no_tiles", [(True, False), (False, True), (True, True)])
-def test_cuda_specialised_kernel_variants(lib, name, p, kw, no_jit, no_tiles):
-    """the specialised kernel without the NVRTC step (bytecode interpreter inside the kernel) and / or with the
-    direct instead of the tile-staged scatter"""
-    r = U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles)
+@pytest.mark.parametrize("no_jit,no_tiles,no_ws", [(True, False, False), (False, True, False), (True, True, False), (False, False, True)])
+def test_cuda_specialised_kernel_variants(lib, name, p, kw, no_jit, no_tiles, no_ws):
+    """the specialised kernel without the NVRTC step (bytecode interpreter inside the kernel), with the direct
+    instead of the tile-staged scatter, and the tile-staged scatter without warp specialisation"""
+    r = U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws)
     if r["path"] != "generic":          # cases with state-dependent coefficients stay on the generic kernel
         assert ("nvrtc" in r["path"]) == (not no_jit) and ("tiled" in r["path"]) == (not no_tiles), r
-    U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles, jacobian=False)
+        assert r["path"].endswith("-ws") == (not no_jit and not no_tiles and not no_ws), r
+    U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws, jacobian=False)
 
 
-def test_default_path_is_nvrtc_and_tiled(lib):
+def test_default_path_is_nvrtc_tiled_warp_specialised(lib):
     r = U.check_case(problems.config_c2(6), {}, lib, on_gpu=True)
-    assert r["path"] == "nvrtc-specialised+tiled", r
+    assert r["path"] == "nvrtc-specialised+tiled-ws", r
 
 
 @pytest.mark.parametrize("n", [(5, 3, 7), (8, 4, 4), (17, 9, 6)])
@@ -52,6 +53,7 @@ def test_tiled_scatter_on_ragged_meshes(lib, n):
     p = problems.config_c2(4)
     p["mesh"]["NX"], p["mesh"]["NY"], p["mesh"]["NZ"] = n
     U.check_case(p, {}, lib, on_gpu=True)
+    U.check_case(p, {}, lib, on_gpu=True, no_ws=True)
 
 
 def test_mid_size_c2_against_oracle(lib):
