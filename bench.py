@@ -200,6 +200,12 @@ def run_gpu(args):
     ms_step = t.item() / K
     value = world * s["nelem"] / (ms_step * 1e-3)
 
+    if args.kernel_only:
+        if rank == 0:
+            print(json.dumps({"kernel_only": True, "ms_per_step": ms_step, "value": value, "volume_kernel_ms": float(np.mean(vol_ms)), "path": e.kernel_path()}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
     # ---- end to end through the host-buffer entry point: pinned u in, res + Jacobian values out, every step --
     Ke = max(1, min(K, 5))
     hu = torch.from_numpy(u_host).pin_memory()
@@ -265,6 +271,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--n", type=int, default=256, help="elements per direction per GPU")
     ap.add_argument("--impl", default="b200")
+    ap.add_argument("--kernel-only", action="store_true", help="profiling aid: skip the e2e and cpu_baseline legs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

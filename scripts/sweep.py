@@ -7,7 +7,7 @@ import problems
 from mrhyde_b200 import Engine
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
-variants = [dict(no_ws=False, creg="232", sreg="40"), dict(no_ws=False, creg="240", sreg="24")]
+variants = [dict(no_ws=False, creg="232", sreg="40")]
 dev = torch.device("cuda", 0)
 for v in variants:
     os.environ["MRH_WS_CREG"] = v["creg"]; os.environ["MRH_WS_SREG"] = v["sreg"]

@@ -62,14 +62,17 @@ def test_mid_size_c2_against_oracle(lib):
     assert r["launches"] == 2          # one volume kernel + the DBC diagonal kernel
 
 
-def test_large_mesh_properties(lib):
-    """Size-independent properties at a size the oracle does not reach in seconds (96^3 thermal Q1):
+@pytest.mark.parametrize("n", [96, 256])
+def test_large_mesh_properties(lib, n):
+    """Size-independent properties at sizes the oracle does not reach in seconds (thermal Q1 at 96^3 and at
+    BASELINE.json's full 256^3):
     Jacobian rows of non-fixed interior DOFs sum to ~0 (constants are in the Laplacian's kernel), J is symmetric in
     its action (x.Jy == y.Jx on free DOFs), res(u) = -(J u - b) is affine in u (linearity), and repeated assembly
-    accumulates exactly twice the values up to atomics ordering."""
+    accumulates exactly twice the values up to atomics ordering; the stencil of an interior row equals the stencil
+    of the oracle-checked 24^3 mesh scaled by the mesh-width ratio (uniform bricks, constant diffusion)."""
     import torch
     from mrhyde_b200 import Engine
-    p = problems.config_c2(96)
+    p = problems.config_c2(n)
     e = Engine.from_problem(p, lib=lib)
     s = e.sizes()
     rp, ci = e.crs()
@@ -105,6 +108,24 @@ def test_large_mesh_properties(lib):
                                        size=(s["nlocal"], s["nlocal"])) @ ones)
     assert torch.allclose(rowsum2[interior], 2 * rowsum[interior], atol=1e-9)
     assert s["npatterns"] >= 1 and s["npatterns"] < 4096
+    # cross-size check against the mesh size that is compared with the oracle entry by entry
+    def centre_row(eng, m, values):
+        sz = eng.sizes(); rp_, ci_ = eng.crs(); xyz_, _ = eng.dof_coords()
+        c = int(np.argmin(np.abs(xyz_ - 0.5).sum(axis=1)))          # the DOF at the centre of the unit cube
+        seg = slice(int(rp_[c]), int(rp_[c + 1]))
+        cols = ci_[seg]
+        order = np.lexsort((xyz_[cols, 0], xyz_[cols, 1], xyz_[cols, 2]))      # geometric order of the 27 neighbours
+        return values[seg].cpu().numpy()[order]
+    small = Engine.from_problem(problems.config_c2(24), lib=lib)
+    ss = small.sizes(); sxyz, svar = small.dof_coords()
+    su = torch.from_numpy(problems.synthetic_state(sxyz, svar)).to(dev)
+    sres = torch.zeros(ss["nlocal"], dtype=torch.float64, device=dev); sjac = torch.zeros(ss["nnz"], dtype=torch.float64, device=dev)
+    small.assemble_jacres(su, sres, sjac)
+    torch.cuda.synchronize()
+    big_row = 0.5 * centre_row(e, n, jac)                              # jac holds two accumulated assemblies
+    small_row = centre_row(small, 24, sjac)
+    assert big_row.shape == small_row.shape == (27,)
+    assert np.abs(big_row - small_row * (24.0 / n)).max() < 1e-12 * np.abs(big_row).max()
 
 
 def test_host_buffer_entry_point(lib):
