@@ -235,6 +235,14 @@ def run_gpu(args):
         ach_gbs = BYTES_PER_ELEM * s["nelem"] / vk / 1e9
         ach_tf = FLOPS_PER_ELEM * s["nelem"] / vk / 1e12
         cpu_rate, cpu_sps = cpu_port_rate(64, 1, 1, 0)
+        traffic, traffic_src = None, None
+        try:      # DRAM bytes of one launch of the dominant kernel from the committed ncu --set full capture of this command
+            prof = json.load(open(os.path.join(ROOT, "profiles", "r1_ws_thermal_n256_ncu_summary.json")))
+            if n == 256 and world == 1 and e.kernel_path() == "nvrtc-specialised+tiled-ws":
+                traffic = prof["derived"]["dram_bytes_per_launch"]
+                traffic_src = "profiles/r1_ws_thermal_n256_ncu_summary.json (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+        except Exception:
+            pass
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -244,7 +252,7 @@ def run_gpu(args):
                        "l2": "inputs+outputs (4.6 GB/step) exceed the 126 MB L2; no flush needed",
                        "timing": "CUDA events on the launch stream, K steps, max over ranks", "setup_s": round(t_setup, 1)},
             "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
-                         "traffic": None, "peak_source": "MEASURED_PEAKS.json (of measured)" if pk else "fallback 6650 (of fallback)",
+                         "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_src, "peak_source": "MEASURED_PEAKS.json (of measured)" if pk else "fallback 6650 (of fallback)",
                          "kernel": "thermal Q1 hex specialised kernel (" + e.kernel_path() + ")", "kernel_ms": vk * 1e3,
                          "bytes_per_elem": BYTES_PER_ELEM, "binding_roof": "fp64 (see roofline_fp64)"},
             "roofline_fp64": {"bound": "fp64", "achieved": ach_tf, "peak": dfma.value, "unit": "TFLOP/s",

@@ -314,7 +314,7 @@ struct ThermalHexQ1 {
     int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
     if (tid == 0) Ks[NE * 128] = 0.0;                     // masked contributions read this cell
     const int64_t tstep = gridDim.x;
-    auto element_of = [&](int64_t t) -> int { const int64_t e0 = t * 128 + tid; return (t < tp.ntiles && e0 < kp.nwork) ? tp.perm[e0] : -1; };
+    auto element_of = [&](int64_t t) -> int { const int64_t e0 = t * 128 + tid; return (t < tp.tile_end && e0 < kp.nwork) ? tp.perm[e0] : -1; };
     auto fetch_rows = [&](int e) {
       if (e < 0) return;
       cp_async16(rowbuf, kp.lids + (int64_t)e * 8); cp_async16(rowbuf + 4, kp.lids + (int64_t)e * 8 + 4);
@@ -322,7 +322,8 @@ struct ThermalHexQ1 {
     };
     // software pipeline over the CTA's tiles: while tile t is scattered, the gather loads of tile t + 1 are in
     // flight and the LID / node rows of tile t + 2 are being copied into rowbuf
-    int e_cur = element_of(blockIdx.x), e_next = element_of(blockIdx.x + tstep), e_next2 = element_of(blockIdx.x + 2 * tstep);
+    const int64_t tfirst = tp.tile_begin + blockIdx.x;
+    int e_cur = element_of(tfirst), e_next = element_of(tfirst + tstep), e_next2 = element_of(tfirst + 2 * tstep);
     double X[8][3], us[8], ud[8];
     {
       int lid[8];
@@ -330,7 +331,7 @@ struct ThermalHexQ1 {
     }
     fetch_rows(e_next);
     asm volatile("cp.async.commit_group;" ::: "memory");
-    for (int64_t t = blockIdx.x; t < tp.ntiles; t += tstep) {
+    for (int64_t t = tfirst; t < tp.tile_end; t += tstep) {
       const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
       const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
       for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + eb + k);
@@ -441,11 +442,11 @@ struct ThermalHexQ1 {
       // ================================= scatter warpgroup =================================
       asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MRH_WS_SREG));
       if (tid < 2) sm[tid * KSZ + NE * 128] = 0.0;          // masked contributions read these cells
-      for (int64_t t0 = 2 * (int64_t)blockIdx.x; t0 < tp.ntiles; t0 += tstep) {
+      for (int64_t t0 = tp.tile_begin + 2 * (int64_t)blockIdx.x; t0 < tp.tile_end; t0 += tstep) {
 #pragma unroll 1
         for (int g = 0; g < 2; ++g) {
           const int64_t t = t0 + g;
-          if (t >= tp.ntiles) break;
+          if (t >= tp.tile_end) break;
           const double* Ks = sm + g * KSZ;
           const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
           const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
@@ -506,13 +507,13 @@ struct ThermalHexQ1 {
       const int g = wg - 1;
       double* Ks = sm + g * KSZ;
       int* rowbuf = rowbase + (g * 128 + tid) * 16;         // my next element's 8 LIDs | 8 node ids
-      auto element_of = [&](int64_t t) -> int { const int64_t e0 = t * 128 + tid; return (t < tp.ntiles && e0 < kp.nwork) ? tp.perm[e0] : -1; };
+      auto element_of = [&](int64_t t) -> int { const int64_t e0 = t * 128 + tid; return (t < tp.tile_end && e0 < kp.nwork) ? tp.perm[e0] : -1; };
       auto fetch_rows = [&](int e) {
         if (e < 0) return;
         cp_async16(rowbuf, kp.lids + (int64_t)e * 8); cp_async16(rowbuf + 4, kp.lids + (int64_t)e * 8 + 4);
         cp_async16(rowbuf + 8, kp.e2n + (int64_t)e * 8); cp_async16(rowbuf + 12, kp.e2n + (int64_t)e * 8 + 4);
       };
-      const int64_t tfirst = 2 * (int64_t)blockIdx.x + g;
+      const int64_t tfirst = tp.tile_begin + 2 * (int64_t)blockIdx.x + g;
       int e_cur = element_of(tfirst), e_next = element_of(tfirst + tstep), e_next2 = element_of(tfirst + 2 * tstep);
       double X[8][3], us[8], ud[8];
       {
@@ -522,7 +523,7 @@ struct ThermalHexQ1 {
       fetch_rows(e_next);
       asm volatile("cp.async.commit_group;" ::: "memory");
       bool first = true;
-      for (int64_t t = tfirst; t < tp.ntiles; t += tstep) {
+      for (int64_t t = tfirst; t < tp.tile_end; t += tstep) {
         double r[8], K[NK];
         if (e_cur >= 0) work(kp, X, us, ud, nullptr, 0, r, K);
         asm volatile("cp.async.wait_group 0;" ::: "memory");             // my rows of the next tile

@@ -53,6 +53,11 @@ struct DeviceImpl {
   JitCache jit;
   struct TileDev* tiles = nullptr;     // engine_tiles.inl
   bool jit_used = false;
+  // chunked copy-out of the host-buffer entry point (engine_launch.inl build_chunk_plan)
+  bool chunk_ready = false;
+  std::vector<int64_t> chunk_tile_end, chunk_val_end;
+  std::vector<cudaEvent_t> chunk_ev;
+  cudaStream_t copy_stream = nullptr;
   const char* last_path = "none";
 };
 

@@ -40,7 +40,7 @@ void device_finalize(mrh_engine* h) {
   EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
   CUDA_CK(cudaSetDevice(D.device));
   H.finalizeHost();
-  D.ready = false;
+  D.ready = false; D.chunk_ready = false;
   D.nodes.upload(H.mesh.nodes); D.e2n.upload(H.mesh.elem2node); D.lids.upload(H.dofs.lids); D.fixed.upload(H.isFixed);
   D.rowptr.upload(H.crs.rowptr); D.colind.upload(H.crs.colind);
   D.code.upload(H.ec.code); D.cpool.upload(H.ec.cpool);
@@ -115,7 +115,46 @@ void launch_thermal_tiled(const DeviceImpl& D, const KParams& kp, size_t acc_byt
   }
 }
 
-int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac) {
+// Chunks of consecutive tiles and, for each, the end of the CRS value prefix whose rows no later chunk touches
+// (host, once per finalize).  On first-encounter numberings rows complete roughly in element order, so the prefix
+// grows with every chunk; on other numberings the plan degenerates to one copy at the end.
+void build_chunk_plan(EngineHost& H, DeviceImpl& D) {
+  if (D.chunk_ready) return;
+  D.chunk_ready = true;
+  D.chunk_tile_end.clear(); D.chunk_val_end.clear();
+  if (!D.tiles || !D.tiles->ok) return;
+  const int64_t nt = D.tiles->ntiles;
+  const int64_t nchunk = std::max<int64_t>(1, std::min<int64_t>(16, nt / (8 * (int64_t)D.num_sms)));
+  if (nchunk < 2) return;
+  const std::vector<int> perm = H.tileOrder();
+  const int64_t nrows = H.crs.nrows, nelem = H.mesh.nelem;
+  std::vector<int> last((size_t)nrows, 0);
+  for (int64_t c = 0; c < nchunk; ++c) {
+    const int64_t tb = nt * c / nchunk, te = nt * (c + 1) / nchunk;
+    D.chunk_tile_end.push_back(te);
+    for (int64_t k = tb * 128; k < std::min<int64_t>(te * 128, nelem); ++k) {
+      const int* l = H.dofs.lids.data() + (size_t)perm[k] * 8;
+      for (int i = 0; i < 8; ++i) last[l[i]] = (int)c;
+    }
+  }
+  // rows below R_c are complete after chunk c: first row whose running maximum of `last` exceeds c
+  int64_t r = 0; int run = 0;
+  for (int64_t c = 0; c < nchunk; ++c) {
+    while (r < nrows && std::max(run, last[r]) <= c) { run = std::max(run, last[r]); ++r; }
+    D.chunk_val_end.push_back(c + 1 == nchunk ? (int64_t)H.crs.colind.size() : H.crs.rowptr[r]);
+  }
+  if (!D.copy_stream) CUDA_CK(cudaStreamCreateWithFlags(&D.copy_stream, cudaStreamNonBlocking));
+  while ((int64_t)D.chunk_ev.size() < nchunk) { cudaEvent_t e; CUDA_CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); D.chunk_ev.push_back(e); }
+}
+
+// Copy-out plan of the host-buffer entry point: the volume launch is cut into chunks of consecutive tiles and the
+// CRS values of all rows completed by chunk k are copied to the host while later chunks are computed.
+struct HostCopy {
+  double* jac_host = nullptr;
+  bool used = false;
+};
+
+int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac, HostCopy* hc = nullptr) {
   EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
   if (!D.ready) throw std::runtime_error("mrh_finalize has not been called");
   CUDA_CK(cudaSetDevice(D.device));
@@ -150,10 +189,33 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
           jk->ws_smem_set = ws_bytes;
         }
         D.last_path = "nvrtc-specialised+tiled-ws";
-        const unsigned grid = (unsigned)std::min<int64_t>((D.tiles->ntiles + 1) / 2, (int64_t)D.num_sms);
-        void* args[] = {(void*)&kp};
-        if (api.LaunchKernel(jk->fn_ws, grid, 1, 1, 384, 1, 1, (unsigned)ws_bytes, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
-          throw std::runtime_error("CUDA error: cuLaunchKernel failed for the warp-specialised NVRTC kernel");
+        bool any_side = false;
+        for (auto& sl : H.side_launches) any_side = any_side || sl.active;
+        const bool chunked = hc && !any_side && !H.cfg.fix_zero_rows && D.chunk_tile_end.size() > 1;
+        const size_t nchunk = chunked ? D.chunk_tile_end.size() : 1;
+        if (chunked) {            // fixed rows are never scattered into: their unit diagonal can be written first
+          const int64_t nd = (int64_t)H.dbc_dofs.size();
+          if (nd > 0) { dbc_diag_kernel<<<blocks_for(nd, 256), 256, 0, stream>>>(D.dbc_slots.p, nd, jac); CUDA_CK(cudaGetLastError()); D.launches++; }
+          hc->used = true;
+        }
+        int64_t tb = 0, vb = 0;
+        for (size_t c = 0; c < nchunk; ++c) {
+          const int64_t te = chunked ? D.chunk_tile_end[c] : D.tiles->ntiles;
+          kp.tile.tile_begin = tb; kp.tile.tile_end = te;
+          const unsigned grid = (unsigned)std::min<int64_t>((te - tb + 1) / 2, (int64_t)D.num_sms);
+          void* args[] = {(void*)&kp};
+          if (grid > 0 && api.LaunchKernel(jk->fn_ws, grid, 1, 1, 384, 1, 1, (unsigned)ws_bytes, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+            throw std::runtime_error("CUDA error: cuLaunchKernel failed for the warp-specialised NVRTC kernel");
+          if (chunked) {
+            const int64_t ve = D.chunk_val_end[c];
+            CUDA_CK(cudaEventRecord(D.chunk_ev[c], stream));
+            CUDA_CK(cudaStreamWaitEvent(D.copy_stream, D.chunk_ev[c], 0));
+            if (ve > vb) CUDA_CK(cudaMemcpyAsync(hc->jac_host + vb, jac + vb, (size_t)(ve - vb) * sizeof(double), cudaMemcpyDeviceToHost, D.copy_stream));
+            vb = ve;
+            if (c > 0) D.launches++;
+          }
+          tb = te;
+        }
       } else if (jk) {
         const int64_t nblk = (kp.nwork + 127) / 128;
         unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * jk->blocks_per_sm * 4);
@@ -184,7 +246,7 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
     if (side < 0) CUDA_CK(cudaEventRecord(D.ev1, stream));
     D.launches++;
   }
-  if (jac) {
+  if (jac && !(hc && hc->used)) {
     const int64_t nd = (int64_t)H.dbc_dofs.size();
     if (nd > 0) { dbc_diag_kernel<<<blocks_for(nd, 256), 256, 0, stream>>>(D.dbc_slots.p, nd, jac); CUDA_CK(cudaGetLastError()); D.launches++; }
     if (H.cfg.fix_zero_rows) {
@@ -243,6 +305,8 @@ static void backend_destroy(mrh_engine* h) {
   if (!D) return;
   cudaSetDevice(D->device);
   if (D->ev0) { cudaEventDestroy(D->ev0); cudaEventDestroy(D->ev1); }
+  for (cudaEvent_t e : D->chunk_ev) cudaEventDestroy(e);
+  if (D->copy_stream) cudaStreamDestroy(D->copy_stream);
   delete D->tiles;
   delete D;
 }
@@ -288,10 +352,13 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res
   CUDA_CK(cudaMemsetAsync(D.h_res.p, 0, nl * sizeof(double), s));
   CUDA_CK(cudaMemsetAsync(D.h_jac.p, 0, nnz * sizeof(double), s));
   mrh_state st = *st_host; st.u = D.h_u.p;
-  const int rc = device_assemble(h, &st, D.h_res.p, D.h_jac.p);
+  build_chunk_plan(H, D);
+  HostCopy hc; hc.jac_host = jac_host;
+  const int rc = device_assemble(h, &st, D.h_res.p, D.h_jac.p, &hc);
   CUDA_CK(cudaMemcpyAsync(res_host, D.h_res.p, nl * sizeof(double), cudaMemcpyDeviceToHost, s));
-  CUDA_CK(cudaMemcpyAsync(jac_host, D.h_jac.p, nnz * sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (!hc.used) CUDA_CK(cudaMemcpyAsync(jac_host, D.h_jac.p, nnz * sizeof(double), cudaMemcpyDeviceToHost, s));
   CUDA_CK(cudaStreamSynchronize(s));
+  if (hc.used) CUDA_CK(cudaStreamSynchronize(D.copy_stream));
   return rc;
   MRH_CATCH_CUDA(h)
 }

@@ -196,7 +196,7 @@ std::string build_tile_plan(const std::vector<int>& perm_host, int64_t nelem, co
 
 void fill_tile_params(const TileDev& T, TilePlan& tp) {
   tp.perm = T.perm.p; tp.eptr = T.eptr.p; tp.rptr = T.rptr.p; tp.base = T.base.p; tp.off = T.off.p; tp.rows = T.rows.p;
-  tp.clist = T.clist.p; tp.cbase = T.cbase.p; tp.cl_id = T.cl_id.p; tp.ntiles = T.ntiles; tp.max_acc = T.max_acc; tp.nk = T.nk; tp.max_e = T.max_e; tp.max_r = T.max_r;
+  tp.clist = T.clist.p; tp.cbase = T.cbase.p; tp.cl_id = T.cl_id.p; tp.ntiles = T.ntiles; tp.tile_begin = 0; tp.tile_end = T.ntiles; tp.max_acc = T.max_acc; tp.nk = T.nk; tp.max_e = T.max_e; tp.max_r = T.max_r;
 }
 
 }  // namespace

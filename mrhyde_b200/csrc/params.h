@@ -55,6 +55,7 @@ struct TilePlan {          // tile-staged scatter of the specialised kernels (bu
   const uint16_t* cbase;     // (nlist, 128) index in [slots | rows | masked] of the destination of thread t's first contribution
   const int* cl_id;          // (ntiles)  contribution list of each tile (lists are de-duplicated)
   int64_t ntiles;
+  int64_t tile_begin, tile_end; // tiles this launch covers (the host-buffer entry point assembles in chunks to overlap the copy-out)
   int max_acc;               // largest E_t + R_t: accumulation doubles per CTA (+1 cell for masked contributions)
   int nk;                    // 36 (symmetric element matrix) or 64: entry numbering the lists were built for
   int max_e, max_r;          // largest E_t, largest R_t (staged slot / row lists)

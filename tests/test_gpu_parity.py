@@ -141,3 +141,26 @@ def test_host_buffer_entry_point(lib):
     o = Oracle(U.oracle_problem(p))
     ores, ojac = o.assemble(u)
     assert U.rel_errors(res, ores)[0] < U.TOL and U.rel_errors(jac, ojac)[0] < U.TOL
+
+
+def test_host_buffer_entry_point_chunked_copy_out(lib):
+    """96^3 is large enough for the host-buffer entry point to assemble in chunks of tiles and copy completed CRS
+    rows out while later chunks run: the result must equal the device-buffer entry point's."""
+    import torch
+    from mrhyde_b200 import Engine
+    e = Engine.from_problem(problems.config_c2(96), lib=lib)
+    s = e.sizes()
+    xyz, var = e.dof_coords()
+    u = problems.synthetic_state(xyz, var)
+    hu = torch.from_numpy(u).pin_memory()
+    hres = torch.full((s["nlocal"],), 7.0, dtype=torch.float64).pin_memory()
+    hjac = torch.full((s["nnz"],), 7.0, dtype=torch.float64).pin_memory()
+    e.assemble_jacres_host(hu, hres, hjac)
+    n_host_launches = e.launch_count()
+    dev = torch.device("cuda:0")
+    res = torch.zeros(s["nlocal"], dtype=torch.float64, device=dev); jac = torch.zeros(s["nnz"], dtype=torch.float64, device=dev)
+    e.assemble_jacres(torch.from_numpy(u).to(dev), res, jac)
+    torch.cuda.synchronize()
+    assert n_host_launches > e.launch_count()        # several volume launches (chunks) against one
+    assert U.rel_errors(hres.numpy(), res.cpu().numpy())[0] < U.TOL
+    assert U.rel_errors(hjac.numpy(), jac.cpu().numpy())[0] < U.TOL
