@@ -63,6 +63,17 @@ struct ThermalHexQ1 {
   // stage: per-thread scratch for the coefficient values at the 8 points, element k of array m at
   // stage[(m*8+k)*stride] (shared memory, stride = blockDim.x, on the device).
   MRH_HDN static void element(const KParams& kp, int64_t e, double* stage, int stride) {
+#if defined(MRH_DEBUG_KSMEM_COMPUTE) && defined(__CUDA_ARCH__)     // tuning experiment: element computation only, K accumulated in shared memory
+    {
+      __shared__ double kbuf[NK * 128];
+      int lid[8]; double r[8], X[8][3], us[8], ud[8];
+      gather(kp, kp.lids + e * 8, kp.e2n + e * 8, lid, X, us, ud);
+      KSmem acc{kbuf + threadIdx.x};
+      work(kp, X, us, ud, stage, stride, r, acc);
+      kp.res[lid[0]] = r[0] + acc.get(0) + acc.get(NK - 1);
+      return;
+    }
+#endif
     int lid[8]; double r[8], K[NK];
     compute(kp, e, stage, stride, lid, r, K);
     scatter(kp, e, lid, r, K);
@@ -110,8 +121,18 @@ struct ThermalHexQ1 {
     }
   }
   // ---- geometry + point loop of one element: r = element residual, K = element matrix -----------------------
-  MRH_HDN static void work(const KParams& kp, const double (&X)[8][3], const double (&us)[8], const double (&ud)[8], double* stage, int stride,
+  // element-matrix accumulators: registers, or one column of an entry-major shared-memory array (stride 128)
+  struct KReg { static constexpr bool in_smem = false; double (&K)[NK]; MRH_HD double get(int k) const { return K[k]; } MRH_HD void set(int k, double v) { K[k] = v; } };
+  struct KSmem { static constexpr bool in_smem = true; double* p; MRH_HD double get(int k) const { return p[k * 128]; } MRH_HD void set(int k, double v) { p[k * 128] = v; } };
+  MRH_HDN static void work(const KParams& kp, double (&X)[8][3], double (&us)[8], const double (&ud)[8], double* stage, int stride,
                            double (&r)[8], double (&K)[NK]) {
+    KReg acc{K};
+    work(kp, X, us, ud, stage, stride, r, acc);
+  }
+  // X and us are overwritten by their monomial coefficients (see below)
+  template <class KA>
+  MRH_HDN static void work(const KParams& kp, double (&X)[8][3], double (&us)[8], const double (&ud)[8], double* stage, int stride,
+                           double (&r)[8], KA& K) {
     const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
 
     // ---- coefficients at the 8 points (vector interpreter), staged for the rolled point loop ------------
@@ -143,11 +164,40 @@ struct ThermalHexQ1 {
       if (ADV) { put(TH_BX); put(TH_BY); put(TH_BZ); }
     }
 
+    // ---- trilinear map and solution in monomial form --------------------------------------------------
+    // x(xi, eta, zeta) = sum_m C_m xi^i eta^j zeta^k, m = i + 2 j + 4 k: a three-stage butterfly over the vertex sign
+    // bits.  The Jacobian of the (general) trilinear map then costs 30 FP64 operations per point instead of 81
+    // and the reference gradient of u 9 instead of 24.
+    double (&C)[8][3] = X;
+    double (&A)[8] = us;
+    {
+      double v[4][8];
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+          for (int a = 0; a < 2; ++a) {
+            const int sv = vtx(a, b, c), m = a + 2 * b + 4 * c;
+            v[0][m] = X[sv][0]; v[1][m] = X[sv][1]; v[2][m] = X[sv][2]; v[3][m] = us[sv];
+          }
+#pragma unroll
+      for (int d = 0; d < 4; ++d) {
+#pragma unroll
+        for (int bit = 1; bit < 8; bit <<= 1)
+#pragma unroll
+          for (int m = 0; m < 8; ++m)
+            if (!(m & bit)) { const double lo = v[d][m], hi = v[d][m | bit]; v[d][m] = hi + lo; v[d][m | bit] = hi - lo; }
+      }
+#pragma unroll
+      for (int m = 0; m < 8; ++m) { C[m][0] = 0.125 * v[0][m]; C[m][1] = 0.125 * v[1][m]; C[m][2] = 0.125 * v[2][m]; A[m] = 0.125 * v[3][m]; }
+    }
+
     // ---- point loop (rolled: the body stays resident in the instruction cache) ------------------------
 #pragma unroll
     for (int s = 0; s < 8; ++s) r[s] = 0.0;
 #pragma unroll
-    for (int k = 0; k < NK; ++k) K[k] = 0.0;
+    for (int k = 0; k < NK; ++k) K.set(k, 0.0);
 
 #pragma unroll 1
     for (int q = 0; q < 8; ++q) {
@@ -159,20 +209,14 @@ struct ThermalHexQ1 {
       for (int a = 0; a < 2; ++a)
 #pragma unroll
         for (int b = 0; b < 2; ++b) { yz[a][b] = ly[a] * lz[b]; xz[a][b] = lx[a] * lz[b]; xy[a][b] = lx[a] * ly[b]; }
-      // J_ij = sum_s X_s,i dN_s/dxi_j written with edge differences (dN/dxi = +-1/2 * product of the other two)
+      // J_ij = d x_i / d xi_j of the trilinear map, from its monomial coefficients
+      const double xe = sx * sy, ez2 = sy * sz, xz2 = sx * sz, xez = xe * sz;
       double J[3][3];
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
-        double c0 = 0.0, c1 = 0.0, c2 = 0.0;
-#pragma unroll
-        for (int a = 0; a < 2; ++a)
-#pragma unroll
-          for (int b = 0; b < 2; ++b) {
-            c0 += yz[a][b] * (X[vtx(1, a, b)][i] - X[vtx(0, a, b)][i]);
-            c1 += xz[a][b] * (X[vtx(a, 1, b)][i] - X[vtx(a, 0, b)][i]);
-            c2 += xy[a][b] * (X[vtx(a, b, 1)][i] - X[vtx(a, b, 0)][i]);
-          }
-        J[i][0] = 0.5 * c0; J[i][1] = 0.5 * c1; J[i][2] = 0.5 * c2;
+        J[i][0] = C[1][i] + C[3][i] * sy + C[5][i] * sz + C[7][i] * ez2;
+        J[i][1] = C[2][i] + C[3][i] * sx + C[6][i] * sz + C[7][i] * xz2;
+        J[i][2] = C[4][i] + C[5][i] * sx + C[6][i] * sy + C[7][i] * xe;
       }
       double Ji[3][3];
       const double det = det_inv<3>(J, Ji);
@@ -187,8 +231,15 @@ struct ThermalHexQ1 {
         gx[s] = Ji[0][0] * d0 + Ji[1][0] * d1 + Ji[2][0] * d2;
         gy[s] = Ji[0][1] * d0 + Ji[1][1] * d1 + Ji[2][1] * d2;
         gz[s] = Ji[0][2] * d0 + Ji[1][2] * d1 + Ji[2][2] * d2;
-        ex += us[s] * gx[s]; ey += us[s] * gy[s]; ez += us[s] * gz[s];
         if (TRANSIENT) edot += ud[s] * Nq[s];
+      }
+      {
+        const double g0 = A[1] + A[3] * sy + A[5] * sz + A[7] * ez2;        // reference gradient of u
+        const double g1 = A[2] + A[3] * sx + A[6] * sz + A[7] * xz2;
+        const double g2 = A[4] + A[5] * sx + A[6] * sy + A[7] * xe;
+        ex = Ji[0][0] * g0 + Ji[1][0] * g1 + Ji[2][0] * g2;
+        ey = Ji[0][1] * g0 + Ji[1][1] * g1 + Ji[2][1] * g2;
+        ez = Ji[0][2] * g0 + Ji[1][2] * g1 + Ji[2][2] * g2;
       }
       double srcq, kapq, rcpq = 0.0, bxq = 0.0, byq = 0.0, bzq = 0.0;
       if constexpr (CF::staged) {
@@ -197,9 +248,11 @@ struct ThermalHexQ1 {
         if (TRANSIENT) rcpq = stage[(2 * 8 + q) * stride];
         if (ADV) { bxq = stage[((AB + 0) * 8 + q) * stride]; byq = stage[((AB + 1) * 8 + q) * stride]; bzq = stage[((AB + 2) * 8 + q) * stride]; }
       } else {
-        double x = 0.0, y = 0.0, z = 0.0;
+        double pt[3];
 #pragma unroll
-        for (int s = 0; s < 8; ++s) { x += X[s][0] * Nq[s]; y += X[s][1] * Nq[s]; z += X[s][2] * Nq[s]; }
+        for (int i = 0; i < 3; ++i)
+          pt[i] = C[0][i] + C[1][i] * sx + C[2][i] * sy + C[4][i] * sz + C[3][i] * xe + C[5][i] * xz2 + C[6][i] * ez2 + C[7][i] * xez;
+        const double x = pt[0], y = pt[1], z = pt[2];
         const double t = kp.tp.time;
         srcq = CF::source(x, y, z, t); kapq = CF::diff(x, y, z, t);
         if (TRANSIENT) rcpq = CF::rhocp(x, y, z, t);
@@ -215,27 +268,49 @@ struct ThermalHexQ1 {
       if (JAC) {
         const double kwa = kw * au;
         const double mw = TRANSIENT ? rcpq * at * w : 0.0;
+        // accumulators in shared memory are walked row by row with the next row's loads issued ahead of this row's
+        // arithmetic; the compiler barrier keeps it from hoisting all 36 loads (72 registers) at once
+        double knext[8];
+        if constexpr (KA::in_smem) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) knext[j] = K.get(ADV ? j : HexQ1::tri(0, j));
+        }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const double ax = kwa * gx[i], ay = kwa * gy[i], az = kwa * gz[i];
           const double mi = TRANSIENT ? mw * Nq[i] : 0.0;
+          double kcur[8];
+          if constexpr (KA::in_smem) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) kcur[j] = knext[j];
+            if (i < 7) {
+#pragma unroll
+              for (int j = (ADV ? 0 : i + 1); j < 8; ++j) knext[j] = K.get(ADV ? (i + 1) * 8 + j : HexQ1::tri(i + 1, j));
+            }
+          } else {
+#pragma unroll
+            for (int j = (ADV ? 0 : i); j < 8; ++j) kcur[j] = K.get(ADV ? i * 8 + j : HexQ1::tri(i, j));
+          }
           if (!ADV) {
 #pragma unroll
             for (int j = i; j < 8; ++j) {
-              double v = K[HexQ1::tri(i, j)] + ax * gx[j] + ay * gy[j] + az * gz[j];
+              double v = kcur[j] + ax * gx[j] + ay * gy[j] + az * gz[j];
               if (TRANSIENT) v += mi * Nq[j];
-              K[HexQ1::tri(i, j)] = v;
+              K.set(HexQ1::tri(i, j), v);
             }
           } else {
             const double ci = au * w * Nq[i];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              double v = K[i * 8 + j] + ax * gx[j] + ay * gy[j] + az * gz[j];
+              double v = kcur[j] + ax * gx[j] + ay * gy[j] + az * gz[j];
               v += ci * (bxq * gx[j] + byq * gy[j] + bzq * gz[j]);
               if (TRANSIENT) v += mi * Nq[j];
-              K[i * 8 + j] = v;
+              K.set(i * 8 + j, v);
             }
           }
+#if defined(__CUDA_ARCH__)
+          if constexpr (KA::in_smem) asm volatile("" ::: "memory");
+#endif
         }
       }
     }
@@ -417,10 +492,11 @@ struct ThermalHexQ1 {
   // barrier; warpgroup 0 (MRH_WS_SREG registers) does everything else for both streams: contribution-list run sums, carry
   // adds, RED flush, list copies.  The FP64 pipe therefore always sees two computing warps per scheduler instead of
   // alternating with the scatter phases of the same warps.
-  // dynamic shared memory: Ks[2][NE * 128 + 2] | acc[(max_acc + 2) & ~1] | carry[128] | rowbuf[2][128][16] int
+  // dynamic shared memory: Ks[WS_NBUF][NE * 128 + 2] | acc[(max_acc + 2) & ~1] | carry[128] | rowbuf[2][128][16] int
   //                        | off[max_e] uint32 | rows[max_r] int
+  static constexpr int WS_NBUF = 3;               // element stores shared by the two compute groups (see tiled_ws)
   __host__ __device__ static constexpr size_t ws_smem_bytes(int max_acc, int max_e, int max_r) {
-    return (2 * ((size_t)NE * 128 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 2 * 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+    return (WS_NBUF * ((size_t)NE * 128 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 2 * 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + 16;
   }
 #if defined(MRH_WS_CREG)
   __device__ __forceinline__ static void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
@@ -431,81 +507,89 @@ struct ThermalHexQ1 {
     const TilePlan& tp = kp.tile;
     const int wg = threadIdx.x >> 7, tid = threadIdx.x & 127;
     constexpr int KSZ = NE * 128 + 2;
-    double* acc = sm + 2 * KSZ;
+    double* acc = sm + WS_NBUF * KSZ;
     double* carry = acc + ((tp.max_acc + 2) & ~1);
     int* rowbase = reinterpret_cast<int*>(carry + 128);
     unsigned* s_off = reinterpret_cast<unsigned*>(rowbase + 2 * 128 * 16);
     int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
     const int64_t tstep = 2 * (int64_t)gridDim.x;
-    constexpr int BAR_FULL = 1, BAR_EMPTY = 3, BAR_SCATTER = 5;        // named barriers (0 is __syncthreads)
+    // The CTA's tiles in hand-over order: sequence number s = 2 i + g is tile i of compute group g; it lives in
+    // element store s % WS_NBUF.  Named barriers (0 is __syncthreads): FULL[b] compute -> scatter, EMPTY[b] back.
+    constexpr int BAR_FULL = 1, BAR_EMPTY = 1 + WS_NBUF, BAR_SCATTER = 1 + 2 * WS_NBUF;
+    auto tile_of = [&](int s) -> int64_t { return tp.tile_begin + 2 * (int64_t)blockIdx.x + (s & 1) + (int64_t)(s >> 1) * tstep; };
     if (wg == 0) {
       // ================================= scatter warpgroup =================================
       asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MRH_WS_SREG));
-      if (tid < 2) sm[tid * KSZ + NE * 128] = 0.0;          // masked contributions read these cells
-      for (int64_t t0 = tp.tile_begin + 2 * (int64_t)blockIdx.x; t0 < tp.tile_end; t0 += tstep) {
-#pragma unroll 1
-        for (int g = 0; g < 2; ++g) {
-          const int64_t t = t0 + g;
-          if (t >= tp.tile_end) break;
-          const double* Ks = sm + g * KSZ;
-          const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
-          const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
-          for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + eb + k);
-          for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + rb + k);
-          asm volatile("cp.async.commit_group;" ::: "memory");
-          const size_t cid = (size_t)tp.cl_id[t] * 128 + tid;
-          const uint4* cl = reinterpret_cast<const uint4*>(tp.clist + cid * 72);
-          uint4 wv = __ldg(cl);
-          const int loc0 = tp.cbase[cid];
-          const bool cont = (wv.x & 0x8000u) == 0;          // my first run started in the previous thread's chunk
-          bar_sync(BAR_FULL + g, 256);                      // element store of stream g complete
-          {
-            double sum = 0.0;
-            int loc = loc0;
-            double* dst = cont ? carry + tid : acc + loc;
+      if (tid < WS_NBUF) sm[tid * KSZ + NE * 128] = 0.0;    // masked contributions read these cells
+      struct TileMeta { int64_t eb, rb, base; int E, R, clid; };
+      auto load_meta = [&](int64_t t, TileMeta& m) {
+        if (t >= tp.tile_end) { m.E = m.R = 0; m.clid = 0; m.eb = m.rb = m.base = 0; return; }
+        m.eb = tp.eptr[t]; m.rb = tp.rptr[t]; m.base = tp.base[t];
+        m.E = (int)(tp.eptr[t + 1] - m.eb); m.R = (int)(tp.rptr[t + 1] - m.rb); m.clid = tp.cl_id[t];
+      };
+      TileMeta cur, nxt;
+      load_meta(tile_of(0), cur);
+      int b = 0;                                            // element store of sequence number s
+      for (int s = 0; tile_of(s) < tp.tile_end; ++s) {
+        const double* Ks = sm + b * KSZ;
+        const int E = cur.E, R = cur.R;
+        for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + cur.eb + k);
+        for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + cur.rb + k);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        const size_t cid = (size_t)cur.clid * 128 + tid;
+        const uint4* cl = reinterpret_cast<const uint4*>(tp.clist + cid * 72);
+        uint4 wv = __ldg(cl);
+        const int loc0 = tp.cbase[cid];
+        const bool cont = (wv.x & 0x8000u) == 0;            // my first run started in the previous thread's chunk
+        load_meta(tile_of(s + 1), nxt);                     // in flight during this tile's scatter
+        bar_sync(BAR_FULL + b, 256);                        // element store b complete
+        {
+          double sum = 0.0;
+          int loc = loc0;
+          double* dst = cont ? carry + tid : acc + loc;
 #pragma unroll
-            for (int c = 0; c < 9; ++c) {
-              const unsigned w[4] = {wv.x, wv.y, wv.z, wv.w};
-              if (c < 8) wv = __ldg(cl + c + 1);
-              double v[8];
+          for (int c = 0; c < 9; ++c) {
+            const unsigned w[4] = {wv.x, wv.y, wv.z, wv.w};
+            if (c < 8) wv = __ldg(cl + c + 1);
+            double v[8];
 #pragma unroll
-              for (int u = 0; u < 8; ++u) {
-                const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
-                v[u] = Ks[cc & 0x7fffu];
-              }
-#pragma unroll
-              for (int u = 0; u < 8; ++u) {
-                const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
-                if ((c > 0 || u > 0) && (cc & 0x8000u)) { *dst = sum; ++loc; dst = acc + loc; sum = 0.0; }
-                sum += v[u];
-              }
+            for (int u = 0; u < 8; ++u) {
+              const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
+              v[u] = Ks[cc & 0x7fffu];
             }
-            *dst = sum;
-          }
-          bar_sync(BAR_SCATTER, 128);                       // run totals stored, element store no longer read
-          bar_arrive(BAR_EMPTY + g, 256);
-          if (cont) atomicAdd(acc + loc0, carry[tid]);
-          asm volatile("cp.async.wait_group 0;" ::: "memory");
-          bar_sync(BAR_SCATTER, 128);
-          {
-            double* jb = kp.jac + tp.base[t];
-            for (int k0 = tid; k0 < E; k0 += 512) {
-              unsigned o[4]; double v[4];
 #pragma unroll
-              for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) { o[u] = s_off[k]; v[u] = acc[k]; } }
-#pragma unroll
-              for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) atomicAdd(jb + o[u], v[u]); }
+            for (int u = 0; u < 8; ++u) {
+              const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
+              if ((c > 0 || u > 0) && (cc & 0x8000u)) { *dst = sum; ++loc; dst = acc + loc; sum = 0.0; }
+              sum += v[u];
             }
-            for (int k = tid; k < R; k += 128) atomicAdd(kp.res + s_rows[k], acc[E + k]);
           }
-          bar_sync(BAR_SCATTER, 128);                       // lists and accumulation array free again
+          *dst = sum;
         }
+        bar_sync(BAR_SCATTER, 128);                         // run totals stored, element store no longer read
+        bar_arrive(BAR_EMPTY + b, 256);
+        if (cont) atomicAdd(acc + loc0, carry[tid]);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        bar_sync(BAR_SCATTER, 128);
+        {
+          double* jb = kp.jac + cur.base;
+          for (int k0 = tid; k0 < E; k0 += 512) {
+            unsigned o[4]; double v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) { o[u] = s_off[k]; v[u] = acc[k]; } }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) atomicAdd(jb + o[u], v[u]); }
+          }
+          for (int k = tid; k < R; k += 128) atomicAdd(kp.res + s_rows[k], acc[E + k]);
+        }
+        bar_sync(BAR_SCATTER, 128);                         // lists and accumulation array free again
+        cur = nxt;
+        b = (b + 1 == WS_NBUF) ? 0 : b + 1;
       }
     } else {
       // ================================= compute warpgroups =================================
       asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MRH_WS_CREG));
       const int g = wg - 1;
-      double* Ks = sm + g * KSZ;
       int* rowbuf = rowbase + (g * 128 + tid) * 16;         // my next element's 8 LIDs | 8 node ids
       auto element_of = [&](int64_t t) -> int { const int64_t e0 = t * 128 + tid; return (t < tp.tile_end && e0 < kp.nwork) ? tp.perm[e0] : -1; };
       auto fetch_rows = [&](int e) {
@@ -513,7 +597,9 @@ struct ThermalHexQ1 {
         cp_async16(rowbuf, kp.lids + (int64_t)e * 8); cp_async16(rowbuf + 4, kp.lids + (int64_t)e * 8 + 4);
         cp_async16(rowbuf + 8, kp.e2n + (int64_t)e * 8); cp_async16(rowbuf + 12, kp.e2n + (int64_t)e * 8 + 4);
       };
-      const int64_t tfirst = tp.tile_begin + 2 * (int64_t)blockIdx.x + g;
+      const int64_t tfirst = tile_of(g);
+      // pipeline per thread: registers hold the gathered data of tile i, rowbuf the LID / node rows of tile i + 1.
+      // (An explicit L2 prefetch of tile i + 2's vertices was measured slower: CCTL.PF2 stalls the issuing warp.)
       int e_cur = element_of(tfirst), e_next = element_of(tfirst + tstep), e_next2 = element_of(tfirst + 2 * tstep);
       double X[8][3], us[8], ud[8];
       {
@@ -522,30 +608,31 @@ struct ThermalHexQ1 {
       }
       fetch_rows(e_next);
       asm volatile("cp.async.commit_group;" ::: "memory");
-      bool first = true;
+      int s = g, b = g % WS_NBUF;
       for (int64_t t = tfirst; t < tp.tile_end; t += tstep) {
-        double r[8], K[NK];
-        if (e_cur >= 0) work(kp, X, us, ud, nullptr, 0, r, K);
+        double* Ks = sm + b * KSZ + tid;
+        if (s >= WS_NBUF) bar_sync(BAR_EMPTY + b, 256);                  // the scatter group has consumed this store's previous tile
+        if (e_cur >= 0) {
+          // the element matrix is accumulated in place in the shared element store: no register copy of K, which
+          // removes every spill from the point loop and leaves the scheduler room to overlap dependent chains
+          double r[8];
+          KSmem kacc{Ks};
+          work(kp, X, us, ud, nullptr, 0, r, kacc);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) Ks[(NK + k) * 128] = -r[k];
+        }
+        bar_arrive(BAR_FULL + b, 256);
         asm volatile("cp.async.wait_group 0;" ::: "memory");             // my rows of the next tile
         if (e_next >= 0) {
           int lid[8];
-          gather(kp, rowbuf, rowbuf + 8, lid, X, us, ud);                // in flight while K is parked
+          gather(kp, rowbuf, rowbuf + 8, lid, X, us, ud);
         }
         const int e_next3 = element_of(t + 3 * tstep);
-        if (!first) bar_sync(BAR_EMPTY + g, 256);                        // the scatter group has consumed my previous tile
-        first = false;
-        if (e_cur >= 0) {
-#pragma unroll
-          for (int k = 0; k < NK; ++k) Ks[k * 128 + tid] = K[k];
-#pragma unroll
-          for (int s = 0; s < 8; ++s) Ks[(NK + s) * 128 + tid] = -r[s];
-        }
-        bar_arrive(BAR_FULL + g, 256);
         fetch_rows(e_next2);                                             // rowbuf was consumed by the gather above
         asm volatile("cp.async.commit_group;" ::: "memory");
         e_cur = e_next; e_next = e_next2; e_next2 = e_next3;
+        s += 2; b = (b + 2) % WS_NBUF;
       }
-      if (!first) bar_sync(BAR_EMPTY + g, 256);                          // pairs with the scatter group's last arrive
     }
   }
 #endif  // MRH_WS_CREG

@@ -168,7 +168,7 @@ class JitCache {
         "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
         "  typedef mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n"
         "  extern __shared__ double dsm[];\n" +
-        (jac ? "  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, dsm); return; }\n" : "") +
+        (jac ? "#if !defined(MRH_DEBUG_KSMEM_COMPUTE)\n  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, dsm); return; }\n#endif\n" : "") +
         "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
         "    Kern::element(kp, e, nullptr, 0);\n}\n";
     if (jac)          // warp-specialised variant: 384 threads, one CTA per SM (assemble_fast.h tiled_ws)
@@ -183,7 +183,7 @@ class JitCache {
     if (const char* ev = getenv("MRH_JIT_MINB")) minb = std::string("-DMRH_JIT_MINB=") + ev;          // tuning experiments
     std::string extra = "-DMRH_JIT_EXTRA=0";
     if (const char* ev = getenv("MRH_JIT_DEFINE")) extra = std::string("-D") + ev;                    // tuning experiments
-    std::string creg = "-DMRH_WS_CREG=232", sreg = "-DMRH_WS_SREG=40";                              // 256 * CREG + 128 * SREG <= 384 * 168
+    std::string creg = "-DMRH_WS_CREG=200", sreg = "-DMRH_WS_SREG=96";                              // 256 * CREG + 128 * SREG <= 384 * 168
     if (const char* ev = getenv("MRH_WS_CREG")) creg = std::string("-DMRH_WS_CREG=") + ev;
     if (const char* ev = getenv("MRH_WS_SREG")) sreg = std::string("-DMRH_WS_SREG=") + ev;
     const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", minb.c_str(), extra.c_str(), creg.c_str(), sreg.c_str()};

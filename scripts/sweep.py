@@ -7,7 +7,7 @@ import problems
 from mrhyde_b200 import Engine
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
-variants = [dict(no_ws=False, creg="232", sreg="40")]
+variants = [dict(no_ws=False, creg="200", sreg="96"), dict(no_ws=False, creg="192", sreg="112"), dict(no_ws=False, creg="184", sreg="128"), dict(no_ws=False, creg="176", sreg="144")]
 dev = torch.device("cuda", 0)
 for v in variants:
     os.environ["MRH_WS_CREG"] = v["creg"]; os.environ["MRH_WS_SREG"] = v["sreg"]

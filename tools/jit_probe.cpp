@@ -25,19 +25,20 @@ int main() {
       "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) k(const __grid_constant__ mrh::KParams kp) {\n"
       "  typedef mrh::ThermalHexQ1<false, false, true, mrh::JitCoefs> Kern;\n"
       "  extern __shared__ double dsm[];\n"
-      "  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, dsm); return; }\n"
+      "#if !defined(MRH_DEBUG_KSMEM_COMPUTE)\n  if (kp.tile.ntiles > 0) { Kern::tiled(kp, nullptr, 0, dsm); return; }\n#endif\n"
       "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
       "    Kern::element(kp, e, nullptr, 0);\n}\n"
       "extern \"C\" __global__ void __launch_bounds__(384, 1) kws(const __grid_constant__ mrh::KParams kp) {\n"
       "  typedef mrh::ThermalHexQ1<false, false, true, mrh::JitCoefs> Kern;\n"
       "  extern __shared__ double dsm[];\n  Kern::tiled_ws(kp, dsm);\n}\n";
+  const char* extra_env = getenv("MRH_JIT_DEFINE"); const std::string extra = std::string("-D") + (extra_env ? extra_env : "MRH_JIT_EXTRA=0");
   const char* creg_env = getenv("MRH_WS_CREG"); const char* sreg_env = getenv("MRH_WS_SREG");
-  const std::string creg = std::string("-DMRH_WS_CREG=") + (creg_env ? creg_env : "232"), sreg = std::string("-DMRH_WS_SREG=") + (sreg_env ? sreg_env : "40");
+  const std::string creg = std::string("-DMRH_WS_CREG=") + (creg_env ? creg_env : "200"), sreg = std::string("-DMRH_WS_SREG=") + (sreg_env ? sreg_env : "96");
   std::vector<const char*> hs, hn;
   for (int i = 0; i < k_num_embedded_headers; ++i) { hn.push_back(k_embedded_headers[i].name); hs.push_back(k_embedded_headers[i].text); }
   nvrtcProgram p; nvrtcCreateProgram(&p, full.c_str(), "probe.cu", (int)hs.size(), hs.data(), hn.data());
-  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", "--ptxas-options=-v", minb.c_str(), creg.c_str(), sreg.c_str()};
-  nvrtcResult rc = nvrtcCompileProgram(p, 8, opts);
+  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", "--ptxas-options=-v", minb.c_str(), creg.c_str(), sreg.c_str(), extra.c_str()};
+  nvrtcResult rc = nvrtcCompileProgram(p, 9, opts);
   size_t ls; nvrtcGetProgramLogSize(p, &ls); std::string log(ls, ' '); nvrtcGetProgramLog(p, &log[0]);
   printf("rc=%d\n%s\n", (int)rc, log.c_str());
   if (rc == NVRTC_SUCCESS) { size_t cs; nvrtcGetCUBINSize(p, &cs); std::vector<char> c(cs); nvrtcGetCUBIN(p, c.data()); FILE* f = fopen("/tmp/jit_probe.cubin", "wb"); fwrite(c.data(), 1, cs, f); fclose(f); printf("cubin %zu bytes\n", cs); }
