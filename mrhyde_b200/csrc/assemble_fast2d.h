@@ -1,0 +1,205 @@
+// Specialised assembly for thermal on Q1 quadrilaterals with the 4-point Gauss rule (BASELINE.json config C1:
+// regression/thermal/2D_verification at scale).  One thread owns one element; vertices, DOFs, the 4x4 element matrix
+// (10 upper entries, 16 with advection) and the residual live in registers.  Same conventions as the hex kernel
+// (assemble_fast.h): shards vertex order, descending Gauss abscissae (point 0 = (+,+)), residual subtracted, Jacobian
+// added, fixed rows skipped (thermal.cpp:71-165, assemblyManager.cpp:4031-4145).  The bilinear map and the solution are
+// held in monomial form (x = c0 + c1 xi + c2 eta + c3 xi eta), the general bilinear Jacobian is evaluated at every
+// point (no affine shortcut).
+#pragma once
+#include "assemble_fast.h"
+
+namespace mrh {
+
+#if !defined(__CUDACC_RTC__)
+inline bool thermal_quad_q1_eligible(int phys, int dim, int order, int nq, bool state_independent, int lump_mass) {
+  return phys == PHYS_THERMAL && dim == 2 && order == 1 && nq == 4 && state_independent && !lump_mass;
+}
+#endif
+
+template <bool TRANSIENT, bool ADV, bool JAC, class CF = InterpCoefs>
+struct ThermalQuadQ1 {
+  static constexpr int NK = ADV ? 16 : 10;
+  MRH_HD static constexpr int tri(int i, int j) { return i * 4 - (i * (i - 1)) / 2 + (j - i); }      // i <= j, 10 entries
+  MRH_HD static constexpr int bx(int s) { return (s == 1 || s == 2) ? 1 : 0; }                        // shards vertex -> tensor bits
+  MRH_HD static constexpr int by(int s) { return (s == 2 || s == 3) ? 1 : 0; }
+  MRH_HD static constexpr int vtx(int a, int b) { return b ? (a ? 2 : 3) : (a ? 1 : 0); }
+
+  // coefficient `slot` at a point: the NVRTC policy inlines the expression, the default policy runs the bytecode
+  template <int SLOT>
+  MRH_HDN static double coef(const KParams& kp, double x, double y, double t) {
+    if constexpr (CF::staged) {
+      PointState<double> ps;
+      ps.x[0] = x; ps.x[1] = y; ps.x[2] = 0.0; ps.time = t; ps.fields = nullptr;
+      for (int c = 0; c < 3; ++c) { ps.nrm[c] = 0.0; ps.tng[c] = 0.0; }
+      return eval_prog<double>(kp.progs[SLOT], kp.code, kp.cpool, ps);
+    } else {
+      if constexpr (SLOT == TH_SOURCE) return CF::source(x, y, 0.0, t);
+      else if constexpr (SLOT == TH_DIFF) return CF::diff(x, y, 0.0, t);
+      else if constexpr (SLOT == TH_CP) return CF::cp_(x, y, 0.0, t);
+      else if constexpr (SLOT == TH_RHO) return CF::rho_(x, y, 0.0, t);
+      else if constexpr (SLOT == TH_BX) return CF::bx(x, y, 0.0, t);
+      else return CF::by(x, y, 0.0, t);
+    }
+  }
+
+  MRH_HDN static void element(const KParams& kp, int64_t e) {
+    // ---- gather ----------------------------------------------------------------------------------------------
+    int lid[4];
+    {
+      const int4 a = *reinterpret_cast<const int4*>(kp.lids + e * 4);
+      lid[0] = a.x; lid[1] = a.y; lid[2] = a.z; lid[3] = a.w;
+    }
+    double X[4][2], us[4], ud[4];
+    {
+      const int4 a = *reinterpret_cast<const int4*>(kp.e2n + e * 4);
+      const int nd[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int s = 0; s < 4; ++s) { const double* p = kp.nodes + (int64_t)nd[s] * 2; X[s][0] = p[0]; X[s][1] = p[1]; }
+    }
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const double uval = kp.u[lid[s]];
+      if (!TRANSIENT) { us[s] = uval; ud[s] = 0.0; }
+      else {                                                // Workset::computeSolnTransientSeeded (workset.cpp:594-620)
+        const TimeParams& tp = kp.tp;
+        const double prev0 = kp.u_prev[(size_t)lid[s] * tp.nsteps];
+        double beta_u = (1.0 - tp.alpha_u) * prev0;
+        for (int k = 0; k < tp.stage; ++k) beta_u += tp.a_over_b[k] * (kp.u_stage[(size_t)lid[s] * tp.nstages + k] - prev0);
+        double beta_t = 0.0;
+        for (int k = 1; k <= tp.nsteps; ++k) beta_t += tp.bdf[k] * kp.u_prev[(size_t)lid[s] * tp.nsteps + (k - 1)];
+        us[s] = tp.alpha_u * uval + beta_u;
+        ud[s] = tp.alpha_t * uval + beta_t * tp.timewt;
+      }
+    }
+    const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
+
+    // ---- monomial coefficients, index m = i + 2 j for xi^i eta^j ------------------------------------------------
+    double C[4][2], A[4];
+    {
+      double v[3][4];
+#pragma unroll
+      for (int b = 0; b < 2; ++b)
+#pragma unroll
+        for (int a = 0; a < 2; ++a) { const int sv = vtx(a, b), m = a + 2 * b; v[0][m] = X[sv][0]; v[1][m] = X[sv][1]; v[2][m] = us[sv]; }
+#pragma unroll
+      for (int d = 0; d < 3; ++d)
+#pragma unroll
+        for (int bit = 1; bit < 4; bit <<= 1)
+#pragma unroll
+          for (int m = 0; m < 4; ++m)
+            if (!(m & bit)) { const double lo = v[d][m], hi = v[d][m | bit]; v[d][m] = hi + lo; v[d][m | bit] = hi - lo; }
+#pragma unroll
+      for (int m = 0; m < 4; ++m) { C[m][0] = 0.25 * v[0][m]; C[m][1] = 0.25 * v[1][m]; A[m] = 0.25 * v[2][m]; }
+    }
+
+    double r[4], K[NK];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) r[s] = 0.0;
+#pragma unroll
+    for (int k = 0; k < NK; ++k) K[k] = 0.0;
+
+    // ---- point loop -------------------------------------------------------------------------------------------------
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const double g = HexQ1::g;
+      const double sx = (q & 1) ? -g : g, sy = (q & 2) ? -g : g;
+      const double lx[2] = {0.5 - 0.5 * sx, 0.5 + 0.5 * sx}, ly[2] = {0.5 - 0.5 * sy, 0.5 + 0.5 * sy};
+      const double J00 = C[1][0] + C[3][0] * sy, J01 = C[2][0] + C[3][0] * sx;       // d x / d (xi, eta)
+      const double J10 = C[1][1] + C[3][1] * sy, J11 = C[2][1] + C[3][1] * sx;       // d y / d (xi, eta)
+      const double det = J00 * J11 - J01 * J10;
+      const double idet = 1.0 / det;
+      const double Ji00 = J11 * idet, Ji01 = -J01 * idet, Ji10 = -J10 * idet, Ji11 = J00 * idet;   // inverse Jacobian
+      const double w = fabs(det);                            // reference weights are 1
+      double gx[4], gy[4], Nq[4];
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        const int a = bx(s), b = by(s);
+        const double d0 = (a ? 0.5 : -0.5) * ly[b], d1 = (b ? 0.5 : -0.5) * lx[a];
+        Nq[s] = lx[a] * ly[b];
+        gx[s] = Ji00 * d0 + Ji10 * d1;                       // grad phi = J^-T grad_ref phi
+        gy[s] = Ji01 * d0 + Ji11 * d1;
+      }
+      const double g0 = A[1] + A[3] * sy, g1 = A[2] + A[3] * sx;
+      const double ex = Ji00 * g0 + Ji10 * g1, ey = Ji01 * g0 + Ji11 * g1;
+      double edot = 0.0;
+      if (TRANSIENT) {
+#pragma unroll
+        for (int s = 0; s < 4; ++s) edot += ud[s] * Nq[s];
+      }
+      const double xe = sx * sy;
+      const double x = C[0][0] + C[1][0] * sx + C[2][0] * sy + C[3][0] * xe;
+      const double y = C[0][1] + C[1][1] * sx + C[2][1] * sy + C[3][1] * xe;
+      const double t = kp.tp.time;
+      const double srcq = coef<TH_SOURCE>(kp, x, y, t), kapq = coef<TH_DIFF>(kp, x, y, t);
+      double rcpq = 0.0, bxq = 0.0, byq = 0.0;
+      if (TRANSIENT) rcpq = coef<TH_RHO>(kp, x, y, t) * coef<TH_CP>(kp, x, y, t);
+      if (ADV) { bxq = coef<TH_BX>(kp, x, y, t); byq = coef<TH_BY>(kp, x, y, t); }
+      const double kw = kapq * w;
+      double f0 = -srcq * w;
+      if (TRANSIENT) f0 += rcpq * edot * w;
+      if (ADV) f0 += (bxq * ex + byq * ey) * w;
+      const double fx = kw * ex, fy = kw * ey;
+#pragma unroll
+      for (int s = 0; s < 4; ++s) r[s] += f0 * Nq[s] + fx * gx[s] + fy * gy[s];
+      if (JAC) {
+        const double kwa = kw * au;
+        const double mw = TRANSIENT ? rcpq * at * w : 0.0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const double ax = kwa * gx[i], ay = kwa * gy[i];
+          const double mi = TRANSIENT ? mw * Nq[i] : 0.0;
+          if (!ADV) {
+#pragma unroll
+            for (int j = i; j < 4; ++j) {
+              double v = K[tri(i, j)] + ax * gx[j] + ay * gy[j];
+              if (TRANSIENT) v += mi * Nq[j];
+              K[tri(i, j)] = v;
+            }
+          } else {
+            const double ci = au * w * Nq[i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              double v = K[i * 4 + j] + ax * gx[j] + ay * gy[j];
+              v += ci * (bxq * gx[j] + byq * gy[j]);
+              if (TRANSIENT) v += mi * Nq[j];
+              K[i * 4 + j] = v;
+            }
+          }
+        }
+      }
+    }
+
+    // ---- scatter: one RED per entry through the slot-pattern dictionary --------------------------------------------------
+    bool fx_[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      fx_[s] = kp.fixed[lid[s]] != 0;
+      if (!fx_[s]) atomic_add(kp.res + lid[s], -r[s]);
+    }
+    if (!JAC) return;
+    uint16_t pat[16];
+    {
+      const uint4* pp = reinterpret_cast<const uint4*>(kp.pat + (size_t)kp.pat_id[e] * 16);
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const uint4 v = pp[k];
+        pat[k * 8 + 0] = (uint16_t)(v.x & 0xffff); pat[k * 8 + 1] = (uint16_t)(v.x >> 16);
+        pat[k * 8 + 2] = (uint16_t)(v.y & 0xffff); pat[k * 8 + 3] = (uint16_t)(v.y >> 16);
+        pat[k * 8 + 4] = (uint16_t)(v.z & 0xffff); pat[k * 8 + 5] = (uint16_t)(v.z >> 16);
+        pat[k * 8 + 6] = (uint16_t)(v.w & 0xffff); pat[k * 8 + 7] = (uint16_t)(v.w >> 16);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (fx_[i]) continue;
+      double* jrow = kp.jac + kp.rowptr[lid[i]];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const double v = ADV ? K[i * 4 + j] : (i <= j ? K[tri(i, j)] : K[tri(j, i)]);
+        atomic_add(jrow + pat[i * 4 + j], v);
+      }
+    }
+  }
+};
+
+}  // namespace mrh

@@ -10,6 +10,7 @@
 
 #include "capi_host.inl"
 #include "assemble_fast.h"
+#include "assemble_fast2d.h"
 #include "generic_kernels.h"
 #include "jit.hpp"
 
@@ -67,6 +68,12 @@ __global__ void __launch_bounds__(128) thermal_hex_q1_kernel(const __grid_consta
   __shared__ double stage[ThermalHexQ1<TRANSIENT, ADV, JAC>::NSTAGE * 8 * 128];
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (int64_t)gridDim.x * blockDim.x)
     ThermalHexQ1<TRANSIENT, ADV, JAC>::element(kp, e, stage + threadIdx.x, 128);
+}
+
+template <bool TRANSIENT, bool ADV, bool JAC>
+__global__ void __launch_bounds__(128) thermal_quad_q1_kernel(const __grid_constant__ KParams kp) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (int64_t)gridDim.x * blockDim.x)
+    ThermalQuadQ1<TRANSIENT, ADV, JAC>::element(kp, e);
 }
 
 template <bool TRANSIENT, bool ADV>

@@ -61,7 +61,8 @@ void device_finalize(mrh_engine* h) {
   }
   // NVRTC specialisation of the coefficient expressions for the specialised thermal kernel (jit.hpp)
   D.jit.clear();
-  if (!(H.cfg.flags & 3) && thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
+  const bool quad2d = thermal_quad_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass);
+  if (!(H.cfg.flags & 3) && (quad2d || thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass))) {
     try {
       std::string src;
       src += jit_function_source("source", H.vol_progs[TH_SOURCE], H.ec.code, H.ec.cpool);
@@ -72,7 +73,7 @@ void device_finalize(mrh_engine* h) {
       src += jit_function_source("bx", H.vol_progs[TH_BX], H.ec.code, H.ec.cpool);
       src += jit_function_source("by", H.vol_progs[TH_BY], H.ec.code, H.ec.cpool);
       src += jit_function_source("bz", H.vol_progs[TH_BZ], H.ec.code, H.ec.cpool);
-      D.jit.setCoefficientSource(src);
+      D.jit.setCoefficientSource(src, quad2d ? 2 : 3);
       const bool adv = H.cfg.include_advection != 0;
       if (!D.jit.thermal(false, adv, true) || !D.jit.thermal(false, adv, false)) h->err = "NVRTC specialisation unavailable, using the in-kernel interpreter: " + D.jit.last_error;
     } catch (const std::exception& ex) { D.jit.clear(); h->err = std::string("NVRTC specialisation skipped: ") + ex.what(); }
@@ -92,6 +93,18 @@ void device_finalize(mrh_engine* h) {
 template <bool T, bool A, bool J>
 void launch_thermal_fast(const DeviceImpl& D, const KParams& kp, cudaStream_t stream) {
   auto kern = thermal_hex_q1_kernel<T, A, J>;
+  int per_sm = 1;
+  CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, 0));
+  if (per_sm < 1) per_sm = 1;
+  const int64_t nblk = (kp.nwork + 127) / 128;
+  const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * per_sm * 4);
+  kern<<<grid, 128, 0, stream>>>(kp);
+  CUDA_CK(cudaGetLastError());
+}
+
+template <bool T, bool A, bool J>
+void launch_thermal_quad(const DeviceImpl& D, const KParams& kp, cudaStream_t stream) {
+  auto kern = thermal_quad_q1_kernel<T, A, J>;
   int per_sm = 1;
   CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, 0));
   if (per_sm < 1) per_sm = 1;
@@ -168,7 +181,26 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
     if (side < 0) CUDA_CK(cudaEventRecord(D.ev0, stream));
     const bool fast = side < 0 && !(H.cfg.flags & 1) &&
         thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass);
-    if (fast) {
+    const bool fast2d = side < 0 && !(H.cfg.flags & 1) &&
+        thermal_quad_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass);
+    if (fast2d) {
+      const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
+      JitKernel* jk = (H.cfg.flags & 2) ? nullptr : D.jit.thermal(tr, adv, jc);
+      D.jit_used = jk != nullptr;
+      D.last_path = jk ? "nvrtc-specialised-2d" : "specialised-2d";
+      if (jk) {
+        const int64_t nblk = (kp.nwork + 127) / 128;
+        const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * jk->blocks_per_sm * 4);
+        void* args[] = {(void*)&kp};
+        if (JitApi::get().LaunchKernel(jk->fn, grid, 1, 1, 128, 1, 1, 0, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+          throw std::runtime_error("CUDA error: cuLaunchKernel failed for the NVRTC-specialised 2-D kernel");
+      } else {
+#define MRH_FAST2D(T, A, Jc) if (tr == T && adv == A && jc == Jc) launch_thermal_quad<T, A, Jc>(D, kp, stream);
+        MRH_FAST2D(false, false, false) MRH_FAST2D(false, false, true) MRH_FAST2D(false, true, false) MRH_FAST2D(false, true, true)
+        MRH_FAST2D(true, false, false) MRH_FAST2D(true, false, true) MRH_FAST2D(true, true, false) MRH_FAST2D(true, true, true)
+#undef MRH_FAST2D
+      }
+    } else if (fast) {
       const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
       JitKernel* jk = (H.cfg.flags & 2) ? nullptr : D.jit.thermal(tr, adv, jc);
       D.jit_used = jk != nullptr;

@@ -151,7 +151,7 @@ class JitCache {
   std::string last_error;
   ~JitCache() { for (auto& kv : kernels_) if (kv.second.mod && JitApi::get().ok) JitApi::get().ModuleUnload(kv.second.mod); }
   void clear() { for (auto& kv : kernels_) if (kv.second.mod && JitApi::get().ok) JitApi::get().ModuleUnload(kv.second.mod); kernels_.clear(); coef_src_.clear(); }
-  void setCoefficientSource(const std::string& s) { clear(); coef_src_ = s; }
+  void setCoefficientSource(const std::string& s, int dim = 3) { clear(); coef_src_ = s; dim_ = dim; }
   bool hasSource() const { return !coef_src_.empty(); }
 
   // returns nullptr (and sets last_error) when the variant cannot be built
@@ -164,6 +164,13 @@ class JitCache {
     if (!api.ok) { last_error = api.why; return nullptr; }
     if (coef_src_.empty()) { last_error = "no coefficient source"; return nullptr; }
     auto B = [](bool b) { return b ? "true" : "false"; };
+    if (dim_ == 2) {          // Q1 quadrilaterals: direct-scatter kernel only (assemble_fast2d.h)
+      K.source = std::string("#include \"assemble_fast2d.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
+          "};\n}\nextern \"C\" __global__ void __launch_bounds__(128) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
+          "  typedef mrh::ThermalQuadQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n"
+          "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
+          "    Kern::element(kp, e);\n}\n";
+    } else {
     K.source = std::string("#include \"assemble_fast.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
         "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
         "  typedef mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n"
@@ -175,6 +182,7 @@ class JitCache {
       K.source += std::string("extern \"C\" __global__ void __launch_bounds__(384, 1) mrh_jit_thermal_hex_q1_ws(const __grid_constant__ mrh::KParams kp) {\n") +
           "  typedef mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", true, mrh::JitCoefs> Kern;\n"
           "  extern __shared__ double dsm[];\n  Kern::tiled_ws(kp, dsm);\n}\n";
+    }
     std::vector<const char*> hdr_src, hdr_name;
     for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
     nvrtcProgram prog;
@@ -198,13 +206,14 @@ class JitCache {
     if (api.ModuleLoadData(&K.mod, cubin.data()) != CUDA_SUCCESS) { last_error = "cuModuleLoadData failed"; K.mod = nullptr; return nullptr; }
     if (api.ModuleGetFunction(&K.fn, K.mod, "mrh_jit_thermal_hex_q1") != CUDA_SUCCESS) { last_error = "kernel symbol not found"; K.fn = nullptr; return nullptr; }
     if (api.OccupancyMaxActiveBlocks(&K.blocks_per_sm, K.fn, 128, 0) != CUDA_SUCCESS || K.blocks_per_sm < 1) K.blocks_per_sm = 1;
-    if (!jac || api.ModuleGetFunction(&K.fn_ws, K.mod, "mrh_jit_thermal_hex_q1_ws") != CUDA_SUCCESS) K.fn_ws = nullptr;
+    if (!jac || dim_ == 2 || api.ModuleGetFunction(&K.fn_ws, K.mod, "mrh_jit_thermal_hex_q1_ws") != CUDA_SUCCESS) K.fn_ws = nullptr;
     return &K;
   }
 
  private:
   std::map<int, JitKernel> kernels_;
   std::string coef_src_;
+  int dim_ = 3;
 };
 
 }  // namespace mrh

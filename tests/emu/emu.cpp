@@ -5,6 +5,7 @@
 #include "../../mrhyde_b200/csrc/capi_host.inl"
 #include "../../mrhyde_b200/csrc/dispatch.h"
 #include "../../mrhyde_b200/csrc/assemble_fast.h"
+#include "../../mrhyde_b200/csrc/assemble_fast2d.h"
 
 using namespace mrh;
 
@@ -59,6 +60,18 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
         MRH_FAST(false, false, false) MRH_FAST(false, false, true) MRH_FAST(false, true, false) MRH_FAST(false, true, true)
         MRH_FAST(true, false, false) MRH_FAST(true, false, true) MRH_FAST(true, true, false) MRH_FAST(true, true, true)
 #undef MRH_FAST
+      }
+      E->launches++; E->fast_launches++;
+      continue;
+    }
+    if (side < 0 && !(H.cfg.flags & 1) &&
+        thermal_quad_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
+      const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
+      for (int64_t e = 0; e < kp.nwork; ++e) {
+#define MRH_FAST2D(T, A, Jc) if (tr == T && adv == A && jc == Jc) ThermalQuadQ1<T, A, Jc>::element(kp, e);
+        MRH_FAST2D(false, false, false) MRH_FAST2D(false, false, true) MRH_FAST2D(false, true, false) MRH_FAST2D(false, true, true)
+        MRH_FAST2D(true, false, false) MRH_FAST2D(true, false, true) MRH_FAST2D(true, true, false) MRH_FAST2D(true, true, true)
+#undef MRH_FAST2D
       }
       E->launches++; E->fast_launches++;
       continue;

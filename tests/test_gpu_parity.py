@@ -42,6 +42,19 @@ def test_cuda_specialised_kernel_variants(lib, name, p, kw, no_jit, no_tiles, no
     U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws, jacobian=False)
 
 
+@pytest.mark.parametrize("name,p,kw", [c for c in CASES if c[1]["physics"] == "thermal" and c[1]["mesh"]["dim"] == 2],
+                         ids=lambda v: v if isinstance(v, str) else "")
+@pytest.mark.parametrize("force_generic,no_jit", [(False, False), (False, True), (True, False)])
+def test_cuda_thermal_quad_kernel_variants(lib, name, p, kw, force_generic, no_jit):
+    """2-D thermal Q1 cases through the specialised quadrilateral kernel (NVRTC-printed coefficients, or the bytecode
+    interpreter inside the kernel) and through the generic kernel"""
+    r = U.check_case(p, kw, lib, on_gpu=True, force_generic=force_generic, no_jit=no_jit)
+    if r["path"] != "generic":
+        assert not force_generic
+        assert r["path"] == ("specialised-2d" if no_jit else "nvrtc-specialised-2d"), r
+    U.check_case(p, kw, lib, on_gpu=True, force_generic=force_generic, no_jit=no_jit, jacobian=False)
+
+
 def test_default_path_is_nvrtc_tiled_warp_specialised(lib):
     r = U.check_case(problems.config_c2(6), {}, lib, on_gpu=True)
     assert r["path"] == "nvrtc-specialised+tiled-ws", r

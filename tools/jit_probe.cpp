@@ -34,6 +34,12 @@ int main() {
   const char* extra_env = getenv("MRH_JIT_DEFINE"); const std::string extra = std::string("-D") + (extra_env ? extra_env : "MRH_JIT_EXTRA=0");
   const char* creg_env = getenv("MRH_WS_CREG"); const char* sreg_env = getenv("MRH_WS_SREG");
   const std::string creg = std::string("-DMRH_WS_CREG=") + (creg_env ? creg_env : "200"), sreg = std::string("-DMRH_WS_SREG=") + (sreg_env ? sreg_env : "96");
+  if (getenv("MRH_PROBE_2D"))
+    full = std::string("#include \"assemble_fast2d.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + src +
+      "};\n}\nextern \"C\" __global__ void __launch_bounds__(128) k(const __grid_constant__ mrh::KParams kp) {\n"
+      "  typedef mrh::ThermalQuadQ1<false, false, true, mrh::JitCoefs> Kern;\n"
+      "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
+      "    Kern::element(kp, e);\n}\n";
   std::vector<const char*> hs, hn;
   for (int i = 0; i < k_num_embedded_headers; ++i) { hn.push_back(k_embedded_headers[i].name); hs.push_back(k_embedded_headers[i].text); }
   nvrtcProgram p; nvrtcCreateProgram(&p, full.c_str(), "probe.cu", (int)hs.size(), hs.data(), hn.data());
