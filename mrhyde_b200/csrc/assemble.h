@@ -80,7 +80,7 @@ struct GenPhases {
   MRH_HD static int64_t elem_of(const KParams& kp, int64_t w) { return kp.elem_list ? (int64_t)kp.elem_list[w] : w; }
 
   // ---- phase 0: gather (items: EB*N dof slots, then EB*NV vertices) --------------------------------
-  MRH_HDN static void gather_dof(const KParams& kp, const GenSmem<C>& L, double* sm, int64_t blk0, int item) {
+  template <class LAY> MRH_HDN static void gather_dof(const KParams& kp, const LAY& L, double* sm, int64_t blk0, int item) {
     const int le = item / N, k = item % N;
     if (blk0 + le >= kp.nwork) return;
     const int64_t e = elem_of(kp, blk0 + le);
@@ -99,7 +99,7 @@ struct GenPhases {
     sm[L.oU() + (size_t)le * N + k] = tp.alpha_u * uval + beta_u;
     sm[L.oUd() + (size_t)le * N + k] = tp.alpha_t * uval + beta_t;
   }
-  MRH_HDN static void gather_vertex(const KParams& kp, const GenSmem<C>& L, double* sm, int64_t blk0, int item) {
+  template <class LAY> MRH_HDN static void gather_vertex(const KParams& kp, const LAY& L, double* sm, int64_t blk0, int item) {
     const int le = item / NV, a = item % NV;
     if (blk0 + le >= kp.nwork) return;
     const int64_t e = elem_of(kp, blk0 + le);
@@ -108,7 +108,7 @@ struct GenPhases {
   }
 
   // ---- phase 1a: geometry + physical basis at one (element, point) ---------------------------------
-  MRH_HDN static void geometry(const KParams& kp, const GenSmem<C>& L, double* sm, int64_t blk0, int item) {
+  template <class LAY> MRH_HDN static void geometry(const KParams& kp, const LAY& L, double* sm, int64_t blk0, int item) {
     const int nq = L.nq, le = item / nq, q = item % nq;
     if (blk0 + le >= kp.nwork) return;
     const double* X = sm + L.oX() + (size_t)le * NV * DIM;

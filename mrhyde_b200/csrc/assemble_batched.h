@@ -1,0 +1,359 @@
+// Batched fused assembly (volume terms, residual + Jacobian) for the multi-variable / higher-order configurations
+// (C3 cdr Q2, C4 linear elasticity, C5 Navier-Stokes; also every state-dependent thermal case).  Same reference chain
+// as assemble.h (performGather -> computeSoln*Seeded -> getPhysicalVolumetricBasis -> volumeResidual -> scatter,
+// /root/reference/src/managers/assemblyManager.cpp:2150-2665, :3598-3643, :4031-4145), restructured around what the
+// profiles of the generic kernel showed (profiles/r1_generic_c4_n64_*, r1_batched_v1_*): the PAD<P> interpreter spilled
+// 10 KB per thread, only nq threads per element worked in the point phase, every RED lane hit its own sector, and the
+// DFMA contraction was bound by shared-memory operand loads at 8 warps per SM.  Here ONE WARP owns ONE ELEMENT from
+// gather to scatter (no CTA barrier; warps of an SM drift apart so that scatter, point physics and contraction overlap):
+//   * state-independent coefficient programs are evaluated once per point on plain doubles (phase `prep`);
+//   * the point physics runs on lane chunks: lane (point, variable m) carries PAD<1+dim> and differentiates the point
+//     fluxes with respect to (u_m, grad u_m); fields and fluxes stay in registers;
+//   * the element contraction K = sum_q T^T D T and r = sum_q T^T f runs on the FP64 tensor path
+//     (mma.sync m8n8k4, DMMA.8x8x4): measured 37 TFLOP/s with one warp per scheduler (profiles/r1_dmma_microbench.txt)
+//     against 8x the issue slots and one shared-memory operand per FMA for the DFMA form.  D is written by the point
+//     phase directly in B-fragment order with the columns of a tile interleaved (m even | m odd) so that the C
+//     fragment of the first product IS the A fragment of the second - no shuffle, no shared-memory round trip;
+//   * the scatter walks a row of K with lanes along (node, variable), i.e. along consecutive CRS slots.
+// Phase functions are __host__ __device__ and written against WV (one value per lane): tests/emu steps the same code
+// on the CPU with WV = 32 explicit lanes.
+#pragma once
+#include "assemble.h"
+
+namespace mrh {
+
+constexpr int MRH_NCOEF = 8;      // volume program slots of one physics module (params.h: at most CDR's 8)
+
+// ---- one value per lane of a warp --------------------------------------------------------------------------
+#if defined(__CUDA_ARCH__)
+struct WV { double x; };
+MRH_HD double wv_get(const WV& v, int) { return v.x; }
+MRH_HD WV wv_zero() { return WV{0.0}; }
+template <class F> MRH_HD WV wv_make(F f) { return WV{f((int)(threadIdx.x & 31))}; }
+template <class F> MRH_HD void wv_each(F f) { f((int)(threadIdx.x & 31)); }
+// c(8x8) += a(8x4) b(4x8): lane holds a[lane/4][lane%4], b[lane%4][lane/4], c[lane/4][2(lane%4) + {0,1}]
+MRH_HD void wv_mma(WV& c0, WV& c1, const WV& a, const WV& b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0.x), "+d"(c1.x) : "d"(a.x), "d"(b.x));
+}
+MRH_HD void warp_sync() { __syncwarp(); }
+#else
+struct WV { double x[32]; };
+MRH_HD double wv_get(const WV& v, int lane) { return v.x[lane]; }
+MRH_HD WV wv_zero() { WV r; for (int l = 0; l < 32; ++l) r.x[l] = 0.0; return r; }
+template <class F> MRH_HD WV wv_make(F f) { WV r; for (int l = 0; l < 32; ++l) r.x[l] = f(l); return r; }
+template <class F> MRH_HD void wv_each(F f) { for (int l = 0; l < 32; ++l) f(l); }
+MRH_HD void wv_mma(WV& c0, WV& c1, const WV& a, const WV& b) {
+  for (int l = 0; l < 32; ++l) {
+    const int row = l / 4, p = l % 4;
+    for (int k = 0; k < 4; ++k) {
+      c0.x[l] += a.x[row * 4 + k] * b.x[(2 * p) * 4 + k];
+      c1.x[l] += a.x[row * 4 + k] * b.x[(2 * p + 1) * 4 + k];
+    }
+  }
+}
+MRH_HD void warp_sync() {}
+#endif
+
+MRH_HD void st2(double* p, double a, double b) {
+#if defined(__CUDA_ARCH__)
+  *reinterpret_cast<double2*>(p) = make_double2(a, b);
+#else
+  p[0] = a; p[1] = b;
+#endif
+}
+
+MRH_HD size_t even_up(size_t x) { return (x + 1) & ~(size_t)1; }
+
+// shared-memory carve-up of ONE element / warp (offsets in doubles, every region 16-byte aligned)
+template <class C>
+struct WarpSmem {
+  int nq;
+  bool transient;
+  static constexpr int N = C::N, NVAR = C::NVAR, NB = C::NB, TA = C::TA;
+  static constexpr int NT = (NVAR + 1) / 2;                    // column tiles of D: variables (2t, 2t+1)
+  static constexpr int NRT = (NB + 7) / 8;                     // row tiles of 8 basis functions
+  static constexpr int QS = NVAR * NT * 32 + 2;                // D fragments of one point (+2: spreads points over banks)
+  static constexpr int KS = ((N + 7) / 16) * 16 + 8;           // row stride of K, == 8 (mod 16): conflict-free 16-byte stores
+  static_assert(KS >= N, "row stride of the element matrix");
+  MRH_HD WarpSmem(int nq_, bool tr) : nq(nq_), transient(tr) {}
+  MRH_HD size_t dsize() const { return (size_t)nq * QS; }
+  MRH_HD bool k_aliases_d() const { return (size_t)N * KS <= dsize(); }
+  MRH_HD size_t oX() const { return 0; }
+  MRH_HD size_t oU() const { return even_up(oX() + (size_t)C::NV * C::DIM); }
+  MRH_HD size_t oUd() const { return even_up(oU() + N); }
+  MRH_HD size_t oW() const { return even_up(oUd() + (transient ? N : 0)); }
+  MRH_HD size_t oXq() const { return even_up(oW() + nq); }
+  MRH_HD size_t oT() const { return even_up(oXq() + (size_t)nq * 3); }
+  MRH_HD size_t oF() const { return even_up(oT() + (size_t)nq * NB * TA); }
+  MRH_HD size_t oD() const { return even_up(oF() + (size_t)nq * NVAR * TA); }
+  MRH_HD size_t oKx() const { return even_up(oD() + dsize()); }                       // separate K only when it cannot alias D
+  MRH_HD size_t oCoef() const { return even_up(oKx() + (k_aliases_d() ? 0 : (size_t)N * KS)); }
+  MRH_HD size_t oH() const { return even_up(oCoef() + (size_t)nq * MRH_NCOEF); }
+  MRH_HD size_t oR() const { return even_up(oH() + 1); }
+  MRH_HD size_t oRowBase() const { return even_up(oR() + N); }                         // int64 per natural row
+  MRH_HD size_t oLid() const { return even_up(oRowBase() + N); }
+  MRH_HD size_t total_doubles() const { return even_up(oLid() + (N + 1) / 2 + 1); }
+  MRH_HD size_t oK() const { return k_aliases_d() ? oD() : oKx(); }
+  // what GenPhases::gather_* expect of a layout
+  int EB = 1;
+};
+
+// What a physics routine sees at one point in the batched kernel: same interface as PointIn<S> (physics.h), but the
+// interpolated fields are a by-value array with compile-time indices (registers) and state-independent programs
+// come pre-evaluated from shared memory.
+template <class S, int NVAR, int DIM>
+struct PointBat {
+  const KParams* kp;
+  S f[NVAR][5];            // value, d/dx, d/dy, d/dz, d/dt
+  const double* coef;      // [MRH_NCOEF] pre-evaluated programs of kind 1 at this point
+  PointState<S> ps;        // x, time; fields -> FIELD_KINDS-strided copy, written only when a state-dependent program exists
+  double w, h;
+  MRH_HD S fn(int k) const {
+    const Prog& pr = kp->progs[k];
+    if (pr.kind == 0) return S(pr.cval);
+    if (pr.kind == 1) return S(coef[k]);
+    return eval_code<S>(kp->code, kp->cpool, pr.start, pr.len, ps);
+  }
+  MRH_HD const S& U(int m) const { return f[m][0]; }
+  MRH_HD const S& dU(int m, int c) const { return f[m][1 + c]; }
+  MRH_HD const S& Ut(int m) const { return f[m][4]; }
+};
+
+template <class C>
+struct BatPhases {
+  static constexpr int DIM = C::DIM, NB = C::NB, NV = C::NV, N = C::N, NVAR = C::NVAR, P = C::P, TA = C::TA;
+  static constexpr int LCH = TA, NCH = NVAR;                   // one lane chunk per variable: (u_m, grad u_m)
+  using S = PAD<LCH>;
+  using LAY = WarpSmem<C>;
+  static constexpr int NT = LAY::NT, NRT = LAY::NRT, QS = LAY::QS, KS = LAY::KS;
+  static_assert(N <= 32, "one lane per element row");
+
+  // ---- geometry + physical basis, item = (point, part): every part rebuilds J, part p fills basis rows j == p (mod nparts)
+  MRH_HD static int geom_parts(int nq) { return nq * 4 <= 32 ? 4 : (nq * 2 <= 32 ? 2 : 1); }
+  MRH_HDN static void geometry(const KParams& kp, const LAY& L, double* sm, int item, int nparts) {
+    const int q = item / nparts, part = item - q * nparts;
+    const double* X = sm + L.oX();
+    const RefTab& tb = kp.tab;
+    double J[DIM][DIM], Ji[DIM][DIM], xq[3] = {0.0, 0.0, 0.0};
+    for (int i = 0; i < DIM; ++i) for (int j = 0; j < DIM; ++j) J[i][j] = 0.0;
+    for (int a = 0; a < NV; ++a) {
+      const double vb = tb.VB[q * NV + a];
+      for (int i = 0; i < DIM; ++i) {
+        const double xa = X[a * DIM + i];
+        xq[i] += xa * vb;
+        for (int j = 0; j < DIM; ++j) J[i][j] += xa * tb.VG[(q * NV + a) * DIM + j];
+      }
+    }
+    const double det = det_inv<DIM>(J, Ji);
+    if (part == 0) {
+      sm[L.oW() + q] = fabs(det) * tb.W[q];
+      for (int c = 0; c < 3; ++c) sm[L.oXq() + (size_t)q * 3 + c] = xq[c];
+    }
+    double* T = sm + L.oT() + (size_t)q * NB * TA;
+    for (int j = part; j < NB; j += nparts) {
+      T[j * TA] = tb.B[q * NB + j];
+      for (int c = 0; c < DIM; ++c) {
+        double s = 0.0;
+        for (int m = 0; m < DIM; ++m) s += Ji[m][c] * tb.G[(q * NB + j) * DIM + m];
+        T[j * TA + 1 + c] = s;
+      }
+    }
+  }
+
+  // ---- prep: state-independent programs, item = (point, i-th program of kind 1); lane 0 adds the element size ----
+  MRH_HD static int num_kind1(const KParams& kp) { int n = 0; for (int k = 0; k < MRH_NCOEF; ++k) n += (kp.progs[k].kind == 1); return n; }
+  MRH_HDN static void prep(const KParams& kp, const LAY& L, double* sm, int item, int n1) {
+    const int q = item / n1; int idx = item - q * n1, k = 0;
+    for (; k < MRH_NCOEF; ++k) if (kp.progs[k].kind == 1 && idx-- == 0) break;
+    PointState<double> pd;
+    for (int c = 0; c < 3; ++c) { pd.x[c] = sm[L.oXq() + (size_t)q * 3 + c]; pd.nrm[c] = 0.0; pd.tng[c] = 0.0; }
+    pd.time = kp.tp.time; pd.fields = nullptr;
+    sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = eval_code<double>(kp.code, kp.cpool, kp.progs[k].start, kp.progs[k].len, pd);
+  }
+  MRH_HDN static void element_size(const LAY& L, double* sm) {
+    double vol = 0.0;
+    for (int k = 0; k < L.nq; ++k) vol += sm[L.oW() + k];
+    sm[L.oH()] = pow(vol, 1.0 / (double)DIM);
+  }
+
+  // ---- point physics on one lane chunk, item = (point, variable m) ----------------------------------------
+  MRH_HDN static void point_chunk(const KParams& kp, const LAY& L, double* sm, int item) {
+    const int q = item / NCH, ch = item - q * NCH;
+    const int lane0 = ch * LCH;
+    const double* T = sm + L.oT() + (size_t)q * NB * TA;
+    const double* U = sm + L.oU();
+    const double* Ud = sm + L.oUd();
+    const bool tr = kp.tp.transient != 0;
+    const double au = tr ? kp.tp.alpha_u : 1.0;
+    PointBat<S, NVAR, DIM> in;
+#pragma unroll
+    for (int m = 0; m < NVAR; ++m) {
+      double fv[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+      for (int j = 0; j < NB; ++j) {
+        const int slot = kp.offsets[m * NB + j];
+        const double uj = U[slot], b = T[j * TA];
+        fv[0] += uj * b;
+#pragma unroll
+        for (int c = 0; c < DIM; ++c) fv[1 + c] += uj * T[j * TA + 1 + c];
+        if (tr) fv[4] += Ud[slot] * b;
+      }
+#pragma unroll
+      for (int k = 0; k < 5; ++k) in.f[m][k] = S(fv[k]);
+#pragma unroll
+      for (int k = 0; k <= DIM; ++k)
+#pragma unroll
+        for (int l = 0; l < LCH; ++l) if (m * TA + k == lane0 + l) in.f[m][k].d[l] = au;
+      if (tr) {
+#pragma unroll
+        for (int l = 0; l < LCH; ++l) if (m * TA == lane0 + l) in.f[m][4].d[l] = kp.tp.alpha_t;
+      }
+    }
+    bool sd = false;
+    for (int k = 0; k < MRH_NCOEF; ++k) sd = sd || (kp.progs[k].kind == 2);
+    S fm[NVAR * FIELD_KINDS];
+    if (sd) {
+#pragma unroll
+      for (int m = 0; m < NVAR; ++m)
+#pragma unroll
+        for (int k = 0; k < FIELD_KINDS; ++k) fm[m * FIELD_KINDS + k] = (k < 5) ? in.f[m][k] : S(0.0);
+    }
+    in.kp = &kp; in.coef = sm + L.oCoef() + (size_t)q * MRH_NCOEF;
+    in.ps.fields = fm; in.ps.time = kp.tp.time;
+    for (int c = 0; c < 3; ++c) { in.ps.x[c] = sm[L.oXq() + (size_t)q * 3 + c]; in.ps.nrm[c] = 0.0; in.ps.tng[c] = 0.0; }
+    in.w = sm[L.oW() + q];
+    in.h = sm[L.oH()];
+    S F[NVAR][TA];
+#pragma unroll
+    for (int v = 0; v < NVAR; ++v)
+#pragma unroll
+      for (int a = 0; a < TA; ++a) F[v][a] = S(0.0);
+    Physics<C::PHYS, DIM, S>::volume(in, F);
+    // f -> F[q][v][a];  dF_(v,a)/d(m,b) -> B-fragment order: tile (v, t = m/2), lane = a + 4 ((m & 1) + 2 b)
+    double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
+    double* Dq = sm + L.oD() + (size_t)q * QS;
+    const int t = ch >> 1, half = ch & 1;
+    const bool phantom = (NVAR & 1) && ch == NVAR - 1;           // odd variable count: this lane also zeroes column m + 1
+#pragma unroll
+    for (int v = 0; v < NVAR; ++v) {
+      double* Dt = Dq + (size_t)(v * NT + t) * 32;
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        if (a < TA && ch == 0) sF[v * TA + a] = F[v][a < TA ? a : 0].v;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          Dt[a + 4 * (half + 2 * b)] = (a < TA && b < TA) ? F[v][a < TA ? a : 0].d[b < LCH ? b : 0] : 0.0;
+          if (phantom) Dt[a + 4 * (1 + 2 * b)] = 0.0;
+        }
+      }
+    }
+  }
+
+  // ---- contraction on the FP64 tensor path (warp-collective) ------------------------------------------------
+  // step 1 (per v, column tile t):  L = T_rt (8 x 4: basis i, slot a) x D_(v,t) (4 x 8: slot a, columns (b, m & 1))
+  // step 2 (per m of the tile)   :  K_(v,rt),(m,ct) += L_m (8 x 4: basis i, slot b) x T_ct^T (4 x 8: slot b, basis j)
+  // The A fragment of step 2 is the C fragment of step 1; the B fragment of step 2 is the A fragment of step 1.
+  struct Acc { WV k[NVAR][NRT][NVAR][NRT][2]; WV r[NRT][2]; };
+  MRH_HD static void contract(const LAY& L, const double* sm, Acc& A) {
+#pragma unroll
+    for (int v = 0; v < NVAR; ++v)
+#pragma unroll
+      for (int rt = 0; rt < NRT; ++rt)
+#pragma unroll
+        for (int m = 0; m < NVAR; ++m)
+#pragma unroll
+          for (int ct = 0; ct < NRT; ++ct) { A.k[v][rt][m][ct][0] = wv_zero(); A.k[v][rt][m][ct][1] = wv_zero(); }
+#pragma unroll
+    for (int rt = 0; rt < NRT; ++rt) { A.r[rt][0] = wv_zero(); A.r[rt][1] = wv_zero(); }
+    for (int q = 0; q < L.nq; ++q) {
+      const double* T = sm + L.oT() + (size_t)q * NB * TA;
+      const double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
+      const double* Dq = sm + L.oD() + (size_t)q * QS;
+      WV tf[NRT];
+#pragma unroll
+      for (int rt = 0; rt < NRT; ++rt)
+        tf[rt] = wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? T[j * TA + a] : 0.0; });
+      const WV ff = wv_make([&](int lane) { const int v = lane >> 2, a = lane & 3; return (v < NVAR && a < TA) ? sF[v * TA + a] : 0.0; });
+#pragma unroll
+      for (int rt = 0; rt < NRT; ++rt) wv_mma(A.r[rt][0], A.r[rt][1], tf[rt], ff);
+#pragma unroll
+      for (int v = 0; v < NVAR; ++v)
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+          const double* Dt = Dq + (size_t)(v * NT + t) * 32;
+          const WV df = wv_make([&](int lane) { return Dt[lane]; });
+#pragma unroll
+          for (int rt = 0; rt < NRT; ++rt) {
+            WV l0 = wv_zero(), l1 = wv_zero();
+            wv_mma(l0, l1, tf[rt], df);
+#pragma unroll
+            for (int ct = 0; ct < NRT; ++ct) {
+              wv_mma(A.k[v][rt][2 * t][ct][0], A.k[v][rt][2 * t][ct][1], l0, tf[ct]);
+              if (2 * t + 1 < NVAR) wv_mma(A.k[v][rt][(2 * t + 1 < NVAR) ? 2 * t + 1 : 0][ct][0], A.k[v][rt][(2 * t + 1 < NVAR) ? 2 * t + 1 : 0][ct][1], l1, tf[ct]);
+            }
+          }
+        }
+    }
+  }
+
+  // ---- park K (natural order: row (v, i), column (m, j)) and r in shared memory; lane = fragment lane ------
+  MRH_HD static void store_acc(const LAY& L, double* sm, const Acc& A) {
+    double* K = sm + L.oK();
+    double* R = sm + L.oR();
+    wv_each([&](int lane) {
+      const int i0 = lane >> 2, p = lane & 3;
+#pragma unroll
+      for (int rt = 0; rt < NRT; ++rt) {
+        const int i = rt * 8 + i0;
+        if (i >= NB) continue;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) { const int v = 2 * p + e; if (v < NVAR) R[v * NB + i] = wv_get(A.r[rt][e], lane); }
+#pragma unroll
+        for (int v = 0; v < NVAR; ++v)
+#pragma unroll
+          for (int m = 0; m < NVAR; ++m)
+#pragma unroll
+            for (int ct = 0; ct < NRT; ++ct) {
+              const int j = ct * 8 + 2 * p;
+              double* dst = K + (size_t)(v * NB + i) * KS + m * NB + j;
+              const double k0 = wv_get(A.k[v][rt][m][ct][0], lane), k1 = wv_get(A.k[v][rt][m][ct][1], lane);
+              if ((NB & 1) == 0) { if (j < NB) st2(dst, k0, k1); }
+              else { if (j < NB) dst[0] = k0; if (j + 1 < NB) dst[1] = k1; }
+            }
+      }
+    });
+  }
+
+  // ---- per-row data: CRS row base (or -1 for isFixedDOF rows), lumping; lane = natural row ----------------
+  MRH_HDN static void row_setup(const KParams& kp, const LAY& L, double* sm, const int* offs, int lane) {
+    if (lane >= N) return;
+    const int* sLid = reinterpret_cast<const int*>(sm + L.oLid());
+    const int rowslot = offs[lane], row = sLid[rowslot];
+    reinterpret_cast<int64_t*>(sm + L.oRowBase())[lane] = kp.fixed[row] ? (int64_t)-1 : kp.rowptr[row];
+    if (kp.lump_mass) {                                              // assemblyManager.cpp:4130-4132
+      double* K = sm + L.oK() + (size_t)lane * KS;
+      double s = 0.0;
+      for (int c = 0; c < N; ++c) { s += K[c]; K[c] = 0.0; }
+      K[lane] = s;
+    }
+  }
+
+  // ---- scatter: rows one after the other, lanes along (node j, variable m) = consecutive element slots -----
+  MRH_HDN static void scatter(const KParams& kp, const LAY& L, const double* sm, const int* offs, int64_t e, int lane) {
+    const int64_t* rb = reinterpret_cast<const int64_t*>(sm + L.oRowBase());
+    const int* sLid = reinterpret_cast<const int*>(sm + L.oLid());
+    const double* K = sm + L.oK();
+    if (lane < N && rb[lane] >= 0) atomic_add(kp.res + sLid[offs[lane]], -sm[L.oR() + lane]);
+    if (lane >= N) return;
+    const int col = (lane % NVAR) * NB + lane / NVAR;                // natural column this lane serves
+    const int colslot = offs[col];
+    const uint16_t* pat = kp.pat + (size_t)kp.pat_id[e] * N * N + colslot;
+    for (int r = 0; r < N; ++r) {
+      const int64_t base = rb[r];
+      if (base < 0) continue;
+      atomic_add(kp.jac + base + pat[(size_t)offs[r] * N], K[(size_t)r * KS + col]);
+    }
+  }
+};
+
+}  // namespace mrh

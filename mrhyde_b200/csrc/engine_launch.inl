@@ -271,9 +271,16 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
 #undef MRH_FAST
       }
     } else {
-      if (side < 0) D.last_path = "generic";
-      const bool ok = launch_generic_assembly(H.phys, H.dim, H.order, jac != nullptr, D.num_sms, kp, (void*)stream);
-      if (!ok) throw std::runtime_error("configuration not supported: no kernel for this physics/dimension/order");
+      // volume residual + Jacobian: batched kernel (assemble_batched.h); side launches, residual-only passes and
+      // element blocks that do not fit its shared-memory layout go through the generic kernel
+      bool done = false;
+      if (side < 0 && jac != nullptr && !(H.cfg.flags & 16))
+        done = launch_batched_assembly(H.phys, H.dim, H.order, D.num_sms, kp, (void*)stream);
+      if (side < 0) D.last_path = done ? "batched" : "generic";
+      if (!done) {
+        const bool ok = launch_generic_assembly(H.phys, H.dim, H.order, jac != nullptr, D.num_sms, kp, (void*)stream);
+        if (!ok) throw std::runtime_error("configuration not supported: no kernel for this physics/dimension/order");
+      }
     }
     if (side < 0) CUDA_CK(cudaEventRecord(D.ev1, stream));
     D.launches++;

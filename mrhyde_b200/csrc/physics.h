@@ -37,10 +37,11 @@ template <int PHYS, int DIM, class S> struct Physics;
 template <int DIM, class S>
 struct Physics<PHYS_THERMAL, DIM, S> {
   static constexpr int NVAR = 1;
-  MRH_HDN static void volume(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
+  template <class IN> MRH_HD static void volume(const IN& in, S (&F)[NVAR][1 + DIM]) {
     const S source = in.fn(TH_SOURCE), diff = in.fn(TH_DIFF), cp = in.fn(TH_CP), rho = in.fn(TH_RHO);
     const double w = in.w;
     F[0][0] = (rho * cp * in.Ut(0) - source) * w;
+#pragma unroll
     for (int c = 0; c < DIM; ++c) F[0][1 + c] = diff * in.dU(0, c) * w;
     if (in.kp->ph.have_advection) {
       S adv = in.fn(TH_BX) * in.dU(0, 0);
@@ -59,8 +60,10 @@ struct Physics<PHYS_THERMAL, DIM, S> {
       const double epen = 10.0, sf = in.kp->ph.formparam;
       const S dT = in.U(0) - nsource;
       S gn = in.dU(0, 0) * in.ps.nrm[0];
+#pragma unroll
       for (int c = 1; c < DIM; ++c) gn = gn + in.dU(0, c) * in.ps.nrm[c];
       F[0][0] = F[0][0] + epen / in.h * diff * dT * w + (-diff * gn) * w;
+#pragma unroll
       for (int c = 0; c < DIM; ++c) F[0][1 + c] = F[0][1 + c] + (-sf * diff * dT * w) * in.ps.nrm[c];
     }
   }
@@ -70,13 +73,15 @@ struct Physics<PHYS_THERMAL, DIM, S> {
 template <int DIM, class S>
 struct Physics<PHYS_CDR, DIM, S> {
   static constexpr int NVAR = 1;
-  MRH_HDN static void volume(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
+  template <class IN> MRH_HD static void volume(const IN& in, S (&F)[NVAR][1 + DIM]) {
     const S source = in.fn(CDR_SOURCE), diff = in.fn(CDR_DIFF), cp = in.fn(CDR_CP), rho = in.fn(CDR_RHO), reax = in.fn(CDR_REACTION);
     const double w = in.w;
     S f = in.Ut(0);
+#pragma unroll
     for (int c = 0; c < DIM; ++c) f = f + in.fn(CDR_XVEL + c) * in.dU(0, c);
     F[0][0] = (f + reax - source) * w;
     const S k = 1.0 / (rho * cp) * diff;
+#pragma unroll
     for (int c = 0; c < DIM; ++c) F[0][1 + c] = k * in.dU(0, c) * w;
   }
   MRH_HDN static void boundary(const PointIn<S>&, S (&)[NVAR][1 + DIM]) {}   // cdr.cpp:148-150 is empty
@@ -86,8 +91,10 @@ struct Physics<PHYS_CDR, DIM, S> {
 template <int DIM, class S>
 struct Physics<PHYS_LE, DIM, S> {
   static constexpr int NVAR = DIM;
-  MRH_HDN static void stress(const PointIn<S>& in, const S& lambda, const S& mu, S (&Sg)[DIM][DIM]) {
+  template <class IN> MRH_HD static void stress(const IN& in, const S& lambda, const S& mu, S (&Sg)[DIM][DIM]) {
+#pragma unroll
     for (int a = 0; a < DIM; ++a)
+#pragma unroll
       for (int b = 0; b < DIM; ++b) {
         if (a == b) {
           S s = (2.0 * mu + lambda) * in.dU(a, a);
@@ -100,24 +107,30 @@ struct Physics<PHYS_LE, DIM, S> {
         }
       }
   }
-  MRH_HDN static void volume(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
+  template <class IN> MRH_HD static void volume(const IN& in, S (&F)[NVAR][1 + DIM]) {
     const S lambda = in.fn(LE_LAMBDA), mu = in.fn(LE_MU);
     S Sg[DIM][DIM];
     stress(in, lambda, mu, Sg);
+#pragma unroll
     for (int a = 0; a < DIM; ++a) {
       F[a][0] = (-in.fn(LE_SRC0 + a)) * in.w;
+#pragma unroll
       for (int c = 0; c < DIM; ++c) F[a][1 + c] = Sg[a][c] * in.w;
     }
   }
   MRH_HDN static void boundary(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
     const int* bc = in.kp->ph.bc;
     bool alld = true;
+#pragma unroll
     for (int c = 0; c < DIM; ++c) if (bc[c] != BC_DIRICHLET) alld = false;
     if (alld) return;
     bool anyweak = false;
+#pragma unroll
     for (int c = 0; c < DIM; ++c) if (bc[c] == BC_WEAK_DIRICHLET) anyweak = true;
     S src[DIM];
+#pragma unroll
     for (int c = 0; c < DIM; ++c) src[c] = (bc[c] == BC_NEUMANN || bc[c] == BC_WEAK_DIRICHLET) ? in.fn(SIDE_BCSRC + c) : S(0.0);
+#pragma unroll
     for (int a = 0; a < DIM; ++a) if (bc[a] == BC_NEUMANN) F[a][0] = F[a][0] + (-src[a]) * in.w;
     if (!anyweak) return;
     const S lam = in.fn(SIDE_LAMBDA), mu = in.fn(SIDE_MU);
@@ -126,13 +139,17 @@ struct Physics<PHYS_LE, DIM, S> {
     const double* n = in.ps.nrm;
     const S penalty = in.kp->ph.le_penalty * (lam + 2.0 * mu) / in.h;
     S delta[DIM];
+#pragma unroll
     for (int c = 0; c < DIM; ++c) delta[c] = in.U(c) - src[c];
+#pragma unroll
     for (int a = 0; a < DIM; ++a) {
       if (bc[a] != BC_WEAK_DIRICHLET) continue;
       S bvec[DIM];
+#pragma unroll
       for (int c = 0; c < DIM; ++c) {
         if (c == a) {
           S t = ((0 == a) ? (lam + 2.0 * mu) * delta[0] * n[0] : lam * delta[0] * n[0]);
+#pragma unroll
           for (int m = 1; m < DIM; ++m) t = t + ((m == a) ? (lam + 2.0 * mu) * delta[m] * n[m] : lam * delta[m] * n[m]);
           bvec[c] = t;
         } else {
@@ -141,8 +158,10 @@ struct Physics<PHYS_LE, DIM, S> {
         }
       }
       S sn = -Sg[a][0] * n[0];
+#pragma unroll
       for (int c = 1; c < DIM; ++c) sn = sn - Sg[a][c] * n[c];
       F[a][0] = F[a][0] + (sn + penalty * delta[a]) * in.w;
+#pragma unroll
       for (int c = 0; c < DIM; ++c) F[a][1 + c] = F[a][1 + c] + (-in.kp->ph.formparam * in.w) * bvec[c];
     }
   }
@@ -153,9 +172,10 @@ template <int DIM, class S>
 struct Physics<PHYS_NS, DIM, S> {
   static constexpr int NVAR = DIM + 1;
   MRH_HD static int uvar(int a) { return a == 0 ? 0 : a + 1; }       // varlist = ux, pr, uy, uz
-  MRH_HDN static S tau(const S& visc, const S* vel, double h, double dt, int transient) {
+  MRH_HD static S tau(const S& visc, const S* vel, double h, double dt, int transient) {
     const double C1 = 4.0, C2 = 2.0, C3 = transient ? 2.0 : 0.0;
     S nvel = vel[0] * vel[0];
+#pragma unroll
     for (int c = 1; c < DIM; ++c) nvel = nvel + vel[c] * vel[c];
     if (val(nvel) > 1E-12) nvel = f_sqrt(nvel);
     const S a = C1 * visc / h / h, b = C2 * nvel / h;
@@ -163,22 +183,27 @@ struct Physics<PHYS_NS, DIM, S> {
     S t = a * a + b * b + c3 * c3;
     return 1.0 / f_sqrt(t);
   }
-  MRH_HDN static void volume(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
+  template <class IN> MRH_HD static void volume(const IN& in, S (&F)[NVAR][1 + DIM]) {
     const double w = in.w;
     const int srcslot[3] = {NS_SRC_UX, NS_SRC_UY, NS_SRC_UZ};
     const S dens = in.fn(NS_DENSITY), visc = in.fn(NS_VISCOSITY);
+#pragma unroll
     for (int v = 0; v < NVAR; ++v) for (int a = 0; a <= DIM; ++a) F[v][a] = S(0.0);
     S vel[DIM], src[DIM], strong[DIM];
+#pragma unroll
     for (int c = 0; c < DIM; ++c) { vel[c] = in.U(uvar(c)); src[c] = in.fn(srcslot[c]); }
     const S pr = in.U(1);
     const bool need_tau = in.kp->ph.useSUPG || in.kp->ph.usePSPG;
     S tauv = S(0.0);
     if (need_tau) tauv = tau(visc, vel, in.h, in.kp->tp.dt, in.kp->tp.transient);
+#pragma unroll
     for (int a = 0; a < DIM; ++a) {
       const int ua = uvar(a);
       const int rowvar = (DIM == 3 && a == 2) ? uvar(1) : ua;        // reference quirk, navierstokes.cpp:688
       S conv = vel[0] * in.dU(ua, 0);
+#pragma unroll
       for (int c = 1; c < DIM; ++c) conv = conv + vel[c] * in.dU(ua, c);
+#pragma unroll
       for (int c = 0; c < DIM; ++c) {
         S Fc = visc * in.dU(ua, c);
         if (c == a) Fc = Fc - pr;
@@ -186,16 +211,22 @@ struct Physics<PHYS_NS, DIM, S> {
       }
       F[rowvar][0] = F[rowvar][0] + (in.Ut(ua) + conv - src[a]) * (dens * w);
       strong[a] = dens * in.Ut(ua) + dens * conv + in.dU(1, a) - dens * src[a];
-      if (in.kp->ph.useSUPG)
+      if (in.kp->ph.useSUPG) {
+#pragma unroll
         for (int c = 0; c < DIM; ++c) F[rowvar][1 + c] = F[rowvar][1 + c] + tauv * strong[a] * vel[c] * w;
+      }
     }
     S divu = in.dU(uvar(0), 0);
+#pragma unroll
     for (int c = 1; c < DIM; ++c) divu = divu + in.dU(uvar(c), c);
     F[1][0] = F[1][0] + divu * w;
-    if (in.kp->ph.usePSPG)
+    if (in.kp->ph.usePSPG) {
+#pragma unroll
       for (int c = 0; c < DIM; ++c) F[1][1 + c] = F[1][1 + c] + strong[c] * (tauv * w / dens);
+    }
   }
   MRH_HDN static void boundary(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
+#pragma unroll
     for (int a = 0; a < DIM; ++a) {
       const int ua = uvar(a);
       if (in.kp->ph.bc[ua] == BC_NEUMANN) F[ua][0] = F[ua][0] + (-in.fn(SIDE_BCSRC + ua)) * in.w;

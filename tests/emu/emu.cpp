@@ -2,16 +2,18 @@
 // (mrhyde_b200/csrc/assemble.h) on the CPU so the kernel arithmetic can be checked against the oracle in the
 // GPU-less build container.  Exports the same C ABI as libmrhyde_b200.so so tests drive both with one wrapper.
 // The product library never links or calls this file; without a GPU the product fails with MRH_ECUDA.
+#include <memory>
 #include "../../mrhyde_b200/csrc/capi_host.inl"
 #include "../../mrhyde_b200/csrc/dispatch.h"
 #include "../../mrhyde_b200/csrc/assemble_fast.h"
 #include "../../mrhyde_b200/csrc/assemble_fast2d.h"
+#include "../../mrhyde_b200/csrc/assemble_batched.h"
 
 using namespace mrh;
 
 struct EmuImpl {
   std::vector<uint16_t> pat; std::vector<int> pat_id;
-  int64_t launches = 0, fast_launches = 0;
+  int64_t launches = 0, fast_launches = 0, batched_launches = 0;
 };
 
 static int backend_create(mrh_engine* h) { h->impl = new EmuImpl(); return MRH_OK; }
@@ -36,6 +38,31 @@ static void run_launch(const KParams& kp) {
   }
 }
 
+// the batched volume kernel (batched_kernels.cu), stepped phase by phase: one "warp" of 32 explicit lanes per element
+template <class C>
+static bool run_batched(const KParams& kp) {
+  using G = GenPhases<C>;
+  using B = BatPhases<C>;
+  WarpSmem<C> L(kp.tab.nq, kp.tp.transient != 0);
+  std::vector<double> sm(L.total_doubles());
+  std::vector<int> offs(kp.offsets, kp.offsets + C::N);
+  const int nq = L.nq, nparts = B::geom_parts(nq), n1 = B::num_kind1(kp);
+  auto acc = std::make_unique<typename B::Acc>();
+  for (int64_t w = 0; w < kp.nwork; ++w) {
+    for (int it = 0; it < C::N; ++it) G::gather_dof(kp, L, sm.data(), w, it);
+    for (int it = 0; it < C::NV; ++it) G::gather_vertex(kp, L, sm.data(), w, it);
+    for (int it = 0; it < nq * nparts; ++it) B::geometry(kp, L, sm.data(), it, nparts);
+    for (int it = 0; it < nq * n1; ++it) B::prep(kp, L, sm.data(), it, n1);
+    B::element_size(L, sm.data());
+    for (int it = 0; it < nq * B::NCH; ++it) B::point_chunk(kp, L, sm.data(), it);
+    B::contract(L, sm.data(), *acc);
+    B::store_acc(L, sm.data(), *acc);
+    for (int lane = 0; lane < 32; ++lane) B::row_setup(kp, L, sm.data(), offs.data(), lane);
+    for (int lane = 0; lane < 32; ++lane) B::scatter(kp, L, sm.data(), offs.data(), G::elem_of(kp, w), lane);
+  }
+  return true;
+}
+
 static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac) {
   auto& H = h->host; auto* E = (EmuImpl*)h->impl;
   if (!H.host_final || E->pat_id.empty()) throw std::runtime_error("mrh_finalize has not been called");
@@ -47,7 +74,7 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
     for (int c = 0; c < 3; ++c) { r.tanU[c] = T.tanU[c]; r.tanV[c] = T.tanV[c]; } return r; };
   bp.vol_tab = tab(H.ref.vol);
   for (int s = 0; s < H.ref.nsides; ++s) bp.side_tab[s] = tab(H.ref.side[s]);
-  E->launches = 0; E->fast_launches = 0;
+  E->launches = 0; E->fast_launches = 0; E->batched_launches = 0;
   for (int side = -1; side < (int)H.side_launches.size(); ++side) {
     if (side >= 0 && !H.side_launches[side].active) continue;
     KParams kp;
@@ -74,6 +101,11 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
 #undef MRH_FAST2D
       }
       E->launches++; E->fast_launches++;
+      continue;
+    }
+    if (side < 0 && jac && !(H.cfg.flags & 16)) {
+      if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_batched<decltype(c)>(kp); })) throw std::runtime_error("configuration not supported");
+      E->launches++; E->batched_launches++;
       continue;
     }
     if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_launch<decltype(c)>(kp); }))
@@ -131,7 +163,11 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st, double* res, dou
   return emu_assemble(h, st, res, jac);
   MRH_CATCH(h)
 }
-const char* mrh_last_kernel_path(mrh_handle h) { return (h && ((EmuImpl*)h->impl)->fast_launches) ? "specialised" : "generic"; }
+const char* mrh_last_kernel_path(mrh_handle h) {
+  if (!h) return "generic";
+  auto* E = (EmuImpl*)h->impl;
+  return E->fast_launches ? "specialised" : E->batched_launches ? "batched" : "generic";
+}
 int64_t mrh_last_launch_count(mrh_handle h) { return h ? ((EmuImpl*)h->impl)->launches : 0; }
 double mrh_last_volume_kernel_ms(mrh_handle h) { return h ? -(double)((EmuImpl*)h->impl)->fast_launches : 0.0; }  // emu: -#specialised launches
 int mrh_microbench(int32_t, double*, double*, double*) { return MRH_EUNSUPPORTED; }

@@ -25,8 +25,23 @@ def test_cuda_matches_oracle(lib, name, p, kw):
 
 @pytest.mark.parametrize("name,p,kw", [c for c in CASES if c[1]["physics"] == "thermal" and c[1]["mesh"]["dim"] == 3],
                          ids=lambda v: v if isinstance(v, str) else "")
-def test_cuda_generic_kernel_on_specialised_cases(lib, name, p, kw):
-    U.check_case(p, kw, lib, on_gpu=True, force_generic=True)
+def test_cuda_batched_kernel_on_specialised_cases(lib, name, p, kw):
+    """thermal 3-D cases through the batched volume kernel instead of the specialised one"""
+    r = U.check_case(p, kw, lib, on_gpu=True, force_generic=True)
+    assert r["path"] == "batched", r
+
+
+@pytest.mark.parametrize("name,p,kw", CASES, ids=[c[0] for c in CASES])
+def test_cuda_generic_kernel_alone(lib, name, p, kw):
+    """every case through the generic kernel only (no specialised, no batched volume kernel)"""
+    r = U.check_case(p, kw, lib, on_gpu=True, force_generic=True, no_batched=True)
+    assert r["path"] == "generic", r
+
+
+def test_default_path_of_multivariable_configs_is_batched(lib):
+    for mk, n in ((problems.config_c3, 3), (problems.config_c4, 5), (problems.config_c5, 4)):
+        r = U.check_case(mk(n), {}, lib, on_gpu=True)
+        assert r["path"] == "batched", r
 
 
 @pytest.mark.parametrize("name,p,kw", [c for c in CASES if c[1]["physics"] == "thermal" and c[1]["mesh"]["dim"] == 3],
@@ -36,7 +51,7 @@ def test_cuda_specialised_kernel_variants(lib, name, p, kw, no_jit, no_tiles, no
     """the specialised kernel without the NVRTC step (bytecode interpreter inside the kernel), with the direct
     instead of the tile-staged scatter, and the tile-staged scatter without warp specialisation"""
     r = U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws)
-    if r["path"] != "generic":          # cases with state-dependent coefficients stay on the generic kernel
+    if r["path"] not in ("generic", "batched"):   # cases with state-dependent coefficients use the batched kernel
         assert ("nvrtc" in r["path"]) == (not no_jit) and ("tiled" in r["path"]) == (not no_tiles), r
         assert r["path"].endswith("-ws") == (not no_jit and not no_tiles and not no_ws), r
     U.check_case(p, kw, lib, on_gpu=True, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws, jacobian=False)
@@ -49,7 +64,7 @@ def test_cuda_thermal_quad_kernel_variants(lib, name, p, kw, force_generic, no_j
     """2-D thermal Q1 cases through the specialised quadrilateral kernel (NVRTC-printed coefficients, or the bytecode
     interpreter inside the kernel) and through the generic kernel"""
     r = U.check_case(p, kw, lib, on_gpu=True, force_generic=force_generic, no_jit=no_jit)
-    if r["path"] != "generic":
+    if r["path"] not in ("generic", "batched"):
         assert not force_generic
         assert r["path"] == ("specialised-2d" if no_jit else "nvrtc-specialised-2d"), r
     U.check_case(p, kw, lib, on_gpu=True, force_generic=force_generic, no_jit=no_jit, jacobian=False)
