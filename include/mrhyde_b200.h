@@ -58,7 +58,8 @@ typedef struct mrh_config {
   double le_penalty;          /* LE "penalty" (default 10.0) */
   int32_t device;             /* CUDA device ordinal */
   int32_t flags;              /* bit 0: force the generic kernel; bit 1: no NVRTC specialisation;
-                               * bit 2: direct instead of tile-staged scatter; bit 3: no warp-specialised kernel; bit 4: no batched kernel (tests) */
+                               * bit 2: direct instead of tile-staged scatter; bit 3: no warp-specialised kernel; bit 4: no batched kernel;
+                               * bit 5: NVRTC-specialise the batched kernel on small meshes too (tests) */
 } mrh_config;
 
 /* Workset time data: Workset::{time,deltat,isTransient,current_stage,butcher_A,butcher_b,BDF_wts}

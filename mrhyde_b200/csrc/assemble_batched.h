@@ -73,11 +73,12 @@ struct WarpSmem {
   static constexpr int N = C::N, NVAR = C::NVAR, NB = C::NB, TA = C::TA;
   static constexpr int NT = (NVAR + 1) / 2;                    // column tiles of D: variables (2t, 2t+1)
   static constexpr int NRT = (NB + 7) / 8;                     // row tiles of 8 basis functions
-  static constexpr int QS = NVAR * NT * 32 + 2;                // D fragments of one point (+2: spreads points over banks)
+  static constexpr int QS = NVAR * NT * 32 + 1;                // D fragments of one point; with dq() the lanes (q, m) of one store spread evenly over the banks
   static constexpr int KS = ((N + 7) / 16) * 16 + 8;           // row stride of K, == 8 (mod 16): conflict-free 16-byte stores
   static_assert(KS >= N, "row stride of the element matrix");
   MRH_HD WarpSmem(int nq_, bool tr) : nq(nq_), transient(tr) {}
-  MRH_HD size_t dsize() const { return (size_t)nq * QS; }
+  MRH_HD static size_t dq(int q) { return (size_t)q * QS + (size_t)((q >> 2) << 2); }
+  MRH_HD size_t dsize() const { return even_up(dq(nq)); }
   MRH_HD bool k_aliases_d() const { return (size_t)N * KS <= dsize(); }
   MRH_HD size_t oX() const { return 0; }
   MRH_HD size_t oU() const { return even_up(oX() + (size_t)C::NV * C::DIM); }
@@ -231,7 +232,7 @@ struct BatPhases {
     Physics<C::PHYS, DIM, S>::volume(in, F);
     // f -> F[q][v][a];  dF_(v,a)/d(m,b) -> B-fragment order: tile (v, t = m/2), lane = a + 4 ((m & 1) + 2 b)
     double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
-    double* Dq = sm + L.oD() + (size_t)q * QS;
+    double* Dq = sm + L.oD() + LAY::dq(q);
     const int t = ch >> 1, half = ch & 1;
     const bool phantom = (NVAR & 1) && ch == NVAR - 1;           // odd variable count: this lane also zeroes column m + 1
 #pragma unroll
@@ -268,7 +269,7 @@ struct BatPhases {
     for (int q = 0; q < L.nq; ++q) {
       const double* T = sm + L.oT() + (size_t)q * NB * TA;
       const double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
-      const double* Dq = sm + L.oD() + (size_t)q * QS;
+      const double* Dq = sm + L.oD() + LAY::dq(q);
       WV tf[NRT];
 #pragma unroll
       for (int rt = 0; rt < NRT; ++rt)
@@ -348,12 +349,124 @@ struct BatPhases {
     const int col = (lane % NVAR) * NB + lane / NVAR;                // natural column this lane serves
     const int colslot = offs[col];
     const uint16_t* pat = kp.pat + (size_t)kp.pat_id[e] * N * N + colslot;
-    for (int r = 0; r < N; ++r) {
-      const int64_t base = rb[r];
-      if (base < 0) continue;
-      atomic_add(kp.jac + base + pat[(size_t)offs[r] * N], K[(size_t)r * KS + col]);
+    constexpr int UR = 4;                                            // rows in flight: the slot loads of UR rows overlap
+    for (int r0 = 0; r0 < N; r0 += UR) {
+      int64_t base[UR]; uint16_t slot[UR];
+#pragma unroll
+      for (int k = 0; k < UR; ++k) {
+        const int r = r0 + k;
+        base[k] = r < N ? rb[r] : (int64_t)-1;
+        slot[k] = base[k] >= 0 ? pat[(size_t)offs[r] * N] : (uint16_t)0;
+      }
+#pragma unroll
+      for (int k = 0; k < UR; ++k)
+        if (base[k] >= 0) atomic_add(kp.jac + base[k] + slot[k], K[(size_t)(r0 + k) * KS + col]);
     }
   }
 };
+
+#if defined(__CUDACC__)
+// Coefficient-program policy of the kernel body: the bytecode interpreter (ahead-of-time build, batched_kernels.cu)
+// or straight-line functions printed from the bytecode and compiled with NVRTC at mrh_finalize (jit.hpp: JitProgs).
+struct InterpProgs {
+  static constexpr bool jit = false;
+  static __device__ __forceinline__ double eval(int, double, double, double, double) { return 0.0; }
+};
+
+// One warp per element, grid-stride over the elements of the launch.  smem_all: [offsets | one WarpSmem block per warp].
+template <class C, class PROGS>
+__device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all) {
+  using G = GenPhases<C>;
+  using B = BatPhases<C>;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const WarpSmem<C> L(kp.tab.nq, kp.tp.transient != 0);
+  int* offs = reinterpret_cast<int*>(smem_all);                        // offsets(var, basis) -> element slot, CTA-shared
+  for (int k = threadIdx.x; k < C::N; k += blockDim.x) offs[k] = kp.offsets[k];
+  __syncthreads();
+  double* sm = smem_all + even_up((C::N + 1) / 2) + (size_t)warp * L.total_doubles();
+  const int nq = L.nq, nparts = B::geom_parts(nq), n1 = B::num_kind1(kp);
+  // Steady-state gather, software-pipelined two elements deep: the element -> DOF / vertex indices of element w + 2 stride
+  // and the solution / coordinate values of element w + stride are in flight while element w is processed
+  // (lane k < N owns DOF slot k, lane a < NV owns vertex a).  Transient launches use the plain gather (stage / BDF sums).
+  const bool pipelined = !kp.tp.transient;
+  const int64_t w_first = (int64_t)blockIdx.x * nwarp + warp, w_stride = (int64_t)gridDim.x * nwarp;
+  int lidA = 0, ndA = 0, lidB = 0, ndB = 0;
+  double uA = 0.0, xA[C::DIM];
+  auto load_idx = [&](int64_t w, int& lid, int& nd) {
+    const int64_t e = G::elem_of(kp, w);
+    if (lane < C::N) lid = kp.lids[e * C::N + lane];
+    if (lane < C::NV) nd = kp.e2n[e * C::NV + lane];
+  };
+  auto load_val = [&](int lid, int nd) {
+    if (lane < C::N) uA = kp.u[lid];
+    if (lane < C::NV) {
+#pragma unroll
+      for (int c = 0; c < C::DIM; ++c) xA[c] = kp.nodes[(int64_t)nd * C::DIM + c];
+    }
+  };
+  if (pipelined && w_first < kp.nwork) {
+    load_idx(w_first, lidA, ndA);
+    if (w_first + w_stride < kp.nwork) load_idx(w_first + w_stride, lidB, ndB);
+    load_val(lidA, ndA);
+  }
+  for (int64_t w = w_first; w < kp.nwork; w += w_stride) {
+    if (pipelined) {
+      if (lane < C::N) { reinterpret_cast<int*>(sm + L.oLid())[lane] = lidA; sm[L.oU() + lane] = uA; }
+      if (lane < C::NV) {
+#pragma unroll
+        for (int c = 0; c < C::DIM; ++c) sm[L.oX() + lane * C::DIM + c] = xA[c];
+      }
+      if (w + w_stride < kp.nwork) { lidA = lidB; ndA = ndB; load_val(lidA, ndA); }
+      if (w + 2 * w_stride < kp.nwork) load_idx(w + 2 * w_stride, lidB, ndB);
+    } else {
+      for (int it = lane; it < C::N; it += 32) G::gather_dof(kp, L, sm, w, it);
+      for (int it = lane; it < C::NV; it += 32) G::gather_vertex(kp, L, sm, w, it);
+    }
+    __syncwarp();
+    for (int it = lane; it < nq * nparts; it += 32) B::geometry(kp, L, sm, it, nparts);
+    __syncwarp();
+    if (PROGS::jit) {
+      for (int q = lane; q < nq; q += 32) {
+        const double x = sm[L.oXq() + (size_t)q * 3], y = sm[L.oXq() + (size_t)q * 3 + 1], z = sm[L.oXq() + (size_t)q * 3 + 2];
+#pragma unroll
+        for (int k = 0; k < MRH_NCOEF; ++k)
+          if (kp.progs[k].kind == 1) sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = PROGS::eval(k, x, y, z, kp.tp.time);
+      }
+    } else {
+      for (int it = lane; it < nq * n1; it += 32) B::prep(kp, L, sm, it, n1);
+    }
+    if (lane == 31) B::element_size(L, sm);
+    __syncwarp();
+    for (int it = lane; it < nq * B::NCH; it += 32) B::point_chunk(kp, L, sm, it);
+    __syncwarp();
+    typename B::Acc acc;
+    B::contract(L, sm, acc);
+    __syncwarp();                                          // every lane is done with D: K may take its place
+    B::store_acc(L, sm, acc);
+    __syncwarp();
+    B::row_setup(kp, L, sm, offs, lane);
+    __syncwarp();
+    B::scatter(kp, L, sm, offs, G::elem_of(kp, w), lane);
+    __syncwarp();                                          // the next element reuses the block
+  }
+}
+#endif
+
+#if !defined(__CUDACC_RTC__)
+constexpr int MRH_BATCHED_MAXW = 4;       // warps per CTA (fewer when one element's shared-memory block is large)
+// warps per CTA that put the most warps on one SM, and the dynamic shared memory of such a CTA; false: does not fit
+template <class C>
+inline bool batched_shape(int nq, bool transient, int& nw, size_t& smem) {
+  const size_t per = WarpSmem<C>(nq, transient).total_doubles() * sizeof(double);
+  const size_t head = even_up((C::N + 1) / 2) * sizeof(double);
+  nw = 0; size_t best = 0;
+  for (int c = MRH_BATCHED_MAXW; c >= 1; --c) {
+    const size_t total = ((size_t)227 * 1024 / (head + c * per + 1024)) * c;
+    if (total > best) { best = total; nw = c; }
+  }
+  smem = head + (size_t)nw * per;
+  return nw > 0;
+}
+#endif
 
 }  // namespace mrh

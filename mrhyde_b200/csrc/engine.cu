@@ -11,6 +11,8 @@
 #include "capi_host.inl"
 #include "assemble_fast.h"
 #include "assemble_fast2d.h"
+#include "assemble_batched.h"
+#include "dispatch.h"
 #include "generic_kernels.h"
 #include "jit.hpp"
 

@@ -78,6 +78,25 @@ void device_finalize(mrh_engine* h) {
       if (!D.jit.thermal(false, adv, true) || !D.jit.thermal(false, adv, false)) h->err = "NVRTC specialisation unavailable, using the in-kernel interpreter: " + D.jit.last_error;
     } catch (const std::exception& ex) { D.jit.clear(); h->err = std::string("NVRTC specialisation skipped: ") + ex.what(); }
   }
+  // NVRTC specialisation of the state-independent programs for the batched volume kernel (assemble_batched.h): pays off
+  // on large meshes only (the compile takes seconds), flag bit 5 forces it (tests)
+  {
+    const bool thermal_fast = !(H.cfg.flags & 1) && (quad2d || thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass));
+    bool any1 = false;
+    for (int k = 0; k < MRH_NCOEF; ++k) any1 = any1 || H.vol_progs[k].kind == 1;
+    if (!thermal_fast && any1 && !(H.cfg.flags & (2 | 16)) && (H.mesh.nelem >= 32768 || (H.cfg.flags & 32))) {
+      try {
+        std::string src;
+        for (int k = 0; k < MRH_NCOEF; ++k) {
+          const std::string name = "p" + std::to_string(k);
+          if (H.vol_progs[k].kind == 1) src += jit_function_source(name, H.vol_progs[k], H.ec.code, H.ec.cpool);
+          else src += "  static __device__ __forceinline__ double " + name + "(double, double, double, double) { return 0.0; }\n";
+        }
+        D.jit.setBatchedSource(src, H.phys, H.dim, H.order);
+        if (!D.jit.batched()) h->err = "NVRTC specialisation of the batched kernel unavailable, using the in-kernel interpreter: " + D.jit.last_error;
+      } catch (const std::exception& ex) { h->err = std::string("NVRTC specialisation of the batched kernel skipped: ") + ex.what(); }
+    }
+  }
   D.dbc.upload(H.dbc_dofs); D.dbc_slots.alloc(H.dbc_dofs.size());
   if (!H.dbc_dofs.empty()) {
     dbc_slot_kernel<<<blocks_for((int64_t)H.dbc_dofs.size(), 128), 128>>>(D.dbc.p, (int64_t)H.dbc_dofs.size(), D.rowptr.p, D.colind.p, D.dbc_slots.p);
@@ -273,10 +292,31 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
     } else {
       // volume residual + Jacobian: batched kernel (assemble_batched.h); side launches, residual-only passes and
       // element blocks that do not fit its shared-memory layout go through the generic kernel
-      bool done = false;
-      if (side < 0 && jac != nullptr && !(H.cfg.flags & 16))
-        done = launch_batched_assembly(H.phys, H.dim, H.order, D.num_sms, kp, (void*)stream);
-      if (side < 0) D.last_path = done ? "batched" : "generic";
+      bool done = false, jitted = false;
+      if (side < 0 && jac != nullptr && !(H.cfg.flags & 16)) {
+        JitKernel* jk = D.jit.hasBatchedSource() ? D.jit.batched() : nullptr;
+        if (jk) {
+          int nw = 0; size_t smem = 0; bool fits = false;
+          dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { fits = batched_shape<decltype(c)>(kp.tab.nq, kp.tp.transient != 0, nw, smem); });
+          if (fits) {
+            JitApi& api = JitApi::get();
+            if (jk->smem_set != smem) {
+              if (api.FuncSetAttribute(jk->fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem) != CUDA_SUCCESS)
+                throw std::runtime_error("CUDA error: cuFuncSetAttribute(shared memory) failed");
+              if (api.OccupancyMaxActiveBlocks(&jk->blocks_per_sm, jk->fn, 32 * nw, smem) != CUDA_SUCCESS || jk->blocks_per_sm < 1) jk->blocks_per_sm = 1;
+              jk->smem_set = smem;
+            }
+            kp.elems_per_block = nw;
+            const unsigned grid = (unsigned)std::min<int64_t>((kp.nwork + nw - 1) / nw, (int64_t)D.num_sms * jk->blocks_per_sm);
+            void* args[] = {(void*)&kp};
+            if (api.LaunchKernel(jk->fn, grid, 1, 1, 32 * nw, 1, 1, (unsigned)smem, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+              throw std::runtime_error("CUDA error: cuLaunchKernel failed for the NVRTC-specialised batched kernel");
+            done = jitted = true;
+          }
+        }
+        if (!done) done = launch_batched_assembly(H.phys, H.dim, H.order, D.num_sms, kp, (void*)stream);
+      }
+      if (side < 0) D.last_path = jitted ? "nvrtc-batched" : done ? "batched" : "generic";
       if (!done) {
         const bool ok = launch_generic_assembly(H.phys, H.dim, H.order, jac != nullptr, D.num_sms, kp, (void*)stream);
         if (!ok) throw std::runtime_error("configuration not supported: no kernel for this physics/dimension/order");

@@ -149,8 +149,13 @@ struct JitKernel {
 class JitCache {
  public:
   std::string last_error;
-  ~JitCache() { for (auto& kv : kernels_) if (kv.second.mod && JitApi::get().ok) JitApi::get().ModuleUnload(kv.second.mod); }
-  void clear() { for (auto& kv : kernels_) if (kv.second.mod && JitApi::get().ok) JitApi::get().ModuleUnload(kv.second.mod); kernels_.clear(); coef_src_.clear(); }
+  ~JitCache() { clear(); }
+  void clear() {
+    for (auto& kv : kernels_) if (kv.second.mod && JitApi::get().ok) JitApi::get().ModuleUnload(kv.second.mod);
+    kernels_.clear(); coef_src_.clear();
+    if (bat_.mod && JitApi::get().ok) JitApi::get().ModuleUnload(bat_.mod);
+    bat_ = JitKernel(); bat_tried_ = false;
+  }
   void setCoefficientSource(const std::string& s, int dim = 3) { clear(); coef_src_ = s; dim_ = dim; }
   bool hasSource() const { return !coef_src_.empty(); }
 
@@ -210,7 +215,48 @@ class JitCache {
     return &K;
   }
 
+  // ---- batched volume kernel (assemble_batched.h) with the state-independent programs printed as functions p0..p7 ----
+  void setBatchedSource(const std::string& progs, int phys, int dim, int order) {
+    if (bat_.mod && JitApi::get().ok) JitApi::get().ModuleUnload(bat_.mod);
+    bat_ = JitKernel(); bat_tried_ = false;
+    bat_.source = std::string("#include \"assemble_batched.h\"\nnamespace mrh {\nstruct JitProgs {\n  static constexpr bool jit = true;\n") + progs +
+        "  static __device__ __forceinline__ double eval(int k, double x, double y, double z, double t) {\n    switch (k) {\n"
+        "      case 0: return p0(x, y, z, t); case 1: return p1(x, y, z, t); case 2: return p2(x, y, z, t); case 3: return p3(x, y, z, t);\n"
+        "      case 4: return p4(x, y, z, t); case 5: return p5(x, y, z, t); case 6: return p6(x, y, z, t); default: return p7(x, y, z, t);\n    }\n  }\n};\n}\n"
+        "extern \"C\" __global__ void __launch_bounds__(128) mrh_jit_batched(const __grid_constant__ mrh::KParams kp) {\n"
+        "  extern __shared__ __align__(16) double smem_all[];\n"
+        "  mrh::batched_body<mrh::GenCfg<" + std::to_string(phys) + ", " + std::to_string(dim) + ", " + std::to_string(order) + ">, mrh::JitProgs>(kp, smem_all);\n}\n";
+  }
+  bool hasBatchedSource() const { return !bat_.source.empty(); }
+  const std::string& batchedSource() const { return bat_.source; }
+  // returns nullptr (and sets last_error) when the kernel cannot be built; the build is attempted once
+  JitKernel* batched() {
+    if (bat_tried_) return bat_.fn ? &bat_ : nullptr;
+    bat_tried_ = true;
+    JitApi& api = JitApi::get();
+    if (!api.ok) { last_error = api.why; return nullptr; }
+    if (bat_.source.empty()) { last_error = "no program source"; return nullptr; }
+    std::vector<const char*> hdr_src, hdr_name;
+    for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
+    nvrtcProgram prog;
+    if (api.CreateProgram(&prog, bat_.source.c_str(), "mrh_jit_batched.cu", (int)hdr_src.size(), hdr_src.data(), hdr_name.data()) != NVRTC_SUCCESS) { last_error = "nvrtcCreateProgram failed"; return nullptr; }
+    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1"};
+    const nvrtcResult rc = api.CompileProgram(prog, 4, opts);
+    size_t ls = 0; api.GetProgramLogSize(prog, &ls);
+    if (ls > 1) { bat_.log.resize(ls); api.GetProgramLog(prog, &bat_.log[0]); }
+    if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + bat_.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }
+    size_t cs = 0; api.GetCUBINSize(prog, &cs);
+    std::vector<char> cubin(cs);
+    api.GetCUBIN(prog, cubin.data());
+    api.DestroyProgram(&prog);
+    if (api.ModuleLoadData(&bat_.mod, cubin.data()) != CUDA_SUCCESS) { last_error = "cuModuleLoadData failed"; bat_.mod = nullptr; return nullptr; }
+    if (api.ModuleGetFunction(&bat_.fn, bat_.mod, "mrh_jit_batched") != CUDA_SUCCESS) { last_error = "kernel symbol not found"; bat_.fn = nullptr; return nullptr; }
+    return &bat_;
+  }
+
  private:
+  JitKernel bat_;
+  bool bat_tried_ = false;
   std::map<int, JitKernel> kernels_;
   std::string coef_src_;
   int dim_ = 3;

@@ -38,6 +38,17 @@ def test_cuda_generic_kernel_alone(lib, name, p, kw):
     assert r["path"] == "generic", r
 
 
+JIT_BATCHED = ("cdr/2D_manufactured", "le/3D_manufactured", "C3 cdr Q2 hex", "LE 3D weak Dirichlet + Neumann", "LE 2D weak Dirichlet",
+               "thermal 3D nonlinear diffusion + advection", "thermal 3D transient BE", "cdr 2D transient DIRK2", "thermal 2D lump mass")
+
+
+@pytest.mark.parametrize("name,p,kw", [c for c in CASES if c[0] in JIT_BATCHED], ids=lambda v: v if isinstance(v, str) else "")
+def test_cuda_nvrtc_specialised_batched_kernel(lib, name, p, kw):
+    """the batched volume kernel with its state-independent coefficient programs compiled by NVRTC (forced on small meshes)"""
+    r = U.check_case(p, kw, lib, on_gpu=True, force_generic=True, jit_batched=True)
+    assert r["path"] == "nvrtc-batched", r
+
+
 def test_default_path_of_multivariable_configs_is_batched(lib):
     for mk, n in ((problems.config_c3, 3), (problems.config_c4, 5), (problems.config_c5, 4)):
         r = U.check_case(mk(n), {}, lib, on_gpu=True)
