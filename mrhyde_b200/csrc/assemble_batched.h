@@ -85,8 +85,10 @@ struct WarpSmem {
   MRH_HD size_t oUd() const { return even_up(oU() + N); }
   MRH_HD size_t oW() const { return even_up(oUd() + (transient ? N : 0)); }
   MRH_HD size_t oXq() const { return even_up(oW() + nq); }
-  MRH_HD size_t oT() const { return even_up(oXq() + (size_t)nq * 3); }
-  MRH_HD size_t oF() const { return even_up(oT() + (size_t)nq * NB * TA); }
+  MRH_HD size_t oJi() const { return even_up(oXq() + (size_t)nq * 3); }                  // J^-1 per point, [m][c]
+  static constexpr bool STORE_T = NB <= 8;                     // physical basis rows kept in shared memory (Q1); rebuilt from J^-1 otherwise
+  MRH_HD size_t oT() const { return even_up(oJi() + (size_t)nq * C::DIM * C::DIM); }     // T[q][j][0..dim], STORE_T only
+  MRH_HD size_t oF() const { return even_up(oT() + (STORE_T ? (size_t)nq * NB * TA : 0)); }
   MRH_HD size_t oD() const { return even_up(oF() + (size_t)nq * NVAR * TA); }
   MRH_HD size_t oKx() const { return even_up(oD() + dsize()); }                       // separate K only when it cannot alias D
   MRH_HD size_t oCoef() const { return even_up(oKx() + (k_aliases_d() ? 0 : (size_t)N * KS)); }
@@ -130,8 +132,12 @@ struct BatPhases {
   static constexpr int NT = LAY::NT, NRT = LAY::NRT, QS = LAY::QS, KS = LAY::KS;
   static_assert(N <= 32, "one lane per element row");
 
-  // ---- geometry + physical basis, item = (point, part): every part rebuilds J, part p fills basis rows j == p (mod nparts)
-  MRH_HD static int geom_parts(int nq) { return nq * 4 <= 32 ? 4 : (nq * 2 <= 32 ? 2 : 1); }
+  // ---- geometry, item = (point, part): every part rebuilds J, det, J^-1; part 0 stores them.  Small bases (STORE_T):
+  //      part p also stores the physical basis rows j == p (mod nparts), T[j][1+c] = sum_m J^-1[m][c] G[j][m].
+  //      Larger bases never store T: the point phase transforms the reference gradient of u and the contraction
+  //      builds its fragments from J^-1 and the reference tables (basis_entry). ----
+  static constexpr bool STORE_T = LAY::STORE_T;
+  MRH_HD static int geom_parts(int nq) { return !STORE_T ? 1 : nq * 4 <= 32 ? 4 : (nq * 2 <= 32 ? 2 : 1); }
   MRH_HDN static void geometry(const KParams& kp, const LAY& L, double* sm, int item, int nparts) {
     const int q = item / nparts, part = item - q * nparts;
     const double* X = sm + L.oX();
@@ -150,16 +156,27 @@ struct BatPhases {
     if (part == 0) {
       sm[L.oW() + q] = fabs(det) * tb.W[q];
       for (int c = 0; c < 3; ++c) sm[L.oXq() + (size_t)q * 3 + c] = xq[c];
+      for (int m = 0; m < DIM; ++m) for (int c = 0; c < DIM; ++c) sm[L.oJi() + (size_t)q * DIM * DIM + m * DIM + c] = Ji[m][c];
     }
-    double* T = sm + L.oT() + (size_t)q * NB * TA;
-    for (int j = part; j < NB; j += nparts) {
-      T[j * TA] = tb.B[q * NB + j];
-      for (int c = 0; c < DIM; ++c) {
-        double s = 0.0;
-        for (int m = 0; m < DIM; ++m) s += Ji[m][c] * tb.G[(q * NB + j) * DIM + m];
-        T[j * TA + 1 + c] = s;
+    if (STORE_T) {
+      double* T = sm + L.oT() + (size_t)q * NB * TA;
+      for (int j = part; j < NB; j += nparts) {
+        T[j * TA] = tb.B[q * NB + j];
+        for (int c = 0; c < DIM; ++c) {
+          double s = 0.0;
+          for (int m = 0; m < DIM; ++m) s += Ji[m][c] * tb.G[(q * NB + j) * DIM + m];
+          T[j * TA + 1 + c] = s;
+        }
       }
     }
+  }
+  // physical basis entry T[j][a] at point q (a = 0: value, a = 1 + c: d/dx_c)
+  MRH_HD static double basis_entry(const RefTab& tb, const double* Ji, int q, int j, int a) {
+    if (a == 0) return tb.B[q * NB + j];
+    double s = 0.0;
+#pragma unroll
+    for (int m = 0; m < DIM; ++m) s += Ji[m * DIM + (a - 1)] * tb.G[(q * NB + j) * DIM + m];
+    return s;
   }
 
   // ---- prep: state-independent programs, item = (point, i-th program of kind 1); lane 0 adds the element size ----
@@ -182,7 +199,8 @@ struct BatPhases {
   MRH_HDN static void point_chunk(const KParams& kp, const LAY& L, double* sm, int item) {
     const int q = item / NCH, ch = item - q * NCH;
     const int lane0 = ch * LCH;
-    const double* T = sm + L.oT() + (size_t)q * NB * TA;
+    const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
+    const RefTab& tb = kp.tab;
     const double* U = sm + L.oU();
     const double* Ud = sm + L.oUd();
     const bool tr = kp.tp.transient != 0;
@@ -191,13 +209,35 @@ struct BatPhases {
 #pragma unroll
     for (int m = 0; m < NVAR; ++m) {
       double fv[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-      for (int j = 0; j < NB; ++j) {
-        const int slot = kp.offsets[m * NB + j];
-        const double uj = U[slot], b = T[j * TA];
-        fv[0] += uj * b;
+      if (STORE_T) {
+        const double* T = sm + L.oT() + (size_t)q * NB * TA;
+        for (int j = 0; j < NB; ++j) {
+          const int slot = kp.offsets[m * NB + j];
+          const double uj = U[slot], b = T[j * TA];
+          fv[0] += uj * b;
 #pragma unroll
-        for (int c = 0; c < DIM; ++c) fv[1 + c] += uj * T[j * TA + 1 + c];
-        if (tr) fv[4] += Ud[slot] * b;
+          for (int c = 0; c < DIM; ++c) fv[1 + c] += uj * T[j * TA + 1 + c];
+          if (tr) fv[4] += Ud[slot] * b;
+        }
+      } else {
+        double gr[DIM];
+#pragma unroll
+        for (int c = 0; c < DIM; ++c) gr[c] = 0.0;
+        for (int j = 0; j < NB; ++j) {
+          const int slot = kp.offsets[m * NB + j];
+          const double uj = U[slot], b = tb.B[q * NB + j];
+          fv[0] += uj * b;
+#pragma unroll
+          for (int c = 0; c < DIM; ++c) gr[c] += uj * tb.G[(q * NB + j) * DIM + c];
+          if (tr) fv[4] += Ud[slot] * b;
+        }
+#pragma unroll
+        for (int c = 0; c < DIM; ++c) {
+          double g = 0.0;
+#pragma unroll
+          for (int mm = 0; mm < DIM; ++mm) g += Ji[mm * DIM + c] * gr[mm];
+          fv[1 + c] = g;
+        }
       }
 #pragma unroll
       for (int k = 0; k < 5; ++k) in.f[m][k] = S(fv[k]);
@@ -223,7 +263,7 @@ struct BatPhases {
     in.ps.fields = fm; in.ps.time = kp.tp.time;
     for (int c = 0; c < 3; ++c) { in.ps.x[c] = sm[L.oXq() + (size_t)q * 3 + c]; in.ps.nrm[c] = 0.0; in.ps.tng[c] = 0.0; }
     in.w = sm[L.oW() + q];
-    in.h = sm[L.oH()];
+    in.h = (C::PHYS == PHYS_NS) ? sm[L.oH()] : 0.0;
     S F[NVAR][TA];
 #pragma unroll
     for (int v = 0; v < NVAR; ++v)
@@ -255,7 +295,8 @@ struct BatPhases {
   // step 2 (per m of the tile)   :  K_(v,rt),(m,ct) += L_m (8 x 4: basis i, slot b) x T_ct^T (4 x 8: slot b, basis j)
   // The A fragment of step 2 is the C fragment of step 1; the B fragment of step 2 is the A fragment of step 1.
   struct Acc { WV k[NVAR][NRT][NVAR][NRT][2]; WV r[NRT][2]; };
-  MRH_HD static void contract(const LAY& L, const double* sm, Acc& A) {
+  MRH_HD static void contract(const KParams& kp, const LAY& L, const double* sm, Acc& A) {
+    const RefTab& tb = kp.tab;
 #pragma unroll
     for (int v = 0; v < NVAR; ++v)
 #pragma unroll
@@ -267,13 +308,13 @@ struct BatPhases {
 #pragma unroll
     for (int rt = 0; rt < NRT; ++rt) { A.r[rt][0] = wv_zero(); A.r[rt][1] = wv_zero(); }
     for (int q = 0; q < L.nq; ++q) {
-      const double* T = sm + L.oT() + (size_t)q * NB * TA;
+      const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
       const double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
       const double* Dq = sm + L.oD() + LAY::dq(q);
       WV tf[NRT];
 #pragma unroll
       for (int rt = 0; rt < NRT; ++rt)
-        tf[rt] = wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? T[j * TA + a] : 0.0; });
+        tf[rt] = wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? (STORE_T ? sm[L.oT() + (size_t)q * NB * TA + j * TA + a] : basis_entry(tb, Ji, q, j, a)) : 0.0; });
       const WV ff = wv_make([&](int lane) { const int v = lane >> 2, a = lane & 3; return (v < NVAR && a < TA) ? sF[v * TA + a] : 0.0; });
 #pragma unroll
       for (int rt = 0; rt < NRT; ++rt) wv_mma(A.r[rt][0], A.r[rt][1], tf[rt], ff);
@@ -435,12 +476,12 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
     } else {
       for (int it = lane; it < nq * n1; it += 32) B::prep(kp, L, sm, it, n1);
     }
-    if (lane == 31) B::element_size(L, sm);
+    if (lane == 31 && C::PHYS == PHYS_NS) B::element_size(L, sm);       // h enters volume terms through the stabilisation only
     __syncwarp();
     for (int it = lane; it < nq * B::NCH; it += 32) B::point_chunk(kp, L, sm, it);
     __syncwarp();
     typename B::Acc acc;
-    B::contract(L, sm, acc);
+    B::contract(kp, L, sm, acc);
     __syncwarp();                                          // every lane is done with D: K may take its place
     B::store_acc(L, sm, acc);
     __syncwarp();
@@ -453,19 +494,24 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
 #endif
 
 #if !defined(__CUDACC_RTC__)
-constexpr int MRH_BATCHED_MAXW = 4;       // warps per CTA (fewer when one element's shared-memory block is large)
-// warps per CTA that put the most warps on one SM, and the dynamic shared memory of such a CTA; false: does not fit
+constexpr int MRH_BATCHED_MAXW = 6;       // most warps per CTA the launchers try
+// dynamic shared memory of a CTA of nw warps (one element block per warp + the CTA-shared offsets table)
 template <class C>
-inline bool batched_shape(int nq, bool transient, int& nw, size_t& smem) {
-  const size_t per = WarpSmem<C>(nq, transient).total_doubles() * sizeof(double);
-  const size_t head = even_up((C::N + 1) / 2) * sizeof(double);
-  nw = 0; size_t best = 0;
-  for (int c = MRH_BATCHED_MAXW; c >= 1; --c) {
-    const size_t total = ((size_t)227 * 1024 / (head + c * per + 1024)) * c;
-    if (total > best) { best = total; nw = c; }
+inline size_t batched_smem(int nq, bool transient, int nw) {
+  return even_up((C::N + 1) / 2) * sizeof(double) + (size_t)nw * WarpSmem<C>(nq, transient).total_doubles() * sizeof(double);
+}
+// warps per CTA that put the most warps on one SM; occ(threads, smem) = resident CTAs per SM of the kernel at hand
+// (registers included, which is why it is asked of the driver instead of computed from the layout).  0: nothing fits.
+template <class C, class OCC>
+inline int batched_pick_warps(int nq, bool transient, OCC occ, int& blocks_per_sm) {
+  int best = 0, nw = 0; blocks_per_sm = 0;
+  for (int c = 1; c <= MRH_BATCHED_MAXW; ++c) {
+    const size_t smem = batched_smem<C>(nq, transient, c);
+    if (smem > (size_t)227 * 1024) break;
+    const int b = occ(32 * c, smem);
+    if (b * c > best) { best = b * c; nw = c; blocks_per_sm = b; }
   }
-  smem = head + (size_t)nw * per;
-  return nw > 0;
+  return nw;
 }
 #endif
 

@@ -18,25 +18,32 @@ using namespace mrh;
 
 namespace {
 
+// register budget per configuration (measured: capping the 3-D Navier-Stokes point phase below its 255 registers to fit
+// 10 warps per SM instead of 8 spills 0.5 KB per thread and is slower: 29.2 ms instead of 23.3-25.7 ms at 128^3)
+template <class C> struct BatBounds { static constexpr int THREADS = 32 * MRH_BATCHED_MAXW, MINB = 1; };
+
 template <class C>
-__global__ void __launch_bounds__(32 * MRH_BATCHED_MAXW) batched_assembly_kernel(const __grid_constant__ KParams kp) {
+__global__ void __launch_bounds__(BatBounds<C>::THREADS, BatBounds<C>::MINB) batched_assembly_kernel(const __grid_constant__ KParams kp) {
   extern __shared__ __align__(16) double smem_all[];
   batched_body<C, InterpProgs>(kp, smem_all);
 }
 
 template <class C>
 bool launch_batched(int num_sms, KParams& kp, cudaStream_t stream) {
-  int nw; size_t smem;
-  if (!batched_shape<C>(kp.tab.nq, kp.tp.transient != 0, nw, smem)) return false;      // caller falls back to the generic kernel
   auto kern = batched_assembly_kernel<C>;
-  CUDA_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 1;
-  CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * nw, smem));
-  if (per_sm < 1) per_sm = 1;
+  const bool tr = kp.tp.transient != 0;
+  static int set_smem = 0;                                   // per instantiation: largest opt-in size requested so far
+  const int want = (int)std::min<size_t>(batched_smem<C>(kp.tab.nq, tr, BatBounds<C>::THREADS / 32), (size_t)227 * 1024);
+  if (want > set_smem) { CUDA_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, want)); set_smem = want; }
+  int per_sm = 0;
+  const int nw = batched_pick_warps<C>(kp.tab.nq, tr, [&](int threads, size_t smem) {
+    if (threads > BatBounds<C>::THREADS) return 0;
+    int b = 0; return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kern, threads, smem) == cudaSuccess ? b : 0; }, per_sm);
+  if (nw == 0) return false;                                 // caller falls back to the generic kernel
   kp.elems_per_block = nw;
   const int64_t nblk = (kp.nwork + nw - 1) / nw;
   const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)num_sms * per_sm);
-  kern<<<grid, 32 * nw, smem, stream>>>(kp);
+  kern<<<grid, 32 * nw, batched_smem<C>(kp.tab.nq, tr, nw), stream>>>(kp);
   CUDA_CK(cudaGetLastError());
   return true;
 }

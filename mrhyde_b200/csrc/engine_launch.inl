@@ -296,20 +296,26 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
       if (side < 0 && jac != nullptr && !(H.cfg.flags & 16)) {
         JitKernel* jk = D.jit.hasBatchedSource() ? D.jit.batched() : nullptr;
         if (jk) {
-          int nw = 0; size_t smem = 0; bool fits = false;
-          dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { fits = batched_shape<decltype(c)>(kp.tab.nq, kp.tp.transient != 0, nw, smem); });
-          if (fits) {
-            JitApi& api = JitApi::get();
-            if (jk->smem_set != smem) {
-              if (api.FuncSetAttribute(jk->fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem) != CUDA_SUCCESS)
+          JitApi& api = JitApi::get();
+          const bool tr = kp.tp.transient != 0;
+          if (jk->smem_set != (size_t)kp.tab.nq * 2 + tr + 1) {     // launch shape of this module: once per (quadrature rule, transient)
+            dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) {
+              using C = decltype(c);
+              const size_t want = std::min<size_t>(batched_smem<C>(kp.tab.nq, tr, MRH_BATCHED_MAXW), (size_t)227 * 1024);
+              if (api.FuncSetAttribute(jk->fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)want) != CUDA_SUCCESS)
                 throw std::runtime_error("CUDA error: cuFuncSetAttribute(shared memory) failed");
-              if (api.OccupancyMaxActiveBlocks(&jk->blocks_per_sm, jk->fn, 32 * nw, smem) != CUDA_SUCCESS || jk->blocks_per_sm < 1) jk->blocks_per_sm = 1;
-              jk->smem_set = smem;
-            }
+              jk->tiled_blocks_per_sm = batched_pick_warps<C>(kp.tab.nq, tr, [&](int threads, size_t smem) {
+                int b = 0; return api.OccupancyMaxActiveBlocks(&b, jk->fn, threads, smem) == CUDA_SUCCESS ? b : 0; }, jk->blocks_per_sm);
+              jk->ws_smem_set = batched_smem<C>(kp.tab.nq, tr, jk->tiled_blocks_per_sm);
+            });
+            jk->smem_set = (size_t)kp.tab.nq * 2 + tr + 1;
+          }
+          const int nw = jk->tiled_blocks_per_sm;                  // (field reused: warps per CTA of the batched module)
+          if (nw > 0) {
             kp.elems_per_block = nw;
             const unsigned grid = (unsigned)std::min<int64_t>((kp.nwork + nw - 1) / nw, (int64_t)D.num_sms * jk->blocks_per_sm);
             void* args[] = {(void*)&kp};
-            if (api.LaunchKernel(jk->fn, grid, 1, 1, 32 * nw, 1, 1, (unsigned)smem, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+            if (api.LaunchKernel(jk->fn, grid, 1, 1, 32 * nw, 1, 1, (unsigned)jk->ws_smem_set, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
               throw std::runtime_error("CUDA error: cuLaunchKernel failed for the NVRTC-specialised batched kernel");
             done = jitted = true;
           }

@@ -223,7 +223,7 @@ class JitCache {
         "  static __device__ __forceinline__ double eval(int k, double x, double y, double z, double t) {\n    switch (k) {\n"
         "      case 0: return p0(x, y, z, t); case 1: return p1(x, y, z, t); case 2: return p2(x, y, z, t); case 3: return p3(x, y, z, t);\n"
         "      case 4: return p4(x, y, z, t); case 5: return p5(x, y, z, t); case 6: return p6(x, y, z, t); default: return p7(x, y, z, t);\n    }\n  }\n};\n}\n"
-        "extern \"C\" __global__ void __launch_bounds__(128) mrh_jit_batched(const __grid_constant__ mrh::KParams kp) {\n"
+        "extern \"C\" __global__ void __launch_bounds__(192) mrh_jit_batched(const __grid_constant__ mrh::KParams kp) {\n"
         "  extern __shared__ __align__(16) double smem_all[];\n"
         "  mrh::batched_body<mrh::GenCfg<" + std::to_string(phys) + ", " + std::to_string(dim) + ", " + std::to_string(order) + ">, mrh::JitProgs>(kp, smem_all);\n}\n";
   }

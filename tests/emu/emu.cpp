@@ -53,9 +53,9 @@ static bool run_batched(const KParams& kp) {
     for (int it = 0; it < C::NV; ++it) G::gather_vertex(kp, L, sm.data(), w, it);
     for (int it = 0; it < nq * nparts; ++it) B::geometry(kp, L, sm.data(), it, nparts);
     for (int it = 0; it < nq * n1; ++it) B::prep(kp, L, sm.data(), it, n1);
-    B::element_size(L, sm.data());
+    if (C::PHYS == PHYS_NS) B::element_size(L, sm.data());
     for (int it = 0; it < nq * B::NCH; ++it) B::point_chunk(kp, L, sm.data(), it);
-    B::contract(L, sm.data(), *acc);
+    B::contract(kp, L, sm.data(), *acc);
     B::store_acc(L, sm.data(), *acc);
     for (int lane = 0; lane < 32; ++lane) B::row_setup(kp, L, sm.data(), offs.data(), lane);
     for (int lane = 0; lane < 32; ++lane) B::scatter(kp, L, sm.data(), offs.data(), G::elem_of(kp, w), lane);

@@ -203,3 +203,62 @@ def test_host_buffer_entry_point_chunked_copy_out(lib):
     assert n_host_launches > e.launch_count()        # several volume launches (chunks) against one
     assert U.rel_errors(hres.numpy(), res.cpu().numpy())[0] < U.TOL
     assert U.rel_errors(hjac.numpy(), jac.cpu().numpy())[0] < U.TOL
+
+
+def _assemble(lib, p, **flags):
+    import torch
+    from mrhyde_b200 import Engine
+    e = Engine.from_problem(p, lib=lib, **flags)
+    s = e.sizes()
+    xyz, var = e.dof_coords()
+    dev = torch.device("cuda:0")
+    u = torch.from_numpy(problems.synthetic_state(xyz, var)).to(dev)
+    res = torch.zeros(s["nlocal"], dtype=torch.float64, device=dev)
+    jac = torch.zeros(s["nnz"], dtype=torch.float64, device=dev)
+    e.assemble_jacres(u, res, jac)
+    torch.cuda.synchronize()
+    return e, u, res, jac
+
+
+@pytest.mark.parametrize("mk,n,jit", [(problems.config_c4, 24, False), (problems.config_c4, 24, True), (problems.config_c5, 24, False),
+                                      (problems.config_c3, 12, False), (problems.config_c3, 12, True)],
+                         ids=["C4-24", "C4-24-nvrtc", "C5-24", "C3-12", "C3-12-nvrtc"])
+def test_batched_kernel_matches_generic_kernel_at_mid_size(lib, mk, n, jit):
+    """meshes large enough that every warp of the persistent batched kernel walks several elements (software-pipelined
+    gather, element block reuse): batched (and NVRTC-batched) against the oracle-checked generic kernel"""
+    p = mk(n)
+    e0, _, res0, jac0 = _assemble(lib, p, force_generic=True, no_batched=True)
+    assert e0.kernel_path() == "generic"
+    e1, _, res1, jac1 = _assemble(lib, p, jit_batched=jit)
+    assert e1.kernel_path() == ("nvrtc-batched" if jit else "batched")
+    for a, b in ((res1, res0), (jac1, jac0)):
+        scale = b.abs().max().item()
+        assert (a - b).abs().max().item() <= 1e-12 * scale
+    e0.close(); e1.close()
+
+
+@pytest.mark.parametrize("mk,n", [(problems.config_c5, 32), (problems.config_c3, 16), (problems.config_c4, 48)], ids=["C5-32", "C3-16", "C4-48"])
+def test_batched_jacobian_is_the_derivative_of_the_residual(lib, mk, n):
+    """size-independent property beyond the oracle's reach: for a random direction v on the free DOFs,
+    (res(u + eps v) - res(u - eps v)) / (2 eps) == -J(u) v  (the residual vector holds -r, the matrix dr/du);
+    exact up to round-off for linear elasticity, O(eps^2) for the nonlinear configurations"""
+    import torch
+    e, u, res, jac = _assemble(lib, mk(n), jit_batched=True)
+    s = e.sizes()
+    rp, ci = e.crs()
+    _, _, fixed, _, _ = e.dofmap()
+    dev = u.device
+    J = torch.sparse_csr_tensor(torch.from_numpy(rp).to(dev), torch.from_numpy(ci.astype(np.int64)).to(dev), jac, size=(s["nlocal"], s["nlocal"]))
+    free = torch.from_numpy(fixed == 0).to(dev)
+    g = torch.Generator(device="cpu").manual_seed(7)
+    v = torch.rand(s["nlocal"], dtype=torch.float64, generator=g).to(dev) - 0.5
+    eps = 1e-5
+    rp_, rm_ = torch.zeros_like(res), torch.zeros_like(res)
+    e.assemble_res(u + eps * v, rp_)
+    e.assemble_res(u - eps * v, rm_)
+    torch.cuda.synchronize()
+    fd = (rp_ - rm_) / (2 * eps)
+    jv = -(J @ v)
+    scale = jv[free].abs().max().item()
+    assert (fd - jv)[free].abs().max().item() <= 2e-7 * scale
+    e.close()
