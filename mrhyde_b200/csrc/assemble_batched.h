@@ -198,6 +198,7 @@ struct BatPhases {
   // ---- point physics on one lane chunk, item = (point, variable m) ----------------------------------------
   MRH_HDN static void point_chunk(const KParams& kp, const LAY& L, double* sm, int item) {
     const int q = item / NCH, ch = item - q * NCH;
+    if (!kp.compute_jac && ch != 0) return;                     // residual-only pass: the values come from chunk 0 alone
     const int lane0 = ch * LCH;
     const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
     const RefTab& tb = kp.tab;
@@ -281,6 +282,7 @@ struct BatPhases {
 #pragma unroll
       for (int a = 0; a < 4; ++a) {
         if (a < TA && ch == 0) sF[v * TA + a] = F[v][a < TA ? a : 0].v;
+        if (!kp.compute_jac) continue;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
           Dt[a + 4 * (half + 2 * b)] = (a < TA && b < TA) ? F[v][a < TA ? a : 0].d[b < LCH ? b : 0] : 0.0;
@@ -318,6 +320,7 @@ struct BatPhases {
       const WV ff = wv_make([&](int lane) { const int v = lane >> 2, a = lane & 3; return (v < NVAR && a < TA) ? sF[v * TA + a] : 0.0; });
 #pragma unroll
       for (int rt = 0; rt < NRT; ++rt) wv_mma(A.r[rt][0], A.r[rt][1], tf[rt], ff);
+      if (!kp.compute_jac) continue;
 #pragma unroll
       for (int v = 0; v < NVAR; ++v)
 #pragma unroll
@@ -339,7 +342,7 @@ struct BatPhases {
   }
 
   // ---- park K (natural order: row (v, i), column (m, j)) and r in shared memory; lane = fragment lane ------
-  MRH_HD static void store_acc(const LAY& L, double* sm, const Acc& A) {
+  MRH_HD static void store_acc(const LAY& L, double* sm, const Acc& A, bool jac) {
     double* K = sm + L.oK();
     double* R = sm + L.oR();
     wv_each([&](int lane) {
@@ -350,6 +353,7 @@ struct BatPhases {
         if (i >= NB) continue;
 #pragma unroll
         for (int e = 0; e < 2; ++e) { const int v = 2 * p + e; if (v < NVAR) R[v * NB + i] = wv_get(A.r[rt][e], lane); }
+        if (!jac) continue;
 #pragma unroll
         for (int v = 0; v < NVAR; ++v)
 #pragma unroll
@@ -372,7 +376,7 @@ struct BatPhases {
     const int* sLid = reinterpret_cast<const int*>(sm + L.oLid());
     const int rowslot = offs[lane], row = sLid[rowslot];
     reinterpret_cast<int64_t*>(sm + L.oRowBase())[lane] = kp.fixed[row] ? (int64_t)-1 : kp.rowptr[row];
-    if (kp.lump_mass) {                                              // assemblyManager.cpp:4130-4132
+    if (kp.lump_mass && kp.compute_jac) {                            // assemblyManager.cpp:4130-4132
       double* K = sm + L.oK() + (size_t)lane * KS;
       double s = 0.0;
       for (int c = 0; c < N; ++c) { s += K[c]; K[c] = 0.0; }
@@ -386,7 +390,7 @@ struct BatPhases {
     const int* sLid = reinterpret_cast<const int*>(sm + L.oLid());
     const double* K = sm + L.oK();
     if (lane < N && rb[lane] >= 0) atomic_add(kp.res + sLid[offs[lane]], -sm[L.oR() + lane]);
-    if (lane >= N) return;
+    if (lane >= N || !kp.compute_jac) return;
     const int col = (lane % NVAR) * NB + lane / NVAR;                // natural column this lane serves
     const int colslot = offs[col];
     const uint16_t* pat = kp.pat + (size_t)kp.pat_id[e] * N * N + colslot;
@@ -483,7 +487,7 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
     typename B::Acc acc;
     B::contract(kp, L, sm, acc);
     __syncwarp();                                          // every lane is done with D: K may take its place
-    B::store_acc(L, sm, acc);
+    B::store_acc(L, sm, acc, kp.compute_jac != 0);
     __syncwarp();
     B::row_setup(kp, L, sm, offs, lane);
     __syncwarp();

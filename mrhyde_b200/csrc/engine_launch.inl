@@ -290,10 +290,10 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
 #undef MRH_FAST
       }
     } else {
-      // volume residual + Jacobian: batched kernel (assemble_batched.h); side launches, residual-only passes and
+      // volume terms (residual + Jacobian, or residual only): batched kernel (assemble_batched.h); side launches and
       // element blocks that do not fit its shared-memory layout go through the generic kernel
       bool done = false, jitted = false;
-      if (side < 0 && jac != nullptr && !(H.cfg.flags & 16)) {
+      if (side < 0 && !(H.cfg.flags & 16)) {
         JitKernel* jk = D.jit.hasBatchedSource() ? D.jit.batched() : nullptr;
         if (jk) {
           JitApi& api = JitApi::get();

@@ -56,7 +56,7 @@ static bool run_batched(const KParams& kp) {
     if (C::PHYS == PHYS_NS) B::element_size(L, sm.data());
     for (int it = 0; it < nq * B::NCH; ++it) B::point_chunk(kp, L, sm.data(), it);
     B::contract(kp, L, sm.data(), *acc);
-    B::store_acc(L, sm.data(), *acc);
+    B::store_acc(L, sm.data(), *acc, kp.compute_jac != 0);
     for (int lane = 0; lane < 32; ++lane) B::row_setup(kp, L, sm.data(), offs.data(), lane);
     for (int lane = 0; lane < 32; ++lane) B::scatter(kp, L, sm.data(), offs.data(), G::elem_of(kp, w), lane);
   }
@@ -103,7 +103,7 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
       E->launches++; E->fast_launches++;
       continue;
     }
-    if (side < 0 && jac && !(H.cfg.flags & 16)) {
+    if (side < 0 && !(H.cfg.flags & 16)) {
       if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_batched<decltype(c)>(kp); })) throw std::runtime_error("configuration not supported");
       E->launches++; E->batched_launches++;
       continue;

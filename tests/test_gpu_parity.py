@@ -227,13 +227,21 @@ def test_batched_kernel_matches_generic_kernel_at_mid_size(lib, mk, n, jit):
     """meshes large enough that every warp of the persistent batched kernel walks several elements (software-pipelined
     gather, element block reuse): batched (and NVRTC-batched) against the oracle-checked generic kernel"""
     p = mk(n)
-    e0, _, res0, jac0 = _assemble(lib, p, force_generic=True, no_batched=True)
+    e0, u0, res0, jac0 = _assemble(lib, p, force_generic=True, no_batched=True)
     assert e0.kernel_path() == "generic"
     e1, _, res1, jac1 = _assemble(lib, p, jit_batched=jit)
     assert e1.kernel_path() == ("nvrtc-batched" if jit else "batched")
+    import torch
     for a, b in ((res1, res0), (jac1, jac0)):
         scale = b.abs().max().item()
         assert (a - b).abs().max().item() <= 1e-12 * scale
+    # residual-only passes of the two kernels
+    r0, r1 = torch.zeros_like(res0), torch.zeros_like(res0)
+    e0.assemble_res(u0, r0); e1.assemble_res(u0, r1)
+    torch.cuda.synchronize()
+    assert e0.kernel_path() == "generic" and e1.kernel_path() == ("nvrtc-batched" if jit else "batched")
+    assert (r1 - r0).abs().max().item() <= 1e-12 * r0.abs().max().item()
+    assert (r1 - res1).abs().max().item() <= 1e-12 * r0.abs().max().item()
     e0.close(); e1.close()
 
 
