@@ -22,6 +22,9 @@
 
 namespace mrh {
 
+#if !defined(MRH_NS_HALF_CHUNKS)
+#define MRH_NS_HALF_CHUNKS 0     // measured on B200, C5 128^3: PAD<2> half-variable chunks at 10 warps / SM 29.9 ms, PAD<4> at 8 warps 23.1 ms
+#endif
 constexpr int MRH_NCOEF = 8;      // volume program slots of one physics module (params.h: at most CDR's 8)
 
 // ---- one value per lane of a warp --------------------------------------------------------------------------
@@ -126,7 +129,11 @@ struct PointBat {
 template <class C>
 struct BatPhases {
   static constexpr int DIM = C::DIM, NB = C::NB, NV = C::NV, N = C::N, NVAR = C::NVAR, P = C::P, TA = C::TA;
-  static constexpr int LCH = TA, NCH = NVAR;                   // one lane chunk per variable: (u_m, grad u_m)
+  // lane chunk of the point phase: LCH of the P = NVAR (1 + dim) point-state lanes per work item.  Default one chunk per
+  // variable (u_m, grad u_m).  MRH_NS_HALF_CHUNKS: 3-D Navier-Stokes with half a variable per item (PAD<2>, 168 instead of
+  // 250 registers, 10 instead of 8 warps per SM) - slower in practice (the point values are recomputed twice as often)
+  static constexpr int LCH = (C::PHYS == PHYS_NS && DIM == 3 && MRH_NS_HALF_CHUNKS) ? 2 : TA, NCH = P / LCH;
+  static_assert(TA % LCH == 0, "a lane chunk must not straddle two variables");
   using S = PAD<LCH>;
   using LAY = WarpSmem<C>;
   static constexpr int NT = LAY::NT, NRT = LAY::NRT, QS = LAY::QS, KS = LAY::KS;
@@ -274,8 +281,10 @@ struct BatPhases {
     // f -> F[q][v][a];  dF_(v,a)/d(m,b) -> B-fragment order: tile (v, t = m/2), lane = a + 4 ((m & 1) + 2 b)
     double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
     double* Dq = sm + L.oD() + LAY::dq(q);
-    const int t = ch >> 1, half = ch & 1;
-    const bool phantom = (NVAR & 1) && ch == NVAR - 1;           // odd variable count: this lane also zeroes column m + 1
+    const int mv = lane0 / TA, b0 = lane0 - mv * TA;              // variable and first slot this chunk differentiates by
+    const int t = mv >> 1, half = mv & 1;
+    const bool phantom = (NVAR & 1) && mv == NVAR - 1;           // odd variable count: this item also zeroes column m + 1
+    const bool last = b0 + LCH == TA;                            // 2-D (3 slots): the last chunk also zeroes slot 3
 #pragma unroll
     for (int v = 0; v < NVAR; ++v) {
       double* Dt = Dq + (size_t)(v * NT + t) * 32;
@@ -284,9 +293,14 @@ struct BatPhases {
         if (a < TA && ch == 0) sF[v * TA + a] = F[v][a < TA ? a : 0].v;
         if (!kp.compute_jac) continue;
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          Dt[a + 4 * (half + 2 * b)] = (a < TA && b < TA) ? F[v][a < TA ? a : 0].d[b < LCH ? b : 0] : 0.0;
+        for (int l = 0; l < LCH; ++l) {
+          const int b = b0 + l;
+          Dt[a + 4 * (half + 2 * b)] = (a < TA) ? F[v][a < TA ? a : 0].d[l] : 0.0;
           if (phantom) Dt[a + 4 * (1 + 2 * b)] = 0.0;
+        }
+        if (TA < 4 && last) {
+#pragma unroll
+          for (int b = TA; b < 4; ++b) { Dt[a + 4 * (half + 2 * b)] = 0.0; if (phantom) Dt[a + 4 * (1 + 2 * b)] = 0.0; }
         }
       }
     }

@@ -21,6 +21,9 @@ namespace {
 // register budget per configuration (measured: capping the 3-D Navier-Stokes point phase below its 255 registers to fit
 // 10 warps per SM instead of 8 spills 0.5 KB per thread and is slower: 29.2 ms instead of 23.3-25.7 ms at 128^3)
 template <class C> struct BatBounds { static constexpr int THREADS = 32 * MRH_BATCHED_MAXW, MINB = 1; };
+#if MRH_NS_HALF_CHUNKS
+template <> struct BatBounds<GenCfg<PHYS_NS, 3, 1>> { static constexpr int THREADS = 160, MINB = 2; };   // <= 204 registers: 10 warps per SM
+#endif
 
 template <class C>
 __global__ void __launch_bounds__(BatBounds<C>::THREADS, BatBounds<C>::MINB) batched_assembly_kernel(const __grid_constant__ KParams kp) {
