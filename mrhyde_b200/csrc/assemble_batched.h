@@ -449,34 +449,28 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
   // (lane k < N owns DOF slot k, lane a < NV owns vertex a).  Transient launches use the plain gather (stage / BDF sums).
   const bool pipelined = !kp.tp.transient;
   const int64_t w_first = (int64_t)blockIdx.x * nwarp + warp, w_stride = (int64_t)gridDim.x * nwarp;
+  // (plain statements, no lambdas: variables captured by reference were placed in local memory, and storing a value
+  //  that is still in flight there stalls the warp on the load - exactly what the pipeline is meant to avoid)
   int lidA = 0, ndA = 0, lidB = 0, ndB = 0;
-  double uA = 0.0, xA[C::DIM];
-  auto load_idx = [&](int64_t w, int& lid, int& nd) {
-    const int64_t e = G::elem_of(kp, w);
-    if (lane < C::N) lid = kp.lids[e * C::N + lane];
-    if (lane < C::NV) nd = kp.e2n[e * C::NV + lane];
-  };
-  auto load_val = [&](int lid, int nd) {
-    if (lane < C::N) uA = kp.u[lid];
-    if (lane < C::NV) {
-#pragma unroll
-      for (int c = 0; c < C::DIM; ++c) xA[c] = kp.nodes[(int64_t)nd * C::DIM + c];
-    }
-  };
+  double uA = 0.0, xA0 = 0.0, xA1 = 0.0, xA2 = 0.0;
+#define MRH_LOAD_IDX(W, LID, ND) { const int64_t e_ = G::elem_of(kp, (W)); \
+    if (lane < C::N) LID = kp.lids[e_ * C::N + lane]; if (lane < C::NV) ND = kp.e2n[e_ * C::NV + lane]; }
+#define MRH_LOAD_VAL(LID, ND) { if (lane < C::N) uA = kp.u[LID]; \
+    if (lane < C::NV) { const double* xp_ = kp.nodes + (int64_t)(ND) * C::DIM; xA0 = xp_[0]; xA1 = xp_[1]; if (C::DIM == 3) xA2 = xp_[C::DIM - 1]; } }
   if (pipelined && w_first < kp.nwork) {
-    load_idx(w_first, lidA, ndA);
-    if (w_first + w_stride < kp.nwork) load_idx(w_first + w_stride, lidB, ndB);
-    load_val(lidA, ndA);
+    MRH_LOAD_IDX(w_first, lidA, ndA)
+    if (w_first + w_stride < kp.nwork) MRH_LOAD_IDX(w_first + w_stride, lidB, ndB)
+    MRH_LOAD_VAL(lidA, ndA)
   }
   for (int64_t w = w_first; w < kp.nwork; w += w_stride) {
     if (pipelined) {
       if (lane < C::N) { reinterpret_cast<int*>(sm + L.oLid())[lane] = lidA; sm[L.oU() + lane] = uA; }
       if (lane < C::NV) {
-#pragma unroll
-        for (int c = 0; c < C::DIM; ++c) sm[L.oX() + lane * C::DIM + c] = xA[c];
+        double* xs_ = sm + L.oX() + lane * C::DIM;
+        xs_[0] = xA0; xs_[1] = xA1; if (C::DIM == 3) xs_[C::DIM - 1] = xA2;
       }
-      if (w + w_stride < kp.nwork) { lidA = lidB; ndA = ndB; load_val(lidA, ndA); }
-      if (w + 2 * w_stride < kp.nwork) load_idx(w + 2 * w_stride, lidB, ndB);
+      if (w + w_stride < kp.nwork) { lidA = lidB; ndA = ndB; MRH_LOAD_VAL(lidA, ndA) }
+      if (w + 2 * w_stride < kp.nwork) MRH_LOAD_IDX(w + 2 * w_stride, lidB, ndB)
     } else {
       for (int it = lane; it < C::N; it += 32) G::gather_dof(kp, L, sm, w, it);
       for (int it = lane; it < C::NV; it += 32) G::gather_vertex(kp, L, sm, w, it);
@@ -508,6 +502,8 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
     B::scatter(kp, L, sm, offs, G::elem_of(kp, w), lane);
     __syncwarp();                                          // the next element reuses the block
   }
+#undef MRH_LOAD_IDX
+#undef MRH_LOAD_VAL
 }
 #endif
 

@@ -32,5 +32,7 @@ int main(int argc, char** argv) {
   const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   size_t ls; nvrtcGetProgramLogSize(p, &ls); std::string log(ls, ' '); nvrtcGetProgramLog(p, &log[0]);
   printf("rc=%d compile %.1f s\n%s\n", (int)rc, dt, log.c_str());
+  if (rc == NVRTC_SUCCESS) { size_t cs; nvrtcGetCUBINSize(p, &cs); std::vector<char> c(cs); nvrtcGetCUBIN(p, c.data());
+    if (FILE* f = fopen("mrhyde_b200/build/jit_probe_batched.cubin", "wb")) { fwrite(c.data(), 1, cs, f); fclose(f); } }
   return rc != NVRTC_SUCCESS;
 }
