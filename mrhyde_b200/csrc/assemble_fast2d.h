@@ -170,11 +170,39 @@ struct ThermalQuadQ1 {
     }
 
     // ---- scatter: one RED per entry through the slot-pattern dictionary --------------------------------------------------
+    // The kernel is RED-bound (20 per element).  Consecutive lanes hold consecutive elements; where the next lane's left
+    // edge (local nodes 0, 3) is this element's right edge (local nodes 1, 2) its contributions to the shared rows and
+    // columns are added here in registers first (6 of 20 REDs saved on structured rows; the LIDs are compared, so any
+    // numbering is handled correctly).
+    bool skip03 = false;                  // this lane's (0,3) x (0,3) block and r0, r3 were handed to the previous lane
+#if defined(__CUDA_ARCH__)
+    {
+      const unsigned mask = __activemask();
+      const int lane = threadIdx.x & 31;
+      const int n0 = __shfl_down_sync(mask, lid[0], 1), n3 = __shfl_down_sync(mask, lid[3], 1);
+      const bool take = lane < 31 && ((mask >> (lane + 1)) & 1u) && n0 == lid[1] && n3 == lid[2];
+      const int gave = __shfl_up_sync(mask, (int)take, 1);
+      skip03 = lane > 0 && ((mask >> (lane - 1)) & 1u) && gave != 0;
+      const double q0 = __shfl_down_sync(mask, r[0], 1), q3 = __shfl_down_sync(mask, r[3], 1);
+      if (take) { r[1] += q0; r[2] += q3; }
+      if (JAC) {
+        if (!ADV) {
+          const double k00 = __shfl_down_sync(mask, K[tri(0, 0)], 1), k03 = __shfl_down_sync(mask, K[tri(0, 3)], 1),
+                       k33 = __shfl_down_sync(mask, K[tri(3, 3)], 1);
+          if (take) { K[tri(1, 1)] += k00; K[tri(1, 2)] += k03; K[tri(2, 2)] += k33; }
+        } else {
+          const double k00 = __shfl_down_sync(mask, K[0 * 4 + 0], 1), k03 = __shfl_down_sync(mask, K[0 * 4 + 3], 1),
+                       k30 = __shfl_down_sync(mask, K[3 * 4 + 0], 1), k33 = __shfl_down_sync(mask, K[3 * 4 + 3], 1);
+          if (take) { K[1 * 4 + 1] += k00; K[1 * 4 + 2] += k03; K[2 * 4 + 1] += k30; K[2 * 4 + 2] += k33; }
+        }
+      }
+    }
+#endif
     bool fx_[4];
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
       fx_[s] = kp.fixed[lid[s]] != 0;
-      if (!fx_[s]) atomic_add(kp.res + lid[s], -r[s]);
+      if (!fx_[s] && !(skip03 && (s == 0 || s == 3))) atomic_add(kp.res + lid[s], -r[s]);
     }
     if (!JAC) return;
     uint16_t pat[16];
@@ -196,6 +224,7 @@ struct ThermalQuadQ1 {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const double v = ADV ? K[i * 4 + j] : (i <= j ? K[tri(i, j)] : K[tri(j, i)]);
+        if (skip03 && (i == 0 || i == 3) && (j == 0 || j == 3)) continue;
         atomic_add(jrow + pat[i * 4 + j], v);
       }
     }
