@@ -323,14 +323,25 @@ struct BatPhases {
           for (int ct = 0; ct < NRT; ++ct) { A.k[v][rt][m][ct][0] = wv_zero(); A.k[v][rt][m][ct][1] = wv_zero(); }
 #pragma unroll
     for (int rt = 0; rt < NRT; ++rt) { A.r[rt][0] = wv_zero(); A.r[rt][1] = wv_zero(); }
-    for (int q = 0; q < L.nq; ++q) {
+    // basis fragments of point q: loaded (Q1) or rebuilt from J^-1 and the reference tables (larger bases) one point
+    // ahead, so that their loads overlap the DMMAs of the current point
+    auto basis_frag = [&](int q, int rt) {
       const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
+      return wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? (STORE_T ? sm[L.oT() + (size_t)q * NB * TA + j * TA + a] : basis_entry(tb, Ji, q, j, a)) : 0.0; });
+    };
+    WV tfn[NRT];
+#pragma unroll
+    for (int rt = 0; rt < NRT; ++rt) tfn[rt] = basis_frag(0, rt);
+    for (int q = 0; q < L.nq; ++q) {
       const double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
       const double* Dq = sm + L.oD() + LAY::dq(q);
       WV tf[NRT];
 #pragma unroll
-      for (int rt = 0; rt < NRT; ++rt)
-        tf[rt] = wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? (STORE_T ? sm[L.oT() + (size_t)q * NB * TA + j * TA + a] : basis_entry(tb, Ji, q, j, a)) : 0.0; });
+      for (int rt = 0; rt < NRT; ++rt) tf[rt] = tfn[rt];
+      if (q + 1 < L.nq) {
+#pragma unroll
+        for (int rt = 0; rt < NRT; ++rt) tfn[rt] = basis_frag(q + 1, rt);
+      }
       const WV ff = wv_make([&](int lane) { const int v = lane >> 2, a = lane & 3; return (v < NVAR && a < TA) ? sF[v * TA + a] : 0.0; });
 #pragma unroll
       for (int rt = 0; rt < NRT; ++rt) wv_mma(A.r[rt][0], A.r[rt][1], tf[rt], ff);
