@@ -296,7 +296,7 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
       if (side < 0 && !(H.cfg.flags & 16)) {
         JitKernel* jk = D.jit.hasBatchedSource() ? D.jit.batched() : nullptr;
         if (jk) {
-          JitApi& api = JitApi::get();
+          JitApi& api = JitApi::get(1);
           const bool tr = kp.tp.transient != 0;
           if (jk->smem_set != (size_t)kp.tab.nq * 2 + tr + 1) {     // launch shape of this module: once per (quadrature rule, transient)
             dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) {

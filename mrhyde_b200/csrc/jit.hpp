@@ -37,13 +37,21 @@ struct JitApi {
   CUresult (*OccupancyMaxActiveBlocks)(int*, CUfunction, int, size_t) = nullptr;
   CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
 
-  static JitApi& get() {
-    static JitApi a;
-    static bool tried = false;
-    if (tried) return a;
-    tried = true;
+  // which = 0: NVRTC found by soname (inside a PyTorch process the wheel-bundled 12.8) - the specialised thermal kernels
+  //            were tuned against it (C2 256^3: 6.46 ms, 6.50 ms with the toolkit's compiler);
+  // which = 1: the CUDA toolkit's NVRTC first - used for the batched kernel, where the 12.8 register allocation spills the
+  //            software-pipelined gather state (212 bytes) and 12.9 keeps it in registers (C4 192^3: 66.5 -> 61.6 ms).
+  // MRH_NVRTC_LIB overrides both.
+  static JitApi& get(int which = 0) {
+    static JitApi inst[2];
+    static bool tried[2] = {false, false};
+    JitApi& a = inst[which ? 1 : 0];
+    if (tried[which ? 1 : 0]) return a;
+    tried[which ? 1 : 0] = true;
     void* hn = nullptr;
-    for (const char* n : {"libnvrtc.so.12", "libnvrtc.so", "/usr/local/cuda/lib64/libnvrtc.so.12"}) if (!hn) hn = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (const char* ev = getenv("MRH_NVRTC_LIB")) hn = dlopen(ev, RTLD_NOW | RTLD_LOCAL);
+    if (which) { if (!hn) hn = dlopen("/usr/local/cuda/lib64/libnvrtc.so.12", RTLD_NOW | RTLD_LOCAL); }
+    for (const char* n : {"libnvrtc.so.12", "libnvrtc.so", "/usr/local/cuda/lib64/libnvrtc.so.12"}) if (!hn) hn = dlopen(n, RTLD_NOW | RTLD_LOCAL);
     void* hc = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
     if (!hn) { a.why = "libnvrtc not found"; return a; }
     if (!hc) { a.why = "libcuda not found"; return a; }
@@ -233,7 +241,7 @@ class JitCache {
   JitKernel* batched() {
     if (bat_tried_) return bat_.fn ? &bat_ : nullptr;
     bat_tried_ = true;
-    JitApi& api = JitApi::get();
+    JitApi& api = JitApi::get(1);
     if (!api.ok) { last_error = api.why; return nullptr; }
     if (bat_.source.empty()) { last_error = "no program source"; return nullptr; }
     std::vector<const char*> hdr_src, hdr_name;

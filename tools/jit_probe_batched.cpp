@@ -12,12 +12,36 @@ using namespace mrh;
 int main(int argc, char** argv) {
   const int phys = argc > 1 ? atoi(argv[1]) : 2, dim = argc > 2 ? atoi(argv[2]) : 3, order = argc > 3 ? atoi(argv[3]) : 1;
   ExprCompiler ec; ec.varlist = {"dx", "dy", "dz"}; ec.dim = 3;
-  ec.addFunction("s0", "3*(pi*pi)*sin(pi*x)*sin(pi*y)*sin(pi*z)-2*pi*pi*cos(pi*x)*cos(pi*y)*sin(pi*z)", "ip");
-  ec.addFunction("s1", "exp(x)*cos(2*pi*y)+z^2", "ip");
+  ec.addFunction("lambda", "1.0", "ip");
+  ec.addFunction("mu", "1.0", "ip");
+  ec.addFunction("A", "1.0", "ip");
+  ec.addFunction("B", "2.0", "ip");
+  ec.addFunction("C", "3.0", "ip");
+  ec.addFunction("dxxx", "(A*pi)*(A*pi)*sin(A*pi*x)*sin(A*pi*y)*sin(A*pi*z)", "ip");
+  ec.addFunction("dxyy", "(A*pi)*(A*pi)*sin(A*pi*x)*sin(A*pi*y)*sin(A*pi*z)", "ip");
+  ec.addFunction("dxzz", "(A*pi)*(A*pi)*sin(A*pi*x)*sin(A*pi*y)*sin(A*pi*z)", "ip");
+  ec.addFunction("dxxy", "-1.0*(A*pi)*(A*pi)*cos(A*pi*x)*cos(A*pi*y)*sin(A*pi*z)", "ip");
+  ec.addFunction("dxxz", "-1.0*(A*pi)*(A*pi)*cos(A*pi*x)*sin(A*pi*y)*cos(A*pi*z)", "ip");
+  ec.addFunction("dxyz", "-1.0*(A*pi)*(A*pi)*sin(A*pi*x)*cos(A*pi*y)*cos(A*pi*z)", "ip");
+  ec.addFunction("dyxx", "(B*pi)*(B*pi)*sin(B*pi*x)*sin(B*pi*y)*sin(B*pi*z)", "ip");
+  ec.addFunction("dyyy", "(B*pi)*(B*pi)*sin(B*pi*x)*sin(B*pi*y)*sin(B*pi*z)", "ip");
+  ec.addFunction("dyzz", "(B*pi)*(B*pi)*sin(B*pi*x)*sin(B*pi*y)*sin(B*pi*z)", "ip");
+  ec.addFunction("dyxy", "-1.0*(B*pi)*(B*pi)*cos(B*pi*x)*cos(B*pi*y)*sin(B*pi*z)", "ip");
+  ec.addFunction("dyxz", "-1.0*(B*pi)*(B*pi)*cos(B*pi*x)*sin(B*pi*y)*cos(B*pi*z)", "ip");
+  ec.addFunction("dyyz", "-1.0*(B*pi)*(B*pi)*sin(B*pi*x)*cos(B*pi*y)*cos(B*pi*z)", "ip");
+  ec.addFunction("dzxx", "(C*pi)*(C*pi)*sin(C*pi*x)*sin(C*pi*y)*sin(C*pi*z)", "ip");
+  ec.addFunction("dzyy", "(C*pi)*(C*pi)*sin(C*pi*x)*sin(C*pi*y)*sin(C*pi*z)", "ip");
+  ec.addFunction("dzzz", "(C*pi)*(C*pi)*sin(C*pi*x)*sin(C*pi*y)*sin(C*pi*z)", "ip");
+  ec.addFunction("dzxy", "-1.0*(C*pi)*(C*pi)*cos(C*pi*x)*cos(C*pi*y)*sin(C*pi*z)", "ip");
+  ec.addFunction("dzxz", "-1.0*(C*pi)*(C*pi)*cos(C*pi*x)*sin(C*pi*y)*cos(C*pi*z)", "ip");
+  ec.addFunction("dzyz", "-1.0*(C*pi)*(C*pi)*sin(C*pi*x)*cos(C*pi*y)*cos(C*pi*z)", "ip");
+  ec.addFunction("source dx", "(lambda+2.0*mu)*dxxx + mu*(dxyy+dyxy+dxzz+dzxz) + lambda*(dyxy+dzxz)", "ip");
+  ec.addFunction("source dy", "(lambda+2.0*mu)*dyyy + mu*(dyxx+dxxy+dyzz+dzyz) + lambda*(dxxy+dzyz)", "ip");
+  ec.addFunction("source dz", "(lambda+2.0*mu)*dzzz + mu*(dzxx+dxxz+dzyy+dyyz) + lambda*(dxxz+dyyz)", "ip");
   std::string src;
   for (int k = 0; k < 8; ++k) {
     const std::string name = "p" + std::to_string(k);
-    if (k < 2) src += jit_function_source(name, ec.compile(k == 0 ? "s0" : "s1", "ip"), ec.code, ec.cpool);
+    if (k >= 2 && k < 5) src += jit_function_source(name, ec.compile(k == 2 ? "source dx" : k == 3 ? "source dy" : "source dz", "ip"), ec.code, ec.cpool);
     else src += "  static __device__ __forceinline__ double " + name + "(double, double, double, double) { return 0.0; }\n";
   }
   JitCache jc; jc.setBatchedSource(src, phys, dim, order);
@@ -26,9 +50,10 @@ int main(int argc, char** argv) {
   for (int i = 0; i < k_num_embedded_headers; ++i) { hn.push_back(k_embedded_headers[i].name); hs.push_back(k_embedded_headers[i].text); }
   std::string full = jc.batchedSource();
   nvrtcProgram p; nvrtcCreateProgram(&p, full.c_str(), "probe.cu", (int)hs.size(), hs.data(), hn.data());
-  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", "--ptxas-options=-v"};
+  const char* extra = getenv("MRH_PROBE_DEFINE") ? getenv("MRH_PROBE_DEFINE") : "-DMRH_PROBE_NONE=1";
+  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", "--ptxas-options=-v", extra};
   const auto t0 = std::chrono::steady_clock::now();
-  nvrtcResult rc = nvrtcCompileProgram(p, 5, opts);
+  nvrtcResult rc = nvrtcCompileProgram(p, 6, opts);
   const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   size_t ls; nvrtcGetProgramLogSize(p, &ls); std::string log(ls, ' '); nvrtcGetProgramLog(p, &log[0]);
   printf("rc=%d compile %.1f s\n%s\n", (int)rc, dt, log.c_str());
