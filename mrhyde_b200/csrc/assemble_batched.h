@@ -98,7 +98,8 @@ struct WarpSmem {
   MRH_HD size_t oH() const { return even_up(oCoef() + (size_t)nq * MRH_NCOEF); }
   MRH_HD size_t oR() const { return even_up(oH() + 1); }
   MRH_HD size_t oRowBase() const { return even_up(oR() + N); }                         // int64 per natural row
-  MRH_HD size_t oLid() const { return even_up(oRowBase() + N); }
+  MRH_HD size_t oPatOff() const { return even_up(oRowBase() + N); }                    // int per natural row: row offset in the slot pattern
+  MRH_HD size_t oLid() const { return even_up(oPatOff() + (N + 1) / 2); }
   MRH_HD size_t total_doubles() const { return even_up(oLid() + (N + 1) / 2 + 1); }
   MRH_HD size_t oK() const { return k_aliases_d() ? oD() : oKx(); }
   // what GenPhases::gather_* expect of a layout
@@ -347,22 +348,27 @@ struct BatPhases {
       for (int rt = 0; rt < NRT; ++rt) wv_mma(A.r[rt][0], A.r[rt][1], tf[rt], ff);
       if (!kp.compute_jac) continue;
 #pragma unroll
-      for (int v = 0; v < NVAR; ++v)
+      for (int v = 0; v < NVAR; ++v) {
+        // all first products of this row variable are issued before the second products that consume them, so a
+        // dependent DMMA never follows its producer back to back
+        WV l0[NT][NRT], l1[NT][NRT];
 #pragma unroll
         for (int t = 0; t < NT; ++t) {
           const double* Dt = Dq + (size_t)(v * NT + t) * 32;
           const WV df = wv_make([&](int lane) { return Dt[lane]; });
 #pragma unroll
-          for (int rt = 0; rt < NRT; ++rt) {
-            WV l0 = wv_zero(), l1 = wv_zero();
-            wv_mma(l0, l1, tf[rt], df);
+          for (int rt = 0; rt < NRT; ++rt) { l0[t][rt] = wv_zero(); l1[t][rt] = wv_zero(); wv_mma(l0[t][rt], l1[t][rt], tf[rt], df); }
+        }
+#pragma unroll
+        for (int t = 0; t < NT; ++t)
+#pragma unroll
+          for (int rt = 0; rt < NRT; ++rt)
 #pragma unroll
             for (int ct = 0; ct < NRT; ++ct) {
-              wv_mma(A.k[v][rt][2 * t][ct][0], A.k[v][rt][2 * t][ct][1], l0, tf[ct]);
-              if (2 * t + 1 < NVAR) wv_mma(A.k[v][rt][(2 * t + 1 < NVAR) ? 2 * t + 1 : 0][ct][0], A.k[v][rt][(2 * t + 1 < NVAR) ? 2 * t + 1 : 0][ct][1], l1, tf[ct]);
+              wv_mma(A.k[v][rt][2 * t][ct][0], A.k[v][rt][2 * t][ct][1], l0[t][rt], tf[ct]);
+              if (2 * t + 1 < NVAR) wv_mma(A.k[v][rt][(2 * t + 1 < NVAR) ? 2 * t + 1 : 0][ct][0], A.k[v][rt][(2 * t + 1 < NVAR) ? 2 * t + 1 : 0][ct][1], l1[t][rt], tf[ct]);
             }
-          }
-        }
+      }
     }
   }
 
@@ -401,6 +407,7 @@ struct BatPhases {
     const int* sLid = reinterpret_cast<const int*>(sm + L.oLid());
     const int rowslot = offs[lane], row = sLid[rowslot];
     reinterpret_cast<int64_t*>(sm + L.oRowBase())[lane] = kp.fixed[row] ? (int64_t)-1 : kp.rowptr[row];
+    reinterpret_cast<int*>(sm + L.oPatOff())[lane] = rowslot * N;
     if (kp.lump_mass && kp.compute_jac) {                            // assemblyManager.cpp:4130-4132
       double* K = sm + L.oK() + (size_t)lane * KS;
       double s = 0.0;
@@ -419,18 +426,21 @@ struct BatPhases {
     const int col = (lane % NVAR) * NB + lane / NVAR;                // natural column this lane serves
     const int colslot = offs[col];
     const uint16_t* pat = kp.pat + (size_t)kp.pat_id[e] * N * N + colslot;
+    const int* po = reinterpret_cast<const int*>(sm + L.oPatOff());
+    const double* Kc = K + col;
     constexpr int UR = 4;                                            // rows in flight: the slot loads of UR rows overlap
+#pragma unroll
     for (int r0 = 0; r0 < N; r0 += UR) {
       int64_t base[UR]; uint16_t slot[UR];
 #pragma unroll
       for (int k = 0; k < UR; ++k) {
         const int r = r0 + k;
         base[k] = r < N ? rb[r] : (int64_t)-1;
-        slot[k] = base[k] >= 0 ? pat[(size_t)offs[r] * N] : (uint16_t)0;
+        slot[k] = base[k] >= 0 ? pat[po[r < N ? r : 0]] : (uint16_t)0;
       }
 #pragma unroll
       for (int k = 0; k < UR; ++k)
-        if (base[k] >= 0) atomic_add(kp.jac + base[k] + slot[k], K[(size_t)(r0 + k) * KS + col]);
+        if (base[k] >= 0) atomic_add(kp.jac + base[k] + slot[k], Kc[(r0 + k) * KS]);
     }
   }
 };

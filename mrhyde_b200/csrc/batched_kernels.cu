@@ -20,7 +20,9 @@ namespace {
 
 // register budget per configuration (measured: capping the 3-D Navier-Stokes point phase below its 255 registers to fit
 // 10 warps per SM instead of 8 spills 0.5 KB per thread and is slower: 29.2 ms instead of 23.3-25.7 ms at 128^3)
-template <class C> struct BatBounds { static constexpr int THREADS = 32 * MRH_BATCHED_MAXW, MINB = 1; };
+// Default: two CTAs of up to 192 threads per SM, i.e. at most 168 registers (12 warps per SM); the Navier-Stokes point
+// phase is left its full register budget.
+template <class C> struct BatBounds { static constexpr int THREADS = 32 * MRH_BATCHED_MAXW, MINB = (C::PHYS == PHYS_NS) ? 1 : 2; };
 #if MRH_NS_HALF_CHUNKS
 template <> struct BatBounds<GenCfg<PHYS_NS, 3, 1>> { static constexpr int THREADS = 160, MINB = 2; };   // <= 204 registers: 10 warps per SM
 #endif
