@@ -82,7 +82,6 @@ struct WarpSmem {
   MRH_HD WarpSmem(int nq_, bool tr) : nq(nq_), transient(tr) {}
   MRH_HD static size_t dq(int q) { return (size_t)q * QS + (size_t)((q >> 2) << 2); }
   MRH_HD size_t dsize() const { return even_up(dq(nq)); }
-  MRH_HD bool k_aliases_d() const { return (size_t)N * KS <= dsize(); }
   MRH_HD size_t oX() const { return 0; }
   MRH_HD size_t oU() const { return even_up(oX() + (size_t)C::NV * C::DIM); }
   MRH_HD size_t oUd() const { return even_up(oU() + N); }
@@ -93,15 +92,19 @@ struct WarpSmem {
   MRH_HD size_t oT() const { return even_up(oJi() + (size_t)nq * C::DIM * C::DIM); }     // T[q][j][0..dim], STORE_T only
   MRH_HD size_t oF() const { return even_up(oT() + (STORE_T ? (size_t)nq * NB * TA : 0)); }
   MRH_HD size_t oD() const { return even_up(oF() + (size_t)nq * NVAR * TA); }
-  MRH_HD size_t oKx() const { return even_up(oD() + dsize()); }                       // separate K only when it cannot alias D
-  MRH_HD size_t oCoef() const { return even_up(oKx() + (k_aliases_d() ? 0 : (size_t)N * KS)); }
-  MRH_HD size_t oH() const { return even_up(oCoef() + (size_t)nq * MRH_NCOEF); }
+  // F, D and the pre-evaluated coefficients are dead once the contraction has read them: the element matrix K takes
+  // their place (a separate block only when even the three together are too small)
+  MRH_HD size_t oCoef() const { return even_up(oD() + dsize()); }
+  MRH_HD size_t dead_end() const { return even_up(oCoef() + (size_t)nq * MRH_NCOEF); }
+  MRH_HD bool k_aliases_d() const { return (size_t)N * KS <= dead_end() - oF(); }
+  MRH_HD size_t oKx() const { return dead_end(); }
+  MRH_HD size_t oH() const { return even_up(oKx() + (k_aliases_d() ? 0 : (size_t)N * KS)); }
   MRH_HD size_t oR() const { return even_up(oH() + 1); }
   MRH_HD size_t oRowBase() const { return even_up(oR() + N); }                         // int64 per natural row
   MRH_HD size_t oPatOff() const { return even_up(oRowBase() + N); }                    // int per natural row: row offset in the slot pattern
   MRH_HD size_t oLid() const { return even_up(oPatOff() + (N + 1) / 2); }
   MRH_HD size_t total_doubles() const { return even_up(oLid() + (N + 1) / 2 + 1); }
-  MRH_HD size_t oK() const { return k_aliases_d() ? oD() : oKx(); }
+  MRH_HD size_t oK() const { return k_aliases_d() ? oF() : oKx(); }
   // what GenPhases::gather_* expect of a layout
   int EB = 1;
 };
