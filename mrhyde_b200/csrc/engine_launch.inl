@@ -305,6 +305,7 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
               if (api.FuncSetAttribute(jk->fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)want) != CUDA_SUCCESS)
                 throw std::runtime_error("CUDA error: cuFuncSetAttribute(shared memory) failed");
               jk->tiled_blocks_per_sm = batched_pick_warps<C>(kp.tab.nq, tr, [&](int threads, size_t smem) {
+                if (threads > D.jit.bat_max_threads) return 0;
                 int b = 0; return api.OccupancyMaxActiveBlocks(&b, jk->fn, threads, smem) == CUDA_SUCCESS ? b : 0; }, jk->blocks_per_sm);
               jk->ws_smem_set = batched_smem<C>(kp.tab.nq, tr, jk->tiled_blocks_per_sm);
             });

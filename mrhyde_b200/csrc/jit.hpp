@@ -224,14 +224,17 @@ class JitCache {
   }
 
   // ---- batched volume kernel (assemble_batched.h) with the state-independent programs printed as functions p0..p7 ----
-  void setBatchedSource(const std::string& progs, int phys, int dim, int order) {
+  // threads / minb: launch bounds of the kernel (minb > 0: register budget 65536 / (threads * minb); 0: ptxas' own choice)
+  void setBatchedSource(const std::string& progs, int phys, int dim, int order, int threads = 192, int minb = 0) {
+    bat_bounds_ = "-DMRH_BAT_BOUNDS=" + std::to_string(threads) + (minb > 0 ? "," + std::to_string(minb) : std::string()); bat_max_threads = threads;
+    if (const char* ev = getenv("MRH_BAT_BOUNDS")) { bat_bounds_ = std::string("-DMRH_BAT_BOUNDS=") + ev; bat_max_threads = atoi(ev); }   // tuning experiments
     if (bat_.mod && JitApi::get().ok) JitApi::get().ModuleUnload(bat_.mod);
     bat_ = JitKernel(); bat_tried_ = false;
     bat_.source = std::string("#include \"assemble_batched.h\"\nnamespace mrh {\nstruct JitProgs {\n  static constexpr bool jit = true;\n") + progs +
         "  static __device__ __forceinline__ double eval(int k, double x, double y, double z, double t) {\n    switch (k) {\n"
         "      case 0: return p0(x, y, z, t); case 1: return p1(x, y, z, t); case 2: return p2(x, y, z, t); case 3: return p3(x, y, z, t);\n"
         "      case 4: return p4(x, y, z, t); case 5: return p5(x, y, z, t); case 6: return p6(x, y, z, t); default: return p7(x, y, z, t);\n    }\n  }\n};\n}\n"
-        "extern \"C\" __global__ void __launch_bounds__(192) mrh_jit_batched(const __grid_constant__ mrh::KParams kp) {\n"
+        "extern \"C\" __global__ void __launch_bounds__(MRH_BAT_BOUNDS) mrh_jit_batched(const __grid_constant__ mrh::KParams kp) {\n"
         "  extern __shared__ __align__(16) double smem_all[];\n"
         "  mrh::batched_body<mrh::GenCfg<" + std::to_string(phys) + ", " + std::to_string(dim) + ", " + std::to_string(order) + ">, mrh::JitProgs>(kp, smem_all);\n}\n";
   }
@@ -248,8 +251,8 @@ class JitCache {
     for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
     nvrtcProgram prog;
     if (api.CreateProgram(&prog, bat_.source.c_str(), "mrh_jit_batched.cu", (int)hdr_src.size(), hdr_src.data(), hdr_name.data()) != NVRTC_SUCCESS) { last_error = "nvrtcCreateProgram failed"; return nullptr; }
-    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1"};
-    const nvrtcResult rc = api.CompileProgram(prog, 4, opts);
+    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", bat_bounds_.c_str()};
+    const nvrtcResult rc = api.CompileProgram(prog, 5, opts);
     size_t ls = 0; api.GetProgramLogSize(prog, &ls);
     if (ls > 1) { bat_.log.resize(ls); api.GetProgramLog(prog, &bat_.log[0]); }
     if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + bat_.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }
@@ -264,6 +267,10 @@ class JitCache {
 
  private:
   JitKernel bat_;
+  std::string bat_bounds_ = "-DMRH_BAT_BOUNDS=192";
+ public:
+  int bat_max_threads = 192;
+ private:
   bool bat_tried_ = false;
   std::map<int, JitKernel> kernels_;
   std::string coef_src_;

@@ -44,16 +44,18 @@ int main(int argc, char** argv) {
     if (k >= 2 && k < 5) src += jit_function_source(name, ec.compile(k == 2 ? "source dx" : k == 3 ? "source dy" : "source dz", "ip"), ec.code, ec.cpool);
     else src += "  static __device__ __forceinline__ double " + name + "(double, double, double, double) { return 0.0; }\n";
   }
-  JitCache jc; jc.setBatchedSource(src, phys, dim, order);
+  const int thr = getenv("MRH_PROBE_THREADS") ? atoi(getenv("MRH_PROBE_THREADS")) : 192, mb = getenv("MRH_PROBE_MINB") ? atoi(getenv("MRH_PROBE_MINB")) : 0;
+  JitCache jc; jc.setBatchedSource(src, phys, dim, order, thr, mb);
+  const std::string o1 = "-DMRH_BAT_BOUNDS=" + std::to_string(thr) + (mb > 0 ? "," + std::to_string(mb) : std::string()), o2 = "-DMRH_PROBE_X=1";
   // same steps as JitCache::batched(), with ptxas -v and without loading the module
   std::vector<const char*> hs, hn;
   for (int i = 0; i < k_num_embedded_headers; ++i) { hn.push_back(k_embedded_headers[i].name); hs.push_back(k_embedded_headers[i].text); }
   std::string full = jc.batchedSource();
   nvrtcProgram p; nvrtcCreateProgram(&p, full.c_str(), "probe.cu", (int)hs.size(), hs.data(), hn.data());
   const char* extra = getenv("MRH_PROBE_DEFINE") ? getenv("MRH_PROBE_DEFINE") : "-DMRH_PROBE_NONE=1";
-  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", "--ptxas-options=-v", extra};
+  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", "--ptxas-options=-v", extra, o1.c_str(), o2.c_str()};
   const auto t0 = std::chrono::steady_clock::now();
-  nvrtcResult rc = nvrtcCompileProgram(p, 6, opts);
+  nvrtcResult rc = nvrtcCompileProgram(p, 8, opts);
   const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   size_t ls; nvrtcGetProgramLogSize(p, &ls); std::string log(ls, ' '); nvrtcGetProgramLog(p, &log[0]);
   printf("rc=%d compile %.1f s\n%s\n", (int)rc, dt, log.c_str());
