@@ -91,6 +91,10 @@ int mrh_build_brick(mrh_handle h, const int32_t* nxyz, const double* lo, const d
 /* ---- ... or hand over what Panzer/Tpetra already built ------------------------------------------- */
 /* nodes (nnode,dim), elem2node (nelem, 4|8) shards vertex order: Group::nodes, assemblyManager.cpp:684-688 */
 int mrh_set_mesh(mrh_handle h, const double* nodes, int64_t nnode, const int32_t* elem2node, int64_t nelem);
+/* replace the vertex coordinates of the current mesh (same topology), before or after mrh_finalize: moving / distorted
+ * meshes.  The reference recomputes its stored bases from Group::nodes (src/tools/group.cpp:137-245 computeBasis);
+ * here nothing geometric is stored, so only the coordinate array is refreshed. */
+int mrh_set_nodes(mrh_handle h, const double* nodes, int64_t nnode);
 /* lids (nelem, nvar*nb) = disc->dof_lids, offsets (nvar, nb) = wkset->offsets (assemblyManager.cpp:656-669) */
 int mrh_set_dofmap(mrh_handle h, const int32_t* lids, const int32_t* offsets, int64_t nlocal);
 /* local graph of the overlapped matrix (linearAlgebraInterface.cpp:219-234); columns ascending per row */

@@ -59,7 +59,9 @@ inline void build_brick(HostMesh& M, int dim, const int* Nin, const double* lo, 
   // side sets in alphabetical order with their shards local side id
   struct Def { const char* name; int ls, axis, high; };
   static const Def d2[4] = {{"bottom", 0, 1, 0}, {"left", 3, 0, 0}, {"right", 1, 0, 1}, {"top", 2, 1, 1}};
-  static const Def d3[6] = {{"back", 2, 1, 1}, {"bottom", 4, 2, 0}, {"front", 0, 1, 0}, {"left", 3, 0, 0}, {"right", 1, 0, 1}, {"top", 5, 2, 1}};
+  // 3-D names follow panzer_stk::CubeHexMeshFactory: bottom/top are the y planes, back/front the z planes (the reference's
+  // inputs pair 'top;bottom' with periodic type 'xz-all', regression/maxwell/Multiblock/input_mesh.yaml)
+  static const Def d3[6] = {{"back", 4, 2, 0}, {"bottom", 0, 1, 0}, {"front", 5, 2, 1}, {"left", 3, 0, 0}, {"right", 1, 0, 1}, {"top", 2, 1, 1}};
   M.sides.clear();
   for (int s = 0; s < ((dim == 3) ? 6 : 4); ++s) {
     const Def& D = (dim == 3) ? d3[s] : d2[s];

@@ -88,7 +88,7 @@ MRH_HDN inline S eval_code(const Instr* code, const double* cpool, int start, in
       case OP_TAN: st[sp - 1] = f_tan(st[sp - 1]); break;
       case OP_EXP: st[sp - 1] = f_exp(st[sp - 1]); break;
       case OP_LOG: st[sp - 1] = f_log(st[sp - 1]); break;
-      case OP_SQRT: st[sp - 1] = f_sqrt(st[sp - 1]); break;
+      case OP_SQRT: st[sp - 1] = f_sqrt0(st[sp - 1]); break;
       case OP_SINH: st[sp - 1] = f_sinh(st[sp - 1]); break;
       case OP_COSH: st[sp - 1] = f_cosh(st[sp - 1]); break;
       case OP_ABS: if (val(st[sp - 1]) < 0.0) st[sp - 1] = -st[sp - 1]; break;
@@ -197,7 +197,7 @@ MRH_HDN inline void eval_code_vec(const Instr* code, const double* cpool, int st
           case OP_TAN: r = tan(t); break;
           case OP_EXP: r = exp(t); break;
           case OP_LOG: r = log(t); break;
-          case OP_SQRT: r = sqrt(t); break;
+          case OP_SQRT: r = t <= 0.0 ? 0.0 : sqrt(t); break;
           case OP_SINH: r = sinh(t); break;
           case OP_COSH: r = cosh(t); break;
           default: r = t < 0.0 ? -t : t; break;

@@ -15,6 +15,7 @@ struct mrh_engine {
 static thread_local std::string g_create_err;
 static int backend_create(mrh_engine* h);
 static void backend_destroy(mrh_engine* h);
+static void backend_nodes_changed(mrh_engine* h);      // vertex coordinates replaced after finalize
 
 #define MRH_TRY(h) try {
 #define MRH_CATCH(h)                                                                                  \
@@ -59,9 +60,21 @@ int mrh_set_mesh(mrh_handle h, const double* nodes, int64_t nnode, const int32_t
   MRH_TRY(h)
   auto& M = h->host.mesh;
   M.dim = h->host.dim; M.nvert = h->host.nv; M.nnode = nnode; M.nelem = nelem;
+  for (int64_t k = 0; k < nelem * M.nvert; ++k) if (elem2node[k] < 0 || elem2node[k] >= nnode) throw std::runtime_error("element vertex id out of range");
   M.nodes.assign(nodes, nodes + nnode * M.dim);
   M.elem2node.assign(elem2node, elem2node + nelem * M.nvert);
+  for (int d = 0; d < 3; ++d) M.NXYZ[d] = 0;
   M.sides.clear(); h->host.have_mesh = true; h->host.host_final = false;
+  return MRH_OK;
+  MRH_CATCH(h)
+}
+
+int mrh_set_nodes(mrh_handle h, const double* nodes, int64_t nnode) {
+  if (!h || !nodes || !h->host.have_mesh || nnode != h->host.mesh.nnode) return MRH_EINVAL;
+  MRH_TRY(h)
+  auto& M = h->host.mesh;
+  M.nodes.assign(nodes, nodes + nnode * M.dim);
+  backend_nodes_changed(h);
   return MRH_OK;
   MRH_CATCH(h)
 }
@@ -99,6 +112,7 @@ int mrh_add_side(mrh_handle h, const char* name, int32_t local_side, const int32
   if (!h || !name || (n > 0 && !elems) || !h->host.have_mesh) return MRH_EINVAL;
   MRH_TRY(h)
   if (local_side < 0 || local_side >= h->host.ref.nsides) throw std::runtime_error("local side id out of range");
+  for (int64_t k = 0; k < n; ++k) if (elems[k] < 0 || elems[k] >= h->host.mesh.nelem) throw std::runtime_error("side-set element id out of range");
   mrh::SideSet S; S.name = name; S.local_side = local_side; S.elems.assign(elems, elems + n);
   h->host.mesh.sides.push_back(S); h->host.host_final = false;
   return MRH_OK;

@@ -397,6 +397,13 @@ static void backend_destroy(mrh_engine* h) {
   delete D;
 }
 
+static void backend_nodes_changed(mrh_engine* h) {
+  auto* D = (DeviceImpl*)h->impl;
+  if (!D || !D->ready) return;                      // not finalized yet: mrh_finalize uploads the new coordinates
+  CUDA_CK(cudaSetDevice(D->device));
+  CUDA_CK(cudaMemcpy(D->nodes.p, h->host.mesh.nodes.data(), h->host.mesh.nodes.size() * sizeof(double), cudaMemcpyHostToDevice));
+}
+
 #define MRH_NEED_GPU(h) if (!(h)->impl) { (h)->err = "no CUDA device available; this engine has no CPU fallback"; return MRH_ECUDA; }
 #define MRH_CATCH_CUDA(h)                                                                             \
   } catch (const std::exception& e) {                                                                 \

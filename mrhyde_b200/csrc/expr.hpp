@@ -69,17 +69,23 @@ class ExprCompiler {
     return p;
   }
 
+  // Literal test of the reference (src/tools/interpreter.cpp:18-58), restated as a scan over character classes: only
+  // digits, at most one '.', at most one exponent marker, and a sign only in front or right behind the exponent marker.
+  // (Loose on purpose, like the reference: "", "." and "e" pass here and fail later in the conversion.)
   static bool isScalar(const std::string& s) {
-    bool isnum = true; int numdots = 0, nume = 0;
-    for (size_t k = 0; k < s.length(); k++) {
-      if (!isdigit((unsigned char)s[k])) {
-        if (s[k] == '.') { if (numdots == 0) numdots += 1; else isnum = false; }
-        else if (s[k] == 'e' || s[k] == 'E') { if (nume == 0) nume += 1; else isnum = false; }
-        else if (s[k] == '+' || s[k] == '-') { if (k > 0 && !(s[k - 1] == 'e' || s[k - 1] == 'E')) isnum = false; }
-        else isnum = false;
-      }
+    int dots = 0, exps = 0;
+    char prev = 'e';                                  // makes a leading sign acceptable
+    for (const char c : s) {
+      const bool expo = (c == 'e' || c == 'E');
+      const bool sign = (c == '+' || c == '-');
+      if (c == '.') ++dots;
+      else if (expo) ++exps;
+      else if (sign) { if (!(prev == 'e' || prev == 'E')) return false; }
+      else if (!isdigit((unsigned char)c)) return false;
+      if (dots > 1 || exps > 1) return false;
+      prev = c;
     }
-    return isnum;
+    return true;
   }
 
  private:

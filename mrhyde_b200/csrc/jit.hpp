@@ -123,7 +123,7 @@ inline std::string jit_function_body(const Prog& pr, const std::vector<Instr>& c
       case OP_TAN: emit("tan(" + a + ")"); break;
       case OP_EXP: emit("exp(" + a + ")"); break;
       case OP_LOG: emit("log(" + a + ")"); break;
-      case OP_SQRT: emit("sqrt(" + a + ")"); break;
+      case OP_SQRT: emit("(" + a + " <= 0.0) ? 0.0 : sqrt(" + a + ")"); break;     // functionManager.cpp:1062-1067
       case OP_SINH: emit("sinh(" + a + ")"); break;
       case OP_COSH: emit("cosh(" + a + ")"); break;
       default: emit("(" + a + " < 0.0) ? -" + a + " : " + a); break;

@@ -137,6 +137,10 @@ template <int P> MRH_HD PAD<P> f_tan(const PAD<P>& a) { const double t = tan(a.v
 template <int P> MRH_HD PAD<P> f_exp(const PAD<P>& a) { const double e = exp(a.v); return chain(a, e, e); }
 template <int P> MRH_HD PAD<P> f_log(const PAD<P>& a) { return chain(a, log(a.v), 1.0 / a.v); }
 template <int P> MRH_HD PAD<P> f_sqrt(const PAD<P>& a) { const double s = sqrt(a.v); return chain(a, s, 0.5 / s); }
+// "sqrt" of the coefficient language: 0 with zero derivatives for arguments <= 0
+// (/root/reference/src/managers/functionManager.cpp:1062-1067, 1258-1262, 1573-1581)
+MRH_HD double f_sqrt0(double x) { return x <= 0.0 ? 0.0 : sqrt(x); }
+template <int P> MRH_HD PAD<P> f_sqrt0(const PAD<P>& a) { if (a.v <= 0.0) return PAD<P>(0.0); return f_sqrt(a); }
 template <int P> MRH_HD PAD<P> f_sinh(const PAD<P>& a) { return chain(a, sinh(a.v), cosh(a.v)); }
 template <int P> MRH_HD PAD<P> f_cosh(const PAD<P>& a) { return chain(a, cosh(a.v), sinh(a.v)); }
 // pow with both arguments possibly active (d/db only when b carries derivatives, like Sacado's pow)

@@ -27,7 +27,7 @@ class MrhState(C.Structure):
                 ("stream", C.c_void_p)]
 
 
-SYMBOLS = ["mrh_default_config", "mrh_create", "mrh_destroy", "mrh_last_error", "mrh_build_brick", "mrh_set_mesh",
+SYMBOLS = ["mrh_default_config", "mrh_create", "mrh_destroy", "mrh_last_error", "mrh_build_brick", "mrh_set_mesh", "mrh_set_nodes",
            "mrh_set_dofmap", "mrh_set_crs", "mrh_add_side", "mrh_set_bc", "mrh_add_function", "mrh_finalize",
            "mrh_finalize_host", "mrh_assemble_res", "mrh_assemble_jacres", "mrh_assemble_jacres_host",
            "mrh_get_sizes", "mrh_get_mesh", "mrh_get_dofmap", "mrh_get_crs", "mrh_get_side", "mrh_get_bc",
@@ -62,6 +62,7 @@ def load_library(path=None):
         getattr(L, n).argtypes = [C.c_void_p]
     L.mrh_build_brick.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.mrh_set_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+    L.mrh_set_nodes.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
     L.mrh_set_dofmap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
     L.mrh_set_crs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
     L.mrh_add_side.argtypes = [C.c_void_p, C.c_char_p, C.c_int32, C.c_void_p, C.c_int64]
@@ -184,6 +185,10 @@ class Engine:
         nodes = np.ascontiguousarray(nodes, dtype=np.float64)
         e2n = np.ascontiguousarray(elem2node, dtype=np.int32)
         self._ck(self.L.mrh_set_mesh(self.h, _ptr(nodes), nodes.shape[0], _ptr(e2n), e2n.shape[0]), "mrh_set_mesh")
+
+    def set_nodes(self, nodes):
+        nodes = np.ascontiguousarray(nodes, dtype=np.float64)
+        self._ck(self.L.mrh_set_nodes(self.h, _ptr(nodes), nodes.shape[0]), "mrh_set_nodes")
 
     def set_dofmap(self, lids, offsets, nlocal):
         lids = np.ascontiguousarray(lids, dtype=np.int32)

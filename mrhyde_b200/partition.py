@@ -26,7 +26,7 @@ def slab_problem(p, rank, world):
     assert m["dim"] == 3, "slab partition is along z"
     z0, L = m.get("zmin", 0.0), m.get("zmax", 1.0) - m.get("zmin", 0.0)
     m["zmin"], m["zmax"] = z0 + rank * L, z0 + (rank + 1) * L
-    phys = [s for s in SIDES3 if not ((s == "bottom" and rank > 0) or (s == "top" and rank < world - 1))]
+    phys = [s for s in SIDES3 if not ((s == "back" and rank > 0) or (s == "front" and rank < world - 1))]   # z planes: back (z-) / front (z+)
     for kind in ("dirichlet", "neumann", "flux"):
         for var, sides in list(q.get(kind, {}).items()):
             new = {}

@@ -32,7 +32,7 @@ def lib():
         L.orc_create.argtypes = [C.c_char_p]
         L.orc_last_error.restype = C.c_char_p
         for name in ("orc_destroy", "orc_sizes", "orc_get_mesh", "orc_get_dofmap", "orc_get_crs",
-                     "orc_get_group_basis", "orc_get_bgroup", "orc_set_time", "orc_last_timing"):
+                     "orc_get_group_basis", "orc_get_bgroup", "orc_set_time", "orc_last_timing", "orc_set_nodes"):
             getattr(L, name).restype = None
         _LIB = L
     return _LIB
@@ -94,6 +94,12 @@ class Oracle:
         e2n = np.zeros((self.nelem, self.nvert), dtype=np.int32)
         self.L.orc_get_mesh(C.c_void_p(self.h), _p(nodes), _p(e2n, C.c_int))
         return nodes, e2n
+
+    def set_nodes(self, nodes):
+        """Replace the vertex coordinates (same topology): distorted, non-affine test meshes."""
+        nodes = np.ascontiguousarray(nodes, dtype=np.float64)
+        assert nodes.shape == (self.nnode, self.dim)
+        self.L.orc_set_nodes(C.c_void_p(self.h), _p(nodes))
 
     def dofmap(self):
         lids = np.zeros((self.nelem, self.ndof_elem), dtype=np.int32)

@@ -10,8 +10,11 @@
 //   BC function names       /root/reference/src/interfaces/physicsInterface.cpp:156-478
 //   var_bcs strings         /root/reference/src/interfaces/discretizationInterface.cpp:2556-2593
 #pragma once
+#include <atomic>
 #include <chrono>
+#include <mutex>
 #include <sstream>
+#include <thread>
 #include "basis.hpp"
 #include "mesh.hpp"
 #include "physics.hpp"
@@ -66,6 +69,13 @@ struct Config {
   }
 };
 
+inline void atomic_add(double* p, double v) {      // Kokkos::atomic_add on the host
+  uint64_t* q = reinterpret_cast<uint64_t*>(p);
+  uint64_t old = __atomic_load_n(q, __ATOMIC_RELAXED), want;
+  do { double d; memcpy(&d, &old, 8); d += v; memcpy(&want, &d, 8); }
+  while (!__atomic_compare_exchange_n(q, &old, want, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED));
+}
+
 struct TimeIntegration {
   int nstages = 1, nsteps = 1, stage = 0;
   std::vector<double> A{1.0}, b{1.0}, bdf{1.0, -1.0};   // backward Euler
@@ -100,6 +110,13 @@ class Oracle {
     const int ndr = dofs.ndof_elem;
     const int sizes[7] = {2, 4, 8, 16, 18, 24, 32};
     type_AD = -1; for (int s : sizes) if (ndr <= s) { type_AD = s; break; }
+  }
+
+  // Replace the vertex coordinates (same topology): distorted / non-affine test meshes.  Stored physical bases are rebuilt,
+  // as Group::computeBasis would after a mesh update (/root/reference/src/tools/group.cpp:137-245).
+  void setNodes(const double* xyz) {
+    mesh.nodes.assign(xyz, xyz + (size_t)mesh.nnode * mesh.dim);
+    groups.clear(); bgroups.clear(); createGroups();
   }
 
   int varIndex(const std::string& v) const { for (size_t i = 0; i < varlist.size(); ++i) if (varlist[i] == v) return (int)i; return -1; }
@@ -213,6 +230,17 @@ class Oracle {
                     double* res_out, double* jac_out, int nthreads) {
     using clk = std::chrono::steady_clock;
     const auto T0 = clk::now();
+    double tg_all = 0, tp_all = 0, ts_all = 0;
+    if (nthreads < 1) nthreads = 1;
+    const bool atomic = nthreads > 1;          // reference: useAtomics when the execution space is concurrent (assemblyManager.cpp:4058-4061)
+    std::string fail;
+    // One Workset / FunctionManager / module per thread (the reference has one per block and lets Kokkos::OpenMP thread over the
+    // elements inside each kernel; threading over whole groups keeps the per-element operation sequence identical).
+    // (std::thread, not OpenMP: the image has no libgomp.)
+    std::atomic<size_t> next_group{0}, next_bgroup{0};
+    std::mutex mu;
+    auto worker = [&]() {
+    try {
     double tg = 0, tp = 0, ts = 0;
     const int nvar = (int)varlist.size(), nb = ref.nb, N = dofs.ndof_elem;
     const int maxElem = (cfg.workset <= 0) ? (int)mesh.nelem : cfg.workset;
@@ -230,7 +258,6 @@ class Oracle {
     const int seedwhat = compute_jacobian ? 1 : 0;
     std::vector<double> gu((size_t)maxElem * N), gprev, gstage;
     if (cfg.transient) { gprev.resize((size_t)maxElem * N * ti.nsteps); gstage.resize((size_t)maxElem * N * ti.nstages); }
-    (void)nthreads;
 
     auto gather = [&](const GroupData& g) {
       for (int le = 0; le < g.numElem; ++le) {
@@ -256,7 +283,8 @@ class Oracle {
         for (int n = 0; n < nvar; ++n) for (int j = 0; j < nb; ++j) {
           const int row = dofs.offsets[n * nb + j], rowIndex = l[row];
           if (isFixed[rowIndex]) continue;
-          res_out[rowIndex] += -value_of(wk.res(le, row));
+          const double rv = -value_of(wk.res(le, row));
+          if (atomic) atomic_add(&res_out[rowIndex], rv); else res_out[rowIndex] += rv;
         }
         if constexpr (ad_traits<EvalT>::lanes > 0) {
           if (compute_jacobian && jac_out) {
@@ -269,7 +297,10 @@ class Oracle {
                 const int col = dofs.offsets[m * nb + k];
                 const int cidx = cfg.lump_mass ? rowIndex : l[col];
                 const double val = wk.res(le, row).fastAccessDx(col);
-                for (int64_t p = rb; p < re; ++p) if (crs.colind[p] == cidx) { jac_out[p] += val; break; }
+                for (int64_t p = rb; p < re; ++p) if (crs.colind[p] == cidx) {
+                  if (atomic) atomic_add(&jac_out[p], val); else jac_out[p] += val;
+                  break;
+                }
               }
             }
           }
@@ -277,7 +308,8 @@ class Oracle {
       }
     };
 
-    for (const auto& g : groups) {
+    for (size_t gi = next_group++; gi < groups.size(); gi = next_group++) {
+      const auto& g = groups[gi];
       auto t0 = clk::now();
       wk.attach(&g, false); gather(g); wk.resetResidual(); seed();
       auto t1 = clk::now();
@@ -287,7 +319,8 @@ class Oracle {
       auto t3 = clk::now();
       tg += std::chrono::duration<double>(t1 - t0).count(); tp += std::chrono::duration<double>(t2 - t1).count(); ts += std::chrono::duration<double>(t3 - t2).count();
     }
-    for (const auto& bg : bgroups) {
+    for (size_t bi = next_bgroup++; bi < bgroups.size(); bi = next_bgroup++) {
+      const auto& bg = bgroups[bi];
       auto t0 = clk::now();
       wk.attach(&bg.g, true); wk.sidename = mesh.sides[bg.side].name; wk.currentside = bg.side;
       gather(bg.g); wk.resetResidual(); seed();
@@ -299,6 +332,14 @@ class Oracle {
       auto t3 = clk::now();
       tg += std::chrono::duration<double>(t1 - t0).count(); tp += std::chrono::duration<double>(t2 - t1).count(); ts += std::chrono::duration<double>(t3 - t2).count();
     }
+    std::lock_guard<std::mutex> lk(mu);
+    tg_all += tg; tp_all += tp; ts_all += ts;
+    } catch (std::exception& e) { std::lock_guard<std::mutex> lk(mu); fail = e.what(); }
+    };
+    if (nthreads == 1) worker();
+    else { std::vector<std::thread> th; for (int t = 0; t < nthreads; ++t) th.emplace_back(worker); for (auto& x : th) x.join(); }
+    if (!fail.empty()) throw std::runtime_error(fail);
+    const double tg = tg_all / nthreads, tp = tp_all / nthreads, ts = ts_all / nthreads;
     if (compute_jacobian && jac_out) {
       if (cfg.strong_dbc) for (auto& vd : dbc_dofs) for (int d : vd) { const int64_t p = crs.find(d, d); if (p >= 0) jac_out[p] = 1.0; }
       if (cfg.fix_zero_rows)

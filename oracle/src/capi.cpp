@@ -44,6 +44,8 @@ void orc_get_crs(void* h, int64_t* rowptr, int* colind) {
   memcpy(rowptr, o->crs.rowptr.data(), o->crs.rowptr.size() * sizeof(int64_t));
   memcpy(colind, o->crs.colind.data(), o->crs.colind.size() * sizeof(int));
 }
+// replace the vertex coordinates (nnode, dim); topology, numbering and graph stay
+void orc_set_nodes(void* h, const double* nodes) { ((Oracle*)h)->setNodes(nodes); }
 // side set s: name into buf, returns element count; elems/local side optional
 int orc_get_side(void* h, int s, char* name, int namelen, int* local_side, int* elems) {
   Oracle* o = (Oracle*)h; const auto& S = o->mesh.sides[s];

@@ -272,7 +272,7 @@ class FunctionManager {
     else if (op == "tan") data = D(tan(t));
     else if (op == "exp") data = D(exp(t));
     else if (op == "log") data = D(log(t));
-    else if (op == "sqrt") data = D(sqrt(t));
+    else if (op == "sqrt") { if (t <= 0.0) data = D(0.0); else data = D(sqrt(t)); }   // functionManager.cpp:1062-1067, 1258-1262: 0 for arguments <= 0
     else if (op == "sinh") data = D(sinh(t));
     else if (op == "cosh") data = D(cosh(t));
     else if (op == "abs") { if (t < 0.0) data = D(-t); else data = D(t); }

@@ -67,7 +67,8 @@ struct BrickMesh {
           if (dim == 3) { v[4] = nid(0, 0, 1); v[5] = nid(1, 0, 1); v[6] = nid(1, 1, 1); v[7] = nid(0, 1, 1); }
         }
     // side sets.  2-D (edges): bottom=0, right=1, top=2, left=3.
-    // 3-D (faces): front(y-)=0, right(x+)=1, back(y+)=2, left(x-)=3, bottom(z-)=4, top(z+)=5.
+    // 3-D (faces), panzer_stk::CubeHexMeshFactory names: bottom(y-)=0, right(x+)=1, top(y+)=2, left(x-)=3, back(z-)=4, front(z+)=5
+    // (bottom/top are the y planes: regression/maxwell/Multiblock/input_mesh.yaml pairs 'top;bottom' with periodic 'xz-all').
     sides.clear();
     auto add = [&](const char* nm, int ls, int axis, int at_hi) {
       SideSet s; s.name = nm; s.local_side = ls;
@@ -80,7 +81,7 @@ struct BrickMesh {
       sides.push_back(s);
     };
     if (dim == 2) { add("bottom", 0, 1, 0); add("left", 3, 0, 0); add("right", 1, 0, 1); add("top", 2, 1, 1); }
-    else { add("back", 2, 1, 1); add("bottom", 4, 2, 0); add("front", 0, 1, 0); add("left", 3, 0, 0); add("right", 1, 0, 1); add("top", 5, 2, 1); }
+    else { add("back", 4, 2, 0); add("bottom", 0, 1, 0); add("front", 5, 2, 1); add("left", 3, 0, 0); add("right", 1, 0, 1); add("top", 2, 1, 1); }
   }
   int side_index(const std::string& nm) const {
     for (size_t i = 0; i < sides.size(); ++i) if (sides[i].name == nm) return (int)i;

@@ -18,6 +18,7 @@ struct EmuImpl {
 
 static int backend_create(mrh_engine* h) { h->impl = new EmuImpl(); return MRH_OK; }
 static void backend_destroy(mrh_engine* h) { delete (EmuImpl*)h->impl; }
+static void backend_nodes_changed(mrh_engine*) {}      // the stepping harness reads the host arrays directly
 
 template <class C>
 static void run_launch(const KParams& kp) {

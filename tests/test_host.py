@@ -49,6 +49,21 @@ def test_indexing_bit_exact_vs_oracle(lib, mk, n):
     assert np.array_equal(e.bc_codes(), o.bc_codes())
 
 
+@pytest.mark.parametrize("side,axis,high", [("left", 0, 0), ("right", 0, 1), ("bottom", 1, 0), ("top", 1, 1), ("back", 2, 0), ("front", 2, 1)])
+def test_3d_side_set_names_follow_the_stk_cube_factory(lib, side, axis, high):
+    """panzer_stk::CubeHexMeshFactory: bottom / top are the y planes, back / front the z planes (the reference's
+    regression/maxwell/Multiblock/input_mesh.yaml pairs 'top;bottom' with periodic type 'xz-all')."""
+    from mrhyde_b200 import Engine
+    p = problems.config_c2(4)
+    p["mesh"].update(NX=3, NY=4, NZ=5, xmax=1.0, ymax=2.0, zmax=3.0)
+    p["dirichlet"] = {"e": {side: "0.0"}}
+    e = Engine.from_problem(p, lib=lib, host_only=True)
+    fixed = e.dofmap()[2].astype(bool)
+    xyz, _ = e.dof_coords()
+    plane = np.isclose(xyz[:, axis], [1.0, 2.0, 3.0][axis] if high else 0.0)
+    assert fixed.any() and np.array_equal(fixed, plane)
+
+
 def test_foreign_dofmap_path_equals_brick_builder(lib):
     """mrh_set_mesh/dofmap/crs/add_side (what a Panzer/Tpetra caller hands over) gives the same tables."""
     from mrhyde_b200 import Engine
@@ -79,7 +94,7 @@ def test_expression_known_answers(lib):
     exprs = {"q1": "8*(pi*pi)*sin(2*pi*x)*sin(2*pi*y)", "q2": "x/2.0*4.0", "q3": "-x+y", "q4": "3.0*x^2", "A": "2.0",
              "f": "A*x+1.0", "q5": "f*f", "q6": "x<0.5", "q7": "exp(sin((x+1.0)*2.0))", "q8": "max(x,y)+min(x,0.25)",
              "q9": "-1.0*(A*pi)*cos(A*pi*x)", "q10": "1.0e-3*x", "q11": "x-y-0.25", "q12": "x/y/2.0", "q13": "abs(x-0.5)+sqrt(y+1.0)",
-             "q14": "t*x"}
+             "q14": "t*x", "q15": "1.0+sqrt(x-0.5)"}
     p["functions"].update(exprs)
     e = Engine.from_problem(p, lib=lib, host_only=True)
     rng = np.random.default_rng(3)
@@ -89,7 +104,8 @@ def test_expression_known_answers(lib):
             "q4": 3.0 * x ** 2, "q5": (2.0 * x + 1.0) ** 2, "q6": (x < 0.5).astype(float), "q7": np.exp(np.sin((x + 1.0) * 2.0)),
             "q8": np.maximum(x, y) + np.minimum(x, 0.25), "q9": -2.0 * np.pi * np.cos(2 * np.pi * x),
             "q10": 1.0 - 3 * x,          # the reference splits the literal at its sign
-            "q11": x - y - 0.25, "q12": x / y / 2.0, "q13": np.abs(x - 0.5) + np.sqrt(y + 1.0), "q14": 0.7 * x}
+            "q11": x - y - 0.25, "q12": x / y / 2.0, "q13": np.abs(x - 0.5) + np.sqrt(y + 1.0), "q14": 0.7 * x,
+            "q15": 1.0 + np.sqrt(np.maximum(x - 0.5, 0.0))}      # sqrt of a non-positive argument is 0 (functionManager.cpp:1062-1067)
     for k, w in want.items():
         np.testing.assert_allclose(e.eval_function(k, X, time=0.7), w, rtol=1e-14, atol=1e-15, err_msg=k)
     from oracle.pyoracle import Oracle
@@ -113,6 +129,13 @@ def test_errors_are_reported_not_thrown(lib):
     p["functions"] = {"thermal source": "emax(x)"}
     with pytest.raises(MrhError, match="not supported"):
         Engine.from_problem(p, lib=lib, host_only=True)
+    # out-of-range indices are argument errors, not out-of-bounds device accesses
+    e = Engine("thermal", 2, lib=lib)
+    with pytest.raises(MrhError, match="out of range"):
+        e.set_mesh(np.zeros((4, 2)), np.array([[0, 1, 2, 4]], dtype=np.int32))
+    e.set_mesh(np.array([[0.0, 0], [1, 0], [1, 1], [0, 1]]), np.array([[0, 1, 2, 3]], dtype=np.int32))
+    with pytest.raises(MrhError, match="out of range"):
+        e.add_side("left", 3, np.array([1], dtype=np.int32))
 
 
 def test_no_cpu_fallback(lib):

@@ -21,8 +21,8 @@ def _worker(rank, world, port, n, q):
         from mrhyde_b200 import Engine, build, partition
         from oracle.pyoracle import Oracle
         base = problems.config_c2(n)
-        base["dirichlet"] = {"e": {"left": "0.0", "front": "0.0", "bottom": "0.0"}}
-        base["neumann"] = {"e": {"top": "1.0+x"}}
+        base["dirichlet"] = {"e": {"left": "0.0", "bottom": "0.0", "back": "0.0"}}      # x-, y-, z- (back / front are the z planes)
+        base["neumann"] = {"e": {"front": "1.0+x"}}
         p = partition.slab_problem(base, rank, world)
         e = Engine.from_problem(p, lib=build.build(), host_only=True)
         o = Oracle(U.oracle_problem(p))
