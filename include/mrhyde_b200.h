@@ -127,6 +127,17 @@ int mrh_assemble_jacres(mrh_handle h, const mrh_state* st, double* res, double* 
 /* Same call with HOST buffers (pinned or pageable): copies u in, zeroes, assembles, copies res and jac out. */
 int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res_host, double* jac_host);
 
+/* Allocation-free variant of the host-buffer residual assembly.  It has NO counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it): copies u in, zeroes, assembles res += -r(u), copies res out, with the device copies of u
+ * and res held in a file-scope `static __device__` array of 2 x MRH_STATIC_SCRATCH_MAX_DOFS doubles (16 MiB, resident on every
+ * GPU that loads the library until exit) - no cudaMalloc / cudaFree / allocating library call is made.  Steady state only.
+ * Meshes with more than MRH_STATIC_SCRATCH_MAX_DOFS local DOFs are rejected with MRH_EINVAL and a message.  Every call (and
+ * every handle on the same GPU) shares the one array, which keeps the previous call's contents (the residual part is cleared
+ * at the start of each call): calls that overlap on the GPU - different streams or host threads - race; serialise them. */
+#define MRH_STATIC_SCRATCH_MAX_DOFS 1048576
+int mrh_assemble_res_host_static(mrh_handle h, const mrh_state* st_host, double* res_host);
+
 /* ---- introspection (parity tests, bindings) ------------------------------------------------------ */
 /* out[16]: dim, nelem, nnode, nvert, nvar, nb, ndof_elem, nlocal, nnz, nq, nqs, nsides, npatterns, nfixed, 0, 0 */
 int mrh_get_sizes(mrh_handle h, int64_t* out);

@@ -62,6 +62,7 @@ struct DeviceImpl {
   std::vector<cudaEvent_t> chunk_ev;
   cudaStream_t copy_stream = nullptr;
   const char* last_path = "none";
+  double* static_scratch = nullptr;    // device address of g_static_scratch on this handle's GPU (set at finalize)
 };
 
 // ------------------------------------------------------------------------------------------------ kernels
@@ -159,6 +160,27 @@ __global__ void fix_zero_rows_kernel(const int64_t* rowptr, const int* colind, i
 }
 
 inline unsigned blocks_for(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
+
+// ---- static scratch of the allocation-free entry point (mrh_assemble_res_host_static) --------------------------------
+// File-scope device array: every GPU that loads the library holds these 16 MiB until exit.  In HOST code the name is only
+// a stand-in for the symbol, not a device address: the address is fetched with cudaGetSymbolAddress, once per device with
+// that device current (static_scratch_of, called from device_finalize), and only that pointer is handed to kernels.
+// Layout: [ u : MRH_STATIC_SCRATCH_MAX_DOFS | res : MRH_STATIC_SCRATCH_MAX_DOFS ] doubles.
+static __device__ __align__(256) double g_static_scratch[2 * (size_t)MRH_STATIC_SCRATCH_MAX_DOFS];
+constexpr int MRH_MAX_DEVICES = 64;
+double* g_static_scratch_addr[MRH_MAX_DEVICES] = {};
+
+double* static_scratch_of(int device) {
+  if (device < 0 || device >= MRH_MAX_DEVICES) throw std::runtime_error("CUDA error: device ordinal beyond the static scratch table");
+  if (!g_static_scratch_addr[device]) {
+    CUDA_CK(cudaSetDevice(device));
+    void* ptr = nullptr;
+    const cudaError_t rc = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (rc != cudaSuccess || !ptr) throw std::runtime_error(std::string("CUDA error: cudaGetSymbolAddress(static scratch) failed: ") + cudaGetErrorString(rc));
+    g_static_scratch_addr[device] = static_cast<double*>(ptr);
+  }
+  return g_static_scratch_addr[device];
+}
 
 }  // namespace
 

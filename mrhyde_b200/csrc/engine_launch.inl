@@ -106,6 +106,7 @@ void device_finalize(mrh_engine* h) {
   D.bp.nodes = D.nodes.p; D.bp.e2n = D.e2n.p; D.bp.lids = D.lids.p; D.bp.fixed = D.fixed.p; D.bp.rowptr = D.rowptr.p;
   D.bp.pat = D.pat.p; D.bp.pat_id = D.pat_id.p; D.bp.code = D.code.p; D.bp.cpool = D.cpool.p;
   if (!D.ev0) { CUDA_CK(cudaEventCreate(&D.ev0)); CUDA_CK(cudaEventCreate(&D.ev1)); }
+  D.static_scratch = static_scratch_of(D.device);      // set-up time, this handle's device current (cudaSetDevice above)
   D.ready = true;
 }
 
@@ -452,6 +453,34 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res
   if (!hc.used) CUDA_CK(cudaMemcpyAsync(jac_host, D.h_jac.p, nnz * sizeof(double), cudaMemcpyDeviceToHost, s));
   CUDA_CK(cudaStreamSynchronize(s));
   if (hc.used) CUDA_CK(cudaStreamSynchronize(D.copy_stream));
+  return rc;
+  MRH_CATCH_CUDA(h)
+}
+// Allocation-free residual assembly with host buffers: the device copies of u and of the residual live in the
+// file-scope static array g_static_scratch (engine.cu) instead of cudaMalloc'ed staging buffers.  Calls no cudaMalloc /
+// cudaFree / allocating library routine: every kernel and table was built by mrh_finalize (steady-state variants are
+// compiled there), so only copies, a memset and launches happen here.
+int mrh_assemble_res_host_static(mrh_handle h, const mrh_state* st_host, double* res_host) {
+  if (!h || !st_host || !st_host->u || !res_host) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h)
+  EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
+  if (!D.ready || !D.static_scratch) throw std::runtime_error("mrh_finalize has not been called");
+  if (st_host->is_transient) throw std::runtime_error("allocation-free entry point is steady-state only; not supported for transient states");
+  const int64_t nl = H.dofs.nlocal;
+  if (nl > (int64_t)MRH_STATIC_SCRATCH_MAX_DOFS)
+    throw std::runtime_error("mrh_assemble_res_host_static: " + std::to_string(nl) + " local DOFs exceed the static scratch limit of " +
+                             std::to_string((int64_t)MRH_STATIC_SCRATCH_MAX_DOFS) + " (MRH_STATIC_SCRATCH_MAX_DOFS); use mrh_assemble_res with caller-owned device buffers");
+  CUDA_CK(cudaSetDevice(D.device));
+  cudaStream_t s = (cudaStream_t)st_host->stream;
+  double* d_u = D.static_scratch;
+  double* d_res = D.static_scratch + (size_t)MRH_STATIC_SCRATCH_MAX_DOFS;
+  CUDA_CK(cudaMemcpyAsync(d_u, st_host->u, (size_t)nl * sizeof(double), cudaMemcpyHostToDevice, s));
+  CUDA_CK(cudaMemsetAsync(d_res, 0, (size_t)nl * sizeof(double), s));      // the array keeps the last call's contents
+  mrh_state st = *st_host; st.u = d_u;
+  const int rc = device_assemble(h, &st, d_res, nullptr);
+  CUDA_CK(cudaMemcpyAsync(res_host, d_res, (size_t)nl * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CUDA_CK(cudaStreamSynchronize(s));
   return rc;
   MRH_CATCH_CUDA(h)
 }

@@ -29,7 +29,7 @@ class MrhState(C.Structure):
 
 SYMBOLS = ["mrh_default_config", "mrh_create", "mrh_destroy", "mrh_last_error", "mrh_build_brick", "mrh_set_mesh", "mrh_set_nodes",
            "mrh_set_dofmap", "mrh_set_crs", "mrh_add_side", "mrh_set_bc", "mrh_add_function", "mrh_finalize",
-           "mrh_finalize_host", "mrh_assemble_res", "mrh_assemble_jacres", "mrh_assemble_jacres_host",
+           "mrh_finalize_host", "mrh_assemble_res", "mrh_assemble_jacres", "mrh_assemble_jacres_host", "mrh_assemble_res_host_static",
            "mrh_get_sizes", "mrh_get_mesh", "mrh_get_dofmap", "mrh_get_crs", "mrh_get_side", "mrh_get_bc",
            "mrh_get_varname", "mrh_eval_function_host", "mrh_last_launch_count", "mrh_last_volume_kernel_ms",
            "mrh_microbench", "mrh_last_kernel_path"]
@@ -71,6 +71,7 @@ def load_library(path=None):
     L.mrh_assemble_res.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p]
     L.mrh_assemble_jacres.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p]
     L.mrh_assemble_jacres_host.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p]
+    L.mrh_assemble_res_host_static.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p]
     L.mrh_get_sizes.argtypes = [C.c_void_p, C.c_void_p]
     L.mrh_get_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.mrh_get_dofmap.argtypes = [C.c_void_p] + [C.c_void_p] * 5
@@ -311,6 +312,11 @@ class Engine:
         st = self._state(u, **kw)
         self._ck(self.L.mrh_assemble_jacres_host(self.h, C.byref(st), _ptr(res), _ptr(jac)),
                  "mrh_assemble_jacres_host")
+
+    def assemble_res_host_static(self, u, res, **kw):
+        """allocation-free host-buffer residual assembly (static device scratch; at most MRH_STATIC_SCRATCH_MAX_DOFS DOFs)"""
+        st = self._state(u, **kw)
+        self._ck(self.L.mrh_assemble_res_host_static(self.h, C.byref(st), _ptr(res)), "mrh_assemble_res_host_static")
 
     def kernel_path(self):
         return self.L.mrh_last_kernel_path(self.h).decode()

@@ -164,6 +164,10 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st, double* res, dou
   return emu_assemble(h, st, res, jac);
   MRH_CATCH(h)
 }
+int mrh_assemble_res_host_static(mrh_handle h, const mrh_state*, double*) {      // device-only entry point
+  if (!h) return MRH_EINVAL;
+  h->err = "not supported by the CPU stepping harness"; return MRH_EUNSUPPORTED;
+}
 const char* mrh_last_kernel_path(mrh_handle h) {
   if (!h) return "generic";
   auto* E = (EmuImpl*)h->impl;
