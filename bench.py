@@ -28,9 +28,16 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 METRIC = "elements/sec assembled (FP64 residual+Jacobian)"
 UNIT = "elements/s"
-# algorithmic work per element of C2 (DESIGN.md "Algorithmic work"):
-BYTES_PER_ELEM = 289.0     # 8*nnz/nelem (217) + u,r (16) + coordinates (24) + element->DOF map (32)
-FLOPS_PER_ELEM = 7208.0    # geometry 2472 + interpolation 512 + residual 640 + Jacobian 3584
+# BASELINE.json configs: (problem factory, timed mesh size, algorithmic bytes / element B, flops / element F)  - SURVEY.md 8d
+CONFIGS = {
+    "C1": ("config_c1", 4096, 120.0, 800.0, "C1: 2D thermal, HGRAD Q1 quads, structured mesh, FP64 residual+Jacobian"),
+    "C2": ("config_c2", 256, 289.0, 7208.0, "C2: 3D thermal, HGRAD Q1 hexes, structured brick, FP64 residual+Jacobian"),
+    "C3": ("config_c3", 128, 4370.0, 213e3, "C3: 3D convection-diffusion-reaction, HGRAD Q2 hexes, FP64 residual+Jacobian"),
+    "C4": ("config_c4", 192, 2123.0, 36.5e3, "C4: 3D linear elasticity, Q1 hexes, 3 DOFs/node, FP64 residual+Jacobian"),
+    "C5": ("config_c5", 128, 3701.0, 150e3, "C5: 3D Navier-Stokes SUPG/PSPG, Q1 hexes, FP64 residual+Jacobian"),
+}
+BYTES_PER_ELEM, FLOPS_PER_ELEM = CONFIGS["C2"][2], CONFIGS["C2"][3]
+CPU_SAMPLE_N = {"C1": 512, "C2": 64, "C3": 16, "C4": 32, "C5": 32}     # bounded CPU sample of each workload (elements per direction)
 
 
 def peaks():
@@ -80,33 +87,25 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_port_rate(n, threads, steps, warmup):
-    """Oracle (CPU restatement of the reference path) assembling thermal Q1 n^3 bricks, one per thread."""
+def cpu_port_rate(config, n, threads, steps, warmup):
+    """Oracle (CPU restatement of the reference path, reference-shaped groups of 100 elements) on ONE n^d mesh of the
+    configuration, `threads` host threads working through the groups (atomic scatter, like the reference's OpenMP build).
+    Returns (median elements/s, median s per pass, timing buckets of the last pass)."""
     import parity_util as U
     import problems
     from oracle.pyoracle import Oracle
-    text = U.oracle_problem(problems.config_c2(n))
-    oracles = [Oracle(text) for _ in range(threads)]
-    _, _, _, xyz, var = oracles[0].dofmap()
+    o = Oracle(U.oracle_problem(getattr(problems, CONFIGS[config][0])(n)))
+    _, _, _, xyz, var = o.dofmap()
     u = problems.synthetic_state(xyz, var)
-
-    def work(o):
-        o.assemble(u, jacobian=True)
-
-    def step():
-        th = [threading.Thread(target=work, args=(o,)) for o in oracles]
-        for t in th:
-            t.start()
-        for t in th:
-            t.join()
-
     for _ in range(warmup):
-        step()
-    t0 = time.time()
+        o.assemble(u, jacobian=True, nthreads=threads)
+    ts = []
     for _ in range(steps):
-        step()
-    dt = time.time() - t0
-    return threads * n ** 3 * steps / dt, dt / steps
+        t0 = time.perf_counter()
+        o.assemble(u, jacobian=True, nthreads=threads)
+        ts.append(time.perf_counter() - t0)
+    med = float(np.median(ts))
+    return o.nelem / med, med, {k: float(v) for k, v in o.timing().items()}
 
 
 def run_reference(args):
@@ -114,19 +113,57 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    n = 32
-    warm = min(args.warmup, 1)
-    steps = max(1, min(args.steps, 5))
-    rate, sps = cpu_port_rate(n, cores, steps, warm)
-    sample = f"{cores} threads x one {n}^3 thermal Q1 brick each per step, {steps} steps"
+    cfg = args.config
+    n = CPU_SAMPLE_N[cfg]
+    warm = 1
+    steps = max(5, min(args.steps, 20))
+    rate, sps, buckets = cpu_port_rate(cfg, n, cores, steps, warm)
+    dim = 2 if cfg == "C1" else 3
+    sample = (f"oracle port, one {n}^{dim} mesh of the workload per step, {cores} threads over the 100-element groups (atomic scatter), "
+              f"1 warm-up + median of {steps}; buckets of the last pass (thread-averaged s): gather {buckets['gather']:.3f}, "
+              f"physics {buckets['physics']:.3f}, scatter {buckets['scatter']:.3f}")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
         "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "C2: 3D thermal, HGRAD Q1 hexes, structured brick, FP64 residual+Jacobian", "mesh": f"{n}^3 per thread (bounded sample of 256^3)"},
+        "config": {"workload": CONFIGS[cfg][4], "mesh": f"{n}^{dim} (bounded sample of {CONFIGS[cfg][1]}^{dim}; per-element cost is size-independent)"},
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+def time_config(cfg, n, dev, local, K, W):
+    """Device-buffer timing of one configuration on one GPU: returns a dict with ms per assembly, elements/s and the
+    fraction of the FP64 roof (filled by the caller), plus the engine for further use (caller closes it)."""
+    import torch
+    import problems
+    from mrhyde_b200 import Engine
+    t0 = time.time()
+    e = Engine.from_problem(getattr(problems, CONFIGS[cfg][0])(n), device=local)
+    s = e.sizes()
+    xyz, var = e.dof_coords()
+    u = torch.from_numpy(problems.synthetic_state(xyz, var)).to(dev)
+    res = torch.zeros(s["nlocal"], dtype=torch.float64, device=dev)
+    jac = torch.zeros(s["nnz"], dtype=torch.float64, device=dev)
+    setup = time.time() - t0
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(W):
+        e.assemble_jacres(u, res, jac, stream=st)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(K):
+        e.assemble_jacres(u, res, jac, stream=st)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1) / K
+    ok = bool(torch.isfinite(res).all().item() and torch.isfinite(jac).all().item())
+    out = {"mesh": n, "elements": s["nelem"], "ms": ms, "elements_per_s": s["nelem"] / (ms * 1e-3), "kernel_ms": e.volume_kernel_ms(),
+           "path": e.kernel_path(), "launches": e.launch_count(), "setup_s": round(setup, 1), "finite": ok}
+    e.close()
+    del u, res, jac
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_gpu(args):
@@ -144,12 +181,17 @@ def run_gpu(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    n = args.n
+    cfg = args.config
+    mk, n_full, B_ELEM, F_ELEM, workload = CONFIGS[cfg]
+    n = args.n if args.n > 0 else n_full
+    dim = 2 if cfg == "C1" else 3
     W, K = max(args.warmup, 3), args.steps
+    if world > 1 and cfg != "C2":
+        raise SystemExit("multi-GPU runs are defined for the C2 workload (z-slab partition)")
 
     # ---- set-up (untimed): mesh, DOFs, CRS graph, slot patterns, synthetic state -------------------------
     t_setup = time.time()
-    p = partition.slab_problem(problems.config_c2(n), rank, world)
+    p = partition.slab_problem(getattr(problems, mk)(n), rank, world)
     e = Engine.from_problem(p, device=local)
     s = e.sizes()
     xyz, var = e.dof_coords()
@@ -224,6 +266,7 @@ def run_gpu(args):
     e2e_value = world * s["nelem"] * Ke / t.item()
     checksum = float(hres.abs().sum())
 
+    kpath = e.kernel_path()
     if rank == 0:
         pk = peaks()
         vk = float(np.mean(vol_ms)) * 1e-3
@@ -232,13 +275,31 @@ def run_gpu(args):
         dfma, red, cpy = C.c_double(0), C.c_double(0), C.c_double(0)
         L.mrh_microbench(local, C.byref(dfma), C.byref(red), C.byref(cpy))
         hbm_peak = pk.get("hbm_gbs", 6650.0)
-        ach_gbs = BYTES_PER_ELEM * s["nelem"] / vk / 1e9
-        ach_tf = FLOPS_PER_ELEM * s["nelem"] / vk / 1e12
-        cpu_rate, cpu_sps = cpu_port_rate(64, 1, 1, 0)
+        ach_gbs = B_ELEM * s["nelem"] / vk / 1e9
+        ach_tf = F_ELEM * s["nelem"] / vk / 1e12
+        cores = os.cpu_count() or 1
+        cpu_n = CPU_SAMPLE_N[cfg]
+        cpu_rate, cpu_sps, cpu_buckets = cpu_port_rate(cfg, cpu_n, cores, 5, 1)
+        # the other BASELINE.json configurations at their full sizes, same process, same clocks (N = 1, default run only)
+        other = {}
+        if world == 1 and cfg == "C2" and args.n <= 0 and not args.no_other:
+            del u, res, jac, hu, hres, hjac
+            e.close()
+            torch.cuda.empty_cache()
+            for oc in ("C1", "C3", "C4", "C5"):
+                try:
+                    r = time_config(oc, CONFIGS[oc][1], dev, local, 5, 3)
+                    r["fp64_tflops"] = CONFIGS[oc][3] * r["elements_per_s"] / 1e12
+                    r["fp64_frac"] = r["fp64_tflops"] / dfma.value if dfma.value > 0 else None
+                    r["hbm_gbs_algorithmic"] = CONFIGS[oc][2] * r["elements_per_s"] / 1e9
+                    r["flops_per_elem"], r["bytes_per_elem"] = CONFIGS[oc][3], CONFIGS[oc][2]
+                    other[oc] = r
+                except Exception as ex:          # a failure here must not lose the headline line
+                    other[oc] = {"error": str(ex)[:200]}
         traffic, traffic_src = None, None
         try:      # DRAM bytes of one launch of the dominant kernel from the committed ncu --set full capture of this command
             prof = json.load(open(os.path.join(ROOT, "profiles", "r1_ws_thermal_n256_ncu_summary.json")))
-            if n == 256 and world == 1 and e.kernel_path() == "nvrtc-specialised+tiled-ws":
+            if cfg == "C2" and n == 256 and world == 1 and kpath == prof.get("kernel_path", "nvrtc-specialised+tiled-ws"):
                 traffic = prof["derived"]["dram_bytes_per_launch"]
                 traffic_src = "profiles/r1_ws_thermal_n256_ncu_summary.json (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
         except Exception:
@@ -246,21 +307,24 @@ def run_gpu(args):
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "C2: 3D thermal, HGRAD Q1 hexes, structured brick, FP64 residual+Jacobian",
-                       "mesh": f"{n}^3 per GPU" + (f", {world} z-slabs" if world > 1 else ""), "elements_per_gpu": s["nelem"],
-                       "dofs_per_gpu": s["nlocal"], "nnz_per_gpu": s["nnz"], "slot_patterns": s["npatterns"], "volume_kernel": e.kernel_path(),
-                       "l2": "inputs+outputs (4.6 GB/step) exceed the 126 MB L2; no flush needed",
-                       "timing": "CUDA events on the launch stream, K steps, max over ranks", "setup_s": round(t_setup, 1)},
+            "config": {"workload": workload,
+                       "mesh": f"{n}^{dim} per GPU" + (f", {world} z-slabs" if world > 1 else ""), "elements_per_gpu": s["nelem"],
+                       "dofs_per_gpu": s["nlocal"], "nnz_per_gpu": s["nnz"], "slot_patterns": s["npatterns"], "volume_kernel": kpath,
+                       "l2": f"inputs+outputs ({8e-9 * (s['nnz'] + 2 * s['nlocal']):.1f} GB/step) exceed the 126 MB L2; no flush needed",
+                       "timing": "CUDA events on the launch stream, K steps, max over ranks; zeroing of res / J is the caller's job "
+                                 "(solverManager.cpp:1528-1533) and outside the timed step, which accumulates", "setup_s": round(t_setup, 1)},
             "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
                          "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_src, "peak_source": "MEASURED_PEAKS.json (of measured)" if pk else "fallback 6650 (of fallback)",
-                         "kernel": "thermal Q1 hex specialised kernel (" + e.kernel_path() + ")", "kernel_ms": vk * 1e3,
-                         "bytes_per_elem": BYTES_PER_ELEM, "binding_roof": "fp64 (see roofline_fp64)"},
+                         "kernel": "volume assembly kernel (" + kpath + ")", "kernel_ms": vk * 1e3,
+                         "bytes_per_elem": B_ELEM, "binding_roof": "fp64 (see roofline_fp64)"},
             "roofline_fp64": {"bound": "fp64", "achieved": ach_tf, "peak": dfma.value, "unit": "TFLOP/s",
-                              "frac": ach_tf / dfma.value if dfma.value > 0 else None, "flops_per_elem": FLOPS_PER_ELEM,
+                              "frac": ach_tf / dfma.value if dfma.value > 0 else None, "flops_per_elem": F_ELEM,
                               "peak_source": "DFMA micro-benchmark run in this process (mrh_microbench)",
                               "red_f64_gops": red.value, "copy_gbs_here": cpy.value},
-            "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": 1, "kind": "port",
-                             "sample": "oracle (CPU restatement, reference-shaped groups of 100) on one 64^3 thermal Q1 brick, 1 pass"},
+            "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"oracle (CPU restatement, reference-shaped groups of 100, atomic scatter) on one {cpu_n}^{dim} mesh of the workload, "
+                                       f"{cores} threads, 1 warm-up + median of 5", "ms_per_pass": cpu_sps * 1e3, "buckets_s": cpu_buckets},
+            "other_configs": other,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 8 * s["nlocal"],
                     "d2h_bytes_per_step": 8 * (s["nlocal"] + s["nnz"]), "steps": Ke, "checksum_abs_res": checksum,
                     "api": "mrh_assemble_jacres_host (pinned host buffers; u in, residual + CRS values out)"},
@@ -277,7 +341,9 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--n", type=int, default=256, help="elements per direction per GPU")
+    ap.add_argument("--n", type=int, default=0, help="elements per direction per GPU (default: the configuration's BASELINE.json size)")
+    ap.add_argument("--config", default="C2", choices=sorted(CONFIGS), help="BASELINE.json configuration (default C2, the headline)")
+    ap.add_argument("--no-other", action="store_true", help="skip the other_configs leg of the default run")
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--kernel-only", action="store_true", help="profiling aid: skip the e2e and cpu_baseline legs")
     args = ap.parse_args()

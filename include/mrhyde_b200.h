@@ -127,6 +127,39 @@ int mrh_assemble_jacres(mrh_handle h, const mrh_state* st, double* res, double* 
 /* Same call with HOST buffers (pinned or pageable): copies u in, zeroes, assembles, copies res and jac out. */
 int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res_host, double* jac_host);
 
+/* ---- the direct caller of the hot path, on the device ----------------------------------------------- */
+/* Solver sublist of the input (src/managers/solverManager.cpp:55-70, src/interfaces/linearAlgebraInterface.cpp:47-50) */
+typedef struct mrh_solver_opts {
+  int32_t max_nonlinear_iters;   /* "max nonlinear iters" (10) */
+  int32_t use_relative_tol;      /* "use relative TOL" (true): stop when |res|_inf / |res_0|_inf < nonlinear_tol */
+  int32_t use_absolute_tol;      /* "use absolute TOL" (false) */
+  int32_t allow_backtracking;    /* "allow backtracking" (true): halve the step while the scaled residual exceeds 1.1 */
+  double nonlinear_tol;          /* "nonlinear TOL" (1e-6) */
+  double nonlinear_abs_tol;      /* "absolute nonlinear TOL" */
+  int32_t linear_method;         /* 0: restarted GMRES(krylov_vectors), 1: conjugate gradients; both Jacobi-preconditioned */
+  int32_t max_linear_iters;      /* "max linear iters" (100) */
+  int32_t krylov_vectors;        /* "krylov vectors" (100) */
+  int32_t verbosity;             /* > 1 prints the reference's per-iteration residual lines */
+  double linear_tol;             /* "linear TOL" (1e-7), relative to |rhs|_2 */
+} mrh_solver_opts;
+typedef struct mrh_solver_info {
+  int32_t nonlinear_iters, linear_iters, converged, time_steps;
+  double resnorm_first, resnorm_last, last_linear_relres, final_time;
+} mrh_solver_info;
+void mrh_default_solver_opts(mrh_solver_opts* opts);
+/* LinearAlgebraInterface::linearSolver(set, J, res, du): jac x = rhs on the engine's CRS graph, x zeroed first; device pointers.
+ * (The reference uses Belos GMRES + MueLu/Amesos2; here GMRES(m) / CG with a Jacobi preconditioner, written as CUDA kernels.) */
+int mrh_linear_solve(mrh_handle h, const double* jac, const double* rhs, double* x, const mrh_solver_opts* opts, mrh_solver_info* info, void* stream);
+/* SolverManager::nonlinearSolver (solverManager.cpp:1465-1709): Newton on `u` (device, nlocal, in/out; Dirichlet values of the
+ * fixed DOFs must already be in u), time data from st (st->u is ignored); res (nlocal) and jac (nnz) are the caller's work arrays.
+ * Returns 0 when converged, 1 when max_nonlinear_iters was reached (the reference's status), < 0 on errors. */
+int mrh_nonlinear_solve(mrh_handle h, const mrh_state* st, double* u, double* res, double* jac, const mrh_solver_opts* opts, mrh_solver_info* info);
+/* SolverManager::transientSolver, forward branch (solverManager.cpp:1229-1340) with setButcherTableau / setBackwardDifference
+ * (:490-830): steps u from start_time to end_time with fixed deltat; tableau "BWE" | "DIRK-1,1" | "CN" | "DIRK-1,2" | "DIRK-2,2" |
+ * "DIRK-2,3" | "DIRK-3,3", BDF order 1..4 (orders > 1 start up with lower orders). */
+int mrh_transient_solve(mrh_handle h, double* u, double start_time, double end_time, double deltat, const char* butcher_tableau,
+                        int32_t bdf_order, double* res, double* jac, const mrh_solver_opts* opts, mrh_solver_info* info, void* stream);
+
 /* Allocation-free variant of the host-buffer residual assembly.  It has NO counterpart in the reference and was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
  * loops, harnesses that forbid it): copies u in, zeroes, assembles res += -r(u), copies res out, with the device copies of u

@@ -501,6 +501,89 @@ struct ThermalHexQ1 {
 #if defined(MRH_WS_CREG)
   __device__ __forceinline__ static void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
   __device__ __forceinline__ static void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+  // scatter warpgroup of the warp-specialised kernels: serves the element stores of NCG compute groups in hand-over order
+  // (sequence number s = NCG i + g is tile i of compute group g and lives in element store s % WS_NBUF).  KPAD: the element
+  // store's entry stride is 128 + KPAD doubles (contribution lists address cells as entry * 128 + thread).
+  template <int NCG, int KPAD>
+  __device__ __forceinline__ static void ws_scatter_group(const KParams& kp, double* sm, int tid, int scratch_bytes) {
+    const TilePlan& tp = kp.tile;
+    constexpr int KSZ = NE * (128 + KPAD) + 2;
+    double* acc = sm + WS_NBUF * KSZ;
+    double* carry = acc + ((tp.max_acc + 2) & ~1);
+    unsigned* s_off = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(carry + 128) + scratch_bytes);
+    int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
+    const int64_t tstep = NCG * (int64_t)gridDim.x;
+    constexpr int BAR_FULL = 1, BAR_EMPTY = 1 + WS_NBUF, BAR_SCATTER = 1 + 2 * WS_NBUF;
+    constexpr int NPAIR = 256;                              // a FULL / EMPTY barrier joins one compute group (128) and the scatter group (128)
+    auto tile_of = [&](int s) -> int64_t { return tp.tile_begin + NCG * (int64_t)blockIdx.x + (s % NCG) + (int64_t)(s / NCG) * tstep; };
+    if (tid < WS_NBUF) sm[tid * KSZ + NE * (128 + KPAD)] = 0.0;    // masked contributions read these cells
+    struct TileMeta { int64_t eb, rb, base; int E, R, clid; };
+    auto load_meta = [&](int64_t t, TileMeta& m) {
+      if (t >= tp.tile_end) { m.E = m.R = 0; m.clid = 0; m.eb = m.rb = m.base = 0; return; }
+      m.eb = tp.eptr[t]; m.rb = tp.rptr[t]; m.base = tp.base[t];
+      m.E = (int)(tp.eptr[t + 1] - m.eb); m.R = (int)(tp.rptr[t + 1] - m.rb); m.clid = tp.cl_id[t];
+    };
+    TileMeta cur, nxt;
+    load_meta(tile_of(0), cur);
+    int b = 0;                                            // element store of sequence number s
+    for (int s = 0; tile_of(s) < tp.tile_end; ++s) {
+      const double* Ks = sm + b * KSZ;
+      const int E = cur.E, R = cur.R;
+      for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + cur.eb + k);
+      for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + cur.rb + k);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      const size_t cid = (size_t)cur.clid * 128 + tid;
+      const uint4* cl = reinterpret_cast<const uint4*>(tp.clist + cid * 72);
+      uint4 wv = __ldg(cl);
+      const int loc0 = tp.cbase[cid];
+      const bool cont = (wv.x & 0x8000u) == 0;            // my first run started in the previous thread's chunk
+      load_meta(tile_of(s + 1), nxt);                     // in flight during this tile's scatter
+      bar_sync(BAR_FULL + b, NPAIR);                        // element store b complete
+      {
+        double sum = 0.0;
+        int loc = loc0;
+        double* dst = cont ? carry + tid : acc + loc;
+#pragma unroll
+        for (int c = 0; c < 9; ++c) {
+          const unsigned w[4] = {wv.x, wv.y, wv.z, wv.w};
+          if (c < 8) wv = __ldg(cl + c + 1);
+          double v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
+            const unsigned cell = cc & 0x7fffu;
+            v[u] = Ks[cell + KPAD * (cell >> 7)];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
+            if ((c > 0 || u > 0) && (cc & 0x8000u)) { *dst = sum; ++loc; dst = acc + loc; sum = 0.0; }
+            sum += v[u];
+          }
+        }
+        *dst = sum;
+      }
+      bar_sync(BAR_SCATTER, 128);                         // run totals stored, element store no longer read
+      bar_arrive(BAR_EMPTY + b, NPAIR);
+      if (cont) atomicAdd(acc + loc0, carry[tid]);
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      bar_sync(BAR_SCATTER, 128);
+      {
+        double* jb = kp.jac + cur.base;
+        for (int k0 = tid; k0 < E; k0 += 512) {
+          unsigned o[4]; double v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) { o[u] = s_off[k]; v[u] = acc[k]; } }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) atomicAdd(jb + o[u], v[u]); }
+        }
+        for (int k = tid; k < R; k += 128) atomicAdd(kp.res + s_rows[k], acc[E + k]);
+      }
+      bar_sync(BAR_SCATTER, 128);                         // lists and accumulation array free again
+      cur = nxt;
+      b = (b + 1 == WS_NBUF) ? 0 : b + 1;
+    }
+  }
   __device__ static void tiled_ws(const KParams& kp, double* sm) {
     static_assert(JAC, "the tile-staged scatter is used for Jacobian assembly only");
     static_assert(!CF::staged, "the warp-specialised kernel is built with NVRTC-printed coefficients");
@@ -518,74 +601,8 @@ struct ThermalHexQ1 {
     constexpr int BAR_FULL = 1, BAR_EMPTY = 1 + WS_NBUF, BAR_SCATTER = 1 + 2 * WS_NBUF;
     auto tile_of = [&](int s) -> int64_t { return tp.tile_begin + 2 * (int64_t)blockIdx.x + (s & 1) + (int64_t)(s >> 1) * tstep; };
     if (wg == 0) {
-      // ================================= scatter warpgroup =================================
       asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MRH_WS_SREG));
-      if (tid < WS_NBUF) sm[tid * KSZ + NE * 128] = 0.0;    // masked contributions read these cells
-      struct TileMeta { int64_t eb, rb, base; int E, R, clid; };
-      auto load_meta = [&](int64_t t, TileMeta& m) {
-        if (t >= tp.tile_end) { m.E = m.R = 0; m.clid = 0; m.eb = m.rb = m.base = 0; return; }
-        m.eb = tp.eptr[t]; m.rb = tp.rptr[t]; m.base = tp.base[t];
-        m.E = (int)(tp.eptr[t + 1] - m.eb); m.R = (int)(tp.rptr[t + 1] - m.rb); m.clid = tp.cl_id[t];
-      };
-      TileMeta cur, nxt;
-      load_meta(tile_of(0), cur);
-      int b = 0;                                            // element store of sequence number s
-      for (int s = 0; tile_of(s) < tp.tile_end; ++s) {
-        const double* Ks = sm + b * KSZ;
-        const int E = cur.E, R = cur.R;
-        for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + cur.eb + k);
-        for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + cur.rb + k);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        const size_t cid = (size_t)cur.clid * 128 + tid;
-        const uint4* cl = reinterpret_cast<const uint4*>(tp.clist + cid * 72);
-        uint4 wv = __ldg(cl);
-        const int loc0 = tp.cbase[cid];
-        const bool cont = (wv.x & 0x8000u) == 0;            // my first run started in the previous thread's chunk
-        load_meta(tile_of(s + 1), nxt);                     // in flight during this tile's scatter
-        bar_sync(BAR_FULL + b, 256);                        // element store b complete
-        {
-          double sum = 0.0;
-          int loc = loc0;
-          double* dst = cont ? carry + tid : acc + loc;
-#pragma unroll
-          for (int c = 0; c < 9; ++c) {
-            const unsigned w[4] = {wv.x, wv.y, wv.z, wv.w};
-            if (c < 8) wv = __ldg(cl + c + 1);
-            double v[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
-              v[u] = Ks[cc & 0x7fffu];
-            }
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const unsigned cc = (u & 1) ? (w[u >> 1] >> 16) : (w[u >> 1] & 0xffffu);
-              if ((c > 0 || u > 0) && (cc & 0x8000u)) { *dst = sum; ++loc; dst = acc + loc; sum = 0.0; }
-              sum += v[u];
-            }
-          }
-          *dst = sum;
-        }
-        bar_sync(BAR_SCATTER, 128);                         // run totals stored, element store no longer read
-        bar_arrive(BAR_EMPTY + b, 256);
-        if (cont) atomicAdd(acc + loc0, carry[tid]);
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        bar_sync(BAR_SCATTER, 128);
-        {
-          double* jb = kp.jac + cur.base;
-          for (int k0 = tid; k0 < E; k0 += 512) {
-            unsigned o[4]; double v[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) { o[u] = s_off[k]; v[u] = acc[k]; } }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) atomicAdd(jb + o[u], v[u]); }
-          }
-          for (int k = tid; k < R; k += 128) atomicAdd(kp.res + s_rows[k], acc[E + k]);
-        }
-        bar_sync(BAR_SCATTER, 128);                         // lists and accumulation array free again
-        cur = nxt;
-        b = (b + 1 == WS_NBUF) ? 0 : b + 1;
-      }
+      ws_scatter_group<2, 0>(kp, sm, tid, 2 * 128 * 64);
     } else {
       // ================================= compute warpgroups =================================
       asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MRH_WS_CREG));
@@ -635,6 +652,105 @@ struct ThermalHexQ1 {
       }
     }
   }
+#if defined(MRH_WS8_NCG)
+  // ---- lane-per-point form of the warp-specialised kernel (device only; NVRTC kernel) --------------------------
+  // Eight consecutive lanes own one element: lane q gathers vertex q and evaluates quadrature point q.  Nothing is
+  // accumulated over points in shared memory: every lane forms the 36 products of ITS point and the eight lanes combine them
+  // with a transposing butterfly (shuffles over lane^4, ^2, ^1; each stage halves the entries a lane keeps), after which lane q
+  // holds entries 5q .. 5q+4 of the element matrix and entry q of the residual and parks them in the shared element store.
+  // Against tiled_ws this removes the 576 shared-memory read-modify-writes per element (its shared-memory pipe was 75 % busy),
+  // needs ~130 instead of 200 registers per compute thread (MRH_WS8_NCG = 3 compute warpgroups) and makes every gather lane
+  // load one vertex.  The element store uses an entry stride of 129 doubles so that the 8 x 4 lanes of a store instruction
+  // fall into different banks; the scatter warpgroup is the same code as in tiled_ws.
+  MRH_HD static constexpr int tri_i(int k) { int i = 0; while (k >= 8 - i) { k -= 8 - i; ++i; } return i; }
+  MRH_HD static constexpr int tri_j(int k) { int i = 0; while (k >= 8 - i) { k -= 8 - i; ++i; } return i + k; }
+  static constexpr int W8_STR = TRANSIENT ? 44 : 36;      // doubles of monomial scratch per element in flight (bank-spread for LDS.128)
+  __host__ __device__ static constexpr size_t ws8_scratch_bytes() { return (size_t)MRH_WS8_NCG * 16 * W8_STR * sizeof(double); }
+  __host__ __device__ static constexpr size_t ws8_smem_bytes(int max_acc, int max_e, int max_r) {
+    return (WS_NBUF * ((size_t)NE * 129 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + ws8_scratch_bytes() + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+  }
+  __device__ __forceinline__ static double shx(double v, int mask) { return __shfl_xor_sync(0xffffffffu, v, mask); }
+  __device__ static void tiled_ws8(const KParams& kp, double* sm) {
+    static_assert(JAC && !ADV, "lane-per-point kernel: symmetric element matrix, Jacobian assembly");
+    static_assert(!CF::staged, "the warp-specialised kernels are built with NVRTC-printed coefficients");
+    constexpr int NCG = MRH_WS8_NCG, KST = 129;
+    constexpr int KSZ = NE * KST + 2;
+    const TilePlan& tp = kp.tile;
+    const int wg = threadIdx.x >> 7, tid = threadIdx.x & 127;
+    constexpr int BAR_FULL = 1, BAR_EMPTY = 1 + WS_NBUF;
+    if (wg == 0) {
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MRH_WS8_SREG));
+      ws_scatter_group<NCG, 1>(kp, sm, tid, (int)ws8_scratch_bytes());
+      return;
+    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MRH_WS8_CREG));
+    const int g = wg - 1;
+    const int q = tid & 7, el = tid >> 3;                   // my vertex / point, my element within a pass of 16
+    const bool b0 = (q & 1) != 0, b1 = (q & 2) != 0, b2 = (q & 4) != 0;
+    const bool hx = ((q ^ (q >> 1)) & 1) != 0;              // tensor x bit of shards vertex q (y bit = b1, z bit = b2)
+    const int mono = (hx ? 1 : 0) + (b1 ? 2 : 0) + (b2 ? 4 : 0);   // monomial this lane holds after the vertex butterfly
+    double* acc = sm + WS_NBUF * KSZ;
+    double* scr = acc + ((tp.max_acc + 2) & ~1) + 128 + (size_t)(g * 16 + el) * W8_STR;
+    // constants of point q (descending 2-point rule: bit 0 -> +g): abscissae, half products of the 1-D shape functions
+    const double gq = HexQ1::g;
+    const double sx = b0 ? -gq : gq, sy = b1 ? -gq : gq, sz = b2 ? -gq : gq;
+    const double sxy = sx * sy, syz = sy * sz, sxz = sx * sz, sxyz = sxy * sz;
+    const double lx[2] = {0.5 - 0.5 * sx, 0.5 + 0.5 * sx}, ly[2] = {0.5 - 0.5 * sy, 0.5 + 0.5 * sy}, lz[2] = {0.5 - 0.5 * sz, 0.5 + 0.5 * sz};
+    double hyz[2][2], hxz[2][2], hxy[2][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) { hyz[a][b] = 0.5 * ly[a] * lz[b]; hxz[a][b] = 0.5 * lx[a] * lz[b]; hxy[a][b] = 0.5 * lx[a] * ly[b]; }
+    const double tlz[2] = {2.0 * lz[0], 2.0 * lz[1]};
+    const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
+    const int64_t tstep = NCG * (int64_t)gridDim.x;
+    const int64_t tfirst = tp.tile_begin + NCG * (int64_t)blockIdx.x + g;
+    // item it = (tile it / 8 of this group, pass it % 8): element position tile * 128 + 16 pass + el
+    auto elem_at = [&](int64_t it) -> int {
+      const int64_t t = tfirst + (it >> 3) * tstep;
+      if (t >= tp.tile_end) return -1;
+      const int64_t pos = t * 128 + (it & 7) * 16 + el;
+      return pos < kp.nwork ? tp.perm[pos] : -1;
+    };
+    // software pipeline over items: vertex values of item it + 1 and indices of item it + 2 are in flight during item it
+    int eC = elem_at(0), eN = elem_at(1), eN2 = elem_at(2);
+    int lidN = 0, ndN = 0;
+    double xC0 = 0.0, xC1 = 0.0, xC2 = 0.0, uC = 0.0, dC = 0.0, xN0 = 0.0, xN1 = 0.0, xN2 = 0.0, uN = 0.0, dN = 0.0;
+#define MRH_W8_VALS(E, LID, ND, X0, X1, X2, U, D)                                                          \
+    if ((E) >= 0) {                                                                                        \
+      const double* p_ = kp.nodes + (int64_t)(ND) * 3; X0 = p_[0]; X1 = p_[1]; X2 = p_[2];                  \
+      const double uval_ = kp.u[LID];                                                                      \
+      if (!TRANSIENT) { U = uval_; D = 0.0; }                                                              \
+      else {                                                                                               \
+        const TimeParams& tq_ = kp.tp;                                                                     \
+        const double prev0_ = kp.u_prev[(size_t)(LID) * tq_.nsteps];                                       \
+        double bu_ = (1.0 - tq_.alpha_u) * prev0_;                                                         \
+        for (int k_ = 0; k_ < tq_.stage; ++k_) bu_ += tq_.a_over_b[k_] * (kp.u_stage[(size_t)(LID) * tq_.nstages + k_] - prev0_); \
+        double bt_ = 0.0;                                                                                  \
+        for (int k_ = 1; k_ <= tq_.nsteps; ++k_) bt_ += tq_.bdf[k_] * kp.u_prev[(size_t)(LID) * tq_.nsteps + (k_ - 1)]; \
+        U = tq_.alpha_u * uval_ + bu_; D = tq_.alpha_t * uval_ + bt_ * tq_.timewt;                         \
+      }                                                                                                    \
+    }
+    if (eC >= 0) { const int lid_ = kp.lids[(int64_t)eC * 8 + q], nd_ = kp.e2n[(int64_t)eC * 8 + q]; MRH_W8_VALS(eC, lid_, nd_, xC0, xC1, xC2, uC, dC) }
+    if (eN >= 0) { lidN = kp.lids[(int64_t)eN * 8 + q]; ndN = kp.e2n[(int64_t)eN * 8 + q]; }
+    int sq = g;                                             // hand-over sequence number of the tile being filled
+    for (int64_t it = 0; tfirst + (it >> 3) * tstep < tp.tile_end; ++it) {
+      const int pass = (int)(it & 7);
+      const int b = sq % WS_NBUF;
+      double* Kst = sm + (size_t)b * KSZ + pass * 16 + el;  // my element's column of the element store
+      if (pass == 0 && sq >= WS_NBUF) bar_sync(BAR_EMPTY + b, 256);       // the scatter group has consumed this store's previous tile
+      MRH_W8_VALS(eN, lidN, ndN, xN0, xN1, xN2, uN, dN)
+      int lidN2 = 0, ndN2 = 0;
+      if (eN2 >= 0) { lidN2 = kp.lids[(int64_t)eN2 * 8 + q]; ndN2 = kp.e2n[(int64_t)eN2 * 8 + q]; }
+      const int eN3 = elem_at(it + 3);
+//@W8_BODY@
+      if (pass == 7) { bar_arrive(BAR_FULL + b, 256); sq += NCG; }
+      eC = eN; xC0 = xN0; xC1 = xN1; xC2 = xN2; uC = uN; dC = dN;
+      eN = eN2; lidN = lidN2; ndN = ndN2; eN2 = eN3;
+    }
+#undef MRH_W8_VALS
+  }
+#endif  // MRH_WS8_NCG
 #endif  // MRH_WS_CREG
 #endif
 };

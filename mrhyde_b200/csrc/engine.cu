@@ -62,6 +62,7 @@ struct DeviceImpl {
   std::vector<cudaEvent_t> chunk_ev;
   cudaStream_t copy_stream = nullptr;
   const char* last_path = "none";
+  std::shared_ptr<void> solver;        // SolverWork (solver.inl), created at the first solve
   double* static_scratch = nullptr;    // device address of g_static_scratch on this handle's GPU (set at finalize)
 };
 
@@ -186,3 +187,4 @@ double* static_scratch_of(int device) {
 
 #include "engine_tiles.inl"
 #include "engine_launch.inl"
+#include "solver.inl"

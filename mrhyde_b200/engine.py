@@ -27,12 +27,25 @@ class MrhState(C.Structure):
                 ("stream", C.c_void_p)]
 
 
+class MrhSolverOpts(C.Structure):
+    _fields_ = [("max_nonlinear_iters", C.c_int32), ("use_relative_tol", C.c_int32), ("use_absolute_tol", C.c_int32),
+                ("allow_backtracking", C.c_int32), ("nonlinear_tol", C.c_double), ("nonlinear_abs_tol", C.c_double),
+                ("linear_method", C.c_int32), ("max_linear_iters", C.c_int32), ("krylov_vectors", C.c_int32), ("verbosity", C.c_int32),
+                ("linear_tol", C.c_double)]
+
+
+class MrhSolverInfo(C.Structure):
+    _fields_ = [("nonlinear_iters", C.c_int32), ("linear_iters", C.c_int32), ("converged", C.c_int32), ("time_steps", C.c_int32),
+                ("resnorm_first", C.c_double), ("resnorm_last", C.c_double), ("last_linear_relres", C.c_double), ("final_time", C.c_double)]
+
+
 SYMBOLS = ["mrh_default_config", "mrh_create", "mrh_destroy", "mrh_last_error", "mrh_build_brick", "mrh_set_mesh", "mrh_set_nodes",
            "mrh_set_dofmap", "mrh_set_crs", "mrh_add_side", "mrh_set_bc", "mrh_add_function", "mrh_finalize",
            "mrh_finalize_host", "mrh_assemble_res", "mrh_assemble_jacres", "mrh_assemble_jacres_host", "mrh_assemble_res_host_static",
            "mrh_get_sizes", "mrh_get_mesh", "mrh_get_dofmap", "mrh_get_crs", "mrh_get_side", "mrh_get_bc",
            "mrh_get_varname", "mrh_eval_function_host", "mrh_last_launch_count", "mrh_last_volume_kernel_ms",
-           "mrh_microbench", "mrh_last_kernel_path"]
+           "mrh_microbench", "mrh_last_kernel_path", "mrh_default_solver_opts", "mrh_linear_solve", "mrh_nonlinear_solve",
+           "mrh_transient_solve"]
 
 
 def lib_path():
@@ -81,6 +94,13 @@ def load_library(path=None):
     L.mrh_eval_function_host.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_void_p, C.c_double,
                                          C.c_void_p]
     L.mrh_microbench.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+    if hasattr(L, "mrh_nonlinear_solve"):            # device-only entry points (absent from the CPU stepping harness)
+        L.mrh_default_solver_opts.argtypes = [C.POINTER(MrhSolverOpts)]
+        L.mrh_default_solver_opts.restype = None
+        L.mrh_linear_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo), C.c_void_p]
+        L.mrh_nonlinear_solve.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo)]
+        L.mrh_transient_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_char_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                          C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo), C.c_void_p]
     _LIBS[path] = L
     return L
 
@@ -317,6 +337,39 @@ class Engine:
         """allocation-free host-buffer residual assembly (static device scratch; at most MRH_STATIC_SCRATCH_MAX_DOFS DOFs)"""
         st = self._state(u, **kw)
         self._ck(self.L.mrh_assemble_res_host_static(self.h, C.byref(st), _ptr(res)), "mrh_assemble_res_host_static")
+
+    # ---- the caller of the hot path (Newton / time stepping / Krylov on the device) ------------------------------
+    def solver_opts(self, **kw):
+        o = MrhSolverOpts()
+        self.L.mrh_default_solver_opts(C.byref(o))
+        for k, v in kw.items():
+            setattr(o, k, v)
+        return o
+
+    @staticmethod
+    def _info(i):
+        return {f[0]: getattr(i, f[0]) for f in MrhSolverInfo._fields_}
+
+    def linear_solve(self, jac, rhs, x, stream=None, **opts):
+        o, i = self.solver_opts(**opts), MrhSolverInfo()
+        self._ck(self.L.mrh_linear_solve(self.h, _ptr(jac), _ptr(rhs), _ptr(x), C.byref(o), C.byref(i), stream), "mrh_linear_solve")
+        return self._info(i)
+
+    def nonlinear_solve(self, u, res, jac, u_prev=None, u_stage=None, time_int=None, stream=None, **opts):
+        st = self._state(u, u_prev=u_prev, u_stage=u_stage, time_int=time_int, stream=stream)
+        o, i = self.solver_opts(**opts), MrhSolverInfo()
+        rc = self._ck(self.L.mrh_nonlinear_solve(self.h, C.byref(st), _ptr(u), _ptr(res), _ptr(jac), C.byref(o), C.byref(i)), "mrh_nonlinear_solve")
+        out = self._info(i)
+        out["status"] = rc
+        return out
+
+    def transient_solve(self, u, res, jac, t0, t1, dt, tableau="BWE", bdf_order=1, stream=None, **opts):
+        o, i = self.solver_opts(**opts), MrhSolverInfo()
+        rc = self._ck(self.L.mrh_transient_solve(self.h, _ptr(u), t0, t1, dt, tableau.encode(), bdf_order, _ptr(res), _ptr(jac), C.byref(o),
+                                                 C.byref(i), stream), "mrh_transient_solve")
+        out = self._info(i)
+        out["status"] = rc
+        return out
 
     def kernel_path(self):
         return self.L.mrh_last_kernel_path(self.h).decode()

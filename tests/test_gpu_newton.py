@@ -1,0 +1,130 @@
+"""The caller of the hot path on the device: mrh_nonlinear_solve / mrh_linear_solve / mrh_transient_solve.
+The reference's own 6-digit regression golds (tests/golden/reference_golds.json) are reproduced FROM THE GPU SOLUTION: CUDA
+assembly + CUDA Krylov solve + Newton update; the oracle only integrates the L2 error of the vector it is handed."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import parity_util as U
+import problems
+
+pytestmark = pytest.mark.gpu
+GOLD = json.load(open(os.path.join(U.HERE, "golden", "reference_golds.json")))
+
+CASES = [
+    ("thermal/2D_verification", problems.regression_thermal_2d, 1),
+    ("thermal/3D_verification", problems.regression_thermal_3d, 1),
+    ("cdr/2D_manufactured", problems.regression_cdr_2d, 0),
+    ("le/2D_manufactured", problems.regression_le_2d, 1),
+    ("le/3D_manufactured", problems.regression_le_3d, 0),
+    ("navierstokes/channel", problems.regression_ns_channel, 0),
+]
+VARS = {"thermal": ["e"], "cdr": ["c"], "linearelasticity": ["dx", "dy", "dz"], "navierstokes": ["ux", "pr", "uy", "uz"]}
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import torch
+    from mrhyde_b200 import lib_path
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return lib_path()
+
+
+def _buffers(e):
+    import torch
+    s = e.sizes()
+    dev = torch.device("cuda:0")
+    return (torch.zeros(s["nlocal"], dtype=torch.float64, device=dev), torch.zeros(s["nlocal"], dtype=torch.float64, device=dev),
+            torch.zeros(s["nnz"], dtype=torch.float64, device=dev))
+
+
+@pytest.mark.parametrize("path,make,method", CASES, ids=[c[0] for c in CASES])
+def test_reference_golds_from_the_gpu_solution(lib, path, make, method):
+    import torch
+    from mrhyde_b200 import Engine
+    from oracle.pyoracle import Oracle
+    p = make()
+    e = Engine.from_problem(p, lib=lib)
+    u, res, jac = _buffers(e)
+    info = e.nonlinear_solve(u, res, jac, linear_method=method, linear_tol=1e-12, max_linear_iters=20000, krylov_vectors=300,
+                             nonlinear_tol=1e-9, max_nonlinear_iters=12)
+    torch.cuda.synchronize()
+    assert info["status"] == 0 and info["converged"] == 1, info
+    assert info["last_linear_relres"] <= 1e-10, info
+    o = Oracle(U.oracle_problem(p))
+    uh = u.cpu().numpy()
+    names = VARS[p["physics"]][: (o.dim if p["physics"] == "linearelasticity" else o.dim + 1 if p["physics"] == "navierstokes" else 1)]
+    for var, gold in GOLD["l2"][path].items():
+        if var not in p["true"]:
+            continue
+        err = o.l2_error(uh, names.index(var), p["true"][var])
+        assert err == pytest.approx(gold, rel=2e-5, abs=1e-9), (path, var, err, gold, info)
+    e.close()
+
+
+@pytest.mark.parametrize("method", [0, 1], ids=["gmres", "cg"])
+def test_linear_solve_against_a_direct_solver(lib, method):
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    import torch
+    from mrhyde_b200 import Engine
+    p = problems.config_c2(9)
+    e = Engine.from_problem(p, lib=lib)
+    xyz, var = e.dof_coords()
+    u, res, jac = _buffers(e)
+    u.copy_(torch.from_numpy(problems.synthetic_state(xyz, var)))
+    e.assemble_jacres(u, res, jac)
+    x = torch.zeros_like(res)
+    info = e.linear_solve(jac, res, x, linear_method=method, linear_tol=1e-13, max_linear_iters=5000, krylov_vectors=60)
+    rp, ci = e.crs()
+    J = sp.csr_matrix((jac.cpu().numpy(), ci, rp), shape=(len(rp) - 1,) * 2).tocsc()
+    want = spl.spsolve(J, res.cpu().numpy())
+    assert info["converged"] == 1 and info["linear_iters"] > 5, info
+    assert np.abs(x.cpu().numpy() - want).max() <= 1e-10 * np.abs(want).max(), info
+    e.close()
+
+
+def test_newton_converges_quadratically_on_the_nonlinear_configs(lib):
+    """C3 (reaction 0.5 c^2) and C5 (convection + SUPG/PSPG) at small sizes: residual drops below 1e-10 of its start"""
+    import torch
+    from mrhyde_b200 import Engine
+    for mk, n in ((problems.config_c3, 4), (problems.config_c5, 5)):
+        e = Engine.from_problem(mk(n), lib=lib)
+        u, res, jac = _buffers(e)
+        info = e.nonlinear_solve(u, res, jac, linear_tol=1e-12, max_linear_iters=20000, krylov_vectors=400, nonlinear_tol=1e-10,
+                                 max_nonlinear_iters=15)
+        torch.cuda.synchronize()
+        assert info["status"] == 0 and 2 <= info["nonlinear_iters"] <= 10, info
+        assert info["resnorm_last"] <= 1e-10 * info["resnorm_first"], info
+        e.close()
+
+
+@pytest.mark.parametrize("tableau,order,rate", [("BWE", 1, 1.0), ("DIRK-2,2", 1, 2.0), ("BWE", 2, 2.0)])
+def test_transient_solver_order_of_accuracy(lib, tableau, order, rate):
+    """thermal 2-D with source = 0, u(x, y, 0) = sin(pi x) sin(pi y), exact nodal decay known for the SEMI-discrete system
+    only through a fine-step run: halving dt must reduce the error against a 16x finer run by 2^rate."""
+    import torch
+    from mrhyde_b200 import Engine
+    p = problems.regression_thermal_2d(8)
+    p["functions"] = {"thermal source": "0.0", "density": "1.0", "specific heat": "1.0"}
+    p["extra"] = {"transient": True}
+    e = Engine.from_problem(p, lib=lib)
+    xyz, _ = e.dof_coords()
+    u0 = np.sin(np.pi * xyz[:, 0]) * np.sin(np.pi * xyz[:, 1])
+    T = 0.04
+
+    def run(nsteps):
+        u, res, jac = _buffers(e)
+        u.copy_(torch.from_numpy(u0))
+        info = e.transient_solve(u, res, jac, 0.0, T, T / nsteps, tableau=tableau, bdf_order=order, linear_method=1, linear_tol=1e-13,
+                                 max_linear_iters=2000, nonlinear_tol=1e-11)
+        assert info["status"] == 0 and info["time_steps"] == nsteps and abs(info["final_time"] - T) < 1e-12, info
+        return u.cpu().numpy()
+    fine = run(256)
+    e4, e8 = np.abs(run(4) - fine).max(), np.abs(run(8) - fine).max()
+    assert 0.0 < e8 < e4 < 0.1
+    assert np.log2(e4 / e8) == pytest.approx(rate, abs=0.35), (e4, e8)
+    assert 0.3 < fine.max() < 0.6                                    # exp(-2 pi^2 0.04) = 0.454 for the continuous problem
+    e.close()
