@@ -7,8 +7,10 @@
 One "step" = one mrh_assemble_jacres call (volume + boundary terms + DBC fix-up) accumulating into the
 caller's residual vector and CRS values, all tables prebuilt — what the reference times as
 "computeJacRes() - total assembly" (/root/reference/src/managers/assemblyManager.hpp:1218).
-N > 1 (torchrun, one rank per GPU): weak scaling, each rank owns a 256x256x256 z-slab of a 256x256x(256 N)
-brick; interface rows go to their owner rank over NCCL every step (mrhyde_b200/partition.py).
+N > 1 (torchrun, one rank per GPU): weak scaling by default, each rank owns a 256x256x256 z-slab of a 256x256x(256 N)
+brick (the line also carries a "strong" record: the 256^3 mesh itself cut into N blocks); --scaling strong makes that the
+headline.  Interface rows go to their owner rank inside mrh_assemble_jacres (library pack / NCCL send-recv / unpack,
+interface tiles first and overlapped with the interior; csrc/exchange.inl).
 --impl reference: the CPU restatement of the reference path (oracle/, kind "port" — the reference itself needs
 Trilinos and cannot be built here) on all host cores, same metric and config, bounded sample per step.
 """
@@ -171,7 +173,6 @@ def run_gpu(args):
     import torch.distributed as dist
     import problems
     from mrhyde_b200 import Engine, load_library
-    from mrhyde_b200 import partition
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -187,26 +188,48 @@ def run_gpu(args):
     dim = 2 if cfg == "C1" else 3
     W, K = max(args.warmup, 3), args.steps
     if world > 1 and cfg != "C2":
-        raise SystemExit("multi-GPU runs are defined for the C2 workload (z-slab partition)")
+        pass     # any configuration partitions; only C2's kernels overlap the exchange with the interior
 
     # ---- set-up (untimed): mesh, DOFs, CRS graph, slot patterns, synthetic state -------------------------
+    STRONG_GRID = {1: (1, 1, 1), 2: (1, 1, 2), 4: (1, 2, 2), 8: (2, 2, 2)}
+
+    def make_engine(strong):
+        """this rank's block: weak = n^3 elements per GPU (z-slabs of an n x n x (n world) brick), strong = the n^3 mesh itself
+        cut into a Px x Py x Pz grid; the NCCL id travels over torch.distributed (plumbing), the exchange is the library's"""
+        p = getattr(problems, mk)(n)
+        if world == 1:
+            return Engine.from_problem(p, device=local), (1, 1, 1)
+        if strong:
+            procs = STRONG_GRID.get(world) or (1, 1, world)
+        else:
+            procs = (1, 1, world)
+            p["mesh"]["NZ"] = n * world
+            p["mesh"]["zmax"] = float(world)
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.from_numpy(Engine(p["physics"], dim, p.get("order", 1), device=local).comm_unique_id().copy()))
+        dist.broadcast(idt, 0)
+        return Engine.from_problem(p, device=local, part=(procs, rank), comm_id=idt.cpu().numpy()), procs
+
     t_setup = time.time()
-    p = partition.slab_problem(getattr(problems, mk)(n), rank, world)
-    e = Engine.from_problem(p, device=local)
+    strong_mode = args.scaling == "strong"
+    e, procs = make_engine(strong_mode)
     s = e.sizes()
     xyz, var = e.dof_coords()
     u_host = problems.synthetic_state(xyz, var)
     u = torch.from_numpy(u_host).to(dev)
     res = torch.zeros(s["nlocal"], dtype=torch.float64, device=dev)
     jac = torch.zeros(s["nnz"], dtype=torch.float64, device=dev)
-    xch = partition.InterfaceExchange(e, rank, world, dev) if world > 1 else None
+    xch = None
     t_setup = time.time() - t_setup
     stream = torch.cuda.current_stream().cuda_stream
+    nelem_total = torch.tensor([s["nelem"]], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(nelem_total)
+    nelem_total = int(nelem_total.item())
 
     def step():
-        e.assemble_jacres(u, res, jac, stream=stream)
-        if xch is not None:
-            xch.exchange(res, jac)
+        e.assemble_jacres(u, res, jac, stream=stream)      # with a communicator attached this includes the interface exchange
 
     def sync():
         torch.cuda.synchronize()
@@ -217,7 +240,7 @@ def run_gpu(args):
     for _ in range(W):
         step()
     sync()
-    launches_per_step = e.launch_count() + (xch.launches_per_step if xch else 0)
+    launches_per_step = e.launch_count()
     sampler = ClockSampler(local) if rank == 0 else None
     vol_ms = []
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -240,7 +263,34 @@ def run_gpu(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = t.item() / K
-    value = world * s["nelem"] / (ms_step * 1e-3)
+    value = nelem_total / (ms_step * 1e-3)
+
+    # ---- strong scaling of the SAME n^3 mesh (BASELINE.json north_star: "the mesh is partitioned ... across the 8 GPUs") ----
+    strong_rec = None
+    if world > 1 and not strong_mode and not args.no_other and not args.kernel_only:
+        e2, procs2 = make_engine(True)
+        s2 = e2.sizes()
+        xyz2, var2 = e2.dof_coords()
+        u2 = torch.from_numpy(problems.synthetic_state(xyz2, var2)).to(dev)
+        res2 = torch.zeros(s2["nlocal"], dtype=torch.float64, device=dev)
+        jac2 = torch.zeros(s2["nnz"], dtype=torch.float64, device=dev)
+        for _ in range(W):
+            e2.assemble_jacres(u2, res2, jac2, stream=stream)
+        sync()
+        ev0.record()
+        for _ in range(K):
+            e2.assemble_jacres(u2, res2, jac2, stream=stream)
+        ev1.record()
+        sync()
+        t2 = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        ms2 = t2.item() / K
+        strong_rec = {"scaling": "strong", "mesh": f"{n}^{dim} cut into {procs2[0]}x{procs2[1]}x{procs2[2]} blocks", "ms_per_step": ms2,
+                      "value": n ** dim / (ms2 * 1e-3), "unit": UNIT, "elements_per_gpu": s2["nelem"], "gpu_launches_per_step": e2.launch_count(),
+                      "volume_kernel": e2.kernel_path(), "note": "efficiency = value / (N x the N=1 value of this bench)"}
+        e2.close()
+        del u2, res2, jac2
+        torch.cuda.empty_cache()
 
     if args.kernel_only:
         if rank == 0:
@@ -263,7 +313,7 @@ def run_gpu(args):
     t = torch.tensor([te], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * s["nelem"] * Ke / t.item()
+    e2e_value = nelem_total * Ke / t.item()
     checksum = float(hres.abs().sum())
 
     kpath = e.kernel_path()
@@ -306,9 +356,11 @@ def run_gpu(args):
             pass
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong" if strong_mode else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload,
-                       "mesh": f"{n}^{dim} per GPU" + (f", {world} z-slabs" if world > 1 else ""), "elements_per_gpu": s["nelem"],
+                       "mesh": (f"{n}^{dim} cut into {procs[0]}x{procs[1]}x{procs[2]} blocks" if strong_mode and world > 1 else
+                                f"{n}^{dim} per GPU" + (f", {world} z-slabs" if world > 1 else "")), "elements_per_gpu": s["nelem"],
+                       "exchange": "library: pack kernel -> ncclSend/ncclRecv per neighbour -> unpack kernel, interface tiles first and overlapped" if world > 1 else None,
                        "dofs_per_gpu": s["nlocal"], "nnz_per_gpu": s["nnz"], "slot_patterns": s["npatterns"], "volume_kernel": kpath,
                        "l2": f"inputs+outputs ({8e-9 * (s['nnz'] + 2 * s['nlocal']):.1f} GB/step) exceed the 126 MB L2; no flush needed",
                        "timing": "CUDA events on the launch stream, K steps, max over ranks; zeroing of res / J is the caller's job "
@@ -325,6 +377,7 @@ def run_gpu(args):
                              "sample": f"oracle (CPU restatement, reference-shaped groups of 100, atomic scatter) on one {cpu_n}^{dim} mesh of the workload, "
                                        f"{cores} threads, 1 warm-up + median of 5", "ms_per_pass": cpu_sps * 1e3, "buckets_s": cpu_buckets},
             "other_configs": other,
+            "strong": strong_rec,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 8 * s["nlocal"],
                     "d2h_bytes_per_step": 8 * (s["nlocal"] + s["nnz"]), "steps": Ke, "checksum_abs_res": checksum,
                     "api": "mrh_assemble_jacres_host (pinned host buffers; u in, residual + CRS values out)"},
@@ -344,6 +397,7 @@ def main():
     ap.add_argument("--n", type=int, default=0, help="elements per direction per GPU (default: the configuration's BASELINE.json size)")
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS), help="BASELINE.json configuration (default C2, the headline)")
     ap.add_argument("--no-other", action="store_true", help="skip the other_configs leg of the default run")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"], help="N > 1: n^3 elements per GPU (weak, default) or the n^3 mesh cut into N blocks (strong)")
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--kernel-only", action="store_true", help="profiling aid: skip the e2e and cpu_baseline legs")
     args = ap.parse_args()

@@ -59,7 +59,8 @@ typedef struct mrh_config {
   int32_t device;             /* CUDA device ordinal */
   int32_t flags;              /* bit 0: force the generic kernel; bit 1: no NVRTC specialisation;
                                * bit 2: direct instead of tile-staged scatter; bit 3: no warp-specialised kernel; bit 4: no batched kernel;
-                               * bit 5: NVRTC-specialise the batched kernel on small meshes too (tests) */
+                               * bit 5: NVRTC-specialise the batched kernel on small meshes too (tests); bit 6: no lane-per-point thermal kernel;
+                               * bit 7: no exchange inside mrh_assemble_* when a communicator is attached */
 } mrh_config;
 
 /* Workset time data: Workset::{time,deltat,isTransient,current_stage,butcher_A,butcher_b,BDF_wts}
@@ -127,6 +128,36 @@ int mrh_assemble_jacres(mrh_handle h, const mrh_state* st, double* res, double* 
 /* Same call with HOST buffers (pinned or pageable): copies u in, zeroes, assembles, copies res and jac out. */
 int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res_host, double* jac_host);
 
+/* ---- multi-GPU: element-block partition + additive interface exchange ---------------------------------- */
+/* One process per GPU.  Every rank assembles its own elements into its OVERLAPPED vector / matrix; rows of DOFs it holds but does
+ * not own are then added onto the owner: LinearAlgebraInterface::exportVectorFromOverlapped / exportMatrixFromOverlapped
+ * (src/interfaces/linearAlgebraInterface.hpp:296-337, Tpetra doExport ADD).  With a communicator attached mrh_assemble_res /
+ * mrh_assemble_jacres include that exchange (flag bit 7 of mrh_config.flags: leave it to an explicit mrh_exchange); the
+ * tile-staged thermal kernels assemble the interface tiles first and overlap the exchange with the interior.  A DOF shared by
+ * several ranks is owned by the lowest one; fixed rows shared by k ranks end with diagonal k (assemblyManager.cpp:1167-1180 + ADD). */
+/* block `rank` of a procs[0] x procs[1] x procs[2] decomposition of the global brick: panzer_stk X/Y/Z Procs
+ * (src/interfaces/meshInterface.cpp:140-155); replaces mrh_build_brick; side sets keep only faces on the physical boundary */
+int mrh_build_brick_part(mrh_handle h, const int32_t* nxyz_global, const double* lo, const double* hi, const int32_t* procs, int32_t rank);
+/* caller-supplied ownership (Panzer getOwnedAndGhostedIndices, discretizationInterface.cpp:2382-2397): global id and owner rank per local DOF */
+int mrh_set_partition(mrh_handle h, const int64_t* gids, const int32_t* owner, int32_t rank, int32_t world);
+int mrh_get_partition(mrh_handle h, int64_t* gids, int32_t* owner);
+/* NCCL: rank 0 creates the 128-byte id and distributes it by any means; every rank then calls mrh_comm_init (collective) */
+int mrh_comm_unique_id(void* id128);
+int mrh_comm_init(mrh_handle h, const void* id128, int32_t rank, int32_t world);
+/* the exchange alone, on `stream` (jac may be NULL: residual only); device pointers */
+int mrh_exchange(mrh_handle h, double* res, double* jac, void* stream);
+/* entries of owned rows whose column is not a local DOF (the off-process columns of Tpetra's non-overlapped matrix): local row, global
+ * column id and - after an exchange - value of each; returns their number (arguments may be NULL) */
+int64_t mrh_get_ghost_block(mrh_handle h, int32_t* rows, int64_t* col_gids, double* values_host);
+/* exchange-plan metadata for a transport of the caller's choice (mrh_comm_init moves it over NCCL itself; the CPU tests use gloo):
+ * words to send to `peer`, the words, and the words received from `peer` */
+int64_t mrh_exchange_meta_size(mrh_handle h, int32_t peer);
+int mrh_exchange_meta_get(mrh_handle h, int32_t peer, int64_t* out);
+int mrh_exchange_meta_put(mrh_handle h, int32_t peer, const int64_t* in, int64_t n);
+/* plan tables of `peer` - which: 0 send rows, 1 send CRS slots, 2 receive rows, 3 receive slots (-(k+1): ghost entry k); 4 / 5: ghost
+ * rows / ghost column ids.  Returns the entry count (out may be NULL). */
+int64_t mrh_get_exchange_table(mrh_handle h, int32_t peer, int32_t which, int64_t* out);
+
 /* ---- the direct caller of the hot path, on the device ----------------------------------------------- */
 /* Solver sublist of the input (src/managers/solverManager.cpp:55-70, src/interfaces/linearAlgebraInterface.cpp:47-50) */
 typedef struct mrh_solver_opts {
@@ -159,6 +190,19 @@ int mrh_nonlinear_solve(mrh_handle h, const mrh_state* st, double* u, double* re
  * "DIRK-2,3" | "DIRK-3,3", BDF order 1..4 (orders > 1 start up with lower orders). */
 int mrh_transient_solve(mrh_handle h, double* u, double start_time, double end_time, double deltat, const char* butcher_tableau,
                         int32_t bdf_order, double* res, double* jac, const mrh_solver_opts* opts, mrh_solver_info* info, void* stream);
+
+/* ---- mass-matrix / L2-projection assembly for Dirichlet and initial data ------------------------------ */
+/* AssemblyManager::setDirichlet (src/managers/assemblyManager.cpp:1855-1948 with getDirichletBoundary / getMassBoundary :6288-6420;
+ * kind 0) and AssemblyManager::setInitial (:1185-1310; kind 1): the L2-projection system of the strong Dirichlet data onto the
+ * fixed DOFs (side mass matrix + side moments of "Dirichlet <var> <side>", identity on every other row) or of "initial <var>"
+ * (registered with mrh_add_function at "ip"; absent = 0) over the volume.  rhs (nlocal) and mass (nnz, on the CRS graph) are
+ * device arrays the caller zeroes; both are accumulated into. */
+int mrh_assemble_projection(mrh_handle h, int32_t kind, double time, double* rhs, double* mass, void* stream);
+/* SolverManager::projectDirichlet + setDirichlet (src/managers/solverManager.cpp:1060-1098, 1876-1935): assembles the system into the
+ * caller's work arrays, solves it (conjugate gradients) and writes the values of the fixed DOFs into u (device, in/out). */
+int mrh_set_dirichlet(mrh_handle h, double* u, double time, double* rhs_work, double* mass_work, const mrh_solver_opts* opts, mrh_solver_info* info, void* stream);
+/* SolverManager::setInitial (L2 projection of the initial data): u = projection of "initial <var>" */
+int mrh_set_initial(mrh_handle h, double* u, double* rhs_work, double* mass_work, const mrh_solver_opts* opts, mrh_solver_info* info, void* stream);
 
 /* Allocation-free variant of the host-buffer residual assembly.  It has NO counterpart in the reference and was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving

@@ -214,6 +214,53 @@ struct GenPhases {
         for (int l = 0; l < P; ++l) sD[(v * TA + a) * P + l] = lane(F[v][a], l);
     }
   }
+  // ---- L2-projection systems (no AD): item = (element, variable v, basis function i) -----------------------------
+  // PROJ_DIRICHLET (side launch): rows of FIXED DOFs collect the side mass matrix of their variable and the side moments of the
+  //   Dirichlet function  - AssemblyManager::setDirichlet / getDirichletBoundary / getMassBoundary
+  //   (/root/reference/src/managers/assemblyManager.cpp:1855-1948, 6288-6420);
+  // PROJ_INITIAL (volume launch): every row collects the element mass matrix of its variable and the moments of "initial <var>"
+  //   - AssemblyManager::setInitial (:1185-1310).  rhs is ADDED to kp.res, the mass entries to kp.jac (lumped when lump_mass).
+  MRH_HDN static void projection(const KParams& kp, const GenSmem<C>& L, double* sm, int64_t blk0, int item) {
+    const int nq = L.nq;
+    const int v = item % NVAR, i = (item / NVAR) % NB, le = item / (NVAR * NB);
+    if (blk0 + le >= kp.nwork) return;
+    const bool dir = kp.ph.proj == PROJ_DIRICHLET;
+    if (dir && kp.ph.bc[v] != BC_DIRICHLET) return;
+    const int* sLid = reinterpret_cast<const int*>(sm + L.oLid()) + le * N;
+    const int rowslot = kp.offsets[v * NB + i];
+    const int row = sLid[rowslot];
+    if (dir && !kp.fixed[row]) return;
+    const Prog& pr = kp.progs[(dir ? SIDE_BCSRC : VOL_INIT) + v];
+    double dval = 0.0, m[NB];
+    for (int k = 0; k < NB; ++k) m[k] = 0.0;
+    for (int q = 0; q < nq; ++q) {
+      const double* T = sm + L.oT() + ((size_t)le * nq + q) * NB * TA;
+      const double w = sm[L.oW() + (size_t)le * nq + q];
+      PointState<double> ps;
+      for (int c = 0; c < 3; ++c) {
+        ps.x[c] = sm[L.oXq() + ((size_t)le * nq + q) * 3 + c];
+        ps.nrm[c] = sm[L.oNrm() + ((size_t)le * nq + q) * 6 + c];
+        ps.tng[c] = sm[L.oNrm() + ((size_t)le * nq + q) * 6 + 3 + c];
+      }
+      ps.time = kp.tp.time; ps.fields = nullptr;
+      const double g = (pr.kind == 0) ? pr.cval : eval_code<double>(kp.code, kp.cpool, pr.start, pr.len, ps);
+      const double Tiw = T[i * TA] * w;
+      dval += g * Tiw;
+      for (int k = 0; k < NB; ++k) m[k] += Tiw * T[k * TA];
+    }
+    atomic_add(kp.res + row, dval);
+    if (!kp.jac) return;
+    const int64_t e = elem_of(kp, blk0 + le);
+    const uint16_t* pat = kp.pat + (size_t)kp.pat_id[e] * N * N + (size_t)rowslot * N;
+    double* jrow = kp.jac + kp.rowptr[row];
+    if (kp.lump_mass && !dir) {
+      double s = 0.0;
+      for (int k = 0; k < NB; ++k) s += m[k];
+      atomic_add(jrow + pat[rowslot], s);
+      return;
+    }
+    for (int k = 0; k < NB; ++k) atomic_add(jrow + pat[kp.offsets[v * NB + k]], m[k]);
+  }
   MRH_HD static void set_lane(double&, int, double) {}
   template <int PP> MRH_HD static void set_lane(PAD<PP>& x, int l, double v) { x.d[l] = v; }
 

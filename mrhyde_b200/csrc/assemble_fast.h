@@ -132,7 +132,12 @@ struct ThermalHexQ1 {
   // X and us are overwritten by their monomial coefficients (see below)
   template <class KA>
   MRH_HDN static void work(const KParams& kp, double (&X)[8][3], double (&us)[8], const double (&ud)[8], double* stage, int stride,
-                           double (&r)[8], KA& K) {
+                           double (&r)[8], KA& K) { work<KA, false>(kp, X, us, ud, stage, stride, r, K, nullptr); }
+  // CSM: the 24 monomial coefficients of the trilinear map live in shared memory (cs[(m * 3 + i) * 128], one column per thread)
+  // and are re-read at every point, which frees 48 registers - enough to keep the element matrix in registers instead
+  template <class KA, bool CSM>
+  MRH_HDN static void work(const KParams& kp, double (&X)[8][3], double (&us)[8], const double (&ud)[8], double* stage, int stride,
+                           double (&r)[8], KA& K, double* cs) {
     const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
 
     // ---- coefficients at the 8 points (vector interpreter), staged for the rolled point loop ------------
@@ -191,6 +196,14 @@ struct ThermalHexQ1 {
       }
 #pragma unroll
       for (int m = 0; m < 8; ++m) { C[m][0] = 0.125 * v[0][m]; C[m][1] = 0.125 * v[1][m]; C[m][2] = 0.125 * v[2][m]; A[m] = 0.125 * v[3][m]; }
+      if constexpr (CSM) {
+#pragma unroll
+        for (int m = 0; m < 8; ++m)
+#pragma unroll
+          for (int i = 0; i < 3; ++i) cs[(m * 3 + i) * 128] = C[m][i];
+#pragma unroll
+        for (int m = 1; m < 8; ++m) cs[(24 + m) * 128] = A[m];
+      }
     }
 
     // ---- point loop (rolled: the body stays resident in the instruction cache) ------------------------
@@ -212,11 +225,21 @@ struct ThermalHexQ1 {
       // J_ij = d x_i / d xi_j of the trilinear map, from its monomial coefficients
       const double xe = sx * sy, ez2 = sy * sz, xz2 = sx * sz, xez = xe * sz;
       double J[3][3];
+      double ptc[3] = {0.0, 0.0, 0.0};                   // CSM: the point's coordinates are formed here, while the coefficients are at hand
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
+        if constexpr (CSM) {
+          const double c0 = cs[(0 * 3 + i) * 128], c1 = cs[(1 * 3 + i) * 128], c2 = cs[(2 * 3 + i) * 128], c3 = cs[(3 * 3 + i) * 128],
+                       c4 = cs[(4 * 3 + i) * 128], c5 = cs[(5 * 3 + i) * 128], c6 = cs[(6 * 3 + i) * 128], c7 = cs[(7 * 3 + i) * 128];
+          J[i][0] = c1 + c3 * sy + c5 * sz + c7 * ez2;
+          J[i][1] = c2 + c3 * sx + c6 * sz + c7 * xz2;
+          J[i][2] = c4 + c5 * sx + c6 * sy + c7 * xe;
+          ptc[i] = c0 + c1 * sx + c2 * sy + c4 * sz + c3 * xe + c5 * xz2 + c6 * ez2 + c7 * xez;
+        } else {
         J[i][0] = C[1][i] + C[3][i] * sy + C[5][i] * sz + C[7][i] * ez2;
         J[i][1] = C[2][i] + C[3][i] * sx + C[6][i] * sz + C[7][i] * xz2;
         J[i][2] = C[4][i] + C[5][i] * sx + C[6][i] * sy + C[7][i] * xe;
+        }
       }
       double Ji[3][3];
       const double det = det_inv<3>(J, Ji);
@@ -234,9 +257,11 @@ struct ThermalHexQ1 {
         if (TRANSIENT) edot += ud[s] * Nq[s];
       }
       {
-        const double g0 = A[1] + A[3] * sy + A[5] * sz + A[7] * ez2;        // reference gradient of u
-        const double g1 = A[2] + A[3] * sx + A[6] * sz + A[7] * xz2;
-        const double g2 = A[4] + A[5] * sx + A[6] * sy + A[7] * xe;
+        double a1 = A[1], a2 = A[2], a3 = A[3], a4 = A[4], a5 = A[5], a6 = A[6], a7 = A[7];
+        if constexpr (CSM) { a1 = cs[25 * 128]; a2 = cs[26 * 128]; a3 = cs[27 * 128]; a4 = cs[28 * 128]; a5 = cs[29 * 128]; a6 = cs[30 * 128]; a7 = cs[31 * 128]; }
+        const double g0 = a1 + a3 * sy + a5 * sz + a7 * ez2;        // reference gradient of u
+        const double g1 = a2 + a3 * sx + a6 * sz + a7 * xz2;
+        const double g2 = a4 + a5 * sx + a6 * sy + a7 * xe;
         ex = Ji[0][0] * g0 + Ji[1][0] * g1 + Ji[2][0] * g2;
         ey = Ji[0][1] * g0 + Ji[1][1] * g1 + Ji[2][1] * g2;
         ez = Ji[0][2] * g0 + Ji[1][2] * g1 + Ji[2][2] * g2;
@@ -251,7 +276,7 @@ struct ThermalHexQ1 {
         double pt[3];
 #pragma unroll
         for (int i = 0; i < 3; ++i)
-          pt[i] = C[0][i] + C[1][i] * sx + C[2][i] * sy + C[4][i] * sz + C[3][i] * xe + C[5][i] * xz2 + C[6][i] * ez2 + C[7][i] * xez;
+          pt[i] = CSM ? ptc[i] : C[0][i] + C[1][i] * sx + C[2][i] * sy + C[4][i] * sz + C[3][i] * xe + C[5][i] * xz2 + C[6][i] * ez2 + C[7][i] * xez;
         const double x = pt[0], y = pt[1], z = pt[2];
         const double t = kp.tp.time;
         srcq = CF::source(x, y, z, t); kapq = CF::diff(x, y, z, t);
@@ -498,25 +523,37 @@ struct ThermalHexQ1 {
   __host__ __device__ static constexpr size_t ws_smem_bytes(int max_acc, int max_e, int max_r) {
     return (WS_NBUF * ((size_t)NE * 128 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 2 * 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + 16;
   }
+  // K-in-registers kernel (tiled_wsk): two element stores, monomial coefficients of both compute groups in shared memory
+  static constexpr int WSK_NBUF = 2;
+  __host__ __device__ static constexpr size_t wsk_smem_bytes(int max_acc, int max_e, int max_r) {
+    return (WSK_NBUF * ((size_t)NE * 128 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 2 * 128 * 64 + 2 * 32 * 128 * sizeof(double) +
+           ((size_t)max_e + (size_t)max_r) * 4 + 16;
+  }
+  // lane-per-point kernel (tiled_ws8): element-store stride 129, NCG compute warpgroups of 16 elements in flight each
+  static constexpr int W8_STR = TRANSIENT ? 44 : 36;      // doubles of monomial scratch per element in flight (bank-spread for LDS.128)
+  __host__ __device__ static constexpr size_t ws8_scratch_bytes_of(int ncg) { return (size_t)ncg * 16 * W8_STR * sizeof(double); }
+  __host__ __device__ static constexpr size_t ws8_smem_bytes(int max_acc, int max_e, int max_r, int ncg) {
+    return (WS_NBUF * ((size_t)NE * 129 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + ws8_scratch_bytes_of(ncg) + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+  }
 #if defined(MRH_WS_CREG)
   __device__ __forceinline__ static void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
   __device__ __forceinline__ static void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
   // scatter warpgroup of the warp-specialised kernels: serves the element stores of NCG compute groups in hand-over order
   // (sequence number s = NCG i + g is tile i of compute group g and lives in element store s % WS_NBUF).  KPAD: the element
   // store's entry stride is 128 + KPAD doubles (contribution lists address cells as entry * 128 + thread).
-  template <int NCG, int KPAD>
+  template <int NCG, int KPAD, int NBUF = WS_NBUF>
   __device__ __forceinline__ static void ws_scatter_group(const KParams& kp, double* sm, int tid, int scratch_bytes) {
     const TilePlan& tp = kp.tile;
     constexpr int KSZ = NE * (128 + KPAD) + 2;
-    double* acc = sm + WS_NBUF * KSZ;
+    double* acc = sm + NBUF * KSZ;
     double* carry = acc + ((tp.max_acc + 2) & ~1);
     unsigned* s_off = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(carry + 128) + scratch_bytes);
     int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
     const int64_t tstep = NCG * (int64_t)gridDim.x;
-    constexpr int BAR_FULL = 1, BAR_EMPTY = 1 + WS_NBUF, BAR_SCATTER = 1 + 2 * WS_NBUF;
+    constexpr int BAR_FULL = 1, BAR_EMPTY = 1 + NBUF, BAR_SCATTER = 1 + 2 * NBUF;
     constexpr int NPAIR = 256;                              // a FULL / EMPTY barrier joins one compute group (128) and the scatter group (128)
     auto tile_of = [&](int s) -> int64_t { return tp.tile_begin + NCG * (int64_t)blockIdx.x + (s % NCG) + (int64_t)(s / NCG) * tstep; };
-    if (tid < WS_NBUF) sm[tid * KSZ + NE * (128 + KPAD)] = 0.0;    // masked contributions read these cells
+    if (tid < NBUF) sm[tid * KSZ + NE * (128 + KPAD)] = 0.0;    // masked contributions read these cells
     struct TileMeta { int64_t eb, rb, base; int E, R, clid; };
     auto load_meta = [&](int64_t t, TileMeta& m) {
       if (t >= tp.tile_end) { m.E = m.R = 0; m.clid = 0; m.eb = m.rb = m.base = 0; return; }
@@ -581,7 +618,7 @@ struct ThermalHexQ1 {
       }
       bar_sync(BAR_SCATTER, 128);                         // lists and accumulation array free again
       cur = nxt;
-      b = (b + 1 == WS_NBUF) ? 0 : b + 1;
+      b = (b + 1 == NBUF) ? 0 : b + 1;
     }
   }
   __device__ static void tiled_ws(const KParams& kp, double* sm) {
@@ -652,6 +689,82 @@ struct ThermalHexQ1 {
       }
     }
   }
+#if defined(MRH_WSK_CREG)
+  // K-in-registers form of tiled_ws: the compute groups keep the element matrix in registers over the point loop and park the
+  // monomial coefficients of the trilinear map in shared memory instead (24 reads per point against 72 read-modify-writes of the
+  // element store, whose traffic made the shared-memory pipe the co-limiter of tiled_ws); the element store is written once per
+  // element at hand-over, so two stores suffice.  Shared memory: Ks[2] | acc | carry | rowbuf[2][128][16] int | Cs[2][32 * 128] | off | rows
+  __device__ static void tiled_wsk(const KParams& kp, double* sm) {
+    static_assert(JAC, "the tile-staged scatter is used for Jacobian assembly only");
+    static_assert(!CF::staged, "the warp-specialised kernel is built with NVRTC-printed coefficients");
+    const TilePlan& tp = kp.tile;
+    const int wg = threadIdx.x >> 7, tid = threadIdx.x & 127;
+    constexpr int KSZ = NE * 128 + 2;
+    double* acc = sm + WSK_NBUF * KSZ;
+    double* carry = acc + ((tp.max_acc + 2) & ~1);
+    int* rowbase = reinterpret_cast<int*>(carry + 128);
+    double* csbase = reinterpret_cast<double*>(rowbase + 2 * 128 * 16);
+    const int64_t tstep = 2 * (int64_t)gridDim.x;
+    // The CTA's tiles in hand-over order: sequence number s = 2 i + g is tile i of compute group g; it lives in
+    // element store s % WS_NBUF.  Named barriers (0 is __syncthreads): FULL[b] compute -> scatter, EMPTY[b] back.
+    constexpr int BAR_FULL = 1, BAR_EMPTY = 1 + WSK_NBUF;
+    auto tile_of = [&](int s) -> int64_t { return tp.tile_begin + 2 * (int64_t)blockIdx.x + (s & 1) + (int64_t)(s >> 1) * tstep; };
+    if (wg == 0) {
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MRH_WSK_SREG));
+      ws_scatter_group<2, 0, WSK_NBUF>(kp, sm, tid, 2 * 128 * 64 + 2 * 32 * 128 * (int)sizeof(double));
+    } else {
+      // ================================= compute warpgroups =================================
+      asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MRH_WSK_CREG));
+      double* cs = csbase + (size_t)(wg - 1) * 32 * 128 + tid;
+      const int g = wg - 1;
+      int* rowbuf = rowbase + (g * 128 + tid) * 16;         // my next element's 8 LIDs | 8 node ids
+      auto element_of = [&](int64_t t) -> int { const int64_t e0 = t * 128 + tid; return (t < tp.tile_end && e0 < kp.nwork) ? tp.perm[e0] : -1; };
+      auto fetch_rows = [&](int e) {
+        if (e < 0) return;
+        cp_async16(rowbuf, kp.lids + (int64_t)e * 8); cp_async16(rowbuf + 4, kp.lids + (int64_t)e * 8 + 4);
+        cp_async16(rowbuf + 8, kp.e2n + (int64_t)e * 8); cp_async16(rowbuf + 12, kp.e2n + (int64_t)e * 8 + 4);
+      };
+      const int64_t tfirst = tile_of(g);
+      // pipeline per thread: registers hold the gathered data of tile i, rowbuf the LID / node rows of tile i + 1.
+      // (An explicit L2 prefetch of tile i + 2's vertices was measured slower: CCTL.PF2 stalls the issuing warp.)
+      int e_cur = element_of(tfirst), e_next = element_of(tfirst + tstep), e_next2 = element_of(tfirst + 2 * tstep);
+      double X[8][3], us[8], ud[8];
+      {
+        int lid[8];
+        if (e_cur >= 0) gather(kp, kp.lids + (int64_t)e_cur * 8, kp.e2n + (int64_t)e_cur * 8, lid, X, us, ud);
+      }
+      fetch_rows(e_next);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      int s = g, b = g % WSK_NBUF;
+      for (int64_t t = tfirst; t < tp.tile_end; t += tstep) {
+        double* Ks = sm + b * KSZ + tid;
+        double r[8], K[NK];
+        if (e_cur >= 0) {
+          KReg kacc{K};
+          work<KReg, true>(kp, X, us, ud, nullptr, 0, r, kacc, cs);
+        }
+        if (s >= WSK_NBUF) bar_sync(BAR_EMPTY + b, 256);                 // the scatter group has consumed this store's previous tile
+        if (e_cur >= 0) {
+#pragma unroll
+          for (int k = 0; k < NK; ++k) Ks[k * 128] = K[k];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) Ks[(NK + k) * 128] = -r[k];
+        }
+        bar_arrive(BAR_FULL + b, 256);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");             // my rows of the next tile
+        if (e_next >= 0) {
+          int lid[8];
+          gather(kp, rowbuf, rowbuf + 8, lid, X, us, ud);
+        }
+        const int e_next3 = element_of(t + 3 * tstep);
+        fetch_rows(e_next2);                                             // rowbuf was consumed by the gather above
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        e_cur = e_next; e_next = e_next2; e_next2 = e_next3;
+        s += 2; b = (b + 2) % WSK_NBUF;
+      }
+    }
+  }
+#endif  // MRH_WSK_CREG
 #if defined(MRH_WS8_NCG)
   // ---- lane-per-point form of the warp-specialised kernel (device only; NVRTC kernel) --------------------------
   // Eight consecutive lanes own one element: lane q gathers vertex q and evaluates quadrature point q.  Nothing is
@@ -664,12 +777,15 @@ struct ThermalHexQ1 {
   // fall into different banks; the scatter warpgroup is the same code as in tiled_ws.
   MRH_HD static constexpr int tri_i(int k) { int i = 0; while (k >= 8 - i) { k -= 8 - i; ++i; } return i; }
   MRH_HD static constexpr int tri_j(int k) { int i = 0; while (k >= 8 - i) { k -= 8 - i; ++i; } return i + k; }
-  static constexpr int W8_STR = TRANSIENT ? 44 : 36;      // doubles of monomial scratch per element in flight (bank-spread for LDS.128)
-  __host__ __device__ static constexpr size_t ws8_scratch_bytes() { return (size_t)MRH_WS8_NCG * 16 * W8_STR * sizeof(double); }
-  __host__ __device__ static constexpr size_t ws8_smem_bytes(int max_acc, int max_e, int max_r) {
-    return (WS_NBUF * ((size_t)NE * 129 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + ws8_scratch_bytes() + ((size_t)max_e + (size_t)max_r) * 4 + 16;
-  }
+  __host__ __device__ static constexpr size_t ws8_scratch_bytes() { return ws8_scratch_bytes_of(MRH_WS8_NCG); }
   __device__ __forceinline__ static double shx(double v, int mask) { return __shfl_xor_sync(0xffffffffu, v, mask); }
+  // c ? a : b as an opaque select: written with ?: on array elements the compiler turns the pair into ONE dynamically indexed
+  // local-memory array (a[j + 10 c]), which puts the butterfly's partial sums on the stack
+  __device__ __forceinline__ static double sel(bool c, double a, double b) {
+    double r;
+    asm("{ .reg .pred p; setp.ne.s32 p, %3, 0; selp.f64 %0, %1, %2, p; }" : "=d"(r) : "d"(a), "d"(b), "r"((int)c));
+    return r;
+  }
   __device__ static void tiled_ws8(const KParams& kp, double* sm) {
     static_assert(JAC && !ADV, "lane-per-point kernel: symmetric element matrix, Jacobian assembly");
     static_assert(!CF::staged, "the warp-specialised kernels are built with NVRTC-printed coefficients");
@@ -701,7 +817,6 @@ struct ThermalHexQ1 {
     for (int a = 0; a < 2; ++a)
 #pragma unroll
       for (int b = 0; b < 2; ++b) { hyz[a][b] = 0.5 * ly[a] * lz[b]; hxz[a][b] = 0.5 * lx[a] * lz[b]; hxy[a][b] = 0.5 * lx[a] * ly[b]; }
-    const double tlz[2] = {2.0 * lz[0], 2.0 * lz[1]};
     const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
     const int64_t tstep = NCG * (int64_t)gridDim.x;
     const int64_t tfirst = tp.tile_begin + NCG * (int64_t)blockIdx.x + g;
@@ -743,7 +858,120 @@ struct ThermalHexQ1 {
       int lidN2 = 0, ndN2 = 0;
       if (eN2 >= 0) { lidN2 = kp.lids[(int64_t)eN2 * 8 + q]; ndN2 = kp.e2n[(int64_t)eN2 * 8 + q]; }
       const int eN3 = elem_at(it + 3);
-//@W8_BODY@
+      {
+        // ---- vertex butterfly over the three tensor bits: lane holds 8 x the monomial coefficient `mono` of x, y, z, u (, du/dt)
+        double v0 = xC0, v1 = xC1, v2 = xC2, v3 = uC, v4 = dC;
+#define MRH_W8_BF(MASK, HI) { const double o0 = shx(v0, MASK), o1 = shx(v1, MASK), o2 = shx(v2, MASK), o3 = shx(v3, MASK); \
+          v0 = (HI) ? v0 - o0 : v0 + o0; v1 = (HI) ? v1 - o1 : v1 + o1; v2 = (HI) ? v2 - o2 : v2 + o2; v3 = (HI) ? v3 - o3 : v3 + o3; \
+          if (TRANSIENT) { const double o4 = shx(v4, MASK); v4 = (HI) ? v4 - o4 : v4 + o4; } }
+        MRH_W8_BF(1, hx) MRH_W8_BF(3, b1) MRH_W8_BF(4, b2)
+#undef MRH_W8_BF
+        __syncwarp();                                       // the previous item's reads of the scratch are complete
+        *reinterpret_cast<double2*>(scr + mono * 4) = make_double2(0.125 * v0, 0.125 * v1);
+        *reinterpret_cast<double2*>(scr + mono * 4 + 2) = make_double2(0.125 * v2, 0.125 * v3);
+        if (TRANSIENT) scr[32 + mono] = 0.125 * v4;
+        __syncwarp();
+        // ---- Jacobian of the trilinear map, point coordinates, reference gradient of u: all from the monomial form
+        double J[3][3], pt[3], g0, g1, g2, edot = 0.0;
+        {
+          const double2* c2 = reinterpret_cast<const double2*>(scr);
+          double C[8][3], A[8];
+#pragma unroll
+          for (int m = 0; m < 8; ++m) { const double2 a = c2[2 * m], bb = c2[2 * m + 1]; C[m][0] = a.x; C[m][1] = a.y; C[m][2] = bb.x; A[m] = bb.y; }
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            J[i][0] = C[1][i] + C[3][i] * sy + C[5][i] * sz + C[7][i] * syz;
+            J[i][1] = C[2][i] + C[3][i] * sx + C[6][i] * sz + C[7][i] * sxz;
+            J[i][2] = C[4][i] + C[5][i] * sx + C[6][i] * sy + C[7][i] * sxy;
+            pt[i] = C[0][i] + C[1][i] * sx + C[2][i] * sy + C[4][i] * sz + C[3][i] * sxy + C[5][i] * sxz + C[6][i] * syz + C[7][i] * sxyz;
+          }
+          g0 = A[1] + A[3] * sy + A[5] * sz + A[7] * syz;
+          g1 = A[2] + A[3] * sx + A[6] * sz + A[7] * sxz;
+          g2 = A[4] + A[5] * sx + A[6] * sy + A[7] * sxy;
+          if (TRANSIENT) {
+            const double* Dm = scr + 32;
+            edot = Dm[0] + Dm[1] * sx + Dm[2] * sy + Dm[4] * sz + Dm[3] * sxy + Dm[5] * sxz + Dm[6] * syz + Dm[7] * sxyz;
+          }
+        }
+        double Ji[3][3];
+        const double det = det_inv<3>(J, Ji);
+        const double w = fabs(det);                         // reference weight 1
+        double gx[8], gy[8], gz[8];
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          const int a = HexQ1::bx(s), bq = HexQ1::by(s), c = HexQ1::bz(s);
+          const double d0 = a ? hyz[bq][c] : -hyz[bq][c], d1 = bq ? hxz[a][c] : -hxz[a][c], d2 = c ? hxy[a][bq] : -hxy[a][bq];
+          gx[s] = Ji[0][0] * d0 + Ji[1][0] * d1 + Ji[2][0] * d2;
+          gy[s] = Ji[0][1] * d0 + Ji[1][1] * d1 + Ji[2][1] * d2;
+          gz[s] = Ji[0][2] * d0 + Ji[1][2] * d1 + Ji[2][2] * d2;
+        }
+        const double ex = Ji[0][0] * g0 + Ji[1][0] * g1 + Ji[2][0] * g2;
+        const double ey = Ji[0][1] * g0 + Ji[1][1] * g1 + Ji[2][1] * g2;
+        const double ez = Ji[0][2] * g0 + Ji[1][2] * g1 + Ji[2][2] * g2;
+        const double tm = kp.tp.time;
+        const double srcq = CF::source(pt[0], pt[1], pt[2], tm), kapq = CF::diff(pt[0], pt[1], pt[2], tm);
+        const double rcpq = TRANSIENT ? CF::rhocp(pt[0], pt[1], pt[2], tm) : 0.0;
+        const double kw = kapq * w;
+        double f0 = -srcq * w;
+        if (TRANSIENT) f0 += rcpq * edot * w;
+        const double fx = kw * ex, fy = kw * ey, fz = kw * ez;
+        // ---- residual: 8 partial entries per lane, reduced over the 8 points by a halving butterfly; lane q keeps entry q
+        double rq;
+        {
+          double r4[4], r2[2];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const double lo = f0 * (2.0 * hxy[HexQ1::bx(j)][HexQ1::by(j)] * lz[0]) + fx * gx[j] + fy * gy[j] + fz * gz[j];
+            const double hi = f0 * (2.0 * hxy[HexQ1::bx(j + 4)][HexQ1::by(j + 4)] * lz[1]) + fx * gx[j + 4] + fy * gy[j + 4] + fz * gz[j + 4];
+            r4[j] = sel(b2, hi, lo) + shx(sel(b2, lo, hi), 4);
+          }
+#pragma unroll
+          for (int j = 0; j < 2; ++j) r2[j] = sel(b1, r4[j + 2], r4[j]) + shx(sel(b1, r4[j], r4[j + 2]), 2);
+          rq = sel(b0, r2[1], r2[0]) + shx(sel(b0, r2[0], r2[1]), 1);
+        }
+        // ---- element matrix: 40 slots (36 upper entries + 4 unused); stage 1 pairs slot j with slot 20 + j
+        const double kwa = kw * au;
+        const double mw = TRANSIENT ? rcpq * at * w : 0.0;
+        double a1[20];
+        // (written out pair by pair: the upper-triangle index arithmetic must be compile-time for gx / gy / gz to stay in registers)
+#define MRH_W8_NQ(S) (2.0 * hxy[HexQ1::bx(S)][HexQ1::by(S)] * lz[HexQ1::bz(S)])
+#define MRH_W8_P(I, J) (kwa * (gx[I] * gx[J] + gy[I] * gy[J] + gz[I] * gz[J]) + (TRANSIENT ? mw * MRH_W8_NQ(I) * MRH_W8_NQ(J) : 0.0))
+#define MRH_W8_PAIR(SLOT, PLO, PHI) { const double plo = PLO, phi = PHI; a1[SLOT] = sel(b2, phi, plo) + shx(sel(b2, plo, phi), 4); }
+        MRH_W8_PAIR(0, MRH_W8_P(0, 0), MRH_W8_P(2, 7))
+        MRH_W8_PAIR(1, MRH_W8_P(0, 1), MRH_W8_P(3, 3))
+        MRH_W8_PAIR(2, MRH_W8_P(0, 2), MRH_W8_P(3, 4))
+        MRH_W8_PAIR(3, MRH_W8_P(0, 3), MRH_W8_P(3, 5))
+        MRH_W8_PAIR(4, MRH_W8_P(0, 4), MRH_W8_P(3, 6))
+        MRH_W8_PAIR(5, MRH_W8_P(0, 5), MRH_W8_P(3, 7))
+        MRH_W8_PAIR(6, MRH_W8_P(0, 6), MRH_W8_P(4, 4))
+        MRH_W8_PAIR(7, MRH_W8_P(0, 7), MRH_W8_P(4, 5))
+        MRH_W8_PAIR(8, MRH_W8_P(1, 1), MRH_W8_P(4, 6))
+        MRH_W8_PAIR(9, MRH_W8_P(1, 2), MRH_W8_P(4, 7))
+        MRH_W8_PAIR(10, MRH_W8_P(1, 3), MRH_W8_P(5, 5))
+        MRH_W8_PAIR(11, MRH_W8_P(1, 4), MRH_W8_P(5, 6))
+        MRH_W8_PAIR(12, MRH_W8_P(1, 5), MRH_W8_P(5, 7))
+        MRH_W8_PAIR(13, MRH_W8_P(1, 6), MRH_W8_P(6, 6))
+        MRH_W8_PAIR(14, MRH_W8_P(1, 7), MRH_W8_P(6, 7))
+        MRH_W8_PAIR(15, MRH_W8_P(2, 2), MRH_W8_P(7, 7))
+        MRH_W8_PAIR(16, MRH_W8_P(2, 3), 0.0)
+        MRH_W8_PAIR(17, MRH_W8_P(2, 4), 0.0)
+        MRH_W8_PAIR(18, MRH_W8_P(2, 5), 0.0)
+        MRH_W8_PAIR(19, MRH_W8_P(2, 6), 0.0)
+#undef MRH_W8_PAIR
+#undef MRH_W8_P
+#undef MRH_W8_NQ
+        double a2[10];
+#pragma unroll
+        for (int j = 0; j < 10; ++j) a2[j] = sel(b1, a1[j + 10], a1[j]) + shx(sel(b1, a1[j], a1[j + 10]), 2);
+        double a3[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) a3[j] = sel(b0, a2[j + 5], a2[j]) + shx(sel(b0, a2[j], a2[j + 5]), 1);
+        if (eC >= 0) {
+#pragma unroll
+          for (int j = 0; j < 5; ++j) { const int k = 5 * q + j; if (k < NK) Kst[k * KST] = a3[j]; }
+          Kst[(NK + q) * KST] = -rq;
+        }
+      }
       if (pass == 7) { bar_arrive(BAR_FULL + b, 256); sq += NCG; }
       eC = eN; xC0 = xN0; xC1 = xN1; xC2 = xN2; uC = uN; dC = dN;
       eN = eN2; lidN = lidN2; ndN = ndN2; eN2 = eN3;

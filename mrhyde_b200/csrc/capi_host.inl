@@ -55,6 +55,58 @@ int mrh_build_brick(mrh_handle h, const int32_t* nxyz, const double* lo, const d
   MRH_TRY(h) h->host.buildBrick(nxyz, lo, hi); return MRH_OK; MRH_CATCH(h)
 }
 
+int mrh_build_brick_part(mrh_handle h, const int32_t* nxyz, const double* lo, const double* hi, const int32_t* procs, int32_t rank) {
+  if (!h || !nxyz || !lo || !hi || !procs) return MRH_EINVAL;
+  MRH_TRY(h) h->host.buildBrickPart(nxyz, lo, hi, procs, rank); return MRH_OK; MRH_CATCH(h)
+}
+int mrh_set_partition(mrh_handle h, const int64_t* gids, const int32_t* owner, int32_t rank, int32_t world) {
+  if (!h || !gids || !owner || world < 1 || rank < 0 || rank >= world) return MRH_EINVAL;
+  MRH_TRY(h) h->host.setPartition(gids, owner, rank, world); return MRH_OK; MRH_CATCH(h)
+}
+int mrh_get_partition(mrh_handle h, int64_t* gids, int32_t* owner) {
+  if (!h || h->host.part.gids.empty()) return MRH_EINVAL;
+  if (gids) memcpy(gids, h->host.part.gids.data(), h->host.part.gids.size() * sizeof(int64_t));
+  if (owner) memcpy(owner, h->host.part.owner.data(), h->host.part.owner.size() * sizeof(int));
+  return MRH_OK;
+}
+// exchange-plan metadata for a transport of the caller's choice (tests: gloo; mrh_comm_init moves it over NCCL itself)
+int64_t mrh_exchange_meta_size(mrh_handle h, int32_t peer) {
+  if (!h || !h->host.part.active()) return 0;
+  return (int64_t)h->host.plan.meta_for(peer, h->host.part, h->host.crs).size();
+}
+int mrh_exchange_meta_get(mrh_handle h, int32_t peer, int64_t* out) {
+  if (!h || !out || !h->host.part.active()) return MRH_EINVAL;
+  MRH_TRY(h)
+  const auto m = h->host.plan.meta_for(peer, h->host.part, h->host.crs);
+  memcpy(out, m.data(), m.size() * sizeof(int64_t));
+  return MRH_OK;
+  MRH_CATCH(h)
+}
+int mrh_exchange_meta_put(mrh_handle h, int32_t peer, const int64_t* in, int64_t n) {
+  if (!h || (n > 0 && !in) || !h->host.part.active()) return MRH_EINVAL;
+  MRH_TRY(h) h->host.plan.ingest(peer, in, n, h->host.part, h->host.crs); return MRH_OK; MRH_CATCH(h)
+}
+// which: 0 send rows, 1 send slots, 2 receive rows, 3 receive slots (-(k+1): ghost entry k) of `peer`; 4 / 5: ghost rows / ghost
+// column gids (peer ignored).  Returns the entry count; out may be NULL to query it.
+int64_t mrh_get_exchange_table(mrh_handle h, int32_t peer, int32_t which, int64_t* out) {
+  if (!h) return MRH_EINVAL;
+  const auto& P = h->host.plan;
+  std::vector<int64_t> v;
+  if (which == 4) v.assign(P.ghost_row.begin(), P.ghost_row.end());
+  else if (which == 5) v = P.ghost_colgid;
+  else {
+    const mrh::ExchangePlan::Peer* p = P.find(peer);
+    if (!p) return 0;
+    if (which == 0) v.assign(p->send_rows.begin(), p->send_rows.end());
+    else if (which == 1) v = p->send_slots;
+    else if (which == 2) v.assign(p->recv_rows.begin(), p->recv_rows.end());
+    else if (which == 3) v = p->recv_slots;
+    else return MRH_EINVAL;
+  }
+  if (out && !v.empty()) memcpy(out, v.data(), v.size() * sizeof(int64_t));
+  return (int64_t)v.size();
+}
+
 int mrh_set_mesh(mrh_handle h, const double* nodes, int64_t nnode, const int32_t* elem2node, int64_t nelem) {
   if (!h || !nodes || !elem2node || nnode <= 0 || nelem <= 0) return MRH_EINVAL;
   MRH_TRY(h)

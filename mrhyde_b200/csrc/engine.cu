@@ -38,6 +38,7 @@ struct DevBuf {
 };
 
 struct TabDev { DevBuf<double> B, G, VB, VG, W; };
+struct ExchangeDev;                    // exchange.inl
 
 struct DeviceImpl {
   int device = 0, num_sms = 148, max_smem_optin = 48 * 1024;
@@ -63,6 +64,8 @@ struct DeviceImpl {
   cudaStream_t copy_stream = nullptr;
   const char* last_path = "none";
   std::shared_ptr<void> solver;        // SolverWork (solver.inl), created at the first solve
+  ExchangeDev* xch = nullptr;          // NCCL communicator + interface exchange tables (exchange.inl), mrh_comm_init
+  int64_t iface_tiles = 0;             // leading tiles of the tile plan that touch DOFs owned by another rank (-1: no split)
   double* static_scratch = nullptr;    // device address of g_static_scratch on this handle's GPU (set at finalize)
 };
 
@@ -160,6 +163,19 @@ __global__ void fix_zero_rows_kernel(const int64_t* rowptr, const int* colind, i
   if (s < 1.0e-14) { const int d = rel_slot(rowptr, colind, (int)r, (int)r); if (d >= 0) jac[rowptr[r] + d] = 1.0; }
 }
 
+// identity rows of the Dirichlet projection system (setDirichlet, assemblyManager.cpp:1926-1943): non-fixed rows get a unit diagonal
+__global__ void projection_identity_kernel(const int64_t* rowptr, const int* colind, const uint8_t* fixed, int64_t nrows, double* mass) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= nrows || fixed[r]) return;
+  const int d = rel_slot(rowptr, colind, (int)r, (int)r);
+  if (d >= 0) mass[rowptr[r] + d] = 1.0;
+}
+// u[i] = x[i] on fixed DOFs (SolverManager::setDirichlet, solverManager.cpp:1919-1932)
+__global__ void copy_fixed_kernel(const uint8_t* fixed, const double* x, double* u, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && fixed[i]) u[i] = x[i];
+}
+
 inline unsigned blocks_for(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
 
 // ---- static scratch of the allocation-free entry point (mrh_assemble_res_host_static) --------------------------------
@@ -186,5 +202,6 @@ double* static_scratch_of(int device) {
 }  // namespace
 
 #include "engine_tiles.inl"
+#include "exchange.inl"
 #include "engine_launch.inl"
 #include "solver.inl"

@@ -10,6 +10,7 @@
 #include <memory>
 #include "../../include/mrhyde_b200.h"
 #include "brick.hpp"
+#include "partition.hpp"
 #include "expr.hpp"
 #include "params.h"
 #include "refdata.hpp"
@@ -37,6 +38,7 @@ class EngineHost {
   int phys = 0, dim = 3, order = 1, nvar = 1, nb = 8, nv = 8, N = 8;
   std::vector<std::string> varlist;
   HostMesh mesh; LocalLayout lay; HostDofs dofs; HostCrs crs; RefElement ref;
+  Partition part; ExchangePlan plan;       // multi-GPU: block partition and interface exchange (partition.hpp)
   bool have_mesh = false, have_dofs = false, have_crs = false, host_final = false;
   std::map<std::string, std::map<std::string, std::string>> dirichlet, weakd, neumann, flux;   // [var][side] -> expr
   std::vector<std::pair<std::string, std::string>> user_fns;    // name -> expr, first registration wins
@@ -46,6 +48,9 @@ class EngineHost {
   ExprCompiler ec;
   Prog vol_progs[MRH_MAXPROG];
   std::vector<SideLaunch> side_launches;
+  std::vector<SideLaunch> dirichlet_launches;       // sides with a strong Dirichlet variable: L2 projection of the data (setDirichlet)
+  Prog init_progs[MRH_MAXPROG];                     // "initial <var>" at "ip" (setInitial), slots VOL_INIT + var
+  std::string proj_unsupported;                     // non-empty: why the projection launches cannot run (state-dependent data)
 
   void configure(const mrh_config& c) {
     cfg = c; physics = c.physics ? c.physics : "";
@@ -72,6 +77,20 @@ class EngineHost {
     build_brick_dofs(dofs, mesh, lay, nvar); have_dofs = true;
     build_crs(crs, dofs.lids.data(), mesh.nelem, N, dofs.nlocal, nvar); have_crs = true;
     host_final = false;
+  }
+
+  // block `rank` of a procs[0] x procs[1] x procs[2] decomposition of the global brick (meshInterface.cpp:140-155 X/Y/Z Procs)
+  void buildBrickPart(const int* nxyz, const double* lo, const double* hi, const int* procs, int rank) {
+    build_brick_part(mesh, dofs, crs, part, lay, dim, nvar, nxyz, lo, hi, procs, rank);
+    have_mesh = have_dofs = have_crs = true; host_final = false;
+    plan.build_send(part, crs);
+  }
+  void setPartition(const int64_t* gids, const int* owner, int rank, int world) {
+    if (!have_dofs || !have_crs) throw std::runtime_error("dofmap and CRS graph must be set before the partition");
+    part.rank = rank; part.world = world;
+    part.gids.assign(gids, gids + dofs.nlocal); part.owner.assign(owner, owner + dofs.nlocal);
+    for (int o : part.owner) if (o < 0 || o >= world) throw std::runtime_error("owner rank out of range");
+    plan.build_send(part, crs);
   }
 
   void addUserFunction(const std::string& name, const std::string& expr, const std::string& location) {
@@ -148,6 +167,27 @@ class EngineHost {
       } else L.active = false;
       side_launches.push_back(L);
     }
+    // L2-projection launches: strong Dirichlet data per side, initial data over the volume.  The functions are registered by
+    // PhysicsInterface under the names "Dirichlet <var> <side>" / "initial <var>" (physicsInterface.cpp:156-478)
+    dirichlet_launches.clear(); proj_unsupported.clear();
+    for (int s = 0; s < nsides && cfg.use_strong_dbc; ++s) {
+      SideLaunch L; L.side = s; L.local_side = mesh.sides[s].local_side;
+      for (auto& p : L.progs) p = zero;
+      for (int j = 0; j < nvar; ++j) {
+        L.bc[j] = var_bcs[j][s];
+        if (L.bc[j] != MRH_BC_DIRICHLET) continue;
+        L.active = true;
+        L.progs[SIDE_BCSRC + j] = ec.compile("Dirichlet " + varlist[j] + " " + mesh.sides[s].name, "side ip");
+        if (L.progs[SIDE_BCSRC + j].kind == 2) proj_unsupported = "Dirichlet data that depends on the solution is not supported";
+      }
+      if (L.active && !mesh.sides[s].elems.empty()) dirichlet_launches.push_back(L);
+    }
+    for (auto& p : init_progs) p = zero;
+    for (int j = 0; j < nvar; ++j) {
+      if (!ec.has("initial " + varlist[j], "ip")) continue;       // no initial condition given: zero
+      init_progs[VOL_INIT + j] = ec.compile("initial " + varlist[j], "ip");
+      if (init_progs[VOL_INIT + j].kind == 2) proj_unsupported = "initial data that depends on the solution is not supported";
+    }
     if (ec.code.empty()) ec.code.push_back({(uint8_t)OP_CONST, 0, 0});
     if (ec.cpool.empty()) ec.cpool.push_back(0.0);
     host_final = true;
@@ -195,8 +235,29 @@ class EngineHost {
     }
   }
 
+  // projection launch: which < 0 the volume (initial data), otherwise index into dirichlet_launches
+  void fillProjectionParams(KParams& kp, const BasePtrs& bp, double time, double* rhs, double* mass, int which, const int* side_elems_ptr) const {
+    memset(&kp, 0, sizeof(kp));
+    kp.nodes = bp.nodes; kp.e2n = bp.e2n; kp.lids = bp.lids; kp.fixed = bp.fixed; kp.rowptr = bp.rowptr;
+    kp.pat = bp.pat; kp.pat_id = bp.pat_id; kp.code = bp.code; kp.cpool = bp.cpool;
+    kp.res = rhs; kp.jac = mass; kp.compute_jac = mass ? 1 : 0; kp.lump_mass = cfg.lump_mass;
+    kp.tp.time = time; kp.tp.dt = 1.0; kp.tp.alpha_u = 1.0;
+    for (int i = 0; i < nvar * nb; ++i) kp.offsets[i] = dofs.offsets[i];
+    if (which < 0) {
+      kp.ph.proj = PROJ_INITIAL; kp.is_side = 0; kp.elem_list = nullptr; kp.nwork = mesh.nelem;
+      for (int i = 0; i < MRH_MAXPROG; ++i) kp.progs[i] = init_progs[i];
+      kp.tab = bp.vol_tab;
+    } else {
+      const SideLaunch& L = dirichlet_launches[which];
+      kp.ph.proj = PROJ_DIRICHLET; kp.is_side = 1; kp.elem_list = side_elems_ptr; kp.nwork = (int64_t)mesh.sides[L.side].elems.size();
+      for (int i = 0; i < MRH_MAXPROG; ++i) kp.progs[i] = L.progs[i];
+      for (int j = 0; j < 4; ++j) kp.ph.bc[j] = L.bc[j];
+      kp.tab = bp.side_tab[L.local_side];
+    }
+  }
+
   // element order of the tile-staged scatter: 8x4x4-element bricks on the structured mesh, identity otherwise
-  std::vector<int> tileOrder() const {
+  std::vector<int> tileOrder(int64_t* iface_tiles = nullptr) const {
     std::vector<int> perm; perm.reserve((size_t)mesh.nelem);
     const int nx = mesh.NXYZ[0], ny = mesh.NXYZ[1], nz = mesh.NXYZ[2];
     if (dim == 3 && nx > 0 && (int64_t)nx * ny * nz == mesh.nelem) {
@@ -205,6 +266,27 @@ class EngineHost {
         for (int k = K; k < std::min(K + bz, nz); ++k) for (int j = J; j < std::min(J + by, ny); ++j) for (int i = I; i < std::min(I + bx, nx); ++i)
           perm.push_back((int)(i + (int64_t)nx * (j + (int64_t)ny * k)));
     } else for (int64_t e = 0; e < mesh.nelem; ++e) perm.push_back((int)e);
+    int64_t niface = 0;
+    if (part.active()) {
+      // tiles (128 consecutive entries) holding an element with a DOF owned elsewhere go first: their rows are complete - and
+      // can be sent - while the interior is still being assembled.  A ragged last tile stays last; when it is an
+      // interface tile itself no split is possible (niface = -1: the exchange then follows the whole launch).
+      const int64_t nt = ((int64_t)perm.size() + 127) / 128;
+      const bool ragged = (perm.size() % 128) != 0;
+      std::vector<char> flag((size_t)nt, 0);
+      for (int64_t k = 0; k < (int64_t)perm.size(); ++k) {
+        const int* l = &dofs.lids[(size_t)perm[k] * N];
+        for (int i = 0; i < N; ++i) if (part.owner[l[i]] != part.rank) { flag[k / 128] = 1; break; }
+      }
+      std::vector<int> out; out.reserve(perm.size());
+      auto put = [&](int64_t t) { out.insert(out.end(), perm.begin() + t * 128, perm.begin() + std::min<int64_t>((t + 1) * 128, (int64_t)perm.size())); };
+      const int64_t nfull = ragged ? nt - 1 : nt;
+      for (int64_t t = 0; t < nfull; ++t) if (flag[t]) { put(t); ++niface; }
+      for (int64_t t = 0; t < nfull; ++t) if (!flag[t]) put(t);
+      if (ragged) { put(nt - 1); if (flag[nt - 1]) niface = -1; }
+      perm.swap(out);
+    }
+    if (iface_tiles) *iface_tiles = niface;
     return perm;
   }
 

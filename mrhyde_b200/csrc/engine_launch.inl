@@ -1,5 +1,13 @@
 // Part of engine.cu: device set-up, launch logic and the GPU-side C-ABI entry points.
 
+constexpr int XCH_RESERVE_SMS = 4;     // SMs the interior launch leaves free for the exchange kernels when it overlaps them
+#if !defined(MRH_WSK_DEFAULT)
+#define MRH_WSK_DEFAULT 0      // K-in-registers thermal kernel: MRH_WSK=1 enables it
+#endif
+#if !defined(MRH_WS8_DEFAULT)
+#define MRH_WS8_DEFAULT 0      // lane-per-point thermal kernel off until it is measured faster (MRH_WS8=1 enables it)
+#endif
+
 namespace {
 
 RefTab upload_tab(TabDev& D, const PointTables& T) {
@@ -55,7 +63,7 @@ void device_finalize(mrh_engine* h) {
   if (!D.tiles) D.tiles = new TileDev();
   D.tiles->release();
   if (!(H.cfg.flags & 5) && thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
-    const std::string why = build_tile_plan(H.tileOrder(), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p,
+    const std::string why = build_tile_plan(H.tileOrder(&D.iface_tiles), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p,
                                             H.cfg.include_advection ? 64 : 36, *D.tiles);
     if (!D.tiles->ok) h->err = "tile-staged scatter unavailable (" + why + "), using direct scatter";
   }
@@ -106,6 +114,7 @@ void device_finalize(mrh_engine* h) {
   D.bp.nodes = D.nodes.p; D.bp.e2n = D.e2n.p; D.bp.lids = D.lids.p; D.bp.fixed = D.fixed.p; D.bp.rowptr = D.rowptr.p;
   D.bp.pat = D.pat.p; D.bp.pat_id = D.pat_id.p; D.bp.code = D.code.p; D.bp.cpool = D.cpool.p;
   if (!D.ev0) { CUDA_CK(cudaEventCreate(&D.ev0)); CUDA_CK(cudaEventCreate(&D.ev1)); }
+  if (D.xch && H.plan.complete) exchange_upload(H, *D.xch);
   D.static_scratch = static_scratch_of(D.device);      // set-up time, this handle's device current (cudaSetDevice above)
   D.ready = true;
 }
@@ -193,6 +202,16 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
   CUDA_CK(cudaSetDevice(D.device));
   cudaStream_t stream = (cudaStream_t)st->stream;
   D.launches = 0;
+  // multi-GPU: with a communicator attached the call also folds the rows of DOFs owned by another rank onto their owner
+  // (exportVector/MatrixFromOverlapped); flag bit 7 leaves that to an explicit mrh_exchange
+  const bool xfuse = D.xch && D.xch->ready && !(H.cfg.flags & 128) && !hc;
+  bool exchanged = false, dbc_first = false, any_side_launch = false;
+  for (auto& sl : H.side_launches) any_side_launch = any_side_launch || sl.active;
+  if (xfuse && jac) {          // fixed rows are never scattered into: their unit diagonal can be written first, so that it travels with the rows
+    const int64_t nd = (int64_t)H.dbc_dofs.size();
+    if (nd > 0) { dbc_diag_kernel<<<blocks_for(nd, 256), 256, 0, stream>>>(D.dbc_slots.p, nd, jac); CUDA_CK(cudaGetLastError()); D.launches++; }
+    dbc_first = true;
+  }
   for (int side = -1; side < (int)H.side_launches.size(); ++side) {
     if (side >= 0 && !H.side_launches[side].active) continue;
     KParams kp;
@@ -233,18 +252,37 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
       const size_t ws_bytes = !tiled ? 0 : adv ? ThermalHexQ1<false, true, true>::ws_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r)
                                                : ThermalHexQ1<false, false, true>::ws_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r);
       const bool ws = tiled && jk && jk->fn_ws && !(H.cfg.flags & 8) && ws_bytes <= (size_t)D.max_smem_optin;
+      // lane-per-point variant (tiled_ws8): symmetric element matrix only; flag bit 6 or MRH_WS8=0 switch it off
+      const int ncg8 = D.jit.ws8_ncg;
+      const size_t ws8_bytes = (!tiled || adv) ? 0 : tr ? ThermalHexQ1<true, false, true>::ws8_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r, ncg8)
+                                                        : ThermalHexQ1<false, false, true>::ws8_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r, ncg8);
+      static const int ws8_env = [] { const char* ev = getenv("MRH_WS8"); return ev ? atoi(ev) : MRH_WS8_DEFAULT; }();
+      const bool ws8 = ws && !adv && jk->fn_ws8 && !(H.cfg.flags & 64) && ws8_env != 0 && ws8_bytes <= (size_t)D.max_smem_optin;
+      // K-in-registers variant (tiled_wsk): MRH_WSK=1 / default per MRH_WSK_DEFAULT
+      const size_t wsk_bytes = !tiled ? 0 : adv ? (tr ? ThermalHexQ1<true, true, true>::wsk_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r)
+                                                      : ThermalHexQ1<false, true, true>::wsk_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r))
+                                                : (tr ? ThermalHexQ1<true, false, true>::wsk_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r)
+                                                      : ThermalHexQ1<false, false, true>::wsk_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r));
+      static const int wsk_env = [] { const char* ev = getenv("MRH_WSK"); return ev ? atoi(ev) : MRH_WSK_DEFAULT; }();
+      const bool wsk = ws && !ws8 && jk->fn_wsk && wsk_env != 0 && wsk_bytes <= (size_t)D.max_smem_optin;
       if (ws) {
         JitApi& api = JitApi::get();
-        if (jk->ws_smem_set != ws_bytes) {
-          if (api.FuncSetAttribute(jk->fn_ws, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)ws_bytes) != CUDA_SUCCESS)
+        const CUfunction fnk = ws8 ? jk->fn_ws8 : wsk ? jk->fn_wsk : jk->fn_ws;
+        const size_t kbytes = ws8 ? ws8_bytes : wsk ? wsk_bytes : ws_bytes;
+        const int ncg = ws8 ? ncg8 : 2, kthreads = ws8 ? 128 * (1 + ncg8) : 384;
+        size_t& set_bytes = ws8 ? jk->ws8_smem_set : wsk ? jk->wsk_smem_set : jk->ws_smem_set;
+        if (set_bytes != kbytes) {
+          if (api.FuncSetAttribute(fnk, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)kbytes) != CUDA_SUCCESS)
             throw std::runtime_error("CUDA error: cuFuncSetAttribute(shared memory) failed");
-          jk->ws_smem_set = ws_bytes;
+          set_bytes = kbytes;
         }
-        D.last_path = "nvrtc-specialised+tiled-ws";
-        bool any_side = false;
-        for (auto& sl : H.side_launches) any_side = any_side || sl.active;
+        D.last_path = ws8 ? "nvrtc-specialised+tiled-ws8" : wsk ? "nvrtc-specialised+tiled-wsk" : "nvrtc-specialised+tiled-ws";
+        const bool any_side = any_side_launch;
         const bool chunked = hc && !any_side && !H.cfg.fix_zero_rows && D.chunk_tile_end.size() > 1;
-        const size_t nchunk = chunked ? D.chunk_tile_end.size() : 1;
+        // interface tiles first, their rows leave on the exchange stream while the interior tiles are assembled; the interior
+        // launch leaves XCH_RESERVE_SMS SMs to the pack / NCCL / unpack kernels (a persistent CTA fills a whole SM)
+        const bool overlap = xfuse && !any_side && D.iface_tiles > 0 && D.iface_tiles < D.tiles->ntiles;
+        const size_t nchunk = chunked ? D.chunk_tile_end.size() : overlap ? 2 : 1;
         if (chunked) {            // fixed rows are never scattered into: their unit diagonal can be written first
           const int64_t nd = (int64_t)H.dbc_dofs.size();
           if (nd > 0) { dbc_diag_kernel<<<blocks_for(nd, 256), 256, 0, stream>>>(D.dbc_slots.p, nd, jac); CUDA_CK(cudaGetLastError()); D.launches++; }
@@ -252,11 +290,12 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
         }
         int64_t tb = 0, vb = 0;
         for (size_t c = 0; c < nchunk; ++c) {
-          const int64_t te = chunked ? D.chunk_tile_end[c] : D.tiles->ntiles;
+          const int64_t te = chunked ? D.chunk_tile_end[c] : (overlap && c == 0) ? D.iface_tiles : D.tiles->ntiles;
           kp.tile.tile_begin = tb; kp.tile.tile_end = te;
-          const unsigned grid = (unsigned)std::min<int64_t>((te - tb + 1) / 2, (int64_t)D.num_sms);
+          const int64_t sms = (overlap && c == 1) ? std::max(1, D.num_sms - XCH_RESERVE_SMS) : D.num_sms;
+          const unsigned grid = (unsigned)std::min<int64_t>((te - tb + ncg - 1) / ncg, sms);
           void* args[] = {(void*)&kp};
-          if (grid > 0 && api.LaunchKernel(jk->fn_ws, grid, 1, 1, 384, 1, 1, (unsigned)ws_bytes, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+          if (grid > 0 && api.LaunchKernel(fnk, grid, 1, 1, kthreads, 1, 1, (unsigned)kbytes, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
             throw std::runtime_error("CUDA error: cuLaunchKernel failed for the warp-specialised NVRTC kernel");
           if (chunked) {
             const int64_t ve = D.chunk_val_end[c];
@@ -265,6 +304,15 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
             if (ve > vb) CUDA_CK(cudaMemcpyAsync(hc->jac_host + vb, jac + vb, (size_t)(ve - vb) * sizeof(double), cudaMemcpyDeviceToHost, D.copy_stream));
             vb = ve;
             if (c > 0) D.launches++;
+          }
+          if (overlap && c == 0) {
+            ExchangeDev& X = *D.xch;
+            CUDA_CK(cudaEventRecord(X.ev_iface, stream));
+            CUDA_CK(cudaStreamWaitEvent(X.xstream, X.ev_iface, 0));
+            exchange_run(D, X, res, jac, X.xstream);
+            CUDA_CK(cudaEventRecord(X.ev_done, X.xstream));
+            D.launches += X.launches + 1;
+            exchanged = true;
           }
           tb = te;
         }
@@ -333,14 +381,51 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
     if (side < 0) CUDA_CK(cudaEventRecord(D.ev1, stream));
     D.launches++;
   }
+  if (xfuse) {
+    if (exchanged) CUDA_CK(cudaStreamWaitEvent(stream, D.xch->ev_done, 0));
+    else { exchange_run(D, *D.xch, res, jac, stream); D.launches += D.xch->launches; }
+  }
   if (jac && !(hc && hc->used)) {
     const int64_t nd = (int64_t)H.dbc_dofs.size();
-    if (nd > 0) { dbc_diag_kernel<<<blocks_for(nd, 256), 256, 0, stream>>>(D.dbc_slots.p, nd, jac); CUDA_CK(cudaGetLastError()); D.launches++; }
+    if (nd > 0 && !dbc_first) { dbc_diag_kernel<<<blocks_for(nd, 256), 256, 0, stream>>>(D.dbc_slots.p, nd, jac); CUDA_CK(cudaGetLastError()); D.launches++; }
     if (H.cfg.fix_zero_rows) {
       fix_zero_rows_kernel<<<blocks_for(H.crs.nrows, 256), 256, 0, stream>>>(D.rowptr.p, D.colind.p, H.crs.nrows, jac);
       CUDA_CK(cudaGetLastError()); D.launches++;
     }
   }
+  return MRH_OK;
+}
+
+// L2-projection systems: kind 0 = strong Dirichlet data on the fixed DOFs (setDirichlet), 1 = initial data
+// (setInitial).  rhs (nlocal) and mass (nnz) are accumulated into; the caller zeroes them.
+int device_projection(mrh_engine* h, int kind, double time, double* rhs, double* mass, cudaStream_t stream) {
+  EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
+  if (!D.ready) throw std::runtime_error("mrh_finalize has not been called");
+  if (!H.proj_unsupported.empty()) throw std::runtime_error(H.proj_unsupported + " (not supported)");
+  CUDA_CK(cudaSetDevice(D.device));
+  D.launches = 0;
+  if (kind == 0) {
+    for (size_t k = 0; k < H.dirichlet_launches.size(); ++k) {
+      KParams kp;
+      H.fillProjectionParams(kp, D.bp, time, rhs, mass, (int)k, D.side_elems[H.dirichlet_launches[k].side]->p);
+      if (!launch_generic_projection(H.phys, H.dim, H.order, D.num_sms, kp, (void*)stream)) throw std::runtime_error("configuration not supported: no kernel for this physics/dimension/order");
+      D.launches++;
+    }
+    if (mass) {
+      projection_identity_kernel<<<blocks_for(H.crs.nrows, 256), 256, 0, stream>>>(D.rowptr.p, D.colind.p, D.fixed.p, H.crs.nrows, mass);
+      CUDA_CK(cudaGetLastError()); D.launches++;
+    }
+  } else {
+    KParams kp;
+    H.fillProjectionParams(kp, D.bp, time, rhs, mass, -1, nullptr);
+    if (!launch_generic_projection(H.phys, H.dim, H.order, D.num_sms, kp, (void*)stream)) throw std::runtime_error("configuration not supported: no kernel for this physics/dimension/order");
+    D.launches++;
+    if (mass) {            // setInitial always fixes zero rows (assemblyManager.cpp:1286-1306)
+      fix_zero_rows_kernel<<<blocks_for(H.crs.nrows, 256), 256, 0, stream>>>(D.rowptr.p, D.colind.p, H.crs.nrows, mass);
+      CUDA_CK(cudaGetLastError()); D.launches++;
+    }
+  }
+  D.last_path = "projection";
   return MRH_OK;
 }
 
@@ -395,6 +480,7 @@ static void backend_destroy(mrh_engine* h) {
   for (cudaEvent_t e : D->chunk_ev) cudaEventDestroy(e);
   if (D->copy_stream) cudaStreamDestroy(D->copy_stream);
   delete D->tiles;
+  delete D->xch;
   delete D;
 }
 
@@ -483,6 +569,66 @@ int mrh_assemble_res_host_static(mrh_handle h, const mrh_state* st_host, double*
   CUDA_CK(cudaStreamSynchronize(s));
   return rc;
   MRH_CATCH_CUDA(h)
+}
+int mrh_assemble_projection(mrh_handle h, int32_t kind, double time, double* rhs, double* mass, void* stream) {
+  if (!h || !rhs || (kind != 0 && kind != 1)) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h) return device_projection(h, kind, time, rhs, mass, (cudaStream_t)stream); MRH_CATCH_CUDA(h)
+}
+// ---- multi-GPU (exchange.inl) ---------------------------------------------------------------------------------------------
+int mrh_comm_unique_id(void* id128) {
+  if (!id128) return MRH_EINVAL;
+  NcclApi& N = NcclApi::get();
+  if (!N.ok) return MRH_ECUDA;
+  ncclUniqueId id;
+  if (N.GetUniqueId(&id) != ncclSuccess) return MRH_ECUDA;
+  static_assert(sizeof(ncclUniqueId) == 128, "NCCL unique id size");
+  memcpy(id128, &id, 128);
+  return MRH_OK;
+}
+int mrh_comm_init(mrh_handle h, const void* id128, int32_t rank, int32_t world) {
+  if (!h || !id128 || world < 1 || rank < 0 || rank >= world) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h)
+  EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
+  NcclApi& N = NcclApi::get();
+  if (!N.ok) throw std::runtime_error("CUDA error: NCCL unavailable: " + N.why);
+  if (!H.part.active() || H.part.rank != rank || H.part.world != world)
+    throw std::runtime_error("mrh_comm_init: set the partition first (mrh_build_brick_part or mrh_set_partition) with the same rank / world");
+  CUDA_CK(cudaSetDevice(D.device));
+  delete D.xch; D.xch = new ExchangeDev();
+  D.xch->rank = rank; D.xch->world = world;
+  ncclUniqueId id; memcpy(&id, id128, 128);
+  NCCL_CK(N.CommInitRank(&D.xch->comm, world, id, rank));
+  H.plan.build_send(H.part, H.crs);
+  exchange_meta_over_nccl(H, *D.xch);
+  if (D.ready) exchange_upload(H, *D.xch);          // otherwise mrh_finalize uploads the tables
+  return MRH_OK;
+  MRH_CATCH_CUDA(h)
+}
+int mrh_exchange(mrh_handle h, double* res, double* jac, void* stream) {
+  if (!h || !res) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h)
+  DeviceImpl& D = *(DeviceImpl*)h->impl;
+  if (!D.xch || !D.xch->ready) throw std::runtime_error("mrh_exchange: no communicator attached (mrh_comm_init) or mrh_finalize not called");
+  CUDA_CK(cudaSetDevice(D.device));
+  exchange_run(D, *D.xch, res, jac, (cudaStream_t)stream);
+  return MRH_OK;
+  MRH_CATCH_CUDA(h)
+}
+int64_t mrh_get_ghost_block(mrh_handle h, int32_t* rows, int64_t* col_gids, double* values_host) {
+  if (!h) return MRH_EINVAL;
+  const auto& P = h->host.plan;
+  const int64_t n = (int64_t)P.ghost_row.size();
+  if (rows) memcpy(rows, P.ghost_row.data(), n * sizeof(int));
+  if (col_gids) memcpy(col_gids, P.ghost_colgid.data(), n * sizeof(int64_t));
+  if (values_host && n > 0) {
+    auto* D = (DeviceImpl*)h->impl;
+    if (!D || !D->xch || !D->xch->ready) return MRH_EINVAL;
+    if (cudaMemcpy(values_host, D->xch->ghost.p, n * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return MRH_ECUDA;
+  }
+  return n;
 }
 const char* mrh_last_kernel_path(mrh_handle h) {
   if (!h || !h->impl) return "none";

@@ -151,7 +151,7 @@ inline std::string jit_function_source(const std::string& name, const Prog& pr, 
 
 // One NVRTC-compiled module holding the specialised thermal kernel for one (TRANSIENT, ADV, JAC) variant.
 struct JitKernel {
-  CUmodule mod = nullptr; CUfunction fn = nullptr, fn_ws = nullptr; size_t ws_smem_set = 0; int blocks_per_sm = 1, tiled_blocks_per_sm = 1; size_t smem_set = 0; std::string source, log;
+  CUmodule mod = nullptr; CUfunction fn = nullptr, fn_ws = nullptr, fn_ws8 = nullptr, fn_wsk = nullptr; size_t ws_smem_set = 0, ws8_smem_set = 0, wsk_smem_set = 0; int blocks_per_sm = 1, tiled_blocks_per_sm = 1; size_t smem_set = 0; std::string source, log;
 };
 
 class JitCache {
@@ -195,6 +195,14 @@ class JitCache {
       K.source += std::string("extern \"C\" __global__ void __launch_bounds__(384, 1) mrh_jit_thermal_hex_q1_ws(const __grid_constant__ mrh::KParams kp) {\n") +
           "  typedef mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", true, mrh::JitCoefs> Kern;\n"
           "  extern __shared__ double dsm[];\n  Kern::tiled_ws(kp, dsm);\n}\n";
+    if (jac)          // K-in-registers variant (assemble_fast.h tiled_wsk)
+      K.source += std::string("extern \"C\" __global__ void __launch_bounds__(384, 1) mrh_jit_thermal_hex_q1_wsk(const __grid_constant__ mrh::KParams kp) {\n") +
+          "  typedef mrh::ThermalHexQ1<" + B(transient) + ", " + B(adv) + ", true, mrh::JitCoefs> Kern;\n"
+          "  extern __shared__ double dsm[];\n  Kern::tiled_wsk(kp, dsm);\n}\n";
+    if (jac && !adv)  // lane-per-point variant: 128 (1 + MRH_WS8_NCG) threads, one CTA per SM (assemble_fast.h tiled_ws8)
+      K.source += std::string("extern \"C\" __global__ void __launch_bounds__(128 * (1 + MRH_WS8_NCG), 1) mrh_jit_thermal_hex_q1_ws8(const __grid_constant__ mrh::KParams kp) {\n") +
+          "  typedef mrh::ThermalHexQ1<" + B(transient) + ", false, true, mrh::JitCoefs> Kern;\n"
+          "  extern __shared__ double dsm[];\n  Kern::tiled_ws8(kp, dsm);\n}\n";
     }
     std::vector<const char*> hdr_src, hdr_name;
     for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
@@ -207,8 +215,19 @@ class JitCache {
     std::string creg = "-DMRH_WS_CREG=200", sreg = "-DMRH_WS_SREG=96";                              // 256 * CREG + 128 * SREG <= 384 * 168
     if (const char* ev = getenv("MRH_WS_CREG")) creg = std::string("-DMRH_WS_CREG=") + ev;
     if (const char* ev = getenv("MRH_WS_SREG")) sreg = std::string("-DMRH_WS_SREG=") + ev;
-    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", minb.c_str(), extra.c_str(), creg.c_str(), sreg.c_str()};
-    const nvrtcResult rc = api.CompileProgram(prog, 8, opts);
+    ws8_ncg = 3;                                                                                    // compute warpgroups of the lane-per-point kernel
+    if (const char* ev = getenv("MRH_WS8_NCG")) ws8_ncg = std::max(1, std::min(3, atoi(ev)));
+    std::string ncg8 = "-DMRH_WS8_NCG=" + std::to_string(ws8_ncg);
+    // register budgets: 128 SREG + 128 NCG CREG <= 65536 / 1 CTA
+    std::string creg8 = std::string("-DMRH_WS8_CREG=") + (ws8_ncg == 3 ? "136" : ws8_ncg == 2 ? "200" : "232"), sreg8 = "-DMRH_WS8_SREG=96";
+    if (const char* ev = getenv("MRH_WS8_CREG")) creg8 = std::string("-DMRH_WS8_CREG=") + ev;
+    if (const char* ev = getenv("MRH_WS8_SREG")) sreg8 = std::string("-DMRH_WS8_SREG=") + ev;
+    std::string cregk = "-DMRH_WSK_CREG=216", sregk = "-DMRH_WSK_SREG=80";                          // 256 * 216 + 128 * 80 = 65536
+    if (const char* ev = getenv("MRH_WSK_CREG")) cregk = std::string("-DMRH_WSK_CREG=") + ev;
+    if (const char* ev = getenv("MRH_WSK_SREG")) sregk = std::string("-DMRH_WSK_SREG=") + ev;
+    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", minb.c_str(), extra.c_str(), creg.c_str(), sreg.c_str(),
+                          ncg8.c_str(), creg8.c_str(), sreg8.c_str(), cregk.c_str(), sregk.c_str()};
+    const nvrtcResult rc = api.CompileProgram(prog, 13, opts);
     size_t ls = 0; api.GetProgramLogSize(prog, &ls);
     if (ls > 1) { K.log.resize(ls); api.GetProgramLog(prog, &K.log[0]); }
     if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + K.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }
@@ -220,6 +239,8 @@ class JitCache {
     if (api.ModuleGetFunction(&K.fn, K.mod, "mrh_jit_thermal_hex_q1") != CUDA_SUCCESS) { last_error = "kernel symbol not found"; K.fn = nullptr; return nullptr; }
     if (api.OccupancyMaxActiveBlocks(&K.blocks_per_sm, K.fn, 128, 0) != CUDA_SUCCESS || K.blocks_per_sm < 1) K.blocks_per_sm = 1;
     if (!jac || dim_ == 2 || api.ModuleGetFunction(&K.fn_ws, K.mod, "mrh_jit_thermal_hex_q1_ws") != CUDA_SUCCESS) K.fn_ws = nullptr;
+    if (!jac || dim_ == 2 || api.ModuleGetFunction(&K.fn_wsk, K.mod, "mrh_jit_thermal_hex_q1_wsk") != CUDA_SUCCESS) K.fn_wsk = nullptr;
+    if (!jac || adv || dim_ == 2 || api.ModuleGetFunction(&K.fn_ws8, K.mod, "mrh_jit_thermal_hex_q1_ws8") != CUDA_SUCCESS) K.fn_ws8 = nullptr;
     return &K;
   }
 
@@ -270,6 +291,7 @@ class JitCache {
   std::string bat_bounds_ = "-DMRH_BAT_BOUNDS=192";
  public:
   int bat_max_threads = 192;
+  int ws8_ncg = 3;
  private:
   bool bat_tried_ = false;
   std::map<int, JitKernel> kernels_;

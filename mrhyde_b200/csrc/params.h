@@ -16,6 +16,8 @@ enum { CDR_SOURCE = 0, CDR_DIFF, CDR_CP, CDR_RHO, CDR_REACTION, CDR_XVEL, CDR_YV
 enum { LE_LAMBDA = 0, LE_MU, LE_SRC0, LE_SRC1, LE_SRC2 };
 enum { NS_SRC_UX = 0, NS_SRC_PR, NS_SRC_UY, NS_SRC_UZ, NS_DENSITY, NS_VISCOSITY };
 enum { SIDE_DIFF = 0, SIDE_LAMBDA = 0, SIDE_MU = 1, SIDE_BCSRC = 8, SIDE_FLUX = 12 };     // "side ip"
+enum { VOL_INIT = 8 };                                                                   // "initial <var>" at "ip" (projection launches)
+enum { PROJ_NONE = 0, PROJ_DIRICHLET = 1, PROJ_INITIAL = 2 };
 
 struct RefTab {          // reference-element tables of one point set (volume rule, or the rule of one local side)
   const double* B;       // [nq][NB]       field basis values
@@ -41,6 +43,8 @@ struct PhysParams {
   int bc[4];             // BC code per variable on the current side
   double formparam;      // thermal/LE "form_param"
   double le_penalty;     // LE "penalty"
+  int proj;              // L2-projection launch (assemble.h projection): PROJ_DIRICHLET on a side set, PROJ_INITIAL over the volume
+  int pad_;
 };
 
 struct TilePlan {          // tile-staged scatter of the specialised kernels (built at finalize, engine_tiles.inl)

@@ -380,7 +380,56 @@ int transient_solve(mrh_engine* h, double* u, double t0, double t1, double dt, c
 
 }  // namespace
 
+namespace {
+// SolverManager::projectDirichlet + setDirichlet (kind 0) / setInitial (kind 1): assemble the L2-projection system into the caller's
+// work arrays, solve it with conjugate gradients (it is a mass matrix plus identity rows) and put the result into u - on the fixed
+// DOFs only for Dirichlet data, everywhere for initial data.
+int project_into(mrh_engine* h, int kind, double time, double* u, double* rhs, double* mass, const mrh_solver_opts& o_in, mrh_solver_info& info, cudaStream_t s) {
+  EngineHost& H = h->host; DeviceImpl& D = *(DeviceImpl*)h->impl;
+  const int64_t n = H.crs.nrows; const size_t nnz = H.crs.colind.size();
+  CUDA_CK(cudaSetDevice(D.device));
+  CUDA_CK(cudaMemsetAsync(rhs, 0, n * sizeof(double), s));
+  CUDA_CK(cudaMemsetAsync(mass, 0, nnz * sizeof(double), s));
+  device_projection(h, kind, time, rhs, mass, s);
+  mrh_solver_opts o = o_in; o.linear_method = 1;
+  SolverWork& W = solver_work(D);
+  W.ensure(n, 1);
+  double relres = 0.0;
+  info = mrh_solver_info{};
+  info.linear_iters = linear_solve(h, mass, rhs, W.du.p, o, s, &relres);
+  info.last_linear_relres = relres; info.converged = relres <= o.linear_tol;
+  if (kind == 0) copy_fixed_kernel<<<blocks_for(n, 256), 256, 0, s>>>(D.fixed.p, W.du.p, u, n);
+  else CUDA_CK(cudaMemcpyAsync(u, W.du.p, n * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  CUDA_CK(cudaGetLastError());
+  CUDA_CK(cudaStreamSynchronize(s));
+  return info.converged ? 0 : 1;
+}
+}  // namespace
+
 extern "C" {
+
+int mrh_set_dirichlet(mrh_handle h, double* u, double time, double* rhs_work, double* mass_work, const mrh_solver_opts* opts, mrh_solver_info* info, void* stream) {
+  if (!h || !u || !rhs_work || !mass_work) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h)
+  mrh_solver_opts o; if (opts) o = *opts; else { mrh_default_solver_opts(&o); o.linear_tol = 1.0e-12; o.max_linear_iters = 1000; }
+  mrh_solver_info si{};
+  const int rc = project_into(h, 0, time, u, rhs_work, mass_work, o, si, (cudaStream_t)stream);
+  if (info) *info = si;
+  return rc;
+  MRH_CATCH_CUDA(h)
+}
+int mrh_set_initial(mrh_handle h, double* u, double* rhs_work, double* mass_work, const mrh_solver_opts* opts, mrh_solver_info* info, void* stream) {
+  if (!h || !u || !rhs_work || !mass_work) return MRH_EINVAL;
+  MRH_NEED_GPU(h)
+  MRH_TRY(h)
+  mrh_solver_opts o; if (opts) o = *opts; else { mrh_default_solver_opts(&o); o.linear_tol = 1.0e-12; o.max_linear_iters = 1000; }
+  mrh_solver_info si{};
+  const int rc = project_into(h, 1, 0.0, u, rhs_work, mass_work, o, si, (cudaStream_t)stream);
+  if (info) *info = si;
+  return rc;
+  MRH_CATCH_CUDA(h)
+}
 
 void mrh_default_solver_opts(mrh_solver_opts* o) {
   if (!o) return;

@@ -44,12 +44,21 @@ SYMBOLS = ["mrh_default_config", "mrh_create", "mrh_destroy", "mrh_last_error", 
            "mrh_finalize_host", "mrh_assemble_res", "mrh_assemble_jacres", "mrh_assemble_jacres_host", "mrh_assemble_res_host_static",
            "mrh_get_sizes", "mrh_get_mesh", "mrh_get_dofmap", "mrh_get_crs", "mrh_get_side", "mrh_get_bc",
            "mrh_get_varname", "mrh_eval_function_host", "mrh_last_launch_count", "mrh_last_volume_kernel_ms",
-           "mrh_microbench", "mrh_last_kernel_path", "mrh_default_solver_opts", "mrh_linear_solve", "mrh_nonlinear_solve",
+           "mrh_microbench", "mrh_last_kernel_path", "mrh_build_brick_part", "mrh_set_partition", "mrh_get_partition", "mrh_comm_unique_id",
+           "mrh_comm_init", "mrh_exchange", "mrh_get_ghost_block", "mrh_exchange_meta_size", "mrh_exchange_meta_get", "mrh_exchange_meta_put",
+           "mrh_get_exchange_table", "mrh_assemble_projection", "mrh_set_dirichlet", "mrh_set_initial", "mrh_default_solver_opts", "mrh_linear_solve", "mrh_nonlinear_solve",
            "mrh_transient_solve"]
 
 
 def lib_path():
     return os.path.join(_HERE, "libmrhyde_b200.so")
+
+
+def _bind(L, name, what, value):
+    """argtypes / restype of one symbol; a library older than this file may lack newer entry points - the strict check that the
+    library exports everything the header declares is tests/test_host.py::test_library_exports_every_declared_symbol"""
+    if hasattr(L, name):
+        setattr(getattr(L, name), what, value)
 
 
 def load_library(path=None):
@@ -73,34 +82,50 @@ def load_library(path=None):
     L.mrh_create.argtypes = [C.POINTER(MrhConfig), C.POINTER(C.c_void_p)]
     for n in ("mrh_destroy", "mrh_finalize", "mrh_finalize_host"):
         getattr(L, n).argtypes = [C.c_void_p]
-    L.mrh_build_brick.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
-    L.mrh_set_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
-    L.mrh_set_nodes.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
-    L.mrh_set_dofmap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
-    L.mrh_set_crs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
-    L.mrh_add_side.argtypes = [C.c_void_p, C.c_char_p, C.c_int32, C.c_void_p, C.c_int64]
-    L.mrh_set_bc.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_char_p]
-    L.mrh_add_function.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p]
-    L.mrh_assemble_res.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p]
-    L.mrh_assemble_jacres.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p]
-    L.mrh_assemble_jacres_host.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p]
-    L.mrh_assemble_res_host_static.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p]
-    L.mrh_get_sizes.argtypes = [C.c_void_p, C.c_void_p]
-    L.mrh_get_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
-    L.mrh_get_dofmap.argtypes = [C.c_void_p] + [C.c_void_p] * 5
-    L.mrh_get_crs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
-    L.mrh_get_side.argtypes = [C.c_void_p, C.c_int32, C.c_char_p, C.c_int32, C.c_void_p, C.c_void_p]
-    L.mrh_get_bc.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
-    L.mrh_eval_function_host.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_void_p, C.c_double,
-                                         C.c_void_p]
-    L.mrh_microbench.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+    _bind(L, "mrh_build_brick", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_set_mesh", "argtypes", [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64])
+    _bind(L, "mrh_set_nodes", "argtypes", [C.c_void_p, C.c_void_p, C.c_int64])
+    _bind(L, "mrh_set_dofmap", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64])
+    _bind(L, "mrh_set_crs", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64])
+    _bind(L, "mrh_add_side", "argtypes", [C.c_void_p, C.c_char_p, C.c_int32, C.c_void_p, C.c_int64])
+    _bind(L, "mrh_set_bc", "argtypes", [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_char_p])
+    _bind(L, "mrh_add_function", "argtypes", [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p])
+    _bind(L, "mrh_assemble_res", "argtypes", [C.c_void_p, C.POINTER(MrhState), C.c_void_p])
+    _bind(L, "mrh_assemble_jacres", "argtypes", [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_assemble_jacres_host", "argtypes", [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_assemble_res_host_static", "argtypes", [C.c_void_p, C.POINTER(MrhState), C.c_void_p])
+    _bind(L, "mrh_get_sizes", "argtypes", [C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_get_mesh", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_get_dofmap", "argtypes", [C.c_void_p] + [C.c_void_p] * 5)
+    _bind(L, "mrh_get_crs", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_get_side", "argtypes", [C.c_void_p, C.c_int32, C.c_char_p, C.c_int32, C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_get_bc", "argtypes", [C.c_void_p, C.c_int32, C.c_int32])
+    _bind(L, "mrh_eval_function_host", "argtypes", [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_void_p, C.c_double, C.c_void_p])
+    _bind(L, "mrh_microbench", "argtypes", [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_build_brick_part", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32])
+    _bind(L, "mrh_set_partition", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32])
+    _bind(L, "mrh_get_partition", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_comm_unique_id", "argtypes", [C.c_void_p])
+    _bind(L, "mrh_comm_init", "argtypes", [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32])
+    _bind(L, "mrh_exchange", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_get_ghost_block", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p])
+    _bind(L, "mrh_get_ghost_block", "restype", C.c_int64)
+    _bind(L, "mrh_exchange_meta_size", "argtypes", [C.c_void_p, C.c_int32])
+    _bind(L, "mrh_exchange_meta_size", "restype", C.c_int64)
+    _bind(L, "mrh_exchange_meta_get", "argtypes", [C.c_void_p, C.c_int32, C.c_void_p])
+    _bind(L, "mrh_exchange_meta_put", "argtypes", [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64])
+    _bind(L, "mrh_get_exchange_table", "argtypes", [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p])
+    _bind(L, "mrh_get_exchange_table", "restype", C.c_int64)
+    _bind(L, "mrh_assemble_projection", "argtypes", [C.c_void_p, C.c_int32, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p])
     if hasattr(L, "mrh_nonlinear_solve"):            # device-only entry points (absent from the CPU stepping harness)
-        L.mrh_default_solver_opts.argtypes = [C.POINTER(MrhSolverOpts)]
-        L.mrh_default_solver_opts.restype = None
-        L.mrh_linear_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo), C.c_void_p]
-        L.mrh_nonlinear_solve.argtypes = [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo)]
-        L.mrh_transient_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_char_p, C.c_int32, C.c_void_p, C.c_void_p,
-                                          C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo), C.c_void_p]
+        _bind(L, "mrh_default_solver_opts", "argtypes", [C.POINTER(MrhSolverOpts)])
+        _bind(L, "mrh_default_solver_opts", "restype", None)
+        _bind(L, "mrh_linear_solve", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo), C.c_void_p])
+        _bind(L, "mrh_nonlinear_solve", "argtypes", [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo)])
+        _bind(L, "mrh_set_dirichlet", "argtypes", [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo), C.c_void_p])
+        _bind(L, "mrh_set_initial", "argtypes", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo), C.c_void_p])
+        _bind(L, "mrh_transient_solve", "argtypes", [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_char_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                                     C.POINTER(MrhSolverOpts), C.POINTER(MrhSolverInfo), C.c_void_p])
     _LIBS[path] = L
     return L
 
@@ -165,7 +190,7 @@ class Engine:
 
     @classmethod
     def from_problem(cls, p, lib=None, device=0, finalize=True, host_only=False, force_generic=False, no_jit=False, no_tiles=False, no_ws=False,
-                     no_batched=False, jit_batched=False):
+                     no_batched=False, jit_batched=False, part=None, comm_id=None):
         """Build an engine from a tests/problems.py style dict (same dict drives the oracle)."""
         extra = p.get("extra", {})
         weak = bool(extra.get("use weak Dirichlet", False))
@@ -178,10 +203,15 @@ class Engine:
         n = [m["NX"], m["NY"], m.get("NZ", 1)]
         lo = [m.get("xmin", 0.0), m.get("ymin", 0.0), m.get("zmin", 0.0)]
         hi = [m.get("xmax", 1.0), m.get("ymax", 1.0), m.get("zmax", 1.0)]
-        e.build_brick(n, lo, hi)
+        if part is None:
+            e.build_brick(n, lo, hi)
+        else:                                    # (procs, rank): this rank's block of the global brick
+            e.build_brick_part(n, lo, hi, part[0], part[1])
         for name, expr in p.get("functions", {}).items():       # physicsInterface.cpp:466-483: both locations
             e.add_function(name, expr, "ip")
             e.add_function(name, expr, "side ip")
+        for var, expr in p.get("initial", {}).items():              # "Initial conditions" of the input: function "initial <var>"
+            e.add_function("initial " + var, expr, "ip")
         for var, sides in p.get("dirichlet", {}).items():
             for side, expr in sides.items():
                 e.set_bc(var, side, "weak_dirichlet" if weak else "dirichlet", expr)
@@ -189,6 +219,8 @@ class Engine:
             for var, sides in p.get(kind, {}).items():
                 for side, expr in sides.items():
                     e.set_bc(var, side, kind, expr)
+        if comm_id is not None:                  # collective: every rank of the processor grid
+            e.comm_init(comm_id, part[1], int(np.prod(part[0])))
         if host_only:
             e.finalize_host()
         elif finalize:
@@ -201,6 +233,61 @@ class Engine:
         lo = np.asarray(list(lo) + [0.0] * (3 - len(lo)), dtype=np.float64)
         hi = np.asarray(list(hi) + [1.0] * (3 - len(hi)), dtype=np.float64)
         self._ck(self.L.mrh_build_brick(self.h, _ptr(n), _ptr(lo), _ptr(hi)), "mrh_build_brick")
+
+    def build_brick_part(self, nxyz, lo, hi, procs, rank):
+        n = np.asarray(list(nxyz) + [1] * (3 - len(nxyz)), dtype=np.int32)
+        lo = np.asarray(list(lo) + [0.0] * (3 - len(lo)), dtype=np.float64)
+        hi = np.asarray(list(hi) + [1.0] * (3 - len(hi)), dtype=np.float64)
+        pr = np.asarray(list(procs) + [1] * (3 - len(procs)), dtype=np.int32)
+        self._ck(self.L.mrh_build_brick_part(self.h, _ptr(n), _ptr(lo), _ptr(hi), _ptr(pr), rank), "mrh_build_brick_part")
+
+    def set_partition(self, gids, owner, rank, world):
+        gids = np.ascontiguousarray(gids, dtype=np.int64)
+        owner = np.ascontiguousarray(owner, dtype=np.int32)
+        self._ck(self.L.mrh_set_partition(self.h, _ptr(gids), _ptr(owner), rank, world), "mrh_set_partition")
+
+    def partition(self):
+        n = self.sizes()["nlocal"]
+        gids, owner = np.zeros(n, dtype=np.int64), np.zeros(n, dtype=np.int32)
+        self._ck(self.L.mrh_get_partition(self.h, _ptr(gids), _ptr(owner)), "mrh_get_partition")
+        return gids, owner
+
+    def comm_unique_id(self):
+        buf = np.zeros(128, dtype=np.uint8)
+        self._ck(self.L.mrh_comm_unique_id(_ptr(buf)), "mrh_comm_unique_id")
+        return buf
+
+    def comm_init(self, id128, rank, world):
+        id128 = np.ascontiguousarray(id128, dtype=np.uint8)
+        self._ck(self.L.mrh_comm_init(self.h, _ptr(id128), rank, world), "mrh_comm_init")
+
+    def exchange(self, res, jac=None, stream=None):
+        self._ck(self.L.mrh_exchange(self.h, _ptr(res), _ptr(jac), stream), "mrh_exchange")
+
+    def exchange_meta(self, peer):
+        n = int(self.L.mrh_exchange_meta_size(self.h, peer))
+        out = np.zeros(n, dtype=np.int64)
+        if n:
+            self._ck(self.L.mrh_exchange_meta_get(self.h, peer, _ptr(out)), "mrh_exchange_meta_get")
+        return out
+
+    def exchange_meta_put(self, peer, meta):
+        meta = np.ascontiguousarray(meta, dtype=np.int64)
+        self._ck(self.L.mrh_exchange_meta_put(self.h, peer, _ptr(meta), len(meta)), "mrh_exchange_meta_put")
+
+    def exchange_table(self, peer, which):
+        n = int(self.L.mrh_get_exchange_table(self.h, peer, which, None))
+        out = np.zeros(max(n, 0), dtype=np.int64)
+        if n > 0:
+            self.L.mrh_get_exchange_table(self.h, peer, which, _ptr(out))
+        return out
+
+    def ghost_block(self, values=False):
+        n = int(self.L.mrh_get_ghost_block(self.h, None, None, None))
+        rows, cols = np.zeros(n, dtype=np.int32), np.zeros(n, dtype=np.int64)
+        vals = np.zeros(n) if values else None
+        self._ck(self.L.mrh_get_ghost_block(self.h, _ptr(rows), _ptr(cols), _ptr(vals)), "mrh_get_ghost_block")
+        return rows, cols, vals
 
     def set_mesh(self, nodes, elem2node):
         nodes = np.ascontiguousarray(nodes, dtype=np.float64)
@@ -361,6 +448,22 @@ class Engine:
         rc = self._ck(self.L.mrh_nonlinear_solve(self.h, C.byref(st), _ptr(u), _ptr(res), _ptr(jac), C.byref(o), C.byref(i)), "mrh_nonlinear_solve")
         out = self._info(i)
         out["status"] = rc
+        return out
+
+    def assemble_projection(self, kind, rhs, mass, time=0.0, stream=None):
+        """kind 0: strong Dirichlet data (setDirichlet), 1: initial data (setInitial); rhs / mass are accumulated into"""
+        self._ck(self.L.mrh_assemble_projection(self.h, kind, time, _ptr(rhs), _ptr(mass), stream), "mrh_assemble_projection")
+
+    def set_dirichlet(self, u, rhs_work, mass_work, time=0.0, stream=None, **opts):
+        o, i = self.solver_opts(linear_tol=1e-12, max_linear_iters=1000, **opts), MrhSolverInfo()
+        rc = self._ck(self.L.mrh_set_dirichlet(self.h, _ptr(u), time, _ptr(rhs_work), _ptr(mass_work), C.byref(o), C.byref(i), stream), "mrh_set_dirichlet")
+        out = self._info(i); out["status"] = rc
+        return out
+
+    def set_initial(self, u, rhs_work, mass_work, stream=None, **opts):
+        o, i = self.solver_opts(linear_tol=1e-12, max_linear_iters=1000, **opts), MrhSolverInfo()
+        rc = self._ck(self.L.mrh_set_initial(self.h, _ptr(u), _ptr(rhs_work), _ptr(mass_work), C.byref(o), C.byref(i), stream), "mrh_set_initial")
+        out = self._info(i); out["status"] = rc
         return out
 
     def transient_solve(self, u, res, jac, t0, t1, dt, tableau="BWE", bdf_order=1, stream=None, **opts):

@@ -169,6 +169,14 @@ class Oracle:
             raise RuntimeError("oracle: " + self.L.orc_last_error().decode())
         return res, jac
 
+    def assemble_dirichlet(self, time=0.0):
+        """setDirichlet: (rhs, mass values) of the L2 projection of the strong Dirichlet data onto the fixed DOFs"""
+        rhs, mass = np.zeros(self.nlocal), np.zeros(self.nnz)
+        rc = self.L.orc_assemble_dirichlet(C.c_void_p(self.h), C.c_double(time), _p(rhs), _p(mass))
+        if rc != 0:
+            raise RuntimeError("oracle: " + self.L.orc_last_error().decode())
+        return rhs, mass
+
     def timing(self):
         t = np.zeros(4)
         self.L.orc_last_timing(C.c_void_p(self.h), _p(t))

@@ -352,6 +352,52 @@ class Oracle {
     last_seconds[3] = std::chrono::duration<double>(clk::now() - T0).count();
   }
 
+  // AssemblyManager::setDirichlet (/root/reference/src/managers/assemblyManager.cpp:1855-1948) with getDirichletBoundary (:6288-6357)
+  // and getMassBoundary (:6360-6420): the L2-projection system of the strong Dirichlet data.  Rows of fixed DOFs collect the side
+  // mass matrix and the side moments of the Dirichlet function, every other row is the identity; rhs / mass are accumulated into
+  // (caller zeroes).  The solve (SolverManager::projectDirichlet, solverManager.cpp:1060-1098) is the caller's.
+  void assembleDirichlet(double time, double* rhs, double* mass) {
+    const int nvar = (int)varlist.size(), nb = ref.nb, N = dofs.ndof_elem;
+    const int maxElem = (cfg.workset <= 0) ? (int)mesh.nelem : cfg.workset;
+    Workset<double> wk; wk.setup(cfg.dim, varlist, nb, dofs.offsets, maxElem, ref.nq, ref.nqs, cfg.transient);
+    wk.var_bcs = var_bcs; wk.time = time;
+    FunctionManager<double> fm(maxElem, ref.nq, ref.nqs); fm.wkset = &wk;
+    auto module = importPhysics<double>(cfg.physics, cfg.settings, cfg.dim);
+    module->defineFunctions(cfg.functions, &fm);
+    for (auto& f : sideFunctions) fm.addFunction(f.first, f.second, "side ip");
+    for (auto& f : cfg.functions) { fm.addFunction(f.first, f.second, "ip"); fm.addFunction(f.first, f.second, "side ip"); }
+    module->setWorkset(&wk);
+    fm.decomposeFunctions();
+    std::vector<double> zero((size_t)maxElem * N, 0.0);
+    for (const auto& bg : bgroups) {
+      const GroupData& g = bg.g;
+      wk.attach(&g, true); wk.sidename = mesh.sides[bg.side].name; wk.currentside = bg.side;
+      wk.computeSolnSteadySeeded(zero, 0);
+      const int nq = g.nq;
+      for (int n = 0; n < nvar; ++n) {
+        if (var_bcs[n][bg.side] != "Dirichlet") continue;
+        auto dip = fm.evaluate("Dirichlet " + varlist[n] + " " + wk.sidename, "side ip");
+        for (int e = 0; e < g.numElem; ++e) {
+          const int* l = &dofs.lids[(size_t)g.elems[e] * N];
+          for (int i = 0; i < nb; ++i) {
+            const int rowIndex = l[dofs.offsets[n * nb + i]];
+            if (!isFixed[rowIndex]) continue;
+            double dval = 0.0;
+            for (int j = 0; j < nq; ++j) dval += dip(e, j) * g.B(e, i, j) * g.wts[(size_t)e * nq + j];
+            rhs[rowIndex] += dval;
+            for (int k = 0; k < nb; ++k) {
+              double m = 0.0;
+              for (int j = 0; j < nq; ++j) m += g.B(e, i, j) * g.B(e, k, j) * g.wts[(size_t)e * nq + j];
+              const int64_t pos = crs.find(rowIndex, l[dofs.offsets[n * nb + k]]);
+              if (pos >= 0) mass[pos] += m;
+            }
+          }
+        }
+      }
+    }
+    for (int64_t r = 0; r < crs.nrows; ++r) if (!isFixed[r]) { const int64_t pos = crs.find((int)r, (int)r); if (pos >= 0) mass[pos] = 1.0; }
+  }
+
   template <class EvalT>
   void fluxConditions(Workset<EvalT>& wk, FunctionManager<EvalT>& fm) {
     const int nb = wk.nb, nq = wk.gd->nq;

@@ -90,6 +90,11 @@ int orc_assemble(void* h, const double* u, const double* u_prev, const double* u
   try { ((Oracle*)h)->assemble(u, u_prev, u_stage, compute_jacobian != 0, res, jac, nthreads); return 0; }
   catch (std::exception& e) { g_err = e.what(); return -1; }
 }
+// L2-projection system of the strong Dirichlet data (setDirichlet): rhs (nlocal) and mass (nnz) are accumulated into
+int orc_assemble_dirichlet(void* h, double time, double* rhs, double* mass) {
+  try { ((Oracle*)h)->assembleDirichlet(time, rhs, mass); return 0; }
+  catch (std::exception& e) { g_err = e.what(); return -1; }
+}
 void orc_last_timing(void* h, double* out4) { memcpy(out4, ((Oracle*)h)->last_seconds, 4 * sizeof(double)); }
 
 // evaluate a user expression at the volume ips of group g (double arithmetic): out (numElem, nq)

@@ -125,6 +125,23 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
   return MRH_OK;
 }
 
+// L2-projection systems stepped on the CPU (GenPhases::projection)
+template <class C>
+static void run_projection(const KParams& kp) {
+  using G = GenPhases<C>;
+  const int EB = 2;
+  GenSmem<C> L(EB, kp.tab.nq, false, false);
+  std::vector<double> sm(L.total_doubles());
+  for (int64_t blk0 = 0; blk0 < kp.nwork; blk0 += EB) {
+    for (int it = 0; it < EB * C::N; ++it) {
+      const int le = it / C::N, k = it % C::N;
+      if (blk0 + le < kp.nwork) reinterpret_cast<int*>(sm.data() + L.oLid())[le * C::N + k] = kp.lids[G::elem_of(kp, blk0 + le) * C::N + k];
+    }
+    for (int it = 0; it < EB * C::NV; ++it) G::gather_vertex(kp, L, sm.data(), blk0, it);
+    for (int it = 0; it < EB * L.nq; ++it) G::geometry(kp, L, sm.data(), blk0, it);
+    for (int it = 0; it < EB * C::NB * C::NVAR; ++it) G::projection(kp, L, sm.data(), blk0, it);
+  }
+}
 extern "C" {
 
 int mrh_finalize(mrh_handle h) {
@@ -163,6 +180,52 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st, double* res, dou
   memset(res, 0, sizeof(double) * h->host.dofs.nlocal); memset(jac, 0, sizeof(double) * h->host.crs.colind.size());
   return emu_assemble(h, st, res, jac);
   MRH_CATCH(h)
+}
+int mrh_assemble_projection(mrh_handle h, int32_t kind, double time, double* rhs, double* mass, void*) {
+  if (!h || !rhs || (kind != 0 && kind != 1)) return MRH_EINVAL;
+  MRH_TRY(h)
+  auto& H = h->host; auto* E = (EmuImpl*)h->impl;
+  if (!H.host_final || E->pat_id.empty()) throw std::runtime_error("mrh_finalize has not been called");
+  if (!H.proj_unsupported.empty()) throw std::runtime_error(H.proj_unsupported + " (not supported)");
+  BasePtrs bp;
+  bp.nodes = H.mesh.nodes.data(); bp.e2n = H.mesh.elem2node.data(); bp.lids = H.dofs.lids.data(); bp.fixed = H.isFixed.data();
+  bp.rowptr = H.crs.rowptr.data(); bp.pat = E->pat.data(); bp.pat_id = E->pat_id.data();
+  bp.code = H.ec.code.data(); bp.cpool = H.ec.cpool.data();
+  auto tab = [](const PointTables& T) { RefTab r{}; r.B = T.B.data(); r.G = T.G.data(); r.VB = T.VB.data(); r.VG = T.VG.data(); r.W = T.W.data(); r.nq = T.nq;
+    for (int c = 0; c < 3; ++c) { r.tanU[c] = T.tanU[c]; r.tanV[c] = T.tanV[c]; } return r; };
+  bp.vol_tab = tab(H.ref.vol);
+  for (int s = 0; s < H.ref.nsides; ++s) bp.side_tab[s] = tab(H.ref.side[s]);
+  auto diag = [&](int r) { for (int64_t p = H.crs.rowptr[r]; p < H.crs.rowptr[r + 1]; ++p) if (H.crs.colind[p] == r) return p; return (int64_t)-1; };
+  if (kind == 0) {
+    for (size_t k = 0; k < H.dirichlet_launches.size(); ++k) {
+      KParams kp;
+      H.fillProjectionParams(kp, bp, time, rhs, mass, (int)k, H.mesh.sides[H.dirichlet_launches[k].side].elems.data());
+      if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_projection<decltype(c)>(kp); })) throw std::runtime_error("configuration not supported");
+    }
+    if (mass) for (int64_t r = 0; r < H.crs.nrows; ++r) if (!H.isFixed[r]) { const int64_t p = diag((int)r); if (p >= 0) mass[p] = 1.0; }
+  } else {
+    KParams kp;
+    H.fillProjectionParams(kp, bp, time, rhs, mass, -1, nullptr);
+    if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_projection<decltype(c)>(kp); })) throw std::runtime_error("configuration not supported");
+    if (mass) for (int64_t r = 0; r < H.crs.nrows; ++r) {
+      double sum = 0.0; for (int64_t p = H.crs.rowptr[r]; p < H.crs.rowptr[r + 1]; ++p) sum += std::fabs(mass[p]);
+      if (sum < 1.0e-14) { const int64_t p = diag((int)r); if (p >= 0) mass[p] = 1.0; }
+    }
+  }
+  return MRH_OK;
+  MRH_CATCH(h)
+}
+int mrh_set_dirichlet(mrh_handle h, double*, double, double*, double*, const mrh_solver_opts*, mrh_solver_info*, void*) { if (h) h->err = "not supported by the CPU stepping harness"; return MRH_EUNSUPPORTED; }
+int mrh_set_initial(mrh_handle h, double*, double*, double*, const mrh_solver_opts*, mrh_solver_info*, void*) { if (h) h->err = "not supported by the CPU stepping harness"; return MRH_EUNSUPPORTED; }
+int mrh_comm_unique_id(void*) { return MRH_EUNSUPPORTED; }
+int mrh_comm_init(mrh_handle h, const void*, int32_t, int32_t) { if (h) h->err = "not supported by the CPU stepping harness"; return MRH_EUNSUPPORTED; }
+int mrh_exchange(mrh_handle h, double*, double*, void*) { if (h) h->err = "not supported by the CPU stepping harness"; return MRH_EUNSUPPORTED; }
+int64_t mrh_get_ghost_block(mrh_handle h, int32_t* rows, int64_t* col_gids, double*) {
+  if (!h) return MRH_EINVAL;
+  const auto& P = h->host.plan; const int64_t n = (int64_t)P.ghost_row.size();
+  if (rows) memcpy(rows, P.ghost_row.data(), n * sizeof(int));
+  if (col_gids) memcpy(col_gids, P.ghost_colgid.data(), n * sizeof(int64_t));
+  return n;
 }
 int mrh_assemble_res_host_static(mrh_handle h, const mrh_state*, double*) {      // device-only entry point
   if (!h) return MRH_EINVAL;

@@ -5,7 +5,9 @@ Run in the build container (where /root/reference exists):  python tests/golden/
 Sources (all under /root/reference/regression):
   discretization/HGRAD/mrhyde.gold            basis values / physical gradients on the unit quad and hex (6 digits)
   thermal/2D_verification, thermal/3D_verification, cdr/2D_manufactured, le/3D_manufactured,
-  le/2D_manufactured, navierstokes/channel     printed L2 errors (6 digits) of the solved problems
+  le/2D_manufactured, navierstokes/channel, thermal/2D_mixed_bcs (Neumann sides), thermal/2D_verification_nonzeroDBC
+  (L2-projected Dirichlet data)                printed L2 errors (6 digits) of the solved problems
+  thermal/2D_verification_transient            the L2 error after every one of its 20 backward-Euler steps
 Only numbers are extracted; no reference source is copied.
 """
 import json
@@ -40,10 +42,21 @@ def l2(path):
     return out
 
 
+def l2_series(path):
+    """transient cases print one line per recorded time: [(time, error), ...] per variable"""
+    out = {}
+    for ln in open(f"{REF}/{path}/mrhyde.gold"):
+        m = re.search(r"L2 norm of the error for (\S+) = ([-\d.e+]+)\s+\(time = ([-\d.e+]+)\)", ln)
+        if m:
+            out.setdefault(m.group(1), []).append((float(m.group(3)), float(m.group(2))))
+    return out
+
+
 if __name__ == "__main__":
     data = {"hgrad": hgrad(), "l2": {}}
     for p in ["thermal/2D_verification", "thermal/3D_verification", "cdr/2D_manufactured", "le/3D_manufactured",
-              "le/2D_manufactured", "navierstokes/channel"]:
+              "le/2D_manufactured", "navierstokes/channel", "thermal/2D_mixed_bcs", "thermal/2D_verification_nonzeroDBC"]:
         data["l2"][p] = l2(p)
+    data["l2_series"] = {"thermal/2D_verification_transient": l2_series("thermal/2D_verification_transient")}
     json.dump(data, open(OUT, "w"), indent=1)
     print("wrote", OUT, {k: v for k, v in data["l2"].items()})

@@ -172,8 +172,8 @@ def config_parity_cases():
 def oracle_problem(p):
     """The oracle's config text does not know engine-only keys."""
     q = copy.deepcopy(p)
-    q.pop("true", None)
-    q.pop("name", None)
+    for k in ("true", "name", "time", "initial"):
+        q.pop(k, None)
     return config_text(**q)
 
 

@@ -24,6 +24,30 @@ def regression_thermal_2d(n=40):
                 true={"e": "sin(2*pi*x)*sin(2*pi*y)"})
 
 
+def regression_thermal_2d_mixed_bcs(n=40):
+    """regression/thermal/2D_mixed_bcs: Dirichlet left / right, Neumann top / bottom (pins the side integration)"""
+    return dict(name="thermal/2D_mixed_bcs", mesh=_mesh(2, (n, n)), physics="thermal", order=1,
+                functions={"thermal source": "8*pi*pi*sin(2*pi*x)*sin(2*pi*y)"},      # (the input's unused "thermal Neumann source" is left out)
+                dirichlet={"e": {"left": "0.0", "right": "0.0"}},
+                neumann={"e": {"top": "2*pi*sin(2*pi*x)*cos(2*pi*y)", "bottom": "-2*pi*sin(2*pi*x)*cos(2*pi*y)"}},
+                true={"e": "sin(2*pi*x)*sin(2*pi*y)"})
+
+
+def regression_thermal_2d_nonzero_dbc(n=40):
+    """regression/thermal/2D_verification_nonzeroDBC: Dirichlet data sin(x) sin(y), L2-projected onto the boundary DOFs"""
+    return dict(name="thermal/2D_verification_nonzeroDBC", mesh=_mesh(2, (n, n)), physics="thermal", order=1,
+                functions={"thermal source": "2.0*sin(x)*sin(y)"}, dirichlet={"e": {"all boundaries": "sin(x)*sin(y)"}},
+                true={"e": "sin(x)*sin(y)"})
+
+
+def regression_thermal_2d_transient(n=40):
+    """regression/thermal/2D_verification_transient: backward Euler, 20 steps to t = 1, zero initial and boundary data"""
+    return dict(name="thermal/2D_verification_transient", mesh=_mesh(2, (n, n)), physics="thermal", order=1,
+                functions={"thermal source": "(8*(pi*pi)*sin(2*pi*t)+2*pi*cos(2*pi*t))*sin(2*pi*x)*sin(2*pi*y)"},
+                dirichlet={"e": {"all boundaries": "0.0"}}, extra={"transient": True},
+                true={"e": "sin(2*pi*t)*sin(2*pi*x)*sin(2*pi*y)"}, time=dict(final=1.0, steps=20, tableau="BWE", bdf=1))
+
+
 def regression_thermal_3d(n=10):
     return dict(name="thermal/3D_verification", mesh=_mesh(3, (n, n, n)), physics="thermal", order=1,
                 functions={"thermal source": "12*(pi*pi)*sin(2*pi*x)*sin(2*pi*y)*sin(2*pi*z)"},

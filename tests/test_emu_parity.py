@@ -75,3 +75,49 @@ def test_boundary_cases_with_caller_supplied_numbering(emu_lib):
         if "transient" in kw or not (p.get("neumann") or p.get("flux") or p.get("extra", {}).get("use weak Dirichlet")):
             continue
         U.check_foreign_numbering(p, emu_lib, False, distort=0.2)
+
+
+# ---- L2-projection systems: setDirichlet / setInitial against the oracle and closed forms -----------------------
+PROJ = [("thermal 2D", "regression_thermal_2d_nonzero_dbc", 9, 0.0), ("thermal 3D", "config_c2", 4, 0.2), ("LE 3D", "config_c4", 3, 0.2)]
+
+
+@pytest.mark.parametrize("tag,mk,n,distort", PROJ, ids=[c[0] for c in PROJ])
+def test_dirichlet_projection_system_matches_oracle(emu_lib, tag, mk, n, distort):
+    import numpy as np
+    import problems
+    from mrhyde_b200 import Engine
+    from oracle.pyoracle import Oracle
+    p = getattr(problems, mk)(n)
+    if mk != "regression_thermal_2d_nonzero_dbc":
+        for v in p["dirichlet"]:
+            p["dirichlet"][v] = {"left": "0.3*y+z", "top": "sin(x)+t", "front": "1.0"}
+    o = Oracle(U.oracle_problem(p))
+    e = Engine.from_problem(p, lib=emu_lib)
+    if distort:
+        nd = U.distorted_nodes(o.mesh()[0], p["mesh"], distort)
+        o.set_nodes(nd); e.set_nodes(nd)
+    orhs, omass = o.assemble_dirichlet(time=0.4)
+    rhs, mass = np.zeros(o.nlocal), np.zeros(o.nnz)
+    e.assemble_projection(0, rhs, mass, time=0.4)
+    assert U.rel_errors(rhs, orhs)[0] <= U.TOL and U.rel_errors(mass, omass, o.crs()[0]) <= (U.TOL, U.TOL)
+
+
+def test_initial_projection_reproduces_a_function_in_the_space(emu_lib):
+    """setInitial: the L2 projection of a (bi)linear function is that function; mass rows sum to the nodal volumes"""
+    import numpy as np
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    import problems
+    from mrhyde_b200 import Engine
+    p = U.shrink(problems.regression_thermal_2d())
+    p["initial"] = {"e": "1.0+2.0*x+y+0.5*x*y"}
+    e = Engine.from_problem(p, lib=emu_lib)
+    s = e.sizes()
+    rhs, mass = np.zeros(s["nlocal"]), np.zeros(s["nnz"])
+    e.assemble_projection(1, rhs, mass)
+    rp, ci = e.crs()
+    M = sp.csr_matrix((mass, ci, rp), shape=(s["nlocal"],) * 2)
+    xyz, _ = e.dof_coords()
+    want = 1.0 + 2.0 * xyz[:, 0] + xyz[:, 1] + 0.5 * xyz[:, 0] * xyz[:, 1]
+    np.testing.assert_allclose(spl.spsolve(M.tocsc(), rhs), want, rtol=1e-11, atol=1e-13)
+    assert M.sum() == pytest.approx(1.0, rel=1e-13)                      # area of the unit square

@@ -20,6 +20,7 @@ CASES = [
     ("le/2D_manufactured", problems.regression_le_2d, 1),
     ("le/3D_manufactured", problems.regression_le_3d, 0),
     ("navierstokes/channel", problems.regression_ns_channel, 0),
+    ("thermal/2D_mixed_bcs", problems.regression_thermal_2d_mixed_bcs, 1),
 ]
 VARS = {"thermal": ["e"], "cdr": ["c"], "linearelasticity": ["dx", "dy", "dz"], "navierstokes": ["ux", "pr", "uy", "uz"]}
 
@@ -61,6 +62,28 @@ def test_reference_golds_from_the_gpu_solution(lib, path, make, method):
             continue
         err = o.l2_error(uh, names.index(var), p["true"][var])
         assert err == pytest.approx(gold, rel=2e-5, abs=1e-9), (path, var, err, gold, info)
+    e.close()
+
+
+def test_transient_regression_series_from_the_gpu(lib):
+    """regression/thermal/2D_verification_transient: mrh_transient_solve one backward-Euler step at a time; the L2 error after
+    every step equals the reference's printed series (6 digits)"""
+    import torch
+    from mrhyde_b200 import Engine
+    from oracle.pyoracle import Oracle
+    p = problems.regression_thermal_2d_transient()
+    e = Engine.from_problem(p, lib=lib)
+    o = Oracle(U.oracle_problem(p))
+    u, res, jac = _buffers(e)
+    nsteps, T = p["time"]["steps"], p["time"]["final"]
+    dt = T / nsteps
+    gold = GOLD["l2_series"]["thermal/2D_verification_transient"]["e"]
+    for k in range(nsteps):
+        info = e.transient_solve(u, res, jac, k * dt, (k + 1) * dt, dt, tableau=p["time"]["tableau"], bdf_order=p["time"]["bdf"],
+                                 linear_method=1, linear_tol=1e-12, max_linear_iters=5000, nonlinear_tol=1e-9)
+        assert info["status"] == 0 and info["time_steps"] == 1, info
+        err = o.l2_error(u.cpu().numpy(), 0, p["true"]["e"], time=(k + 1) * dt)
+        assert err == pytest.approx(gold[k + 1][1], rel=3e-5), (k, err, gold[k + 1], info)
     e.close()
 
 
@@ -127,4 +150,69 @@ def test_transient_solver_order_of_accuracy(lib, tableau, order, rate):
     assert 0.0 < e8 < e4 < 0.1
     assert np.log2(e4 / e8) == pytest.approx(rate, abs=0.35), (e4, e8)
     assert 0.3 < fine.max() < 0.6                                    # exp(-2 pi^2 0.04) = 0.454 for the continuous problem
+    e.close()
+
+
+# ---- L2-projected Dirichlet / initial data on the device -------------------------------------------------------
+def test_nonzero_dirichlet_gold_from_the_gpu(lib):
+    """regression/thermal/2D_verification_nonzeroDBC (1.42007e-05): mrh_set_dirichlet projects sin(x) sin(y) onto the boundary DOFs,
+    mrh_nonlinear_solve keeps them (fixed rows) - all on the device"""
+    import torch
+    from mrhyde_b200 import Engine
+    from oracle.pyoracle import Oracle
+    p = problems.regression_thermal_2d_nonzero_dbc()
+    e = Engine.from_problem(p, lib=lib)
+    u, res, jac = _buffers(e)
+    info = e.set_dirichlet(u, res, jac)
+    assert info["status"] == 0 and info["last_linear_relres"] <= 1e-12, info
+    fixed = e.dofmap(coords=False)[2].astype(bool)
+    u0 = u.cpu().numpy().copy()
+    assert np.all(u0[~fixed] == 0.0) and np.abs(u0[fixed]).max() > 0.5
+    info = e.nonlinear_solve(u, res, jac, linear_method=1, linear_tol=1e-12, max_linear_iters=5000, nonlinear_tol=1e-9)
+    torch.cuda.synchronize()
+    assert info["status"] == 0, info
+    uh = u.cpu().numpy()
+    assert np.array_equal(uh[fixed], u0[fixed])
+    o = Oracle(U.oracle_problem(p))
+    err = o.l2_error(uh, 0, p["true"]["e"])
+    assert err == pytest.approx(GOLD["l2"]["thermal/2D_verification_nonzeroDBC"]["e"], rel=2e-5), err
+    e.close()
+
+
+@pytest.mark.parametrize("mk,n,distort", [("regression_thermal_2d_nonzero_dbc", 12, 0.2), ("config_c2", 6, 0.2), ("config_c4", 4, 0.0), ("config_c3", 3, 0.2)],
+                         ids=["thermal-2D", "thermal-3D", "LE-3D", "cdr-Q2"])
+def test_dirichlet_projection_system_on_the_device(lib, mk, n, distort):
+    import torch
+    from mrhyde_b200 import Engine
+    from oracle.pyoracle import Oracle
+    p = getattr(problems, mk)(n)
+    if mk != "regression_thermal_2d_nonzero_dbc":
+        for v in p["dirichlet"]:
+            p["dirichlet"][v] = {"left": "0.3*y+z", "top": "sin(x)+t", "front": "1.0"}
+    o = Oracle(U.oracle_problem(p))
+    e = Engine.from_problem(p, lib=lib)
+    if distort:
+        nd = U.distorted_nodes(o.mesh()[0], p["mesh"], distort)
+        o.set_nodes(nd); e.set_nodes(nd)
+    orhs, omass = o.assemble_dirichlet(time=0.4)
+    u, rhs, mass = _buffers(e)
+    e.assemble_projection(0, rhs, mass, time=0.4)
+    torch.cuda.synchronize()
+    assert U.rel_errors(rhs.cpu().numpy(), orhs)[0] <= U.TOL
+    assert U.rel_errors(mass.cpu().numpy(), omass, o.crs()[0]) <= (U.TOL, U.TOL)
+    e.close()
+
+
+def test_initial_projection_on_the_device(lib):
+    import torch
+    from mrhyde_b200 import Engine
+    p = problems.config_c4(5)
+    p["initial"] = {"dx": "1.0+2.0*x+y*z", "dz": "x*y*z"}
+    e = Engine.from_problem(p, lib=lib)
+    u, rhs, mass = _buffers(e)
+    info = e.set_initial(u, rhs, mass)
+    assert info["status"] == 0, info
+    xyz, var = e.dof_coords()
+    want = np.where(var == 0, 1.0 + 2.0 * xyz[:, 0] + xyz[:, 1] * xyz[:, 2], np.where(var == 2, xyz[:, 0] * xyz[:, 1] * xyz[:, 2], 0.0))
+    np.testing.assert_allclose(u.cpu().numpy(), want, rtol=1e-9, atol=1e-11)
     e.close()

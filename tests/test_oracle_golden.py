@@ -27,8 +27,20 @@ def sig6(x):
     return float(f"{x:.6g}")
 
 
-def newton(o, iters=8, tol=1e-9):
+def project_dirichlet(o, time=0.0):
+    """SolverManager::projectDirichlet + setDirichlet: L2 projection of the strong Dirichlet data onto the fixed DOFs"""
+    rhs, mass = o.assemble_dirichlet(time)
+    rp, ci = o.crs()
+    M = sp.csr_matrix((mass, ci, rp), shape=(o.nlocal, o.nlocal)).tocsc()
+    x = spl.spsolve(M, rhs)
+    fixed = o.dofmap()[2].astype(bool)
     u = np.zeros(o.nlocal)
+    u[fixed] = x[fixed]
+    return u
+
+
+def newton(o, iters=8, tol=1e-9, u0=None):
+    u = np.zeros(o.nlocal) if u0 is None else u0.copy()
     rp, ci = o.crs()
     for _ in range(iters):
         res, jac = o.assemble(u, jacobian=True)
@@ -59,6 +71,7 @@ CASES = [
     ("le/2D_manufactured", problems.regression_le_2d),
     ("le/3D_manufactured", problems.regression_le_3d),
     ("navierstokes/channel", problems.regression_ns_channel),
+    ("thermal/2D_mixed_bcs", problems.regression_thermal_2d_mixed_bcs),
 ]
 
 
@@ -74,6 +87,46 @@ def test_regression_l2_errors(path, make):
             continue
         err = o.l2_error(u, names.index(var), p["true"][var])
         assert err == pytest.approx(gold, rel=2e-5, abs=1e-9), (path, var, err, gold)
+
+
+def test_nonzero_dirichlet_data_regression():
+    """regression/thermal/2D_verification_nonzeroDBC: Dirichlet data sin(x) sin(y) projected onto the boundary DOFs"""
+    p = problems.regression_thermal_2d_nonzero_dbc()
+    o = Oracle(config_text(**{k: v for k, v in p.items() if k not in ("true", "name")}))
+    u0 = project_dirichlet(o)
+    fixed = o.dofmap()[2].astype(bool)
+    xyz = o.dofmap()[3]
+    assert np.abs(u0[fixed] - (np.sin(xyz[:, 0]) * np.sin(xyz[:, 1]))[fixed]).max() < 1e-4        # projection, not interpolation
+    u = newton(o, u0=u0)
+    assert np.array_equal(u[fixed], u0[fixed])
+    err = o.l2_error(u, 0, p["true"]["e"])
+    assert err == pytest.approx(GOLD["l2"]["thermal/2D_verification_nonzeroDBC"]["e"], rel=2e-5), err
+
+
+def test_transient_regression_series():
+    """regression/thermal/2D_verification_transient: backward Euler, the L2 error after each of the 20 steps (6 digits)"""
+    p = problems.regression_thermal_2d_transient()
+    o = Oracle(config_text(**{k: v for k, v in p.items() if k not in ("true", "name", "time")}))
+    rp, ci = o.crs()
+    nsteps, T = p["time"]["steps"], p["time"]["final"]
+    dt = T / nsteps
+    u = np.zeros(o.nlocal)
+    gold = GOLD["l2_series"]["thermal/2D_verification_transient"]["e"]
+    assert len(gold) == nsteps + 1 and gold[0][1] == 0.0
+    for k in range(nsteps):
+        t = k * dt
+        prev = u.copy().reshape(-1, 1)
+        stage = u.copy().reshape(-1, 1)
+        o.set_time([[1.0]], [1.0], [1.0, -1.0], dt, t + dt, 0)          # workset time = t + c dt, c = 1 for BWE
+        for _ in range(3):
+            res, jac = o.assemble(u, jacobian=True, u_prev=prev, u_stage=stage)
+            if np.max(np.abs(res)) < 1e-11:
+                break
+            J = sp.csr_matrix((jac, ci, rp), shape=(o.nlocal, o.nlocal)).tocsc()
+            u = u + spl.spsolve(J, res)
+        err = o.l2_error(u, 0, p["true"]["e"], time=t + dt)
+        assert abs(gold[k + 1][0] - (t + dt)) < 1e-9
+        assert err == pytest.approx(gold[k + 1][1], rel=3e-5), (k, err, gold[k + 1])
 
 
 def test_interpreter_quirks():
