@@ -44,7 +44,7 @@ enum { MRH_BC_NONE = 0, MRH_BC_DIRICHLET = 1, MRH_BC_WEAK_DIRICHLET = 2, MRH_BC_
  * module settings (thermal.cpp:24-41, linearelasticity.cpp:21-61, navierstokes.cpp:20-62). */
 typedef struct mrh_config {
   int32_t dim;                /* 2 or 3 */
-  const char* physics;        /* "thermal" | "cdr" | "linearelasticity" | "navierstokes" */
+  const char* physics;        /* "thermal" | "cdr" | "linearelasticity" | "navierstokes" | "stokes" */
   int32_t order;              /* HGRAD order, 1 or 2 */
   int32_t quadrature;         /* volume cubature degree; <0 = 2*order (discretizationInterface.cpp:166) */
   int32_t side_quadrature;    /* side cubature degree;   <0 = 2*order (:203) */
@@ -61,6 +61,8 @@ typedef struct mrh_config {
                                * bit 2: direct instead of tile-staged scatter; bit 3: no warp-specialised kernel; bit 4: no batched kernel;
                                * bit 5: NVRTC-specialise the batched kernel on small meshes too (tests); bit 6: no lane-per-point thermal kernel;
                                * bit 7: no exchange inside mrh_assemble_* when a communicator is attached */
+  int32_t use_lsic;           /* stokes "useLSIC" (stokes.cpp:44) */
+  int32_t reserved_;
 } mrh_config;
 
 /* Workset time data: Workset::{time,deltat,isTransient,current_stage,butcher_A,butcher_b,BDF_wts}

@@ -17,6 +17,9 @@
 #define MRHYDE_B200_HPP
 
 #include <cstdint>
+#include <cstdio>
+#include <fstream>
+#include <istream>
 #include <map>
 #include <memory>
 #include <sstream>
@@ -206,6 +209,20 @@ class navierstokes : public PhysicsBase<EvalT> {     // navierstokes.cpp:20-62; 
   bool useSUPG, usePSPG;
 };
 
+template <class EvalT = ScalarT>
+class stokes : public PhysicsBase<EvalT> {           // stokes.cpp:17-46; variable order ux, pr, uy, uz
+ public:
+  stokes(ParameterList& settings, const int& dimension_) : PhysicsBase<EvalT>(settings, dimension_) {
+    this->label = "stokes";
+    this->myvars = {"ux", "pr", "uy", "uz"}; this->myvars.resize(dimension_ + 1);
+    this->mybasistypes.assign(dimension_ + 1, "HGRAD");
+    useLSIC = settings.template get<bool>("useLSIC", false);
+    usePSPG = settings.template get<bool>("usePSPG", false);
+  }
+  void configure(mrh_config& cfg) const override { cfg.use_lsic = useLSIC; cfg.use_pspg = usePSPG; }
+  bool useLSIC, usePSPG;
+};
+
 // PhysicsImporter::import (physicsImporter.cpp:60-190), hot-path modules only
 template <class EvalT = ScalarT>
 inline RCP<PhysicsBase<EvalT>> importPhysics(const string& name, ParameterList& settings, const int& dimension) {
@@ -213,6 +230,7 @@ inline RCP<PhysicsBase<EvalT>> importPhysics(const string& name, ParameterList& 
   if (name == "cdr") return std::make_shared<cdr<EvalT>>(settings, dimension);
   if (name == "linearelasticity") return std::make_shared<linearelasticity<EvalT>>(settings, dimension);
   if (name == "navierstokes") return std::make_shared<navierstokes<EvalT>>(settings, dimension);
+  if (name == "stokes" || name == "Stokes") return std::make_shared<stokes<EvalT>>(settings, dimension);
   throw std::runtime_error("physics module not on the hot path: '" + name + "'");
 }
 
@@ -447,6 +465,72 @@ class AssemblyManager {
   vector<mrh_handle> handles;
   int device_ = 0;
 };
+
+// ---- on-disk formats ---------------------------------------------------------------------------------------
+// readInput: the subset of YAML that MrHyDE's input decks use (UserInterface, /root/reference/src/interfaces/userInterface.hpp:30-270,
+// reads them with Teuchos' YAML reader): nested block mappings by indentation, scalar values (plain, 'single' or "double" quoted),
+// '#' comments, the '%YAML' / '---' / '...' markers and the 'ANONYMOUS:' root.  Sequences, anchors and flow collections are not
+// part of those decks and are rejected.
+inline RCP<ParameterList> readInput(std::istream& in) {
+  auto root = std::make_shared<ParameterList>();
+  struct Level { int indent; ParameterList* list; };
+  vector<Level> stack{{-1, root.get()}};
+  string line; int lineno = 0;
+  auto fail = [&](const string& why) { throw std::runtime_error("input line " + std::to_string(lineno) + ": " + why); };
+  while (std::getline(in, line)) {
+    ++lineno;
+    if (!line.empty() && line.back() == '\r') line.pop_back();
+    // strip comments outside quotes
+    { bool q1 = false, q2 = false; for (size_t k = 0; k < line.size(); ++k) { if (line[k] == '\'' && !q2) q1 = !q1; else if (line[k] == '"' && !q1) q2 = !q2;
+        else if (line[k] == '#' && !q1 && !q2 && (k == 0 || line[k - 1] == ' ' || line[k - 1] == '\t')) { line.erase(k); break; } } }
+    const size_t first = line.find_first_not_of(" \t");
+    if (first == string::npos) continue;
+    if (line.compare(first, 5, "%YAML") == 0 || line.compare(first, 3, "---") == 0 || line.compare(first, 3, "...") == 0) continue;
+    if (line.find('\t') != string::npos && line.find('\t') < first) fail("tabs in the indentation");
+    if (line[first] == '-' || line[first] == '[' || line[first] == '{' || line[first] == '&' || line[first] == '*') fail("YAML sequences / flow collections / anchors are not supported");
+    // key: up to the first ':' that is followed by a space or ends the line (keys of the decks contain spaces, commas, brackets)
+    size_t colon = string::npos;
+    { bool q1 = false, q2 = false; for (size_t k = first; k < line.size(); ++k) { if (line[k] == '\'' && !q2) q1 = !q1; else if (line[k] == '"' && !q1) q2 = !q2;
+        else if (line[k] == ':' && !q1 && !q2 && (k + 1 == line.size() || line[k + 1] == ' ')) { colon = k; break; } } }
+    if (colon == string::npos) fail("expected 'key: value'");
+    auto trim = [](string t) { const size_t a = t.find_first_not_of(" \t"), b = t.find_last_not_of(" \t"); return a == string::npos ? string() : t.substr(a, b - a + 1); };
+    auto unquote = [](string t) { if (t.size() >= 2 && ((t.front() == '\'' && t.back() == '\'') || (t.front() == '"' && t.back() == '"'))) return t.substr(1, t.size() - 2); return t; };
+    const string key = unquote(trim(line.substr(first, colon - first)));
+    const string val = trim(line.substr(colon + 1));
+    const int indent = (int)first;
+    while (stack.size() > 1 && indent <= stack.back().indent) stack.pop_back();
+    ParameterList* cur = stack.back().list;
+    if (val.empty()) {
+      if (key == "ANONYMOUS" && stack.size() == 1) { stack.push_back({indent, root.get()}); continue; }      // the decks' root mapping
+      stack.push_back({indent, &cur->sublist(key)});
+    } else cur->set(key, unquote(val).c_str());
+  }
+  return root;
+}
+inline RCP<ParameterList> readInput(const string& path) {
+  std::ifstream f(path);
+  if (!f) throw std::runtime_error("cannot open input file " + path);
+  return readInput(f);
+}
+
+// Matrix Market (coordinate real general, array real general) dumps of a CRS matrix / a vector on the HOST: what
+// LinearAlgebraInterface::writeToFile produces for J, res, du (/root/reference/src/managers/solverManager.cpp:1653), so that an
+// assembly of this engine can be compared offline with a real MrHyDE build.  1-based indices, 17 significant digits.
+inline void writeMatrixMarket(const string& path, const int64_t* rowptr, const int32_t* colind, const double* values, int64_t nrows, int64_t ncols) {
+  FILE* f = fopen(path.c_str(), "w");
+  if (!f) throw std::runtime_error("cannot write " + path);
+  fprintf(f, "%%%%MatrixMarket matrix coordinate real general\n%lld %lld %lld\n", (long long)nrows, (long long)ncols, (long long)rowptr[nrows]);
+  for (int64_t r = 0; r < nrows; ++r)
+    for (int64_t p = rowptr[r]; p < rowptr[r + 1]; ++p) fprintf(f, "%lld %d %.17g\n", (long long)r + 1, colind[p] + 1, values[p]);
+  fclose(f);
+}
+inline void writeMatrixMarket(const string& path, const double* vec, int64_t n) {
+  FILE* f = fopen(path.c_str(), "w");
+  if (!f) throw std::runtime_error("cannot write " + path);
+  fprintf(f, "%%%%MatrixMarket matrix array real general\n%lld 1\n", (long long)n);
+  for (int64_t i = 0; i < n; ++i) fprintf(f, "%.17g\n", vec[i]);
+  fclose(f);
+}
 
 }  // namespace mrh
 #endif  // MRHYDE_B200_HPP

@@ -275,7 +275,7 @@ struct BatPhases {
     in.ps.fields = fm; in.ps.time = kp.tp.time;
     for (int c = 0; c < 3; ++c) { in.ps.x[c] = sm[L.oXq() + (size_t)q * 3 + c]; in.ps.nrm[c] = 0.0; in.ps.tng[c] = 0.0; }
     in.w = sm[L.oW() + q];
-    in.h = (C::PHYS == PHYS_NS) ? sm[L.oH()] : 0.0;
+    in.h = NeedsElementSize<C::PHYS>::value ? sm[L.oH()] : 0.0;
     S F[NVAR][TA];
 #pragma unroll
     for (int v = 0; v < NVAR; ++v)
@@ -453,7 +453,10 @@ struct BatPhases {
 // or straight-line functions printed from the bytecode and compiled with NVRTC at mrh_finalize (jit.hpp: JitProgs).
 struct InterpProgs {
   static constexpr bool jit = false;
-  static __device__ __forceinline__ double eval(int, double, double, double, double) { return 0.0; }
+  static constexpr int NA = 0;
+  static __device__ __forceinline__ double atom_arg(int, double, double, double, double) { return 0.0; }
+  static __device__ __forceinline__ int atom_shift(int) { return 0; }
+  static __device__ __forceinline__ double eval(int, double, double, double, double, const double*) { return 0.0; }
 };
 
 // One warp per element, grid-stride over the elements of the launch.  smem_all: [offsets | one WarpSmem block per warp].
@@ -503,16 +506,31 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
     for (int it = lane; it < nq * nparts; it += 32) B::geometry(kp, L, sm, it, nparts);
     __syncwarp();
     if (PROGS::jit) {
+      // sin / cos atoms of all points first: every lane busy, uniform code.  They live at the start of the D region, which the
+      // point phase only writes after the programs have read them (jit.hpp checks NA against the region's size).
+      double* at = sm + L.oD();
+      if (PROGS::NA > 0) {
+        for (int it = lane; it < nq * PROGS::NA; it += 32) {
+          const int q = it / PROGS::NA, a = it - q * PROGS::NA;
+          const double arg = PROGS::atom_arg(a, sm[L.oXq() + (size_t)q * 3], sm[L.oXq() + (size_t)q * 3 + 1], sm[L.oXq() + (size_t)q * 3 + 2], kp.tp.time);
+          const int sh = PROGS::atom_shift(a);
+          bool ok = true;
+          double v = trig_fast(arg, sh, ok);
+          if (!ok) v = sh ? cos(arg) : sin(arg);
+          at[it] = v;
+        }
+        __syncwarp();
+      }
       for (int q = lane; q < nq; q += 32) {
         const double x = sm[L.oXq() + (size_t)q * 3], y = sm[L.oXq() + (size_t)q * 3 + 1], z = sm[L.oXq() + (size_t)q * 3 + 2];
 #pragma unroll
         for (int k = 0; k < MRH_NCOEF; ++k)
-          if (kp.progs[k].kind == 1) sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = PROGS::eval(k, x, y, z, kp.tp.time);
+          if (kp.progs[k].kind == 1) sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = PROGS::eval(k, x, y, z, kp.tp.time, at + q * PROGS::NA);
       }
     } else {
       for (int it = lane; it < nq * n1; it += 32) B::prep(kp, L, sm, it, n1);
     }
-    if (lane == 31 && C::PHYS == PHYS_NS) B::element_size(L, sm);       // h enters volume terms through the stabilisation only
+    if (lane == 31 && NeedsElementSize<C::PHYS>::value) B::element_size(L, sm);       // h enters volume terms through the stabilisation only
     __syncwarp();
     for (int it = lane; it < nq * B::NCH; it += 32) B::point_chunk(kp, L, sm, it);
     __syncwarp();

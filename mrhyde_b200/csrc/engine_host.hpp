@@ -63,6 +63,7 @@ class EngineHost {
     else if (physics == "cdr") { phys = PHYS_CDR; varlist = {"c"}; }
     else if (physics == "linearelasticity") { phys = PHYS_LE; varlist = {"dx", "dy", "dz"}; varlist.resize(dim); }
     else if (physics == "navierstokes") { phys = PHYS_NS; varlist = {"ux", "pr", "uy", "uz"}; varlist.resize(dim + 1); }
+    else if (physics == "stokes" || physics == "Stokes") { phys = PHYS_STOKES; varlist = {"ux", "pr", "uy", "uz"}; varlist.resize(dim + 1); }
     else throw std::runtime_error("physics module not on the hot path: '" + physics + "'");
     nvar = (int)varlist.size();
     lay.build(dim, order);
@@ -219,7 +220,7 @@ class EngineHost {
     kp.u = st.u; kp.u_prev = st.u_prev; kp.u_stage = st.u_stage; kp.res = res; kp.jac = jac;
     kp.compute_jac = jac ? 1 : 0; kp.lump_mass = cfg.lump_mass;
     timeParams(kp.tp, st);
-    kp.ph.have_advection = cfg.include_advection; kp.ph.useSUPG = cfg.use_supg; kp.ph.usePSPG = cfg.use_pspg;
+    kp.ph.have_advection = cfg.include_advection; kp.ph.useSUPG = cfg.use_supg; kp.ph.usePSPG = cfg.use_pspg; kp.ph.useLSIC = cfg.use_lsic;
     kp.ph.formparam = cfg.form_param; kp.ph.le_penalty = cfg.le_penalty;
     for (int i = 0; i < nvar * nb; ++i) kp.offsets[i] = dofs.offsets[i];
     if (side < 0) {
@@ -327,6 +328,9 @@ class EngineHost {
       reg("lambda", "lambda", "1.0", "ip"); reg("mu", "mu", "0.5", "ip");
       reg("source dx", "source dx", "0.0", "ip"); reg("source dy", "source dy", "0.0", "ip"); reg("source dz", "source dz", "0.0", "ip");
       reg("lambda", "lambda", "1.0", "side ip"); reg("mu", "mu", "0.5", "side ip");
+    } else if (phys == PHYS_STOKES) {          // stokes.cpp:52-63
+      reg("source ux", "source ux", "0.0", "ip"); reg("source pr", "source pr", "0.0", "ip"); reg("source uy", "source uy", "0.0", "ip");
+      reg("source uz", "source uz", "0.0", "ip"); reg("viscosity", "viscosity", "1.0", "ip");
     } else {
       reg("source ux", "source ux", "0.0", "ip"); reg("source pr", "source pr", "0.0", "ip"); reg("source uy", "source uy", "0.0", "ip");
       reg("source uz", "source uz", "0.0", "ip"); reg("density", "density", "1.0", "ip"); reg("viscosity", "viscosity", "1.0", "ip");
@@ -338,6 +342,7 @@ class EngineHost {
     if (phys == PHYS_CDR) return {{CDR_SOURCE, "source"}, {CDR_DIFF, "diffusion"}, {CDR_CP, "specific heat"}, {CDR_RHO, "density"},
                                   {CDR_REACTION, "reaction"}, {CDR_XVEL, "xvel"}, {CDR_YVEL, "yvel"}, {CDR_ZVEL, "zvel"}};
     if (phys == PHYS_LE) return {{LE_LAMBDA, "lambda"}, {LE_MU, "mu"}, {LE_SRC0, "source dx"}, {LE_SRC1, "source dy"}, {LE_SRC2, "source dz"}};
+    if (phys == PHYS_STOKES) return {{NS_SRC_UX, "source ux"}, {NS_SRC_PR, "source pr"}, {NS_SRC_UY, "source uy"}, {NS_SRC_UZ, "source uz"}, {NS_VISCOSITY, "viscosity"}};
     return {{NS_SRC_UX, "source ux"}, {NS_SRC_PR, "source pr"}, {NS_SRC_UY, "source uy"}, {NS_SRC_UZ, "source uz"},
             {NS_DENSITY, "density"}, {NS_VISCOSITY, "viscosity"}};
   }

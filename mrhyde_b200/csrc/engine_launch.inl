@@ -94,13 +94,20 @@ void device_finalize(mrh_engine* h) {
     for (int k = 0; k < MRH_NCOEF; ++k) any1 = any1 || H.vol_progs[k].kind == 1;
     if (!thermal_fast && any1 && !(H.cfg.flags & (2 | 16)) && (H.mesh.nelem >= 32768 || (H.cfg.flags & 32))) {
       try {
-        std::string src;
-        for (int k = 0; k < MRH_NCOEF; ++k) {
-          const std::string name = "p" + std::to_string(k);
-          if (H.vol_progs[k].kind == 1) src += jit_function_source(name, H.vol_progs[k], H.ec.code, H.ec.cpool);
-          else src += "  static __device__ __forceinline__ double " + name + "(double, double, double, double) { return 0.0; }\n";
+        // sin / cos calls hoisted into a lane-parallel atom table when they fit the kernel's scratch (the smallest D region of a
+        // point is 33 doubles); MRH_BAT_ATOMS=0 keeps the plain printer
+        int natoms = 0;
+        static const int atoms_env = [] { const char* ev = getenv("MRH_BAT_ATOMS"); return ev ? atoi(ev) : 1; }();
+        std::string src = atoms_env ? jit_batched_atom_source(H.vol_progs, MRH_NCOEF, H.ec.code, H.ec.cpool, 32, natoms) : std::string();
+        if (src.empty() || natoms == 0) {
+          natoms = 0; src.clear();
+          for (int k = 0; k < MRH_NCOEF; ++k) {
+            const std::string name = "p" + std::to_string(k);
+            if (H.vol_progs[k].kind == 1) src += jit_function_source(name, H.vol_progs[k], H.ec.code, H.ec.cpool);
+            else src += "  static __device__ __forceinline__ double " + name + "(double, double, double, double) { return 0.0; }\n";
+          }
         }
-        D.jit.setBatchedSource(src, H.phys, H.dim, H.order);
+        D.jit.setBatchedSource(src, H.phys, H.dim, H.order, 192, 0, natoms);
         if (!D.jit.batched()) h->err = "NVRTC specialisation of the batched kernel unavailable, using the in-kernel interpreter: " + D.jit.last_error;
       } catch (const std::exception& ex) { h->err = std::string("NVRTC specialisation of the batched kernel skipped: ") + ex.what(); }
     }

@@ -149,6 +149,96 @@ inline std::string jit_function_source(const std::string& name, const Prog& pr, 
          head + "    bool ok = true;\n" + fast + "    return ok ? result : " + name + "_exact(x, y, z, t);\n  }\n";
 }
 
+// ---- batched kernel: programs with their sin / cos calls hoisted into a table of ATOMS ----------------------------------------
+// A manufactured source such as the linear-elasticity one calls sin / cos 63 times per point, 18 of them distinct; evaluated by one
+// lane per point that was 42 % of the batched kernel's instruction stream (profiles/r1_batched_final_C4_ncu_summary.txt).  The printer
+// therefore collects the distinct (function, argument expression) pairs of ALL programs of the launch; the kernel evaluates the atoms
+// of all points with every lane busy and uniform code (argument by a small switch, then one trig_fast call), and the programs read
+// them from shared memory.
+struct JitAtomTable {
+  std::vector<std::string> arg; std::vector<int> shift;      // shift 0: sin, 1: cos
+  int find_or_add(const std::string& a, int sh) {
+    for (size_t i = 0; i < arg.size(); ++i) if (arg[i] == a && shift[i] == sh) return (int)i;
+    arg.push_back(a); shift.push_back(sh); return (int)arg.size() - 1;
+  }
+};
+// program -> one fully parenthesised expression; sin / cos nodes become at[i]
+inline std::string jit_expr_with_atoms(const Prog& pr, const std::vector<Instr>& code, const std::vector<double>& cpool, JitAtomTable& T) {
+  std::vector<std::string> st;
+  auto leaf = [&](uint8_t op, uint16_t cidx) -> std::string {
+    switch (op) {
+      case OP_CONST: return jit_literal(cpool[cidx]);
+      case OP_X: return "x"; case OP_Y: return "y"; case OP_Z: return "z"; case OP_TIME: return "t";
+      default: return "(0.0)";
+    }
+  };
+  for (int pc = pr.start; pc < pr.start + pr.len; ++pc) {
+    const Instr in = code[pc];
+    if (in.op == OP_FIELD) throw std::runtime_error("state-dependent coefficient cannot be specialised");
+    if (in.op < OP_FIELD) { st.push_back(leaf(in.op, in.cidx)); continue; }
+    if (in.op <= OP_MEAN) {
+      std::string b;
+      if (in.arg != 0) b = leaf(in.arg - 1, in.cidx); else { b = st.back(); st.pop_back(); }
+      const std::string a = st.back(); st.pop_back();
+      std::string r;
+      switch (in.op) {
+        case OP_ADD: r = "(" + a + " + " + b + ")"; break;
+        case OP_SUB: r = "(" + a + " + (-" + b + "))"; break;
+        case OP_MUL: r = "(" + a + " * " + b + ")"; break;
+        case OP_DIV: r = "(" + a + " / " + b + ")"; break;
+        case OP_POW: r = "pow(" + a + ", " + b + ")"; break;
+        case OP_LT: r = "((" + a + " < " + b + ") ? 1.0 : 0.0)"; break;
+        case OP_LTE: r = "((" + a + " <= " + b + ") ? 1.0 : 0.0)"; break;
+        case OP_GT: r = "((" + a + " > " + b + ") ? 1.0 : 0.0)"; break;
+        case OP_GTE: r = "((" + a + " >= " + b + ") ? 1.0 : 0.0)"; break;
+        case OP_MAX: r = "mrh_jmax(" + a + ", " + b + ")"; break;
+        case OP_MIN: r = "mrh_jmin(" + a + ", " + b + ")"; break;
+        default: r = "(0.5 * " + a + " + 0.5 * " + b + ")"; break;
+      }
+      st.push_back(r);
+      continue;
+    }
+    if (in.op == OP_NIP) { const std::string top = st.back(); st.pop_back(); st.pop_back(); st.push_back(top); continue; }
+    const std::string a = st.back(); st.pop_back();
+    switch (in.op) {
+      case OP_SIN: st.push_back("at[" + std::to_string(T.find_or_add(a, 0)) + "]"); break;
+      case OP_COS: st.push_back("at[" + std::to_string(T.find_or_add(a, 1)) + "]"); break;
+      case OP_TAN: st.push_back("tan(" + a + ")"); break;
+      case OP_EXP: st.push_back("exp(" + a + ")"); break;
+      case OP_LOG: st.push_back("log(" + a + ")"); break;
+      case OP_SQRT: st.push_back("mrh_jsqrt0(" + a + ")"); break;
+      case OP_SINH: st.push_back("sinh(" + a + ")"); break;
+      case OP_COSH: st.push_back("cosh(" + a + ")"); break;
+      default: st.push_back("fabs(" + a + ")"); break;
+    }
+  }
+  return st.back();
+}
+// source of struct JitProgs' members for the batched kernel: NA, atom_arg, atom_shift, p0..p7(x, y, z, t, at).  An atom whose argument
+// itself contains an atom (sin(cos(x))) cannot be hoisted: the caller then falls back to the plain printer (returns "").
+inline std::string jit_batched_atom_source(const Prog* progs, int nprog, const std::vector<Instr>& code, const std::vector<double>& cpool, int max_atoms, int& natoms) {
+  JitAtomTable T;
+  std::string fns;
+  for (int k = 0; k < nprog; ++k) {
+    const std::string name = "p" + std::to_string(k);
+    const std::string sig = "  static __device__ __forceinline__ double " + name + "(double x, double y, double z, double t, const double* at) { return ";
+    if (progs[k].kind == 1) fns += sig + jit_expr_with_atoms(progs[k], code, cpool, T) + "; }\n";
+    else fns += sig + "0.0; }\n";
+  }
+  natoms = (int)T.arg.size();
+  if (natoms > max_atoms || natoms > 64) return "";
+  for (auto& a : T.arg) if (a.find("at[") != std::string::npos) return "";
+  unsigned long long mask = 0;
+  std::string out = "  static __device__ __forceinline__ double mrh_jmax(double a, double b) { return (a < b) ? b : a; }\n"
+                    "  static __device__ __forceinline__ double mrh_jmin(double a, double b) { return (a > b) ? b : a; }\n"
+                    "  static __device__ __forceinline__ double mrh_jsqrt0(double a) { return (a <= 0.0) ? 0.0 : sqrt(a); }\n"
+                    "  static constexpr int NA = " + std::to_string(natoms) + ";\n"
+                    "  static __device__ __forceinline__ double atom_arg(int a, double x, double y, double z, double t) {\n    switch (a) {\n";
+  for (int i = 0; i < natoms; ++i) { out += "      case " + std::to_string(i) + ": return " + T.arg[i] + ";\n"; if (T.shift[i]) mask |= 1ull << i; }
+  out += "      default: return 0.0;\n    }\n  }\n  static __device__ __forceinline__ int atom_shift(int a) { return (int)((" + std::to_string(mask) + "ull >> a) & 1ull); }\n";
+  return out + fns;
+}
+
 // One NVRTC-compiled module holding the specialised thermal kernel for one (TRANSIENT, ADV, JAC) variant.
 struct JitKernel {
   CUmodule mod = nullptr; CUfunction fn = nullptr, fn_ws = nullptr, fn_ws8 = nullptr, fn_wsk = nullptr; size_t ws_smem_set = 0, ws8_smem_set = 0, wsk_smem_set = 0; int blocks_per_sm = 1, tiled_blocks_per_sm = 1; size_t smem_set = 0; std::string source, log;
@@ -246,15 +336,25 @@ class JitCache {
 
   // ---- batched volume kernel (assemble_batched.h) with the state-independent programs printed as functions p0..p7 ----
   // threads / minb: launch bounds of the kernel (minb > 0: register budget 65536 / (threads * minb); 0: ptxas' own choice)
-  void setBatchedSource(const std::string& progs, int phys, int dim, int order, int threads = 192, int minb = 0) {
+  int bat_natoms = 0;          // sin / cos atoms hoisted out of the batched kernel's programs (0: plain printer)
+  void setBatchedSource(const std::string& progs, int phys, int dim, int order, int threads = 192, int minb = 0, int natoms = 0) {
+    bat_natoms = natoms;
     bat_bounds_ = "-DMRH_BAT_BOUNDS=" + std::to_string(threads) + (minb > 0 ? "," + std::to_string(minb) : std::string()); bat_max_threads = threads;
     if (const char* ev = getenv("MRH_BAT_BOUNDS")) { bat_bounds_ = std::string("-DMRH_BAT_BOUNDS=") + ev; bat_max_threads = atoi(ev); }   // tuning experiments
     if (bat_.mod && JitApi::get().ok) JitApi::get().ModuleUnload(bat_.mod);
     bat_ = JitKernel(); bat_tried_ = false;
     bat_.source = std::string("#include \"assemble_batched.h\"\nnamespace mrh {\nstruct JitProgs {\n  static constexpr bool jit = true;\n") + progs +
-        "  static __device__ __forceinline__ double eval(int k, double x, double y, double z, double t) {\n    switch (k) {\n"
+        (natoms > 0 ?
+        "  static __device__ __forceinline__ double eval(int k, double x, double y, double z, double t, const double* at) {\n    switch (k) {\n"
+        "      case 0: return p0(x, y, z, t, at); case 1: return p1(x, y, z, t, at); case 2: return p2(x, y, z, t, at); case 3: return p3(x, y, z, t, at);\n"
+        "      case 4: return p4(x, y, z, t, at); case 5: return p5(x, y, z, t, at); case 6: return p6(x, y, z, t, at); default: return p7(x, y, z, t, at);\n    }\n  }\n};\n}\n"
+        :
+        "  static constexpr int NA = 0;\n"
+        "  static __device__ __forceinline__ double atom_arg(int, double, double, double, double) { return 0.0; }\n"
+        "  static __device__ __forceinline__ int atom_shift(int) { return 0; }\n"
+        "  static __device__ __forceinline__ double eval(int k, double x, double y, double z, double t, const double*) {\n    switch (k) {\n"
         "      case 0: return p0(x, y, z, t); case 1: return p1(x, y, z, t); case 2: return p2(x, y, z, t); case 3: return p3(x, y, z, t);\n"
-        "      case 4: return p4(x, y, z, t); case 5: return p5(x, y, z, t); case 6: return p6(x, y, z, t); default: return p7(x, y, z, t);\n    }\n  }\n};\n}\n"
+        "      case 4: return p4(x, y, z, t); case 5: return p5(x, y, z, t); case 6: return p6(x, y, z, t); default: return p7(x, y, z, t);\n    }\n  }\n};\n}\n") +
         "extern \"C\" __global__ void __launch_bounds__(MRH_BAT_BOUNDS) mrh_jit_batched(const __grid_constant__ mrh::KParams kp) {\n"
         "  extern __shared__ __align__(16) double smem_all[];\n"
         "  mrh::batched_body<mrh::GenCfg<" + std::to_string(phys) + ", " + std::to_string(dim) + ", " + std::to_string(order) + ">, mrh::JitProgs>(kp, smem_all);\n}\n";

@@ -7,7 +7,7 @@
 
 namespace mrh {
 
-enum Phys { PHYS_THERMAL = 0, PHYS_CDR = 1, PHYS_LE = 2, PHYS_NS = 3 };
+enum Phys { PHYS_THERMAL = 0, PHYS_CDR = 1, PHYS_LE = 2, PHYS_NS = 3, PHYS_STOKES = 4 };      // stokes: the first module of SURVEY.md 8f3
 enum BC { BC_NONE = 0, BC_DIRICHLET = 1, BC_WEAK_DIRICHLET = 2, BC_NEUMANN = 3, BC_FLUX = 4 };
 
 // program slots inside KParams::progs
@@ -44,7 +44,7 @@ struct PhysParams {
   double formparam;      // thermal/LE "form_param"
   double le_penalty;     // LE "penalty"
   int proj;              // L2-projection launch (assemble.h projection): PROJ_DIRICHLET on a side set, PROJ_INITIAL over the volume
-  int pad_;
+  int useLSIC;           // stokes "useLSIC"
 };
 
 struct TilePlan {          // tile-staged scatter of the specialised kernels (built at finalize, engine_tiles.inl)

@@ -30,6 +30,9 @@ template <int DIM> struct PhysTraits<PHYS_THERMAL, DIM> { static constexpr int N
 template <int DIM> struct PhysTraits<PHYS_CDR, DIM> { static constexpr int NVAR = 1; };
 template <int DIM> struct PhysTraits<PHYS_LE, DIM> { static constexpr int NVAR = DIM; };
 template <int DIM> struct PhysTraits<PHYS_NS, DIM> { static constexpr int NVAR = DIM + 1; };
+template <int DIM> struct PhysTraits<PHYS_STOKES, DIM> { static constexpr int NVAR = DIM + 1; };
+// modules whose volume terms need the element size h = (sum w)^(1/d) (stabilisation parameters)
+template <int PHYS> struct NeedsElementSize { static constexpr bool value = PHYS == PHYS_NS || PHYS == PHYS_STOKES; };
 
 template <int PHYS, int DIM, class S> struct Physics;
 
@@ -232,6 +235,52 @@ struct Physics<PHYS_NS, DIM, S> {
       if (in.kp->ph.bc[ua] == BC_NEUMANN) F[ua][0] = F[ua][0] + (-in.fn(SIDE_BCSRC + ua)) * in.w;
     }
   }
+};
+
+// ----------------------------------------------------------------------------------------------- Stokes
+// /root/reference/src/physics/stokes.cpp:69-440 (volume), :445-447 (boundary: empty).  Variables ux, pr, uy, uz like navierstokes.
+// Quirks kept: the PSPG term is tau (grad p PLUS source) with tau = h / (2 visc) in 2-D (:256-257) and h^2 / (2 visc) in 1-D / 3-D
+// (:402); LSIC adds tau div(u) (d phi/dx + d phi/dy [+ d phi/dz]) to the PRESSURE rows (:268-286).  Program slots as for navierstokes.
+template <int DIM, class S>
+struct Physics<PHYS_STOKES, DIM, S> {
+  static constexpr int NVAR = DIM + 1;
+  MRH_HD static int uvar(int a) { return a == 0 ? 0 : a + 1; }
+  template <class IN> MRH_HD static void volume(const IN& in, S (&F)[NVAR][1 + DIM]) {
+    const double w = in.w;
+    const int srcslot[3] = {NS_SRC_UX, NS_SRC_UY, NS_SRC_UZ};
+    const S visc = in.fn(NS_VISCOSITY);
+#pragma unroll
+    for (int v = 0; v < NVAR; ++v) for (int a = 0; a <= DIM; ++a) F[v][a] = S(0.0);
+    S src[DIM];
+    const S pr = in.U(1);
+#pragma unroll
+    for (int a = 0; a < DIM; ++a) {
+      const int ua = uvar(a);
+      src[a] = in.fn(srcslot[a]);
+#pragma unroll
+      for (int c = 0; c < DIM; ++c) {
+        S Fc = visc * in.dU(ua, c);
+        if (c == a) Fc = Fc - pr;
+        F[ua][1 + c] = Fc * w;
+      }
+      F[ua][0] = (-src[a]) * w;
+    }
+    S divu = in.dU(uvar(0), 0);
+#pragma unroll
+    for (int c = 1; c < DIM; ++c) divu = divu + in.dU(uvar(c), c);
+    F[1][0] = divu * w;
+    if (in.kp->ph.usePSPG) {
+      const S tau = (DIM == 2) ? in.h / (2.0 * visc) : in.h * in.h / (2.0 * visc);
+#pragma unroll
+      for (int c = 0; c < DIM; ++c) F[1][1 + c] = F[1][1 + c] + (in.dU(1, c) + src[c]) * (tau * w);
+    }
+    if (in.kp->ph.useLSIC) {
+      const S Sl = (in.h * in.h / (2.0 * visc)) * divu * w;
+#pragma unroll
+      for (int c = 0; c < DIM; ++c) F[1][1 + c] = F[1][1 + c] + Sl;
+    }
+  }
+  MRH_HDN static void boundary(const PointIn<S>&, S (&)[NVAR][1 + DIM]) {}     // stokes.cpp:445-447 is empty
 };
 
 }  // namespace mrh

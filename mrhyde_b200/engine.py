@@ -17,7 +17,7 @@ class MrhConfig(C.Structure):
                 ("side_quadrature", C.c_int32), ("use_strong_dbc", C.c_int32), ("fix_zero_rows", C.c_int32),
                 ("lump_mass", C.c_int32), ("include_advection", C.c_int32), ("use_supg", C.c_int32),
                 ("use_pspg", C.c_int32), ("form_param", C.c_double), ("le_penalty", C.c_double),
-                ("device", C.c_int32), ("flags", C.c_int32)]
+                ("device", C.c_int32), ("flags", C.c_int32), ("use_lsic", C.c_int32), ("reserved_", C.c_int32)]
 
 
 class MrhState(C.Structure):
@@ -161,6 +161,7 @@ class Engine:
         cfg.include_advection = int(bool(settings.get("include advection", False)))
         cfg.use_supg = int(bool(settings.get("useSUPG", False)))
         cfg.use_pspg = int(bool(settings.get("usePSPG", False)))
+        cfg.use_lsic = int(bool(settings.get("useLSIC", False)))
         cfg.form_param = float(settings.get("form_param", 1.0))
         cfg.le_penalty = float(settings.get("penalty", 10.0))
         cfg.device = device

@@ -462,12 +462,115 @@ struct navierstokes : PhysicsBase<EvalT> {
   }
 };
 
+// ---------------------------------------------------------------------------------------------- stokes
+// /root/reference/src/physics/stokes.cpp: ctor :20-46, defineFunctions :52-63, volumeResidual :69-440 (1-D :90-197, 2-D :199-288,
+// 3-D :290-438), boundaryResidual :445-447 (empty).  Quirks kept: the PSPG term uses grad(p) PLUS the source, and its parameter is
+// h/(2 visc) in 2-D but h^2/(2 visc) in 1-D and 3-D (:256-257, :402); LSIC adds tau div(u) (d phi/dx + d phi/dy [+ d phi/dz]) to the
+// PRESSURE rows.
+template <class EvalT>
+struct stokes : PhysicsBase<EvalT> {
+  using PhysicsBase<EvalT>::wkset; using PhysicsBase<EvalT>::functionManager;
+  int spaceDim; bool useLSIC = false, usePSPG = false;
+  int unum[3] = {0, 0, 0}, pr_num = 0;
+  stokes(const StrMap& settings, int dimension) : spaceDim(dimension) {
+    this->label = "stokes";
+    this->myvars.push_back("ux"); this->myvars.push_back("pr");
+    if (spaceDim > 1) this->myvars.push_back("uy");
+    if (spaceDim > 2) this->myvars.push_back("uz");
+    for (size_t i = 0; i < this->myvars.size(); ++i) this->mybasistypes.push_back("HGRAD");
+    useLSIC = getBool(settings, "useLSIC", false); usePSPG = getBool(settings, "usePSPG", false);
+  }
+  void defineFunctions(const StrMap& fs, FunctionManager<EvalT>* fm) override {
+    functionManager = fm;
+    fm->addFunction("source ux", getOr(fs, "source ux", "0.0"), "ip");
+    fm->addFunction("source pr", getOr(fs, "source pr", "0.0"), "ip");
+    fm->addFunction("source uy", getOr(fs, "source uy", "0.0"), "ip");
+    fm->addFunction("source uz", getOr(fs, "source uz", "0.0"), "ip");
+    fm->addFunction("viscosity", getOr(fs, "viscosity", "1.0"), "ip");
+  }
+  void setWorkset(Workset<EvalT>* w) override {
+    wkset = w; const char* nm[3] = {"ux", "uy", "uz"};
+    for (int c = 0; c < spaceDim; ++c) unum[c] = this->varnum(nm[c]);
+    pr_num = this->varnum("pr");
+  }
+  void volumeResidual() override {
+    const int dim = spaceDim, nb = wkset->nb, nq = wkset->gd->nq;
+    const char* un[3] = {"ux", "uy", "uz"}; const char* sn[3] = {"source ux", "source uy", "source uz"};
+    Vista<EvalT> src[3];
+    src[0] = functionManager->evaluate("source ux", "ip");
+    functionManager->evaluate("source pr", "ip");
+    for (int c = 1; c < dim; ++c) src[c] = functionManager->evaluate(sn[c], "ip");
+    auto visc = functionManager->evaluate("viscosity", "ip");
+    Arr2<EvalT>* du[3][3]; Arr2<EvalT>* dp[3];
+    for (int a = 0; a < dim; ++a) {
+      for (int c = 0; c < dim; ++c) du[a][c] = &wkset->getSolutionField(gradname(un[a], c));
+      dp[a] = &wkset->getSolutionField(gradname("pr", a));
+    }
+    auto& pr = wkset->getSolutionField("pr");
+    auto h = wkset->getElementSize();
+    auto& res = wkset->res; const GroupData& g = *wkset->gd;
+    for (int a = 0; a < dim; ++a)
+      for (int elem = 0; elem < wkset->numElem; ++elem)
+        for (int pt = 0; pt < nq; ++pt) {
+          const double w = wkset->wt(elem, pt);
+          EvalT Fc[3];
+          for (int c = 0; c < dim; ++c) {
+            Fc[c] = visc(elem, pt) * (*du[a][c])(elem, pt);
+            if (c == a) Fc[c] = Fc[c] - pr(elem, pt);
+            Fc[c] *= w;
+          }
+          EvalT gsrc = -src[a](elem, pt) * w;
+          for (int dof = 0; dof < nb; ++dof) {
+            EvalT s = Fc[0] * g.G(elem, dof, pt, 0);
+            for (int c = 1; c < dim; ++c) s = s + Fc[c] * g.G(elem, dof, pt, c);
+            res(elem, wkset->off(unum[a], dof)) += s + gsrc * g.B(elem, dof, pt);
+          }
+        }
+    for (int elem = 0; elem < wkset->numElem; ++elem)
+      for (int pt = 0; pt < nq; ++pt) {
+        EvalT divu = (*du[0][0])(elem, pt);
+        for (int c = 1; c < dim; ++c) divu = divu + (*du[c][c])(elem, pt);
+        divu *= wkset->wt(elem, pt);
+        for (int dof = 0; dof < nb; ++dof) res(elem, wkset->off(pr_num, dof)) += divu * g.B(elem, dof, pt);
+      }
+    if (usePSPG)
+      for (int elem = 0; elem < wkset->numElem; ++elem)
+        for (int pt = 0; pt < nq; ++pt) {
+          const double alpha = 1.0;
+          EvalT tau = (dim == 2) ? alpha * h[elem] / (2. * visc(elem, pt)) : alpha * h[elem] * h[elem] / (2. * visc(elem, pt));
+          EvalT S[3];
+          for (int c = 0; c < dim; ++c) { S[c] = (*dp[c])(elem, pt) + src[c](elem, pt); S[c] *= tau * wkset->wt(elem, pt); }
+          for (int dof = 0; dof < nb; ++dof) {
+            EvalT s = S[0] * g.G(elem, dof, pt, 0);
+            for (int c = 1; c < dim; ++c) s = s + S[c] * g.G(elem, dof, pt, c);
+            res(elem, wkset->off(pr_num, dof)) += s;
+          }
+        }
+    if (useLSIC)
+      for (int elem = 0; elem < wkset->numElem; ++elem)
+        for (int pt = 0; pt < nq; ++pt) {
+          const double alpha = 1.0;
+          EvalT tau = alpha * h[elem] * h[elem] / (2. * visc(elem, pt));
+          EvalT stabres = (*du[0][0])(elem, pt);
+          for (int c = 1; c < dim; ++c) stabres = stabres + (*du[c][c])(elem, pt);
+          EvalT S = tau * stabres * wkset->wt(elem, pt);
+          for (int dof = 0; dof < nb; ++dof) {
+            double gs = g.G(elem, dof, pt, 0);
+            for (int c = 1; c < dim; ++c) gs += g.G(elem, dof, pt, c);
+            res(elem, wkset->off(pr_num, dof)) += S * gs;
+          }
+        }
+  }
+  void boundaryResidual() override {}
+};
+
 template <class EvalT>
 inline std::unique_ptr<PhysicsBase<EvalT>> importPhysics(const std::string& name, const StrMap& settings, int dim) {
   if (name == "thermal") return std::unique_ptr<PhysicsBase<EvalT>>(new thermal<EvalT>(settings, dim));
   if (name == "cdr") return std::unique_ptr<PhysicsBase<EvalT>>(new cdr<EvalT>(settings, dim));
   if (name == "linearelasticity") return std::unique_ptr<PhysicsBase<EvalT>>(new linearelasticity<EvalT>(settings, dim));
   if (name == "navierstokes") return std::unique_ptr<PhysicsBase<EvalT>>(new navierstokes<EvalT>(settings, dim));
+  if (name == "stokes" || name == "Stokes") return std::unique_ptr<PhysicsBase<EvalT>>(new stokes<EvalT>(settings, dim));
   throw std::runtime_error("oracle: physics module not restated: " + name);
 }
 

@@ -3,6 +3,7 @@
 // to libmrhyde_b200.so; the result is compared with the oracle's C API (oracle/src/capi.cpp) on the same state.
 //   facade_test --layout            : prints the C-ABI struct layout (compared with the ctypes mirror; needs no GPU)
 //   facade_test <C2|C4|C5|C2T> <n>  : parity run on the GPU, one JSON line, exit code 0 on success
+//   facade_test --yaml <deck> <pre> : MrHyDE-format input deck in, Matrix Market dumps of J / res / u out
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
@@ -29,7 +30,8 @@ static int layout() {
   F(mrh_config, dim); F(mrh_config, physics); F(mrh_config, order); F(mrh_config, quadrature); F(mrh_config, side_quadrature);
   F(mrh_config, use_strong_dbc); F(mrh_config, fix_zero_rows); F(mrh_config, lump_mass); F(mrh_config, include_advection);
   F(mrh_config, use_supg); F(mrh_config, use_pspg); F(mrh_config, form_param); F(mrh_config, le_penalty); F(mrh_config, device);
-  printf("\"flags\": %zu}, \"state\": {", offsetof(mrh_config, flags));
+  F(mrh_config, flags); F(mrh_config, use_lsic);
+  printf("\"reserved_\": %zu}, \"state\": {", offsetof(mrh_config, reserved_));
   F(mrh_state, u); F(mrh_state, u_prev); F(mrh_state, u_stage); F(mrh_state, is_transient); F(mrh_state, nstages); F(mrh_state, nsteps);
   F(mrh_state, stage); F(mrh_state, butcher_A); F(mrh_state, butcher_b); F(mrh_state, bdf_wts); F(mrh_state, time); F(mrh_state, deltat);
   printf("\"stream\": %zu}}\n", offsetof(mrh_state, stream));
@@ -39,6 +41,40 @@ static int layout() {
 
 int main(int argc, char** argv) {
   if (argc > 1 && !strcmp(argv[1], "--layout")) return layout();
+  if (argc > 3 && !strcmp(argv[1], "--yaml")) {
+    // facade_test --yaml <input.yaml> <prefix>: read a MrHyDE-format deck, assemble residual + Jacobian at a synthetic state and dump
+    // J, res and the state as Matrix Market files (what linalg->writeToFile leaves behind, solverManager.cpp:1653)
+    using namespace mrh;
+    try {
+      auto settings = readInput(std::string(argv[2]));
+      std::vector<BlockData> blocks(1);
+      AssemblyManager<> assembler(settings, blocks);
+      assembler.createGroups(); assembler.allocateGroupStorage(); assembler.createWorkset(); assembler.finalizeFunctions();
+      const auto S = assembler.sizes(0);
+      std::vector<int64_t> rp; std::vector<int32_t> ci, lids, offs, dofvar; std::vector<uint8_t> fixed; std::vector<double> xyz;
+      assembler.getGraph(0, rp, ci); assembler.getDOFs(0, lids, offs, fixed, xyz, dofvar);
+      std::vector<double> u(S.nlocal);
+      for (int64_t i = 0; i < S.nlocal; ++i) { double v = 1.0; for (int d = 0; d < S.dim; ++d) v *= sin(2 * M_PI * xyz[i * S.dim + d]); u[i] = v + 1e-3 * sin(12.9898 * i + 0.1 * dofvar[i]); }
+      auto sol0 = std::make_shared<Vector>(); sol0->nlocal = S.nlocal;
+      auto res = std::make_shared<Vector>(); res->nlocal = S.nlocal;
+      auto J = std::make_shared<CrsMatrix>(); J->rowptr = rp.data(); J->colind = ci.data(); J->nrows = S.nlocal;
+      CK(cudaMalloc((void**)&sol0->data, S.nlocal * sizeof(double))); CK(cudaMemcpy(sol0->data, u.data(), S.nlocal * sizeof(double), cudaMemcpyHostToDevice));
+      CK(cudaMalloc((void**)&res->data, S.nlocal * sizeof(double))); CK(cudaMemset(res->data, 0, S.nlocal * sizeof(double)));
+      CK(cudaMalloc((void**)&J->values, S.nnz * sizeof(double))); CK(cudaMemset(J->values, 0, S.nnz * sizeof(double)));
+      std::vector<vector_RCP> sol{sol0}, none; vector_RCP Psol;
+      assembler.assembleJacRes(0, 0, sol, none, none, none, none, none, true, false, false, res, J, false, 0.0, false, false, 0, Psol, false, 1.0);
+      CK(cudaDeviceSynchronize());
+      std::vector<double> r(S.nlocal), jv(S.nnz);
+      CK(cudaMemcpy(r.data(), res->data, r.size() * sizeof(double), cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(jv.data(), J->values, jv.size() * sizeof(double), cudaMemcpyDeviceToHost));
+      const std::string pre(argv[3]);
+      writeMatrixMarket(pre + "_J.mtx", rp.data(), ci.data(), jv.data(), S.nlocal, S.nlocal);
+      writeMatrixMarket(pre + "_res.mtx", r.data(), S.nlocal);
+      writeMatrixMarket(pre + "_u.mtx", u.data(), S.nlocal);
+      printf("{\"nlocal\": %lld, \"nnz\": %lld, \"path\": \"%s\"}\n", (long long)S.nlocal, (long long)S.nnz, assembler.kernelPath(0));
+      return 0;
+    } catch (const std::exception& e) { fprintf(stderr, "exception: %s\n", e.what()); return 2; }
+  }
   const std::string which = argc > 1 ? argv[1] : "C2";
   const int n = argc > 2 ? atoi(argv[2]) : 12;
   using namespace mrh;

@@ -54,7 +54,7 @@ static bool run_batched(const KParams& kp) {
     for (int it = 0; it < C::NV; ++it) G::gather_vertex(kp, L, sm.data(), w, it);
     for (int it = 0; it < nq * nparts; ++it) B::geometry(kp, L, sm.data(), it, nparts);
     for (int it = 0; it < nq * n1; ++it) B::prep(kp, L, sm.data(), it, n1);
-    if (C::PHYS == PHYS_NS) B::element_size(L, sm.data());
+    if (NeedsElementSize<C::PHYS>::value) B::element_size(L, sm.data());
     for (int it = 0; it < nq * B::NCH; ++it) B::point_chunk(kp, L, sm.data(), it);
     B::contract(kp, L, sm.data(), *acc);
     B::store_acc(L, sm.data(), *acc, kp.compute_jac != 0);

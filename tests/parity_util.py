@@ -95,6 +95,16 @@ def cases():
     out.append((p["name"], p, {"transient": be}))
     p = shrink(P.regression_cdr_2d()); p["extra"] = {"transient": True, "workset size": 40}; p["name"] = "cdr 2D transient DIRK2"
     out.append((p["name"], p, {"transient": dirk}))
+    # stokes: 2-D PSPG (h / 2 nu quirk), 3-D PSPG + LSIC with variable viscosity, 2-D Q2
+    p = shrink(P.regression_stokes_2d(6)); p["name"] = "stokes 2D pspg"
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_stokes_2d(4)); p["name"] = "stokes 3D pspg+lsic"
+    p["mesh"] = shrink(P.config_c5(4))["mesh"]; p["settings"] = {"usePSPG": True, "useLSIC": True}
+    p["functions"] = {"source ux": "1.0", "source uz": "x*y", "viscosity": "1.0+0.5*x"}
+    p["dirichlet"] = {v: {s: "0.0" for s in ("bottom", "top", "front")} for v in ("ux", "uy", "uz")}
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_stokes_2d(5)); p["name"] = "stokes 2D Q2"; p["order"] = 2; p["settings"] = {"useLSIC": True}
+    out.append((p["name"], p, {}))
     # lumped mass, fix-zero-rows
     p = shrink(P.regression_thermal_2d()); p["extra"] = {"lump mass": True, "fix zero rows": True}; p["name"] = "thermal 2D lump mass"
     out.append((p["name"], p, {}))

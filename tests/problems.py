@@ -112,6 +112,14 @@ def regression_ns_channel(nx=50, ny=10):
                 true={"ux": "0.5*y*(1.0-y)", "uy": "0.0", "pr": "0.0"})
 
 
+def regression_stokes_2d(n=4):
+    """regression/stokes/2D_verification_pspg (the next HGRAD module)"""
+    return dict(name="stokes/2D_verification_pspg", mesh=_mesh(2, (n, n)), physics="stokes", order=1,
+                functions={"source ux": "1.0"}, settings={"usePSPG": True}, extra={"workset size": 16},
+                dirichlet={"ux": {"bottom": "0.0", "top": "0.0"}, "uy": {"bottom": "0.0", "top": "0.0"}},
+                true={"ux": "0.5*y*(1.0-y)", "uy": "0.0", "pr": "0.0"})
+
+
 # ---- BASELINE.json configs (SURVEY.md 8d) ------------------------------------------------------------
 def config_c1(n=40):
     p = regression_thermal_2d(n)

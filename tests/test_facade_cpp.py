@@ -51,3 +51,30 @@ def test_facade_program_matches_oracle(case, n):
     assert out["ok"] and out["indexing_bit_exact"], out
     if case.startswith("C2"):
         assert out["bc_top"] == "Neumann", out
+
+
+@pytest.mark.gpu
+def test_yaml_deck_in_matrix_market_out(tmp_path):
+    """SURVEY.md 8f4: a MrHyDE-format input deck read by mrh::readInput, J / res dumped as Matrix Market (the files
+    linalg->writeToFile leaves behind, solverManager.cpp:1653) and compared entry by entry with the oracle on the same deck"""
+    import numpy as np
+    import scipy.io
+    from oracle.pyoracle import Oracle, config_text
+    exe = build_facade_test()
+    deck = os.path.join(ROOT, "tests", "golden", "thermal_3d_input.yaml")
+    pre = str(tmp_path / "dump")
+    r = subprocess.run([exe, "--yaml", deck, pre], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    J = scipy.io.mmread(pre + "_J.mtx").tocsr()
+    res = np.asarray(scipy.io.mmread(pre + "_res.mtx")).ravel()
+    u = np.asarray(scipy.io.mmread(pre + "_u.mtx")).ravel()
+    o = Oracle(config_text(mesh=dict(dim=3, NX=6, NY=5, NZ=7, xmin=0.0, xmax=1.0, ymin=0.0, ymax=2.0, zmin=0.0, zmax=1.0), physics="thermal", order=1,
+                           functions={"thermal source": "12*(pi*pi)*sin(2*pi*x)*sin(2*pi*y)*sin(2*pi*z)", "thermal diffusion": "1.0+0.5*x*y"},
+                           dirichlet={"e": {"all boundaries": "0.0"}}, neumann={"e": {"top": "1.0+x"}}))
+    assert J.shape == (o.nlocal, o.nlocal) and J.nnz <= o.nnz
+    ores, ojac = o.assemble(u)
+    rp, ci = o.crs()
+    import scipy.sparse as sp
+    OJ = sp.csr_matrix((ojac, ci, rp), shape=J.shape)
+    assert abs(J - OJ).max() <= 1e-12 * np.abs(ojac).max()
+    assert np.abs(res - ores).max() <= 1e-12 * np.abs(ores).max()

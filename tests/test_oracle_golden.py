@@ -72,6 +72,7 @@ CASES = [
     ("le/3D_manufactured", problems.regression_le_3d),
     ("navierstokes/channel", problems.regression_ns_channel),
     ("thermal/2D_mixed_bcs", problems.regression_thermal_2d_mixed_bcs),
+    ("stokes/2D_verification_pspg", problems.regression_stokes_2d),
 ]
 
 
@@ -81,7 +82,7 @@ def test_regression_l2_errors(path, make):
     o = Oracle(config_text(**p))
     u = newton(o)
     names = {"thermal": ["e"], "cdr": ["c"], "linearelasticity": ["dx", "dy", "dz"][: o.dim],
-             "navierstokes": ["ux", "pr", "uy", "uz"][: o.dim + 1]}[p["physics"]]
+             "navierstokes": ["ux", "pr", "uy", "uz"][: o.dim + 1], "stokes": ["ux", "pr", "uy", "uz"][: o.dim + 1]}[p["physics"]]
     for var, gold in GOLD["l2"][path].items():
         if var not in p["true"]:
             continue
