@@ -87,7 +87,8 @@ struct WarpSmem {
   MRH_HD size_t oUd() const { return even_up(oU() + N); }
   MRH_HD size_t oW() const { return even_up(oUd() + (transient ? N : 0)); }
   MRH_HD size_t oXq() const { return even_up(oW() + nq); }
-  MRH_HD size_t oJi() const { return even_up(oXq() + (size_t)nq * 3); }                  // J^-1 per point, [m][c]
+  MRH_HD size_t oNrm() const { return even_up(oXq() + (size_t)nq * 3); }                 // side launches: unit normal | tangent per point
+  MRH_HD size_t oJi() const { return even_up(oNrm() + (size_t)nq * 6); }                 // J^-1 per point, [m][c]
   static constexpr bool STORE_T = NB <= 8;                     // physical basis rows kept in shared memory (Q1); rebuilt from J^-1 otherwise
   MRH_HD size_t oT() const { return even_up(oJi() + (size_t)nq * C::DIM * C::DIM); }     // T[q][j][0..dim], STORE_T only
   MRH_HD size_t oF() const { return even_up(oT() + (STORE_T ? (size_t)nq * NB * TA : 0)); }
@@ -122,7 +123,13 @@ struct PointBat {
   MRH_HD S fn(int k) const {
     const Prog& pr = kp->progs[k];
     if (pr.kind == 0) return S(pr.cval);
-    if (pr.kind == 1) return S(coef[k]);
+    if (pr.kind == 1) {
+      if (k < MRH_NCOEF) return S(coef[k]);
+      PointState<double> pd;                                 // side launches: boundary-condition functions (slots SIDE_BCSRC..)
+      for (int c = 0; c < 3; ++c) { pd.x[c] = ps.x[c]; pd.nrm[c] = ps.nrm[c]; pd.tng[c] = ps.tng[c]; }
+      pd.time = ps.time; pd.fields = nullptr;
+      return S(eval_code<double>(kp->code, kp->cpool, pr.start, pr.len, pd));
+    }
     return eval_code<S>(kp->code, kp->cpool, pr.start, pr.len, ps);
   }
   MRH_HD const S& U(int m) const { return f[m][0]; }
@@ -164,7 +171,25 @@ struct BatPhases {
       }
     }
     const double det = det_inv<DIM>(J, Ji);
-    if (part == 0) {
+    if (part == 0 && kp.is_side) {
+      // side launch: weight = |J t_U x J t_V| w (3-D) or |J t| w (2-D), unit outward normal (discretizationInterface.cpp:1681-1787)
+      double nrm[3] = {0.0, 0.0, 0.0}, tng[3] = {0.0, 0.0, 0.0}, measure;
+      if (DIM == 2) {
+        for (int i = 0; i < 2; ++i) { tng[i] = 0.0; for (int j = 0; j < 2; ++j) tng[i] += J[i][j] * tb.tanU[j]; }
+        nrm[0] = tng[1]; nrm[1] = -tng[0];
+        measure = sqrt(tng[0] * tng[0] + tng[1] * tng[1]);
+      } else {
+        double tu[3], tv[3];
+        for (int i = 0; i < DIM; ++i) { tu[i] = tv[i] = 0.0; for (int j = 0; j < DIM; ++j) { tu[i] += J[i][j] * tb.tanU[j]; tv[i] += J[i][j] * tb.tanV[j]; } }
+        nrm[0] = tu[1] * tv[2] - tu[2] * tv[1]; nrm[1] = tu[2] * tv[0] - tu[0] * tv[2]; nrm[2] = tu[0] * tv[1] - tu[1] * tv[0];
+        measure = sqrt(nrm[0] * nrm[0] + nrm[1] * nrm[1] + nrm[2] * nrm[2]);
+      }
+      double nl = 0.0; for (int c = 0; c < DIM; ++c) nl += nrm[c] * nrm[c];
+      nl = 1.0 / sqrt(nl);
+      sm[L.oW() + q] = measure * tb.W[q];
+      for (int c = 0; c < 3; ++c) { sm[L.oXq() + (size_t)q * 3 + c] = xq[c]; sm[L.oNrm() + (size_t)q * 6 + c] = nrm[c] * nl; sm[L.oNrm() + (size_t)q * 6 + 3 + c] = tng[c]; }
+      for (int m = 0; m < DIM; ++m) for (int c = 0; c < DIM; ++c) sm[L.oJi() + (size_t)q * DIM * DIM + m * DIM + c] = Ji[m][c];
+    } else if (part == 0) {
       sm[L.oW() + q] = fabs(det) * tb.W[q];
       for (int c = 0; c < 3; ++c) sm[L.oXq() + (size_t)q * 3 + c] = xq[c];
       for (int m = 0; m < DIM; ++m) for (int c = 0; c < DIM; ++c) sm[L.oJi() + (size_t)q * DIM * DIM + m * DIM + c] = Ji[m][c];
@@ -196,13 +221,17 @@ struct BatPhases {
     const int q = item / n1; int idx = item - q * n1, k = 0;
     for (; k < MRH_NCOEF; ++k) if (kp.progs[k].kind == 1 && idx-- == 0) break;
     PointState<double> pd;
-    for (int c = 0; c < 3; ++c) { pd.x[c] = sm[L.oXq() + (size_t)q * 3 + c]; pd.nrm[c] = 0.0; pd.tng[c] = 0.0; }
+    for (int c = 0; c < 3; ++c) {
+      pd.x[c] = sm[L.oXq() + (size_t)q * 3 + c];
+      pd.nrm[c] = kp.is_side ? sm[L.oNrm() + (size_t)q * 6 + c] : 0.0; pd.tng[c] = kp.is_side ? sm[L.oNrm() + (size_t)q * 6 + 3 + c] : 0.0;
+    }
     pd.time = kp.tp.time; pd.fields = nullptr;
     sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = eval_code<double>(kp.code, kp.cpool, kp.progs[k].start, kp.progs[k].len, pd);
   }
-  MRH_HDN static void element_size(const LAY& L, double* sm) {
+  MRH_HDN static void element_size(const LAY& L, double* sm, bool side = false) {
     double vol = 0.0;
     for (int k = 0; k < L.nq; ++k) vol += sm[L.oW() + k];
+    if (side) { sm[L.oH()] = (DIM == 3) ? sqrt(vol) : vol; return; }          // side element size (sum w_side)^(1/(d-1)), workset.cpp:2681-2697
     sm[L.oH()] = (DIM == 3) ? cbrt(vol) : (DIM == 2) ? sqrt(vol) : vol;      // vol^(1/dim): within an ulp of the reference's pow(), a fifth of its instructions
   }
 
@@ -229,7 +258,7 @@ struct BatPhases {
           fv[0] += uj * b;
 #pragma unroll
           for (int c = 0; c < DIM; ++c) fv[1 + c] += uj * T[j * TA + 1 + c];
-          if (tr) fv[4] += Ud[slot] * b;
+          if (tr && !kp.is_side) fv[4] += Ud[slot] * b;
         }
       } else {
         double gr[DIM];
@@ -241,7 +270,7 @@ struct BatPhases {
           fv[0] += uj * b;
 #pragma unroll
           for (int c = 0; c < DIM; ++c) gr[c] += uj * tb.G[(q * NB + j) * DIM + c];
-          if (tr) fv[4] += Ud[slot] * b;
+          if (tr && !kp.is_side) fv[4] += Ud[slot] * b;
         }
 #pragma unroll
         for (int c = 0; c < DIM; ++c) {
@@ -257,7 +286,7 @@ struct BatPhases {
       for (int k = 0; k <= DIM; ++k)
 #pragma unroll
         for (int l = 0; l < LCH; ++l) if (m * TA + k == lane0 + l) in.f[m][k].d[l] = au;
-      if (tr) {
+      if (tr && !kp.is_side) {
 #pragma unroll
         for (int l = 0; l < LCH; ++l) if (m * TA == lane0 + l) in.f[m][4].d[l] = kp.tp.alpha_t;
       }
@@ -273,15 +302,24 @@ struct BatPhases {
     }
     in.kp = &kp; in.coef = sm + L.oCoef() + (size_t)q * MRH_NCOEF;
     in.ps.fields = fm; in.ps.time = kp.tp.time;
-    for (int c = 0; c < 3; ++c) { in.ps.x[c] = sm[L.oXq() + (size_t)q * 3 + c]; in.ps.nrm[c] = 0.0; in.ps.tng[c] = 0.0; }
+    for (int c = 0; c < 3; ++c) {
+      in.ps.x[c] = sm[L.oXq() + (size_t)q * 3 + c];
+      in.ps.nrm[c] = kp.is_side ? sm[L.oNrm() + (size_t)q * 6 + c] : 0.0; in.ps.tng[c] = kp.is_side ? sm[L.oNrm() + (size_t)q * 6 + 3 + c] : 0.0;
+    }
     in.w = sm[L.oW() + q];
-    in.h = NeedsElementSize<C::PHYS>::value ? sm[L.oH()] : 0.0;
+    in.h = (NeedsElementSize<C::PHYS>::value || kp.is_side) ? sm[L.oH()] : 0.0;
     S F[NVAR][TA];
 #pragma unroll
     for (int v = 0; v < NVAR; ++v)
 #pragma unroll
       for (int a = 0; a < TA; ++a) F[v][a] = S(0.0);
-    Physics<C::PHYS, DIM, S>::volume(in, F);
+    if (!kp.is_side) Physics<C::PHYS, DIM, S>::volume(in, F);
+    else {
+      Physics<C::PHYS, DIM, S>::boundary(in, F);
+#pragma unroll
+      for (int v = 0; v < NVAR; ++v)          // generic "Flux" condition, physicsInterface.cpp:1698-1766
+        if (kp.ph.bc[v] == BC_FLUX) F[v][0] = F[v][0] + (-in.fn(SIDE_FLUX + v)) * in.w;
+    }
     // f -> F[q][v][a];  dF_(v,a)/d(m,b) -> B-fragment order: tile (v, t = m/2), lane = a + 4 ((m & 1) + 2 b)
     double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
     double* Dq = sm + L.oD() + LAY::dq(q);
@@ -530,7 +568,7 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
     } else {
       for (int it = lane; it < nq * n1; it += 32) B::prep(kp, L, sm, it, n1);
     }
-    if (lane == 31 && NeedsElementSize<C::PHYS>::value) B::element_size(L, sm);       // h enters volume terms through the stabilisation only
+    if (lane == 31 && (NeedsElementSize<C::PHYS>::value || kp.is_side)) B::element_size(L, sm, kp.is_side != 0);       // h enters volume terms through the stabilisation only
     __syncwarp();
     for (int it = lane; it < nq * B::NCH; it += 32) B::point_chunk(kp, L, sm, it);
     __syncwarp();

@@ -346,11 +346,11 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
 #undef MRH_FAST
       }
     } else {
-      // volume terms (residual + Jacobian, or residual only): batched kernel (assemble_batched.h); side launches and
-      // element blocks that do not fit its shared-memory layout go through the generic kernel
+      // volume and boundary terms (residual + Jacobian, or residual only): batched kernel (assemble_batched.h); element blocks
+      // that do not fit its shared-memory layout go through the generic kernel
       bool done = false, jitted = false;
-      if (side < 0 && !(H.cfg.flags & 16)) {
-        JitKernel* jk = D.jit.hasBatchedSource() ? D.jit.batched() : nullptr;
+      if (!(H.cfg.flags & 16)) {          // side launches (boundary terms) take the ahead-of-time batched kernel as well
+        JitKernel* jk = (side < 0 && D.jit.hasBatchedSource()) ? D.jit.batched() : nullptr;
         if (jk) {
           JitApi& api = JitApi::get(1);
           const bool tr = kp.tp.transient != 0;

@@ -53,7 +53,7 @@ struct Physics<PHYS_THERMAL, DIM, S> {
       F[0][0] = F[0][0] + adv * w;
     }
   }
-  MRH_HDN static void boundary(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
+  template <class IN> MRH_HDN static void boundary(const IN& in, S (&F)[NVAR][1 + DIM]) {
     const int bc = in.kp->ph.bc[0];
     const double w = in.w;
     if (bc == BC_NEUMANN) {
@@ -87,7 +87,7 @@ struct Physics<PHYS_CDR, DIM, S> {
 #pragma unroll
     for (int c = 0; c < DIM; ++c) F[0][1 + c] = k * in.dU(0, c) * w;
   }
-  MRH_HDN static void boundary(const PointIn<S>&, S (&)[NVAR][1 + DIM]) {}   // cdr.cpp:148-150 is empty
+  template <class IN> MRH_HDN static void boundary(const IN&, S (&)[NVAR][1 + DIM]) {}   // cdr.cpp:148-150 is empty
 };
 
 // ------------------------------------------------------------------------------------ linear elasticity
@@ -121,7 +121,7 @@ struct Physics<PHYS_LE, DIM, S> {
       for (int c = 0; c < DIM; ++c) F[a][1 + c] = Sg[a][c] * in.w;
     }
   }
-  MRH_HDN static void boundary(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
+  template <class IN> MRH_HDN static void boundary(const IN& in, S (&F)[NVAR][1 + DIM]) {
     const int* bc = in.kp->ph.bc;
     bool alld = true;
 #pragma unroll
@@ -228,7 +228,7 @@ struct Physics<PHYS_NS, DIM, S> {
       for (int c = 0; c < DIM; ++c) F[1][1 + c] = F[1][1 + c] + strong[c] * (tauv * w / dens);
     }
   }
-  MRH_HDN static void boundary(const PointIn<S>& in, S (&F)[NVAR][1 + DIM]) {
+  template <class IN> MRH_HDN static void boundary(const IN& in, S (&F)[NVAR][1 + DIM]) {
 #pragma unroll
     for (int a = 0; a < DIM; ++a) {
       const int ua = uvar(a);
@@ -280,7 +280,7 @@ struct Physics<PHYS_STOKES, DIM, S> {
       for (int c = 0; c < DIM; ++c) F[1][1 + c] = F[1][1 + c] + Sl;
     }
   }
-  MRH_HDN static void boundary(const PointIn<S>&, S (&)[NVAR][1 + DIM]) {}     // stokes.cpp:445-447 is empty
+  template <class IN> MRH_HDN static void boundary(const IN&, S (&)[NVAR][1 + DIM]) {}     // stokes.cpp:445-447 is empty
 };
 
 }  // namespace mrh

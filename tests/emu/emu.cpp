@@ -54,7 +54,7 @@ static bool run_batched(const KParams& kp) {
     for (int it = 0; it < C::NV; ++it) G::gather_vertex(kp, L, sm.data(), w, it);
     for (int it = 0; it < nq * nparts; ++it) B::geometry(kp, L, sm.data(), it, nparts);
     for (int it = 0; it < nq * n1; ++it) B::prep(kp, L, sm.data(), it, n1);
-    if (NeedsElementSize<C::PHYS>::value) B::element_size(L, sm.data());
+    if (NeedsElementSize<C::PHYS>::value || kp.is_side) B::element_size(L, sm.data(), kp.is_side != 0);
     for (int it = 0; it < nq * B::NCH; ++it) B::point_chunk(kp, L, sm.data(), it);
     B::contract(kp, L, sm.data(), *acc);
     B::store_acc(L, sm.data(), *acc, kp.compute_jac != 0);
@@ -104,9 +104,9 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
       E->launches++; E->fast_launches++;
       continue;
     }
-    if (side < 0 && !(H.cfg.flags & 16)) {
+    if (!(H.cfg.flags & 16)) {          // volume and side launches through the batched phases
       if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_batched<decltype(c)>(kp); })) throw std::runtime_error("configuration not supported");
-      E->launches++; E->batched_launches++;
+      E->launches++; if (side < 0) E->batched_launches++;
       continue;
     }
     if (!dispatch_cfg(H.phys, H.dim, H.order, [&](auto c) { run_launch<decltype(c)>(kp); }))
