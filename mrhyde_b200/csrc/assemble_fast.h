@@ -394,7 +394,7 @@ struct ThermalHexQ1 {
   //                        | off[max_e] uint32 | rows[max_r] int
   static constexpr int NE = NK + 8;
   __host__ __device__ static constexpr size_t tiled_smem_bytes(int max_acc, int max_e, int max_r) {
-    return ((size_t)NE * 128 + 2 + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+    return ((size_t)NE * 128 + 2 + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + WS_LIST_SLACK;
   }
   __device__ __forceinline__ static void cp_async4(void* smem_dst, const void* gmem_src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
@@ -520,20 +520,21 @@ struct ThermalHexQ1 {
   // dynamic shared memory: Ks[WS_NBUF][NE * 128 + 2] | acc[(max_acc + 2) & ~1] | carry[128] | rowbuf[2][128][16] int
   //                        | off[max_e] uint32 | rows[max_r] int
   static constexpr int WS_NBUF = 3;               // element stores shared by the two compute groups (see tiled_ws)
+  static constexpr int WS_LIST_SLACK = 96;        // bulk-copy staging of the lists: 16-byte groups around each list + one mbarrier
   __host__ __device__ static constexpr size_t ws_smem_bytes(int max_acc, int max_e, int max_r) {
-    return (WS_NBUF * ((size_t)NE * 128 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 2 * 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+    return (WS_NBUF * ((size_t)NE * 128 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 2 * 128 * 64 + ((size_t)max_e + (size_t)max_r) * 4 + WS_LIST_SLACK;
   }
   // K-in-registers kernel (tiled_wsk): two element stores, monomial coefficients of both compute groups in shared memory
   static constexpr int WSK_NBUF = 2;
   __host__ __device__ static constexpr size_t wsk_smem_bytes(int max_acc, int max_e, int max_r) {
     return (WSK_NBUF * ((size_t)NE * 128 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + 2 * 128 * 64 + 2 * 32 * 128 * sizeof(double) +
-           ((size_t)max_e + (size_t)max_r) * 4 + 16;
+           ((size_t)max_e + (size_t)max_r) * 4 + WS_LIST_SLACK;
   }
   // lane-per-point kernel (tiled_ws8): element-store stride 129, NCG compute warpgroups of 16 elements in flight each
   static constexpr int W8_STR = TRANSIENT ? 44 : 36;      // doubles of monomial scratch per element in flight (bank-spread for LDS.128)
   __host__ __device__ static constexpr size_t ws8_scratch_bytes_of(int ncg) { return (size_t)ncg * 16 * W8_STR * sizeof(double); }
   __host__ __device__ static constexpr size_t ws8_smem_bytes(int max_acc, int max_e, int max_r, int ncg) {
-    return (WS_NBUF * ((size_t)NE * 129 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + ws8_scratch_bytes_of(ncg) + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+    return (WS_NBUF * ((size_t)NE * 129 + 2) + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + ws8_scratch_bytes_of(ncg) + ((size_t)max_e + (size_t)max_r) * 4 + WS_LIST_SLACK;
   }
 #if defined(MRH_WS_CREG)
   __device__ __forceinline__ static void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
@@ -547,8 +548,20 @@ struct ThermalHexQ1 {
     constexpr int KSZ = NE * (128 + KPAD) + 2;
     double* acc = sm + NBUF * KSZ;
     double* carry = acc + ((tp.max_acc + 2) & ~1);
+#if defined(MRH_WS_BULK)
+    unsigned* s_off0 = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(carry + 128) + scratch_bytes);       // 16-byte aligned
+    int* s_rows0 = reinterpret_cast<int*>(s_off0 + ((tp.max_e + 7) & ~3));
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(s_rows0 + ((tp.max_r + 7) & ~3));
+    unsigned phase = 0;
+    if (tid == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    bar_sync(1 + 2 * NBUF, 128);
+#else
     unsigned* s_off = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(carry + 128) + scratch_bytes);
     int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
+#endif
     const int64_t tstep = NCG * (int64_t)gridDim.x;
     constexpr int BAR_FULL = 1, BAR_EMPTY = 1 + NBUF, BAR_SCATTER = 1 + 2 * NBUF;
     constexpr int NPAIR = 256;                              // a FULL / EMPTY barrier joins one compute group (128) and the scatter group (128)
@@ -566,9 +579,25 @@ struct ThermalHexQ1 {
     for (int s = 0; tile_of(s) < tp.tile_end; ++s) {
       const double* Ks = sm + b * KSZ;
       const int E = cur.E, R = cur.R;
+#if defined(MRH_WS_BULK)
+      // slot / row lists of the tile by two bulk copies (TMA unit, one thread issues, completion on an mbarrier): whole 16-byte
+      // groups around [eb, eb + E) and [rb, rb + R) land at the start of the staging areas, the lists start (eb & 3) / (rb & 3) in
+      const unsigned* s_off = s_off0 + (cur.eb & 3);
+      const int* s_rows = s_rows0 + (cur.rb & 3);
+      if (tid == 0) {
+        const unsigned nb_e = (unsigned)(((cur.eb & 3) + E + 3) & ~3) * 4u, nb_r = (unsigned)(((cur.rb & 3) + R + 3) & ~3) * 4u;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the previous tile's generic-proxy reads of the staging areas are done (BAR_SCATTER)
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(nb_e + nb_r) : "memory");
+        if (nb_e) asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                               ::"r"((unsigned)__cvta_generic_to_shared(s_off0)), "l"(tp.off + (cur.eb & ~(int64_t)3)), "r"(nb_e), "r"(mbar) : "memory");
+        if (nb_r) asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                               ::"r"((unsigned)__cvta_generic_to_shared(s_rows0)), "l"(tp.rows + (cur.rb & ~(int64_t)3)), "r"(nb_r), "r"(mbar) : "memory");
+      }
+#else
       for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + cur.eb + k);
       for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + cur.rb + k);
       asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
       const size_t cid = (size_t)cur.clid * 128 + tid;
       const uint4* cl = reinterpret_cast<const uint4*>(tp.clist + cid * 72);
       uint4 wv = __ldg(cl);
@@ -603,7 +632,15 @@ struct ThermalHexQ1 {
       bar_sync(BAR_SCATTER, 128);                         // run totals stored, element store no longer read
       bar_arrive(BAR_EMPTY + b, NPAIR);
       if (cont) atomicAdd(acc + loc0, carry[tid]);
+#if defined(MRH_WS_BULK)
+      {
+        unsigned done = 0;
+        while (!done) asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(mbar), "r"(phase) : "memory");
+        phase ^= 1u;
+      }
+#else
       asm volatile("cp.async.wait_group 0;" ::: "memory");
+#endif
       bar_sync(BAR_SCATTER, 128);
       {
         double* jb = kp.jac + cur.base;

@@ -43,8 +43,15 @@ struct ThermalQuadQ1 {
   }
 
   MRH_HDN static void element(const KParams& kp, int64_t e) {
-    // ---- gather ----------------------------------------------------------------------------------------------
     int lid[4];
+    double r[4], K[NK];
+    compute(kp, e, lid, r, K);
+    scatter_direct(kp, e, lid, r, K);
+  }
+
+  // gather + element residual r (not yet negated) and element matrix K of element e
+  MRH_HDN static void compute(const KParams& kp, int64_t e, int (&lid)[4], double (&r)[4], double (&K)[NK]) {
+    // ---- gather ----------------------------------------------------------------------------------------------
     {
       const int4 a = *reinterpret_cast<const int4*>(kp.lids + e * 4);
       lid[0] = a.x; lid[1] = a.y; lid[2] = a.z; lid[3] = a.w;
@@ -92,7 +99,6 @@ struct ThermalQuadQ1 {
       for (int m = 0; m < 4; ++m) { C[m][0] = 0.25 * v[0][m]; C[m][1] = 0.25 * v[1][m]; A[m] = 0.25 * v[2][m]; }
     }
 
-    double r[4], K[NK];
 #pragma unroll
     for (int s = 0; s < 4; ++s) r[s] = 0.0;
 #pragma unroll
@@ -169,6 +175,9 @@ struct ThermalQuadQ1 {
       }
     }
 
+  }
+
+  MRH_HDN static void scatter_direct(const KParams& kp, int64_t e, const int (&lid)[4], double (&r)[4], double (&K)[NK]) {
     // ---- scatter: one RED per entry through the slot-pattern dictionary --------------------------------------------------
     // The kernel is RED-bound (20 per element).  Consecutive lanes hold consecutive elements; where the next lane's left
     // edge (local nodes 0, 3) is this element's right edge (local nodes 1, 2) its contributions to the shared rows and
@@ -229,6 +238,99 @@ struct ThermalQuadQ1 {
       }
     }
   }
+
+#if defined(__CUDACC__)
+  // ---- tile-staged scatter (device only; same scheme as ThermalHexQ1::tiled, engine_tiles.inl builds the plan with NN = 4) --------
+  // A CTA takes tiles of 128 elements (16 x 8 blocks on the structured mesh).  Every thread parks its element matrix and residual in
+  // the shared element store (entry-major), then sums 24 positions of the tile's sorted contribution list in registers and stores
+  // the run totals into the accumulation array; the CTA flushes that array with REDs whose lanes walk consecutive CRS slots.
+  // Against the direct scatter: ~10 instead of 14-20 REDs per element, and 8-9 lanes per row share 32-byte sectors, which is what
+  // bounds RED.F64 throughput (profiles/r1_red_microbench.txt: 105 G/s at one lane per sector, 690 G/s coalesced).
+  // dynamic shared memory: Ks[(NK + 4) * 128] | zero cell | pad | acc[(max_acc + 2) & ~1] | carry[128] | off[max_e] uint32 | rows[max_r] int
+  static constexpr int NE = NK + 4;
+  static constexpr int NCP = 24;                            // stored contributions per thread (20 + 4 pads: three uint4 words)
+  __host__ __device__ static constexpr size_t tiled_smem_bytes(int max_acc, int max_e, int max_r) {
+    return ((size_t)NE * 128 + 2 + (size_t)((max_acc + 2) & ~1) + 128) * sizeof(double) + ((size_t)max_e + (size_t)max_r) * 4 + 16;
+  }
+  __device__ static void tiled(const KParams& kp, double* sm) {
+    static_assert(JAC, "the tile-staged scatter is used for Jacobian assembly only");
+    typedef ThermalHexQ1<TRANSIENT, ADV, JAC, CF> Hex;       // (its cp.async helper)
+    const TilePlan& tp = kp.tile;
+    const int tid = threadIdx.x;
+    double* Ks = sm;
+    double* acc = sm + NE * 128 + 2;
+    double* carry = acc + ((tp.max_acc + 2) & ~1);
+    unsigned* s_off = reinterpret_cast<unsigned*>(carry + 128);
+    int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
+    if (tid == 0) Ks[NE * 128] = 0.0;                       // masked contributions and pads read this cell
+    for (int64_t t = tp.tile_begin + blockIdx.x; t < tp.tile_end; t += gridDim.x) {
+      const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
+      const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
+      for (int k = tid; k < E; k += 128) Hex::cp_async4(s_off + k, tp.off + eb + k);
+      for (int k = tid; k < R; k += 128) Hex::cp_async4(s_rows + k, tp.rows + rb + k);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      const size_t cid = (size_t)tp.cl_id[t] * 128 + tid;
+      unsigned w[NCP / 2];
+      {
+        const uint4* cl = reinterpret_cast<const uint4*>(tp.clist + cid * NCP);
+#pragma unroll
+        for (int i = 0; i < NCP / 8; ++i) { const uint4 v = __ldg(cl + i); w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w; }
+      }
+      const int loc0 = tp.cbase[cid];
+      const int64_t e0 = t * 128 + tid;
+      if (e0 < kp.nwork) {
+        int lid[4];
+        double r[4], K[NK];
+        compute(kp, (int64_t)tp.perm[e0], lid, r, K);
+#pragma unroll
+        for (int k = 0; k < NK; ++k) Ks[k * 128 + tid] = K[k];
+#pragma unroll
+        for (int s = 0; s < 4; ++s) Ks[(NK + s) * 128 + tid] = -r[s];
+      }
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      const bool cont = (w[0] & 0x8000u) == 0;              // my first run started in the previous thread's chunk
+      __syncthreads();                                      // element store and list copies complete
+      {
+        double sum = 0.0;
+        int loc = loc0;
+        double* dst = cont ? carry + tid : acc + loc;
+#pragma unroll
+        for (int g = 0; g < NCP; g += 8) {
+          double v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int k = g + u;
+            const unsigned c = (k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffffu);
+            v[u] = Ks[c & 0x7fffu];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int k = g + u;
+            const unsigned c = (k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffffu);
+            if (k > 0 && (c & 0x8000u)) { *dst = sum; ++loc; dst = acc + loc; sum = 0.0; }
+            sum += v[u];
+          }
+        }
+        *dst = sum;
+      }
+      __syncthreads();                                      // run totals stored
+      if (cont) atomicAdd(acc + loc0, carry[tid]);
+      __syncthreads();
+      {
+        double* jb = kp.jac + tp.base[t];
+        for (int k0 = tid; k0 < E; k0 += 512) {
+          unsigned o[4]; double v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) { o[u] = s_off[k]; v[u] = acc[k]; } }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { const int k = k0 + 128 * u; if (k < E) atomicAdd(jb + o[u], v[u]); }
+        }
+        for (int k = tid; k < R; k += 128) atomicAdd(kp.res + s_rows[k], acc[E + k]);
+      }
+      __syncthreads();                                      // lists, element store and accumulation array free for the next tile
+    }
+  }
+#endif
 };
 
 }  // namespace mrh

@@ -84,6 +84,12 @@ __global__ void __launch_bounds__(128) thermal_quad_q1_kernel(const __grid_const
 }
 
 template <bool TRANSIENT, bool ADV>
+__global__ void __launch_bounds__(128) thermal_quad_q1_tiled_kernel(const __grid_constant__ KParams kp) {
+  extern __shared__ double dsm[];
+  ThermalQuadQ1<TRANSIENT, ADV, true>::tiled(kp, dsm);
+}
+
+template <bool TRANSIENT, bool ADV>
 __global__ void __launch_bounds__(128) thermal_hex_q1_tiled_kernel(const __grid_constant__ KParams kp) {
   __shared__ double stage[ThermalHexQ1<TRANSIENT, ADV, true>::NSTAGE * 8 * 128];
   extern __shared__ double dsm[];

@@ -257,7 +257,7 @@ class EngineHost {
     }
   }
 
-  // element order of the tile-staged scatter: 8x4x4-element bricks on the structured mesh, identity otherwise
+  // element order of the tile-staged scatter: 8x4x4-element bricks (16x8 blocks in 2-D) on the structured mesh, identity otherwise
   std::vector<int> tileOrder(int64_t* iface_tiles = nullptr) const {
     std::vector<int> perm; perm.reserve((size_t)mesh.nelem);
     const int nx = mesh.NXYZ[0], ny = mesh.NXYZ[1], nz = mesh.NXYZ[2];
@@ -266,6 +266,10 @@ class EngineHost {
       for (int K = 0; K < nz; K += bz) for (int J = 0; J < ny; J += by) for (int I = 0; I < nx; I += bx)
         for (int k = K; k < std::min(K + bz, nz); ++k) for (int j = J; j < std::min(J + by, ny); ++j) for (int i = I; i < std::min(I + bx, nx); ++i)
           perm.push_back((int)(i + (int64_t)nx * (j + (int64_t)ny * k)));
+    } else if (dim == 2 && nx > 0 && (int64_t)nx * ny == mesh.nelem) {          // 16x8-element blocks
+      const int bx = 16, by = 8;
+      for (int J = 0; J < ny; J += by) for (int I = 0; I < nx; I += bx)
+        for (int j = J; j < std::min(J + by, ny); ++j) for (int i = I; i < std::min(I + bx, nx); ++i) perm.push_back((int)(i + (int64_t)nx * j));
     } else for (int64_t e = 0; e < mesh.nelem; ++e) perm.push_back((int)e);
     int64_t niface = 0;
     if (part.active()) {

@@ -4,6 +4,9 @@ constexpr int XCH_RESERVE_SMS = 4;     // SMs the interior launch leaves free fo
 #if !defined(MRH_WSK_DEFAULT)
 #define MRH_WSK_DEFAULT 0      // K-in-registers thermal kernel: MRH_WSK=1 enables it
 #endif
+#if !defined(MRH_TILED2D_DEFAULT)
+#define MRH_TILED2D_DEFAULT 1  // tile-staged scatter for the Q1 quadrilateral kernel (MRH_TILED2D=0: direct scatter)
+#endif
 #if !defined(MRH_WS8_DEFAULT)
 #define MRH_WS8_DEFAULT 0      // lane-per-point thermal kernel off until it is measured faster (MRH_WS8=1 enables it)
 #endif
@@ -63,8 +66,14 @@ void device_finalize(mrh_engine* h) {
   if (!D.tiles) D.tiles = new TileDev();
   D.tiles->release();
   if (!(H.cfg.flags & 5) && thermal_hex_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
-    const std::string why = build_tile_plan(H.tileOrder(&D.iface_tiles), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p,
-                                            H.cfg.include_advection ? 64 : 36, *D.tiles);
+    const std::string why = build_tile_plan<8>(H.tileOrder(&D.iface_tiles), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p,
+                                               H.cfg.include_advection ? 64 : 36, *D.tiles);
+    if (!D.tiles->ok) h->err = "tile-staged scatter unavailable (" + why + "), using direct scatter";
+  }
+  static const int tiled2d_env = [] { const char* ev = getenv("MRH_TILED2D"); return ev ? atoi(ev) : MRH_TILED2D_DEFAULT; }();
+  if (tiled2d_env && !(H.cfg.flags & 5) && thermal_quad_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
+    const std::string why = build_tile_plan<4>(H.tileOrder(nullptr), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p,
+                                               H.cfg.include_advection ? 16 : 10, *D.tiles);
     if (!D.tiles->ok) h->err = "tile-staged scatter unavailable (" + why + "), using direct scatter";
   }
   // NVRTC specialisation of the coefficient expressions for the specialised thermal kernel (jit.hpp)
@@ -147,6 +156,18 @@ void launch_thermal_quad(const DeviceImpl& D, const KParams& kp, cudaStream_t st
   const int64_t nblk = (kp.nwork + 127) / 128;
   const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * per_sm * 4);
   kern<<<grid, 128, 0, stream>>>(kp);
+  CUDA_CK(cudaGetLastError());
+}
+
+template <bool T, bool A>
+void launch_thermal_quad_tiled(const DeviceImpl& D, const KParams& kp, size_t acc_bytes, cudaStream_t stream) {
+  auto kern = thermal_quad_q1_tiled_kernel<T, A>;
+  if (acc_bytes > 48 * 1024) CUDA_CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)acc_bytes));
+  int per_sm = 1;
+  CUDA_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, acc_bytes));
+  if (per_sm < 1) per_sm = 1;
+  const unsigned grid = (unsigned)std::min<int64_t>(kp.tile.ntiles, (int64_t)D.num_sms * per_sm * 4);
+  kern<<<grid, 128, acc_bytes, stream>>>(kp);
   CUDA_CK(cudaGetLastError());
 }
 
@@ -233,13 +254,31 @@ int device_assemble(mrh_engine* h, const mrh_state* st, double* res, double* jac
       const bool tr = kp.tp.transient != 0, adv = H.cfg.include_advection != 0, jc = jac != nullptr;
       JitKernel* jk = (H.cfg.flags & 2) ? nullptr : D.jit.thermal(tr, adv, jc);
       D.jit_used = jk != nullptr;
-      D.last_path = jk ? "nvrtc-specialised-2d" : "specialised-2d";
+      const bool tiled = jc && D.tiles && D.tiles->ok && D.tiles->nn == 4 && D.tiles->nk == (adv ? 16 : 10);      // residual-only passes scatter directly
+      if (tiled) fill_tile_params(*D.tiles, kp.tile);
+      const size_t acc_bytes = !tiled ? 0 : adv ? ThermalQuadQ1<false, true, true>::tiled_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r)
+                                                : ThermalQuadQ1<false, false, true>::tiled_smem_bytes(D.tiles->max_acc, D.tiles->max_e, D.tiles->max_r);
+      D.last_path = jk ? (tiled ? "nvrtc-specialised-2d+tiled" : "nvrtc-specialised-2d") : (tiled ? "specialised-2d+tiled" : "specialised-2d");
       if (jk) {
         const int64_t nblk = (kp.nwork + 127) / 128;
-        const unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * jk->blocks_per_sm * 4);
+        unsigned grid = (unsigned)std::min<int64_t>(nblk, (int64_t)D.num_sms * jk->blocks_per_sm * 4);
+        if (tiled) {
+          if (jk->smem_set != acc_bytes) {
+            JitApi& api = JitApi::get();
+            if (acc_bytes > 48 * 1024 && api.FuncSetAttribute(jk->fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)acc_bytes) != CUDA_SUCCESS)
+              throw std::runtime_error("CUDA error: cuFuncSetAttribute(shared memory) failed");
+            if (api.OccupancyMaxActiveBlocks(&jk->tiled_blocks_per_sm, jk->fn, 128, acc_bytes) != CUDA_SUCCESS || jk->tiled_blocks_per_sm < 1) jk->tiled_blocks_per_sm = 1;
+            jk->smem_set = acc_bytes;
+          }
+          grid = (unsigned)std::min<int64_t>(D.tiles->ntiles, (int64_t)D.num_sms * jk->tiled_blocks_per_sm * 4);
+        }
         void* args[] = {(void*)&kp};
-        if (JitApi::get().LaunchKernel(jk->fn, grid, 1, 1, 128, 1, 1, 0, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
+        if (JitApi::get().LaunchKernel(jk->fn, grid, 1, 1, 128, 1, 1, (unsigned)acc_bytes, (CUstream)stream, args, nullptr) != CUDA_SUCCESS)
           throw std::runtime_error("CUDA error: cuLaunchKernel failed for the NVRTC-specialised 2-D kernel");
+      } else if (tiled) {
+#define MRH_FAST2D(T, A) if (tr == T && adv == A) launch_thermal_quad_tiled<T, A>(D, kp, acc_bytes, stream);
+        MRH_FAST2D(false, false) MRH_FAST2D(false, true) MRH_FAST2D(true, false) MRH_FAST2D(true, true)
+#undef MRH_FAST2D
       } else {
 #define MRH_FAST2D(T, A, Jc) if (tr == T && adv == A && jc == Jc) launch_thermal_quad<T, A, Jc>(D, kp, stream);
         MRH_FAST2D(false, false, false) MRH_FAST2D(false, false, true) MRH_FAST2D(false, true, false) MRH_FAST2D(false, true, true)

@@ -5,13 +5,16 @@
 // is the tile's contribution list: thread t of the assembly kernel sums positions [72 t, 72 t + 72).  The distinct
 // destinations give the tile's slot / row lists for the flush.  Contribution lists are de-duplicated into a
 // dictionary (structured meshes collapse to a few dozen lists).
+// The same plan serves the Q1 quadrilateral kernel (assemble_fast2d.h): NN = 4 nodes, 16 + 4 = 20 contributions per element,
+// padded to 24 per thread in the stored lists (pads read the zero cell and never start a run).
 #include <cub/block/block_radix_sort.cuh>
 #include <cub/block/block_scan.cuh>
 
 namespace {
 
 constexpr int TILE_ELEMS = 128;
-constexpr int TILE_NC = 72;                                // contributions per element
+template <int NN> constexpr int tile_nc() { return NN * NN + NN; }                 // contributions per element: 72 (Q1 hex), 20 (Q1 quad)
+template <int NN> constexpr int tile_ncp() { return (tile_nc<NN>() + 7) & ~7; }       // list stride per thread: whole uint4 words
 constexpr int SRC_BITS = 14;                               // entry * 128 + thread < 72 * 128 + 1
 constexpr unsigned long long KEY_SENTINEL = ~0ull;
 constexpr unsigned long long ROW_SPACE = 1ull << 45;       // destination keys: CRS slot | ROW_SPACE + row | masked
@@ -23,14 +26,15 @@ struct TileDev {
   DevBuf<uint32_t> off;
   DevBuf<uint16_t> clist, cbase;
   int64_t ntiles = 0, npatterns = 0;
-  int max_acc = 0, nk = 0, max_e = 0, max_r = 0;
+  int max_acc = 0, nk = 0, max_e = 0, max_r = 0, nn = 8;
   bool ok = false;
   void release() { perm.release(); rows.release(); cl_id.release(); eptr.release(); rptr.release(); base.release(); off.release();
                    clist.release(); cbase.release(); ok = false; }
 };
 
+template <int NN>
 struct TileSmem {
-  typedef cub::BlockRadixSort<unsigned long long, TILE_ELEMS, TILE_NC> Sort;
+  typedef cub::BlockRadixSort<unsigned long long, TILE_ELEMS, tile_nc<NN>()> Sort;
   typedef cub::BlockScan<long long, TILE_ELEMS> Scan;
   union Temp { typename Sort::TempStorage sort; typename Scan::TempStorage scan; };
   Temp temp;
@@ -39,38 +43,42 @@ struct TileSmem {
   unsigned long long first_dest;
 };
 
-// destination keys of the 72 contributions of element e held by thread `tid` (N = 8: Q1 hex, one variable)
+// destination keys of the NN * NN + NN contributions of element e held by thread `tid` (one variable, NN = 8: Q1 hex, 4: Q1 quad)
+template <int NN>
 __device__ __forceinline__ void element_keys(const int* lids, const uint8_t* fixed, const int64_t* rowptr, const int* colind,
-                                             int64_t e, int tid, int nk, unsigned long long (&key)[TILE_NC], int* bad) {
-  const int* l = lids + e * 8;
-  for (int i = 0; i < 8; ++i) {
+                                             int64_t e, int tid, int nk, unsigned long long (&key)[NN * NN + NN], int* bad) {
+  const int* l = lids + e * NN;
+  for (int i = 0; i < NN; ++i) {
     const int li = l[i];
     const bool fx = fixed[li] != 0;
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < NN; ++j) {
       const int s = fx ? -1 : rel_slot(rowptr, colind, li, l[j]);
       if (!fx && s < 0) atomicExch(bad, 1);
-      const int entry = (nk == 64) ? i * 8 + j : (i <= j ? HexQ1::tri(i, j) : HexQ1::tri(j, i));
-      key[i * 8 + j] = (s < 0) ? KEY_SENTINEL : (((unsigned long long)(rowptr[li] + s) << SRC_BITS) | (unsigned)(entry * TILE_ELEMS + tid));
+      const int a = i <= j ? i : j, b = i <= j ? j : i;
+      const int entry = (nk == NN * NN) ? i * NN + j : a * NN - (a * (a - 1)) / 2 + (b - a);      // full or upper-triangular element store
+      key[i * NN + j] = (s < 0) ? KEY_SENTINEL : (((unsigned long long)(rowptr[li] + s) << SRC_BITS) | (unsigned)(entry * TILE_ELEMS + tid));
     }
-    key[64 + i] = fx ? KEY_SENTINEL : (((ROW_SPACE + (unsigned long long)li) << SRC_BITS) | (unsigned)((nk + i) * TILE_ELEMS + tid));
+    key[NN * NN + i] = fx ? KEY_SENTINEL : (((ROW_SPACE + (unsigned long long)li) << SRC_BITS) | (unsigned)((nk + i) * TILE_ELEMS + tid));
   }
 }
 
-template <bool WRITE>
+template <bool WRITE, int NN>
 __global__ void __launch_bounds__(TILE_ELEMS) tile_plan_kernel(const int* perm, int64_t nelem, const int* lids, const uint8_t* fixed,
                                                                const int64_t* rowptr, const int* colind, int nk, int* E_count, int* R_count,
                                                                const int64_t* eptr, const int64_t* rptr, int64_t* tile_base,
                                                                uint32_t* tile_off, int* tile_rows, uint16_t* cl_all, uint16_t* cbase_all,
                                                                uint64_t* tile_hash, int* bad) {
   extern __shared__ __align__(16) unsigned char smraw[];
-  TileSmem& S = *reinterpret_cast<TileSmem*>(smraw);
+  typedef TileSmem<NN> TS;
+  constexpr int TILE_NC = tile_nc<NN>(), TILE_NCP = tile_ncp<NN>();
+  TS& S = *reinterpret_cast<TS*>(smraw);
   const int tid = threadIdx.x;
   const int64_t t = blockIdx.x, e0 = t * TILE_ELEMS + tid;
   unsigned long long key[TILE_NC];
-  if (e0 < nelem) element_keys(lids, fixed, rowptr, colind, (int64_t)perm[e0], tid, nk, key, bad);
+  if (e0 < nelem) element_keys<NN>(lids, fixed, rowptr, colind, (int64_t)perm[e0], tid, nk, key, bad);
   else for (int k = 0; k < TILE_NC; ++k) key[k] = KEY_SENTINEL;
 
-  TileSmem::Sort(S.temp.sort).Sort(key);                   // blocked arrangement: thread t holds positions [72 t, 72 t + 72)
+  typename TS::Sort(S.temp.sort).Sort(key);                // blocked arrangement: thread t holds positions [NC t, NC t + NC)
   S.last[tid] = key[TILE_NC - 1] >> SRC_BITS;
   if (tid == 0) S.first_dest = key[0] >> SRC_BITS;
   __syncthreads();
@@ -86,7 +94,7 @@ __global__ void __launch_bounds__(TILE_ELEMS) tile_plan_kernel(const int* perm, 
     prev = d;
   }
   long long before = 0, total = 0;
-  TileSmem::Scan(S.temp.scan).ExclusiveSum(cnt, before, total);
+  typename TS::Scan(S.temp.scan).ExclusiveSum(cnt, before, total);
   const int E = (int)(total & 0xfffff), R = (int)((total >> 20) & 0xfffff);
   if (!WRITE) { if (tid == 0) { E_count[t] = E; R_count[t] = R; } return; }
 
@@ -94,8 +102,8 @@ __global__ void __launch_bounds__(TILE_ELEMS) tile_plan_kernel(const int* perm, 
   const unsigned long long base = (E > 0) ? S.first_dest : 0ull;
   if (tid == 0) tile_base[t] = (int64_t)base;
   if (E + R > 32000) atomicExch(bad, 4);
-  const int zero_src = (nk + 8) * TILE_ELEMS;
-  uint16_t* out = cl_all + ((size_t)t * TILE_ELEMS + tid) * TILE_NC;
+  const int zero_src = (nk + NN) * TILE_ELEMS;
+  uint16_t* out = cl_all + ((size_t)t * TILE_ELEMS + tid) * TILE_NCP;
   uint64_t h = 0x51ed27ull;
   const int loc0 = starts0 ? run : run - 1;
   cbase_all[(size_t)t * TILE_ELEMS + tid] = (uint16_t)loc0;
@@ -117,44 +125,47 @@ __global__ void __launch_bounds__(TILE_ELEMS) tile_plan_kernel(const int* perm, 
     out[k] = (uint16_t)c; h = mix64(h, c);
     prev = d;
   }
+  for (int k = TILE_NC; k < TILE_NCP; ++k) out[k] = (uint16_t)zero_src;      // pads: add 0.0 to the thread's last run
   S.hash[tid] = h;
   __syncthreads();
   if (tid == 0) { uint64_t g = 0x9d2cull; for (int k = 0; k < TILE_ELEMS; ++k) g = mix64(g, S.hash[k]); tile_hash[t] = g; }
 }
 
-__global__ void clist_fill_kernel(const uint16_t* cl_all, const uint16_t* cbase_all, const int* rep, int64_t npat, uint16_t* clist, uint16_t* cbase) {
+__global__ void clist_fill_kernel(const uint16_t* cl_all, const uint16_t* cbase_all, const int* rep, int64_t npat, uint16_t* clist, uint16_t* cbase, int ncp) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  constexpr int64_t L = (int64_t)TILE_ELEMS * TILE_NC;
+  const int64_t L = (int64_t)TILE_ELEMS * ncp;
   if (k < npat * L) clist[k] = cl_all[(int64_t)rep[k / L] * L + (k % L)];
   if (k < npat * TILE_ELEMS) cbase[k] = cbase_all[(int64_t)rep[k / TILE_ELEMS] * TILE_ELEMS + (k % TILE_ELEMS)];
 }
 // list id of every tile (binary search on the sorted unique hashes) and full verification against the dictionary
 __global__ void clist_assign_kernel(const uint16_t* cl_all, const uint16_t* cbase_all, int64_t ntiles, const uint64_t* hash, const uint64_t* uhash,
-                                    int64_t npat, const uint16_t* clist, const uint16_t* cbase, int* cl_id, int* bad) {
+                                    int64_t npat, const uint16_t* clist, const uint16_t* cbase, int* cl_id, int* bad, int ncp) {
   const int64_t t = blockIdx.x;
   const uint64_t h = hash[t];
   int64_t lo = 0, hi = npat;
   while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (uhash[mid] < h) lo = mid + 1; else hi = mid; }
   if (lo >= npat) { atomicExch(bad, 5); return; }
   if (threadIdx.x == 0) cl_id[t] = (int)lo;
-  constexpr int L = TILE_ELEMS * TILE_NC;
+  const int L = TILE_ELEMS * ncp;
   for (int k = threadIdx.x; k < L; k += blockDim.x) if (clist[lo * L + k] != cl_all[t * L + k]) atomicExch(bad, 5);
   for (int k = threadIdx.x; k < TILE_ELEMS; k += blockDim.x) if (cbase[lo * TILE_ELEMS + k] != cbase_all[t * TILE_ELEMS + k]) atomicExch(bad, 5);
 }
 
 // throws on CUDA errors; leaves T.ok = false (with a reason) when the plan cannot be used
+template <int NN>
 std::string build_tile_plan(const std::vector<int>& perm_host, int64_t nelem, const int* d_lids, const uint8_t* d_fixed,
                             const int64_t* d_rowptr, const int* d_colind, int nk, TileDev& T) {
   T.release();
+  T.nn = NN;
   const int64_t nt = (nelem + TILE_ELEMS - 1) / TILE_ELEMS;
   T.ntiles = nt; T.nk = nk; T.max_e = T.max_r = 0;
   T.perm.upload(perm_host);
   DevBuf<int> Ec, Rc, bad, idx; Ec.alloc(nt); Rc.alloc(nt); bad.alloc(1);
   CUDA_CK(cudaMemset(bad.p, 0, sizeof(int)));
-  const size_t smem = sizeof(TileSmem);
-  CUDA_CK(cudaFuncSetAttribute(tile_plan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  CUDA_CK(cudaFuncSetAttribute(tile_plan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  tile_plan_kernel<false><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, nk, Ec.p, Rc.p,
+  const size_t smem = sizeof(TileSmem<NN>);
+  CUDA_CK(cudaFuncSetAttribute(tile_plan_kernel<false, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CUDA_CK(cudaFuncSetAttribute(tile_plan_kernel<true, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  tile_plan_kernel<false, NN><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, nk, Ec.p, Rc.p,
                                                              nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, bad.p);
   CUDA_CK(cudaGetLastError());
   std::vector<int> hE(nt), hR(nt);
@@ -167,11 +178,11 @@ std::string build_tile_plan(const std::vector<int>& perm_host, int64_t nelem, co
   for (int64_t t = 0; t < nt; ++t) { eptr[t + 1] = eptr[t] + hE[t]; rptr[t + 1] = rptr[t] + hR[t]; max_acc = std::max(max_acc, hE[t] + hR[t]); T.max_e = std::max(T.max_e, hE[t]); T.max_r = std::max(T.max_r, hR[t]); }
   T.max_acc = max_acc;
   T.eptr.upload(eptr); T.rptr.upload(rptr); T.base.alloc(nt);
-  T.off.alloc((size_t)std::max<int64_t>(eptr[nt], 1)); T.rows.alloc((size_t)std::max<int64_t>(rptr[nt], 1));
-  constexpr size_t L = (size_t)TILE_ELEMS * TILE_NC;
+  T.off.alloc((size_t)eptr[nt] + 4); T.rows.alloc((size_t)rptr[nt] + 4);      // + 4: the bulk-copy staging reads whole 16-byte groups
+  constexpr size_t L = (size_t)TILE_ELEMS * tile_ncp<NN>();
   DevBuf<uint16_t> cl_all, cbase_all; cl_all.alloc((size_t)nt * L); cbase_all.alloc((size_t)nt * TILE_ELEMS);
   DevBuf<uint64_t> hash, skey; hash.alloc(nt); skey.alloc(nt); idx.alloc(nt);
-  tile_plan_kernel<true><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, nk, nullptr, nullptr,
+  tile_plan_kernel<true, NN><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, nk, nullptr, nullptr,
                                                             T.eptr.p, T.rptr.p, T.base.p, T.off.p, T.rows.p, cl_all.p, cbase_all.p, hash.p, bad.p);
   CUDA_CK(cudaGetLastError());
   CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
@@ -184,9 +195,9 @@ std::string build_tile_plan(const std::vector<int>& perm_host, int64_t nelem, co
   const int64_t npat = ends.first - kp;
   T.npatterns = npat;
   T.clist.alloc((size_t)npat * L); T.cbase.alloc((size_t)npat * TILE_ELEMS); T.cl_id.alloc(nt);
-  clist_fill_kernel<<<blocks_for(npat * (int64_t)L, 256), 256>>>(cl_all.p, cbase_all.p, idx.p, npat, T.clist.p, T.cbase.p);
+  clist_fill_kernel<<<blocks_for(npat * (int64_t)L, 256), 256>>>(cl_all.p, cbase_all.p, idx.p, npat, T.clist.p, T.cbase.p, tile_ncp<NN>());
   CUDA_CK(cudaGetLastError());
-  clist_assign_kernel<<<(unsigned)nt, 256>>>(cl_all.p, cbase_all.p, nt, hash.p, skey.p, npat, T.clist.p, T.cbase.p, T.cl_id.p, bad.p);
+  clist_assign_kernel<<<(unsigned)nt, 256>>>(cl_all.p, cbase_all.p, nt, hash.p, skey.p, npat, T.clist.p, T.cbase.p, T.cl_id.p, bad.p, tile_ncp<NN>());
   CUDA_CK(cudaGetLastError());
   CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
   if (hbad) { T.release(); return "contribution list dictionary verification failed (hash collision)"; }

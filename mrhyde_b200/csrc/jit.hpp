@@ -267,10 +267,11 @@ class JitCache {
     if (!api.ok) { last_error = api.why; return nullptr; }
     if (coef_src_.empty()) { last_error = "no coefficient source"; return nullptr; }
     auto B = [](bool b) { return b ? "true" : "false"; };
-    if (dim_ == 2) {          // Q1 quadrilaterals: direct-scatter kernel only (assemble_fast2d.h)
+    if (dim_ == 2) {          // Q1 quadrilaterals (assemble_fast2d.h): tile-staged scatter when the launch carries a tile plan, direct scatter otherwise
       K.source = std::string("#include \"assemble_fast2d.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
-          "};\n}\nextern \"C\" __global__ void __launch_bounds__(128) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
-          "  typedef mrh::ThermalQuadQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n"
+          "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB2D) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
+          "  typedef mrh::ThermalQuadQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n" +
+          (jac ? "  extern __shared__ double dsm[];\n  if (kp.tile.ntiles > 0) { Kern::tiled(kp, dsm); return; }\n" : "") +
           "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
           "    Kern::element(kp, e);\n}\n";
     } else {
@@ -300,6 +301,8 @@ class JitCache {
     if (api.CreateProgram(&prog, K.source.c_str(), "mrh_jit_thermal.cu", (int)hdr_src.size(), hdr_src.data(), hdr_name.data()) != NVRTC_SUCCESS) { last_error = "nvrtcCreateProgram failed"; return nullptr; }
     std::string minb = "-DMRH_JIT_MINB=2";                                                          // CTAs of 128 threads per SM the register allocation targets
     if (const char* ev = getenv("MRH_JIT_MINB")) minb = std::string("-DMRH_JIT_MINB=") + ev;          // tuning experiments
+    std::string minb2d = "-DMRH_JIT_MINB2D=3";                                                      // same for the quadrilateral kernel (<= 168 registers)
+    if (const char* ev = getenv("MRH_JIT_MINB2D")) minb2d = std::string("-DMRH_JIT_MINB2D=") + ev;    // tuning experiments
     std::string extra = "-DMRH_JIT_EXTRA=0";
     if (const char* ev = getenv("MRH_JIT_DEFINE")) extra = std::string("-D") + ev;                    // tuning experiments
     std::string creg = "-DMRH_WS_CREG=200", sreg = "-DMRH_WS_SREG=96";                              // 256 * CREG + 128 * SREG <= 384 * 168
@@ -312,12 +315,12 @@ class JitCache {
     std::string creg8 = std::string("-DMRH_WS8_CREG=") + (ws8_ncg == 3 ? "136" : ws8_ncg == 2 ? "200" : "232"), sreg8 = "-DMRH_WS8_SREG=96";
     if (const char* ev = getenv("MRH_WS8_CREG")) creg8 = std::string("-DMRH_WS8_CREG=") + ev;
     if (const char* ev = getenv("MRH_WS8_SREG")) sreg8 = std::string("-DMRH_WS8_SREG=") + ev;
-    std::string cregk = "-DMRH_WSK_CREG=216", sregk = "-DMRH_WSK_SREG=80";                          // 256 * 216 + 128 * 80 = 65536
+    std::string cregk = "-DMRH_WSK_CREG=216", sregk = "-DMRH_WSK_SREG=64";                          // 256 * 216 + 128 * 64 = 63488 <= 384 * 168 (the CTA's pool: a larger sum blocks setmaxnreg.inc forever)
     if (const char* ev = getenv("MRH_WSK_CREG")) cregk = std::string("-DMRH_WSK_CREG=") + ev;
     if (const char* ev = getenv("MRH_WSK_SREG")) sregk = std::string("-DMRH_WSK_SREG=") + ev;
     const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", minb.c_str(), extra.c_str(), creg.c_str(), sreg.c_str(),
-                          ncg8.c_str(), creg8.c_str(), sreg8.c_str(), cregk.c_str(), sregk.c_str()};
-    const nvrtcResult rc = api.CompileProgram(prog, 13, opts);
+                          ncg8.c_str(), creg8.c_str(), sreg8.c_str(), cregk.c_str(), sregk.c_str(), minb2d.c_str()};
+    const nvrtcResult rc = api.CompileProgram(prog, 14, opts);
     size_t ls = 0; api.GetProgramLogSize(prog, &ls);
     if (ls > 1) { K.log.resize(ls); api.GetProgramLog(prog, &K.log[0]); }
     if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + K.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }

@@ -77,7 +77,7 @@ def test_cuda_thermal_quad_kernel_variants(lib, name, p, kw, force_generic, no_j
     r = U.check_case(p, kw, lib, on_gpu=True, force_generic=force_generic, no_jit=no_jit)
     if r["path"] not in ("generic", "batched"):
         assert not force_generic
-        assert r["path"] == ("specialised-2d" if no_jit else "nvrtc-specialised-2d"), r
+        assert r["path"] in (("specialised-2d", "specialised-2d+tiled") if no_jit else ("nvrtc-specialised-2d", "nvrtc-specialised-2d+tiled")), r
     U.check_case(p, kw, lib, on_gpu=True, force_generic=force_generic, no_jit=no_jit, jacobian=False)
 
 
@@ -93,6 +93,19 @@ def test_tiled_scatter_on_ragged_meshes(lib, n):
     p["mesh"]["NX"], p["mesh"]["NY"], p["mesh"]["NZ"] = n
     U.check_case(p, {}, lib, on_gpu=True)
     U.check_case(p, {}, lib, on_gpu=True, no_ws=True)
+
+
+@pytest.mark.parametrize("n", [(5, 3), (16, 8), (37, 19), (64, 40)])
+@pytest.mark.parametrize("no_jit", [False, True])
+def test_tiled_scatter_2d_on_ragged_meshes(lib, n, no_jit):
+    """Q1 quadrilateral kernel with the tile-staged scatter: meshes that do not divide the 16x8 tile, exactly one tile, several tiles;
+    NVRTC-printed and ahead-of-time kernels; distorted nodes and a caller-permuted numbering go through test_foreign_numbering"""
+    p = problems.config_c1(4)
+    p["mesh"]["NX"], p["mesh"]["NY"] = n
+    r = U.check_case(p, {}, lib, on_gpu=True, no_jit=no_jit)
+    assert r["path"] == ("specialised-2d+tiled" if no_jit else "nvrtc-specialised-2d+tiled"), r
+    r = U.check_case(p, {}, lib, on_gpu=True, no_jit=no_jit, no_tiles=True)
+    assert r["path"] == ("specialised-2d" if no_jit else "nvrtc-specialised-2d"), r
 
 
 def test_mid_size_c2_against_oracle(lib):
@@ -313,7 +326,7 @@ def test_non_affine_mesh_nvrtc_batched(lib, name, p, kw):
 def test_baseline_configs_against_oracle_at_parity_sizes(lib, name, p, kw):
     """C2..C5 at 8^3 and 24^3, C1 at 40x40: entry by entry against the oracle, default kernels"""
     r = U.check_case(p, kw, lib, on_gpu=True)
-    assert r["path"] in ("nvrtc-specialised+tiled-ws", "nvrtc-specialised+tiled-ws8", "nvrtc-specialised+tiled-wsk", "batched", "nvrtc-specialised-2d"), r
+    assert r["path"] in ("nvrtc-specialised+tiled-ws", "nvrtc-specialised+tiled-ws8", "nvrtc-specialised+tiled-wsk", "batched", "nvrtc-specialised-2d", "nvrtc-specialised-2d+tiled"), r
     U.check_case(p, kw, lib, on_gpu=True, jacobian=False)
 
 
@@ -333,7 +346,7 @@ def test_every_coefficient_operator_on_the_device(lib, name, p, kw):
     batched kernel, NVRTC-printed batched, generic kernel"""
     state = "(state)" in name
     r = U.check_case(p, kw, lib, on_gpu=True)
-    assert r["path"].replace("-ws8", "-ws").replace("-wsk", "-ws") == ("batched" if state else ("nvrtc-specialised-2d" if p["mesh"]["dim"] == 2 else "nvrtc-specialised+tiled-ws")), r
+    assert r["path"].replace("-ws8", "-ws").replace("-wsk", "-ws").replace("-2d+tiled", "-2d") == ("batched" if state else ("nvrtc-specialised-2d" if p["mesh"]["dim"] == 2 else "nvrtc-specialised+tiled-ws")), r
     U.check_case(p, kw, lib, on_gpu=True, no_jit=True)
     r = U.check_case(p, kw, lib, on_gpu=True, force_generic=True, no_batched=True)
     assert r["path"] == "generic", r
@@ -354,7 +367,7 @@ def test_caller_supplied_numbering_on_the_device(lib, tag, mk, n):
     p = getattr(problems, mk)(n)
     r = U.check_foreign_numbering(p, lib, True, distort=0.2)
     assert r["npatterns"] >= 1
-    want = {"C1": ("nvrtc-specialised-2d",), "C2": ("nvrtc-specialised+tiled-ws", "nvrtc-specialised+tiled-ws8", "nvrtc-specialised+tiled-wsk", "nvrtc-specialised+tiled", "nvrtc-specialised")}.get(tag, ("batched",))
+    want = {"C1": ("nvrtc-specialised-2d", "nvrtc-specialised-2d+tiled"), "C2": ("nvrtc-specialised+tiled-ws", "nvrtc-specialised+tiled-ws8", "nvrtc-specialised+tiled-wsk", "nvrtc-specialised+tiled", "nvrtc-specialised")}.get(tag, ("batched",))
     assert r["path"] in want, r
     U.check_foreign_numbering(p, lib, True, distort=0.2, jacobian=False)
     r = U.check_foreign_numbering(p, lib, True, distort=0.2, force_generic=True, no_batched=True)

@@ -42,8 +42,9 @@ int main() {
   const std::string creg = std::string("-DMRH_WS_CREG=") + (creg_env ? creg_env : "200"), sreg = std::string("-DMRH_WS_SREG=") + (sreg_env ? sreg_env : "96");
   if (getenv("MRH_PROBE_2D"))
     full = std::string("#include \"assemble_fast2d.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + src +
-      "};\n}\nextern \"C\" __global__ void __launch_bounds__(128) k(const __grid_constant__ mrh::KParams kp) {\n"
+      "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) k(const __grid_constant__ mrh::KParams kp) {\n"
       "  typedef mrh::ThermalQuadQ1<false, false, true, mrh::JitCoefs> Kern;\n"
+      "  extern __shared__ double dsm[];\n  if (kp.tile.ntiles > 0) { Kern::tiled(kp, dsm); return; }\n"
       "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
       "    Kern::element(kp, e);\n}\n";
   std::vector<const char*> hs, hn;
