@@ -114,6 +114,11 @@ int mrh_set_bc(mrh_handle h, const char* var, const char* side, int32_t bc_code,
 /* FunctionManager::addFunction(name, expr, location) — src/managers/functionManager.cpp:49-69.
  * Entries of the user's Functions list are added at both "ip" and "side ip" (physicsInterface.cpp:466-483). */
 int mrh_add_function(mrh_handle h, const char* name, const char* expr, const char* location);
+/* Scalar / vector parameter of the input's Parameters block, usable as a leaf `name` (component 0) or `name(k)` / `name(kk)` of the
+ * coefficient expressions (src/managers/functionManager.cpp:270-355).  During assembleJacRes the parameters carry no derivative
+ * with respect to the solution, so they are compiled in as constants of the pass: call again, then mrh_finalize, to change them
+ * (parameter sensitivities - computeParamSteadySeeded - are out of scope).  1 <= n <= 100. */
+int mrh_set_parameter(mrh_handle h, const char* name, const double* values, int32_t n);
 
 /* AssemblyManager::{createGroups, allocateGroupStorage, createWorkset, finalizeFunctions, createFixedDOFs}:
  * compiles the expressions, builds slot-pattern dictionary and fixed-DOF tables, uploads everything. */
@@ -229,8 +234,12 @@ const char* mrh_get_varname(mrh_handle h, int32_t var);
 /* evaluate a registered "ip" function on host doubles at given points (parser known-answer tests) */
 int mrh_eval_function_host(mrh_handle h, const char* name, const char* location, int64_t npts, const double* xyz,
                            double time, double* out);
-/* which volume kernel the last assemble call used: "nvrtc-specialised", "specialised" (in-kernel bytecode
- * interpreter) or "generic" */
+/* which volume kernel the last assemble call used:
+ *   thermal Q1 hexahedra   "nvrtc-specialised+tiled-ws" (default with a Jacobian; "-ws8" / "-wsk": experimental variants behind
+ *                          MRH_WS8=1 / MRH_WSK=1), "nvrtc-specialised+tiled", "nvrtc-specialised" (residual-only passes, or no tile
+ *                          plan), "specialised+tiled", "specialised" (ahead-of-time build with the in-kernel bytecode interpreter)
+ *   thermal Q1 quadrilaterals   "nvrtc-specialised-2d+tiled", "nvrtc-specialised-2d", "specialised-2d+tiled", "specialised-2d"
+ *   every other module / order  "nvrtc-batched", "batched", and "generic" as the last resort */
 const char* mrh_last_kernel_path(mrh_handle h);
 /* number of kernels launched by the last assemble call (bench.py "gpu_launches") */
 int64_t mrh_last_launch_count(mrh_handle h);

@@ -40,6 +40,8 @@ MRH_HD void wv_mma(WV& c0, WV& c1, const WV& a, const WV& b) {
                : "+d"(c0.x), "+d"(c1.x) : "d"(a.x), "d"(b.x));
 }
 MRH_HD void warp_sync() { __syncwarp(); }
+// value of lane src(lane) (a full-warp shuffle)
+template <class F> MRH_HD WV wv_shfl(const WV& v, F src) { return WV{__shfl_sync(0xffffffffu, v.x, src((int)(threadIdx.x & 31)))}; }
 #else
 struct WV { double x[32]; };
 MRH_HD double wv_get(const WV& v, int lane) { return v.x[lane]; }
@@ -56,6 +58,7 @@ MRH_HD void wv_mma(WV& c0, WV& c1, const WV& a, const WV& b) {
   }
 }
 MRH_HD void warp_sync() {}
+template <class F> MRH_HD WV wv_shfl(const WV& v, F src) { WV r; for (int l = 0; l < 32; ++l) r.x[l] = v.x[src(l)]; return r; }
 #endif
 
 MRH_HD void st2(double* p, double a, double b) {
@@ -367,9 +370,31 @@ struct BatPhases {
     for (int rt = 0; rt < NRT; ++rt) { A.r[rt][0] = wv_zero(); A.r[rt][1] = wv_zero(); }
     // basis fragments of point q: loaded (Q1) or rebuilt from J^-1 and the reference tables (larger bases) one point
     // ahead, so that their loads overlap the DMMAs of the current point
+    // Bases that do not store T (Q2): the fragment is itself a tensor product, T_q (8 x 4) = (B | G)_q (8 x 4, reference table
+    // in fragment order, RefTab::FR) x M_q (4 x 4) with M = diag(1, J^-1) - one coalesced load, one DMMA and two shuffles that turn
+    // the product's C layout (lane 4 j + p holds columns 2 p, 2 p + 1) into the A layout (lane 4 j + a holds column a), against
+    // three gathers and three predicated FMAs per lane before (profiles/r1_batched_final_C3: 2/3 of the instructions of C3)
     auto basis_frag = [&](int q, int rt) {
-      const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
-      return wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? (STORE_T ? sm[L.oT() + (size_t)q * NB * TA + j * TA + a] : basis_entry(tb, Ji, q, j, a)) : 0.0; });
+      if constexpr (STORE_T) {
+        return wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? sm[L.oT() + (size_t)q * NB * TA + j * TA + a] : 0.0; });
+#if defined(MRH_BAT_FRAG_GATHER)                // previous form, kept for A/B timing (MRH_BAT_DEFINE=MRH_BAT_FRAG_GATHER)
+      } else if constexpr (true) {
+        const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
+        return wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? basis_entry(tb, Ji, q, j, a) : 0.0; });
+#endif
+      } else {
+        const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
+        const double* fr = tb.FR + ((size_t)q * NRT + rt) * 32;
+        const WV ref = wv_make([&](int lane) { return fr[lane]; });
+        const WV mf = wv_make([&](int lane) {          // B operand: M[k = lane % 4][n = lane / 4]
+          const int k = lane & 3, n = lane >> 2;
+          return (k == 0 && n == 0) ? 1.0 : (k >= 1 && k <= DIM && n >= 1 && n <= DIM) ? Ji[(k - 1) * DIM + (n - 1)] : 0.0; });
+        WV c0 = wv_zero(), c1 = wv_zero();
+        wv_mma(c0, c1, ref, mf);
+        const WV s0 = wv_shfl(c0, [](int lane) { return (lane & ~3) | ((lane & 3) >> 1); });
+        const WV s1 = wv_shfl(c1, [](int lane) { return (lane & ~3) | ((lane & 3) >> 1); });
+        return wv_make([&](int lane) { return (lane & 1) ? wv_get(s1, lane) : wv_get(s0, lane); });
+      }
     };
     WV tfn[NRT];
 #pragma unroll

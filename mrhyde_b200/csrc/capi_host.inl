@@ -186,6 +186,11 @@ int mrh_add_function(mrh_handle h, const char* name, const char* expr, const cha
   MRH_CATCH(h)
 }
 
+int mrh_set_parameter(mrh_handle h, const char* name, const double* values, int32_t n) {
+  if (!h || !name || !values || n < 1 || n > 100) return MRH_EINVAL;
+  MRH_TRY(h) h->host.setParameter(name, values, n); h->host.host_final = false; return MRH_OK; MRH_CATCH(h)
+}
+
 int mrh_finalize_host(mrh_handle h) {
   if (!h) return MRH_EINVAL;
   MRH_TRY(h) h->host.finalizeHost(); return MRH_OK; MRH_CATCH(h)

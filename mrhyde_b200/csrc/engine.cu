@@ -37,7 +37,7 @@ struct DevBuf {
   void upload(const std::vector<T>& v) { upload(v.data(), v.size()); }
 };
 
-struct TabDev { DevBuf<double> B, G, VB, VG, W; };
+struct TabDev { DevBuf<double> B, G, VB, VG, W, FR; };
 struct ExchangeDev;                    // exchange.inl
 
 struct DeviceImpl {

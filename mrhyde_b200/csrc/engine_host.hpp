@@ -94,6 +94,13 @@ class EngineHost {
     plan.build_send(part, crs);
   }
 
+  // scalar / vector parameter usable as a leaf of coefficient expressions (`name`, `name(k)`; the reference's Parameters block,
+  // functionManager.cpp:270-355).  Its values are constants of the assembly pass: set again + mrh_finalize to change them.
+  std::vector<std::pair<std::string, std::vector<double>>> parameters;
+  void setParameter(const std::string& name, const double* vals, int n) {
+    for (auto& pr : parameters) if (pr.first == name) { pr.second.assign(vals, vals + n); return; }
+    parameters.push_back({name, std::vector<double>(vals, vals + n)});
+  }
   void addUserFunction(const std::string& name, const std::string& expr, const std::string& location) {
     bool seen = false;
     for (auto& f : user_fns) if (f.first == name) seen = true;
@@ -113,7 +120,7 @@ class EngineHost {
   void finalizeHost() {
     if (!have_mesh || !have_dofs || !have_crs) throw std::runtime_error("mesh, dofmap and CRS graph must be set before finalize");
     // fresh registry: module functions first, then BC functions, then the user's list (first wins)
-    ec = ExprCompiler(); ec.varlist = varlist; ec.dim = dim;
+    ec = ExprCompiler(); ec.varlist = varlist; ec.dim = dim; ec.parameters = parameters;
     defineModuleFunctions();
     const int nsides = (int)mesh.sides.size();
     var_bcs.assign(nvar, std::vector<int>(nsides, MRH_BC_NONE));

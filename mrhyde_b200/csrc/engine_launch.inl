@@ -14,9 +14,9 @@ constexpr int XCH_RESERVE_SMS = 4;     // SMs the interior launch leaves free fo
 namespace {
 
 RefTab upload_tab(TabDev& D, const PointTables& T) {
-  D.B.upload(T.B); D.G.upload(T.G); D.VB.upload(T.VB); D.VG.upload(T.VG); D.W.upload(T.W);
+  D.B.upload(T.B); D.G.upload(T.G); D.VB.upload(T.VB); D.VG.upload(T.VG); D.W.upload(T.W); D.FR.upload(T.FR);
   RefTab r{};
-  r.B = D.B.p; r.G = D.G.p; r.VB = D.VB.p; r.VG = D.VG.p; r.W = D.W.p; r.nq = T.nq;
+  r.FR = D.FR.p; r.B = D.B.p; r.G = D.G.p; r.VB = D.VB.p; r.VG = D.VG.p; r.W = D.W.p; r.nq = T.nq;
   for (int c = 0; c < 3; ++c) { r.tanU[c] = T.tanU[c]; r.tanV[c] = T.tanV[c]; }
   return r;
 }

@@ -25,6 +25,7 @@ struct FunctionTable {
 class ExprCompiler {
  public:
   std::vector<std::string> varlist;
+  std::vector<std::pair<std::string, std::vector<double>>> parameters;     // scalar / vector parameters: leaves `name`, `name(k)`
   int dim = 3;
   std::vector<FunctionTable> tables;       // one per location
   std::vector<Instr> code;                 // all compiled programs, concatenated
@@ -97,6 +98,21 @@ class ExprCompiler {
     if (op == OP_NIP) return -1;
     return 0;
   }
+  bool findParameter(const std::string& expr, double& val) const {
+    for (auto& pr : parameters) {
+      const std::string& nm = pr.first; const size_t L = nm.length(), n = expr.length();
+      int idx = -1;
+      if (expr == nm) idx = 0;
+      else if (n == L + 3 && expr.compare(0, L, nm) == 0 && expr[n - 3] == '(' && expr[n - 1] == ')' && isdigit((unsigned char)expr[n - 2])) idx = expr[n - 2] - '0';
+      else if (n == L + 4 && expr.compare(0, L, nm) == 0 && expr[n - 4] == '(' && expr[n - 1] == ')' && isdigit((unsigned char)expr[n - 3]) && isdigit((unsigned char)expr[n - 2]))
+        idx = (expr[n - 3] - '0') * 10 + (expr[n - 2] - '0');
+      if (idx >= 0) {
+        if (idx >= (int)pr.second.size()) throw std::runtime_error("parameter component out of range: " + expr);
+        val = pr.second[idx]; return true;
+      }
+    }
+    return false;
+  }
   int constIndex(double v) { cpool.push_back(v); return (int)cpool.size() - 1; }
 
   int fieldId(const std::string& e) const {
@@ -133,6 +149,8 @@ class ExprCompiler {
       static const char* nn[6] = {"n[x]", "n[y]", "n[z]", "t[x]", "t[y]", "t[z]"};
       for (int c = 0; c < 6; ++c) if (expr == nn[c]) { out.push_back({(uint8_t)(OP_NX + c), 0, 0}); return; }
     }
+    // 2b. parameters: `name` is component 0, `name(k)` / `name(kk)` component k (functionManager.cpp:270-355); constants of the pass
+    { double pv = 0.0; if (findParameter(expr, pv)) { out.push_back({(uint8_t)OP_CONST, 0, (uint16_t)constIndex(pv)}); return; } }
     // 3. another function of the same location
     { const int j = T.find(expr); if (j >= 0) { emit(T, T.fns[j].second, out, state, depth + 1); return; } }
     // 4. literal, time, pi

@@ -375,8 +375,10 @@ class JitCache {
     for (int i = 0; i < k_num_embedded_headers; ++i) { hdr_name.push_back(k_embedded_headers[i].name); hdr_src.push_back(k_embedded_headers[i].text); }
     nvrtcProgram prog;
     if (api.CreateProgram(&prog, bat_.source.c_str(), "mrh_jit_batched.cu", (int)hdr_src.size(), hdr_src.data(), hdr_name.data()) != NVRTC_SUCCESS) { last_error = "nvrtcCreateProgram failed"; return nullptr; }
-    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", bat_bounds_.c_str()};
-    const nvrtcResult rc = api.CompileProgram(prog, 5, opts);
+    std::string bat_extra = "-DMRH_BAT_EXTRA=0";
+    if (const char* ev = getenv("MRH_BAT_DEFINE")) bat_extra = std::string("-D") + ev;               // tuning experiments
+    const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", bat_bounds_.c_str(), bat_extra.c_str()};
+    const nvrtcResult rc = api.CompileProgram(prog, 6, opts);
     size_t ls = 0; api.GetProgramLogSize(prog, &ls);
     if (ls > 1) { bat_.log.resize(ls); api.GetProgramLog(prog, &bat_.log[0]); }
     if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + bat_.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }

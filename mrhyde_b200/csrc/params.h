@@ -25,6 +25,7 @@ struct RefTab {          // reference-element tables of one point set (volume ru
   const double* VB;      // [nq][NV]       vertex (geometry) basis values, shards vertex order
   const double* VG;      // [nq][NV][DIM]  vertex basis reference gradients
   const double* W;       // [nq]           reference weights
+  const double* FR;      // [nq][ceil(NB / 8)][32]  (B | G) in DMMA A-fragment order (batched kernel, bases that do not store T)
   int nq;
   int pad_;
   double tanU[3], tanV[3];   // reference side tangents (side launches only)

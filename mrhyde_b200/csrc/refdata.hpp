@@ -14,6 +14,7 @@ namespace mrh {
 struct PointTables {            // point-major layout consumed by the kernels (params.h RefTab)
   int nq = 0;
   std::vector<double> B, G, VB, VG, W, pts;
+  std::vector<double> FR;         // [nq][ceil(nb / 8)][32]: (B | G) in DMMA A-fragment order, lane = 4 (j % 8) + a (a = 0: value, 1 + m: d/dxi_m)
   double tanU[3] = {0, 0, 0}, tanV[3] = {0, 0, 0};
 };
 
@@ -124,9 +125,15 @@ class RefElement {
     T.B.assign((size_t)T.nq * nb, 0.0); T.G.assign((size_t)T.nq * nb * dim, 0.0);
     T.VB.assign((size_t)T.nq * nv, 0.0); T.VG.assign((size_t)T.nq * nv * dim, 0.0);
     std::vector<double> tv(27), tg(81);
+    const int nrt = (nb + 7) / 8;
+    T.FR.assign((size_t)T.nq * nrt * 32, 0.0);
     for (int q = 0; q < T.nq; ++q) {
       tensor(p, &T.pts[(size_t)q * dim], tv.data(), tg.data());
       for (int o = 0; o < nb; ++o) { T.B[(size_t)q * nb + o] = tv[o]; for (int c = 0; c < dim; ++c) T.G[((size_t)q * nb + o) * dim + c] = tg[o * dim + c]; }
+      for (int o = 0; o < nb; ++o) {
+        double* fr = &T.FR[((size_t)q * nrt + o / 8) * 32 + (o % 8) * 4];
+        fr[0] = tv[o]; for (int c = 0; c < dim; ++c) fr[1 + c] = tg[o * dim + c];
+      }
       tensor(1, &T.pts[(size_t)q * dim], tv.data(), tg.data());
       for (int o = 0; o < nv; ++o) { const int s = t2s[o]; T.VB[(size_t)q * nv + s] = tv[o]; for (int c = 0; c < dim; ++c) T.VG[((size_t)q * nv + s) * dim + c] = tg[o * dim + c]; }
     }

@@ -40,7 +40,7 @@ class MrhSolverInfo(C.Structure):
 
 
 SYMBOLS = ["mrh_default_config", "mrh_create", "mrh_destroy", "mrh_last_error", "mrh_build_brick", "mrh_set_mesh", "mrh_set_nodes",
-           "mrh_set_dofmap", "mrh_set_crs", "mrh_add_side", "mrh_set_bc", "mrh_add_function", "mrh_finalize",
+           "mrh_set_dofmap", "mrh_set_crs", "mrh_add_side", "mrh_set_bc", "mrh_add_function", "mrh_set_parameter", "mrh_finalize",
            "mrh_finalize_host", "mrh_assemble_res", "mrh_assemble_jacres", "mrh_assemble_jacres_host", "mrh_assemble_res_host_static",
            "mrh_get_sizes", "mrh_get_mesh", "mrh_get_dofmap", "mrh_get_crs", "mrh_get_side", "mrh_get_bc",
            "mrh_get_varname", "mrh_eval_function_host", "mrh_last_launch_count", "mrh_last_volume_kernel_ms",
@@ -90,6 +90,7 @@ def load_library(path=None):
     _bind(L, "mrh_add_side", "argtypes", [C.c_void_p, C.c_char_p, C.c_int32, C.c_void_p, C.c_int64])
     _bind(L, "mrh_set_bc", "argtypes", [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_char_p])
     _bind(L, "mrh_add_function", "argtypes", [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p])
+    _bind(L, "mrh_set_parameter", "argtypes", [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.c_int32])
     _bind(L, "mrh_assemble_res", "argtypes", [C.c_void_p, C.POINTER(MrhState), C.c_void_p])
     _bind(L, "mrh_assemble_jacres", "argtypes", [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p])
     _bind(L, "mrh_assemble_jacres_host", "argtypes", [C.c_void_p, C.POINTER(MrhState), C.c_void_p, C.c_void_p])
@@ -208,6 +209,8 @@ class Engine:
             e.build_brick(n, lo, hi)
         else:                                    # (procs, rank): this rank's block of the global brick
             e.build_brick_part(n, lo, hi, part[0], part[1])
+        for name, vals in p.get("parameters", {}).items():
+            e.set_parameter(name, vals)
         for name, expr in p.get("functions", {}).items():       # physicsInterface.cpp:466-483: both locations
             e.add_function(name, expr, "ip")
             e.add_function(name, expr, "side ip")
@@ -320,6 +323,11 @@ class Engine:
     def add_function(self, name, expr, location="ip"):
         self._ck(self.L.mrh_add_function(self.h, name.encode(), str(expr).encode(), location.encode()),
                  "mrh_add_function")
+
+    def set_parameter(self, name, values):
+        """scalar / vector parameter usable as a leaf `name` / `name(k)` of coefficient expressions (constant of the pass)"""
+        v = np.ascontiguousarray(np.atleast_1d(values), dtype=np.float64)
+        self._ck(self.L.mrh_set_parameter(self.h, name.encode(), v.ctypes.data_as(C.POINTER(C.c_double)), len(v)), "mrh_set_parameter")
 
     def finalize(self):
         self._ck(self.L.mrh_finalize(self.h), "mrh_finalize")

@@ -57,6 +57,8 @@ def config_text(**kw):
         lines.append(f"{k}: {str(v).lower() if isinstance(v, bool) else v}")
     for k, v in kw.get("functions", {}).items():
         lines.append(f"function.{k}: {v}")
+    for k, v in kw.get("parameters", {}).items():
+        lines.append(f"parameter.{k}: " + " ".join(repr(float(x)) for x in np.atleast_1d(v)))
     for k, v in kw.get("settings", {}).items():
         lines.append(f"setting.{k}: {str(v).lower() if isinstance(v, bool) else v}")
     for sec in ("dirichlet", "neumann", "flux"):

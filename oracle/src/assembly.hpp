@@ -27,6 +27,7 @@ struct Config {
   int order = 1, quadrature = -1, side_quadrature = -1, workset = 100;
   bool transient = false, weak_dbc = false, strong_dbc = true, fix_zero_rows = false, lump_mass = false;
   StrMap functions, settings;
+  std::vector<std::pair<std::string, std::vector<double>>> parameters;      // "parameter.<name>: v0 v1 ..." (scalar / vector parameters, constants of the pass)
   std::map<std::string, StrMap> dirichlet, neumann, flux;   // [var][side or "all boundaries"] -> expr
 
   static std::string trim(const std::string& s) {
@@ -57,6 +58,10 @@ struct Config {
       else if (k == "lump mass") lump_mass = (v == "true");
       else if (pre("function.")) functions[k.substr(9)] = v;
       else if (pre("setting.")) settings[k.substr(8)] = v;
+      else if (pre("parameter.")) {      // (strtod, not operator>>: a process that loaded another libstdc++ first must not resolve our stream extraction into it)
+        std::vector<double> vals; const char* s = v.c_str(); char* end = nullptr;
+        for (double x = strtod(s, &end); end != s; x = strtod(s, &end)) { vals.push_back(x); s = end; }
+        parameters.push_back({k.substr(10), vals}); }
       else if (pre("dirichlet.") || pre("neumann.") || pre("flux.")) {
         const size_t d1 = k.find('.'), d2 = k.find('.', d1 + 1);
         const std::string var = k.substr(d1 + 1, d2 - d1 - 1), side = k.substr(d2 + 1);
@@ -249,6 +254,7 @@ class Oracle {
     wk.butcher_A = ti.A; wk.butcher_b = ti.b; wk.BDF_wts = ti.bdf; wk.nstages = ti.nstages;
     FunctionManager<EvalT> fm(maxElem, ref.nq, ref.nqs); fm.wkset = &wk;
     auto module = importPhysics<EvalT>(cfg.physics, cfg.settings, cfg.dim);
+    fm.parameters = cfg.parameters;
     module->defineFunctions(cfg.functions, &fm);
     for (auto& f : sideFunctions) fm.addFunction(f.first, f.second, "side ip");
     // every entry of the user "Functions" list, both locations (physicsInterface.cpp:466-483)
@@ -363,6 +369,7 @@ class Oracle {
     wk.var_bcs = var_bcs; wk.time = time;
     FunctionManager<double> fm(maxElem, ref.nq, ref.nqs); fm.wkset = &wk;
     auto module = importPhysics<double>(cfg.physics, cfg.settings, cfg.dim);
+    fm.parameters = cfg.parameters;
     module->defineFunctions(cfg.functions, &fm);
     for (auto& f : sideFunctions) fm.addFunction(f.first, f.second, "side ip");
     for (auto& f : cfg.functions) { fm.addFunction(f.first, f.second, "ip"); fm.addFunction(f.first, f.second, "side ip"); }

@@ -65,6 +65,23 @@ class FunctionManager {
   std::vector<std::string> known_ops{"sin", "cos", "exp", "log", "tan", "abs", "max", "min", "mean",
                                      "emax", "emin", "emean", "sqrt", "sinh", "cosh"};
 
+  std::vector<std::pair<std::string, std::vector<double>>> parameters;
+  bool findParameter(const std::string& expr, double& val) const {
+    for (auto& pr : parameters) {
+      const std::string& nm = pr.first; const size_t L = nm.length(), n = expr.length();
+      int idx = -1;
+      if (expr == nm) idx = 0;
+      else if (n == L + 3 && expr.compare(0, L, nm) == 0 && expr[n - 3] == '(' && expr[n - 1] == ')' && isdigit((unsigned char)expr[n - 2])) idx = expr[n - 2] - '0';
+      else if (n == L + 4 && expr.compare(0, L, nm) == 0 && expr[n - 4] == '(' && expr[n - 1] == ')' && isdigit((unsigned char)expr[n - 3]) && isdigit((unsigned char)expr[n - 2]))
+        idx = (expr[n - 3] - '0') * 10 + (expr[n - 2] - '0');
+      if (idx >= 0) {
+        if (idx >= (int)pr.second.size()) throw std::runtime_error("oracle funcman: parameter component out of range: " + expr);
+        val = pr.second[idx]; return true;
+      }
+    }
+    return false;
+  }
+
   FunctionManager(int num_elem, int num_ip, int num_ip_side) {
     forests.resize(2);
     forests[0].location = "ip"; forests[0].dim0 = num_elem; forests[0].dim1 = num_ip;
@@ -194,6 +211,12 @@ class FunctionManager {
               auto& L = side ? wkset->side_scalar_fields : wkset->scalar_fields;
               for (size_t j = 0; j < L.size() && decompose; ++j) if (expr == L[j].expr) {
                 decompose = false; br[k].is_leaf = br[k].is_decomposed = br[k].is_view = br[k].is_workset_data = true; br[k].is_AD = false; br[k].workset_data_index = (int)j; }
+            }
+            // parameters: `name` is component 0, `name(k)` / `name(kk)` component k (functionManager.cpp:270-355).  During
+            // assembleJacRes the parameters are not seeded with respect to the solution, so the leaf is a constant of the pass
+            if (decompose) {
+              double pv = 0.0;
+              if (findParameter(expr, pv)) { br[k].is_leaf = br[k].is_decomposed = br[k].is_constant = true; br[k].sSc = pv; decompose = false; }
             }
             if (decompose) for (size_t j = 0; j < F.trees.size(); j++) if (expr == F.trees[j].name) { br[k].is_decomposed = true; br[k].is_func = true; br[k].func_index = (int)j; decompose = false; }
             if (decompose && interp_isScalar(expr)) { br[k].is_leaf = br[k].is_decomposed = br[k].is_constant = true; br[k].sSc = std::stod(expr); decompose = false; }

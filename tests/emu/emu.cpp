@@ -71,7 +71,7 @@ static int emu_assemble(mrh_engine* h, const mrh_state* st, double* res, double*
   bp.nodes = H.mesh.nodes.data(); bp.e2n = H.mesh.elem2node.data(); bp.lids = H.dofs.lids.data(); bp.fixed = H.isFixed.data();
   bp.rowptr = H.crs.rowptr.data(); bp.pat = E->pat.data(); bp.pat_id = E->pat_id.data();
   bp.code = H.ec.code.data(); bp.cpool = H.ec.cpool.data();
-  auto tab = [](const PointTables& T) { RefTab r{}; r.B = T.B.data(); r.G = T.G.data(); r.VB = T.VB.data(); r.VG = T.VG.data(); r.W = T.W.data(); r.nq = T.nq;
+  auto tab = [](const PointTables& T) { RefTab r{}; r.B = T.B.data(); r.G = T.G.data(); r.VB = T.VB.data(); r.VG = T.VG.data(); r.W = T.W.data(); r.FR = T.FR.data(); r.nq = T.nq;
     for (int c = 0; c < 3; ++c) { r.tanU[c] = T.tanU[c]; r.tanV[c] = T.tanV[c]; } return r; };
   bp.vol_tab = tab(H.ref.vol);
   for (int s = 0; s < H.ref.nsides; ++s) bp.side_tab[s] = tab(H.ref.side[s]);
@@ -191,7 +191,7 @@ int mrh_assemble_projection(mrh_handle h, int32_t kind, double time, double* rhs
   bp.nodes = H.mesh.nodes.data(); bp.e2n = H.mesh.elem2node.data(); bp.lids = H.dofs.lids.data(); bp.fixed = H.isFixed.data();
   bp.rowptr = H.crs.rowptr.data(); bp.pat = E->pat.data(); bp.pat_id = E->pat_id.data();
   bp.code = H.ec.code.data(); bp.cpool = H.ec.cpool.data();
-  auto tab = [](const PointTables& T) { RefTab r{}; r.B = T.B.data(); r.G = T.G.data(); r.VB = T.VB.data(); r.VG = T.VG.data(); r.W = T.W.data(); r.nq = T.nq;
+  auto tab = [](const PointTables& T) { RefTab r{}; r.B = T.B.data(); r.G = T.G.data(); r.VB = T.VB.data(); r.VG = T.VG.data(); r.W = T.W.data(); r.FR = T.FR.data(); r.nq = T.nq;
     for (int c = 0; c < 3; ++c) { r.tanU[c] = T.tanU[c]; r.tanV[c] = T.tanV[c]; } return r; };
   bp.vol_tab = tab(H.ref.vol);
   for (int s = 0; s < H.ref.nsides; ++s) bp.side_tab[s] = tab(H.ref.side[s]);

@@ -162,6 +162,15 @@ def opcode_cases():
         p = shrink(P.regression_thermal_3d()); p["name"] = "opcode(state) " + op
         p["functions"] = dict(p["functions"]); p["functions"]["thermal diffusion"] = ex
         out.append((p["name"], p, {}))
+    # parameter leaves: `kap` is component 0 of a vector parameter, `kap(2)` component 2 (functionManager.cpp:270-355)
+    p = shrink(P.regression_thermal_3d()); p["name"] = "opcode parameter"
+    p["functions"] = dict(p["functions"]); p["functions"]["thermal diffusion"] = "kap+kap(2)*x*y+amp*z"
+    p["parameters"] = {"kap": [1.25, -7.0, 0.5], "amp": 0.75}
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_thermal_3d()); p["name"] = "opcode(state) parameter"
+    p["functions"] = dict(p["functions"]); p["functions"]["thermal diffusion"] = "kap+amp*e*e"
+    p["parameters"] = {"kap": [1.25], "amp": 0.75}
+    out.append((p["name"], p, {}))
     p = shrink(P.regression_thermal_2d()); p["name"] = "opcode 2D mix"
     p["functions"] = dict(p["functions"]); p["functions"]["thermal diffusion"] = "1.0+(x<0.5)*sqrt(y)+min(x,y)^2"
     out.append((p["name"], p, {}))
