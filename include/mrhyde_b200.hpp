@@ -325,6 +325,20 @@ class AssemblyManager {
       mrh_handle h = need(set);
       wkset[set]->varlist = modules[set]->myvars; wkset[set]->dimension = dimension;
       modules[set]->setWorkset(wkset[set]);
+      // "Parameters" block (src/managers/parameterManager.cpp:85-118): type scalar -> `value`, type vector -> the numbers of the
+      // file named by `source`; leaves of the coefficient expressions, constants of the assembly pass
+      if (settings->isSublist("Parameters"))
+        for (auto& pr : settings->sublist("Parameters").sublists()) {
+          const string type = pr.second.template get<string>("type", "scalar");
+          vector<double> vals;
+          if (type == "scalar") vals.push_back(pr.second.template get<double>("value", 0.0));
+          else if (type == "vector") {
+            std::ifstream fin(pr.second.template get<string>("source", ""));
+            double x; while (fin >> x) vals.push_back(x);
+            if (vals.empty()) throw std::runtime_error("parameter '" + pr.first + "': no values in its source file");
+          } else continue;                                         // (discretized parameters have no counterpart here)
+          check(mrh_set_parameter(h, pr.first.c_str(), vals.data(), (int32_t)vals.size()), h, "mrh_set_parameter");
+        }
       modules[set]->defineFunctions(settings->sublist("Functions"), function_managers[set]);
       static const struct { const char* list; int code; } kinds[3] = {{"Dirichlet conditions", MRH_BC_DIRICHLET}, {"Neumann conditions", MRH_BC_NEUMANN}, {"Flux conditions", MRH_BC_FLUX}};
       for (auto& k : kinds) {

@@ -140,8 +140,11 @@ struct PointBat {
   MRH_HD const S& Ut(int m) const { return f[m][4]; }
 };
 
-template <class C>
+// SIDES = false compiles the side-launch branches away (volume-only kernels: the NVRTC build and the ahead-of-time volume
+// instantiation; measured on B200, C4 192^3: 86 ms with the branches present in the volume kernel against 61 ms without)
+template <class C, bool SIDES = true>
 struct BatPhases {
+  MRH_HD static bool is_side(const KParams& kp) { if constexpr (SIDES) return kp.is_side != 0; else return false; }
   static constexpr int DIM = C::DIM, NB = C::NB, NV = C::NV, N = C::N, NVAR = C::NVAR, P = C::P, TA = C::TA;
   // lane chunk of the point phase: LCH of the P = NVAR (1 + dim) point-state lanes per work item.  Default one chunk per
   // variable (u_m, grad u_m).  MRH_NS_HALF_CHUNKS: 3-D Navier-Stokes with half a variable per item (PAD<2>, 168 instead of
@@ -174,7 +177,7 @@ struct BatPhases {
       }
     }
     const double det = det_inv<DIM>(J, Ji);
-    if (part == 0 && kp.is_side) {
+    if (part == 0 && is_side(kp)) {
       // side launch: weight = |J t_U x J t_V| w (3-D) or |J t| w (2-D), unit outward normal (discretizationInterface.cpp:1681-1787)
       double nrm[3] = {0.0, 0.0, 0.0}, tng[3] = {0.0, 0.0, 0.0}, measure;
       if (DIM == 2) {
@@ -226,7 +229,7 @@ struct BatPhases {
     PointState<double> pd;
     for (int c = 0; c < 3; ++c) {
       pd.x[c] = sm[L.oXq() + (size_t)q * 3 + c];
-      pd.nrm[c] = kp.is_side ? sm[L.oNrm() + (size_t)q * 6 + c] : 0.0; pd.tng[c] = kp.is_side ? sm[L.oNrm() + (size_t)q * 6 + 3 + c] : 0.0;
+      pd.nrm[c] = is_side(kp) ? sm[L.oNrm() + (size_t)q * 6 + c] : 0.0; pd.tng[c] = is_side(kp) ? sm[L.oNrm() + (size_t)q * 6 + 3 + c] : 0.0;
     }
     pd.time = kp.tp.time; pd.fields = nullptr;
     sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = eval_code<double>(kp.code, kp.cpool, kp.progs[k].start, kp.progs[k].len, pd);
@@ -261,7 +264,7 @@ struct BatPhases {
           fv[0] += uj * b;
 #pragma unroll
           for (int c = 0; c < DIM; ++c) fv[1 + c] += uj * T[j * TA + 1 + c];
-          if (tr && !kp.is_side) fv[4] += Ud[slot] * b;
+          if (tr && !is_side(kp)) fv[4] += Ud[slot] * b;
         }
       } else {
         double gr[DIM];
@@ -273,7 +276,7 @@ struct BatPhases {
           fv[0] += uj * b;
 #pragma unroll
           for (int c = 0; c < DIM; ++c) gr[c] += uj * tb.G[(q * NB + j) * DIM + c];
-          if (tr && !kp.is_side) fv[4] += Ud[slot] * b;
+          if (tr && !is_side(kp)) fv[4] += Ud[slot] * b;
         }
 #pragma unroll
         for (int c = 0; c < DIM; ++c) {
@@ -289,7 +292,7 @@ struct BatPhases {
       for (int k = 0; k <= DIM; ++k)
 #pragma unroll
         for (int l = 0; l < LCH; ++l) if (m * TA + k == lane0 + l) in.f[m][k].d[l] = au;
-      if (tr && !kp.is_side) {
+      if (tr && !is_side(kp)) {
 #pragma unroll
         for (int l = 0; l < LCH; ++l) if (m * TA == lane0 + l) in.f[m][4].d[l] = kp.tp.alpha_t;
       }
@@ -307,16 +310,16 @@ struct BatPhases {
     in.ps.fields = fm; in.ps.time = kp.tp.time;
     for (int c = 0; c < 3; ++c) {
       in.ps.x[c] = sm[L.oXq() + (size_t)q * 3 + c];
-      in.ps.nrm[c] = kp.is_side ? sm[L.oNrm() + (size_t)q * 6 + c] : 0.0; in.ps.tng[c] = kp.is_side ? sm[L.oNrm() + (size_t)q * 6 + 3 + c] : 0.0;
+      in.ps.nrm[c] = is_side(kp) ? sm[L.oNrm() + (size_t)q * 6 + c] : 0.0; in.ps.tng[c] = is_side(kp) ? sm[L.oNrm() + (size_t)q * 6 + 3 + c] : 0.0;
     }
     in.w = sm[L.oW() + q];
-    in.h = (NeedsElementSize<C::PHYS>::value || kp.is_side) ? sm[L.oH()] : 0.0;
+    in.h = (NeedsElementSize<C::PHYS>::value || is_side(kp)) ? sm[L.oH()] : 0.0;
     S F[NVAR][TA];
 #pragma unroll
     for (int v = 0; v < NVAR; ++v)
 #pragma unroll
       for (int a = 0; a < TA; ++a) F[v][a] = S(0.0);
-    if (!kp.is_side) Physics<C::PHYS, DIM, S>::volume(in, F);
+    if (!is_side(kp)) Physics<C::PHYS, DIM, S>::volume(in, F);
     else {
       Physics<C::PHYS, DIM, S>::boundary(in, F);
 #pragma unroll
@@ -371,10 +374,19 @@ struct BatPhases {
     // basis fragments of point q: loaded (Q1) or rebuilt from J^-1 and the reference tables (larger bases) one point
     // ahead, so that their loads overlap the DMMAs of the current point
     // Bases that do not store T (Q2): the fragment is itself a tensor product, T_q (8 x 4) = (B | G)_q (8 x 4, reference table
-    // in fragment order, RefTab::FR) x M_q (4 x 4) with M = diag(1, J^-1) - one coalesced load, one DMMA and two shuffles that turn
-    // the product's C layout (lane 4 j + p holds columns 2 p, 2 p + 1) into the A layout (lane 4 j + a holds column a), against
-    // three gathers and three predicated FMAs per lane before (profiles/r1_batched_final_C3: 2/3 of the instructions of C3)
-    auto basis_frag = [&](int q, int rt) {
+    // in fragment order, RefTab::FR) x M_q (4 x 4) with M = diag(1, J^-1).  The B operand carries column a of M in column 2 a
+    // (odd columns zero), so that the FIRST accumulator register of lane 4 j + a is T[j][a]: the product's C layout is the A
+    // layout the contraction needs - one coalesced load and one DMMA per fragment, no shuffle, against three gathers and three
+    // predicated FMAs per lane before (profiles/r1_batched_final_C3: 2/3 of the instructions of C3 were fragment building)
+    auto m_frag = [&](int q) {
+      const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
+      return wv_make([&](int lane) {                   // b[k = lane % 4][n = lane / 4] = (n even) ? M[k][n / 2] : 0
+        const int k = lane & 3, n = lane >> 2, a = n >> 1;
+        if (n & 1) return 0.0;
+        if (a == 0) return k == 0 ? 1.0 : 0.0;
+        return (k >= 1 && k <= DIM && a <= DIM) ? Ji[(k - 1) * DIM + (a - 1)] : 0.0; });
+    };
+    auto basis_frag = [&](int q, int rt, const WV& mf) {
       if constexpr (STORE_T) {
         return wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? sm[L.oT() + (size_t)q * NB * TA + j * TA + a] : 0.0; });
 #if defined(MRH_BAT_FRAG_GATHER)                // previous form, kept for A/B timing (MRH_BAT_DEFINE=MRH_BAT_FRAG_GATHER)
@@ -383,22 +395,17 @@ struct BatPhases {
         return wv_make([&](int lane) { const int j = rt * 8 + (lane >> 2), a = lane & 3; return (j < NB && a < TA) ? basis_entry(tb, Ji, q, j, a) : 0.0; });
 #endif
       } else {
-        const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
         const double* fr = tb.FR + ((size_t)q * NRT + rt) * 32;
         const WV ref = wv_make([&](int lane) { return fr[lane]; });
-        const WV mf = wv_make([&](int lane) {          // B operand: M[k = lane % 4][n = lane / 4]
-          const int k = lane & 3, n = lane >> 2;
-          return (k == 0 && n == 0) ? 1.0 : (k >= 1 && k <= DIM && n >= 1 && n <= DIM) ? Ji[(k - 1) * DIM + (n - 1)] : 0.0; });
         WV c0 = wv_zero(), c1 = wv_zero();
         wv_mma(c0, c1, ref, mf);
-        const WV s0 = wv_shfl(c0, [](int lane) { return (lane & ~3) | ((lane & 3) >> 1); });
-        const WV s1 = wv_shfl(c1, [](int lane) { return (lane & ~3) | ((lane & 3) >> 1); });
-        return wv_make([&](int lane) { return (lane & 1) ? wv_get(s1, lane) : wv_get(s0, lane); });
+        return c0;
       }
     };
+    WV mfn = STORE_T ? wv_zero() : m_frag(0);
     WV tfn[NRT];
 #pragma unroll
-    for (int rt = 0; rt < NRT; ++rt) tfn[rt] = basis_frag(0, rt);
+    for (int rt = 0; rt < NRT; ++rt) tfn[rt] = basis_frag(0, rt, mfn);
     for (int q = 0; q < L.nq; ++q) {
       const double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
       const double* Dq = sm + L.oD() + LAY::dq(q);
@@ -406,8 +413,9 @@ struct BatPhases {
 #pragma unroll
       for (int rt = 0; rt < NRT; ++rt) tf[rt] = tfn[rt];
       if (q + 1 < L.nq) {
+        if (!STORE_T) mfn = m_frag(q + 1);
 #pragma unroll
-        for (int rt = 0; rt < NRT; ++rt) tfn[rt] = basis_frag(q + 1, rt);
+        for (int rt = 0; rt < NRT; ++rt) tfn[rt] = basis_frag(q + 1, rt, mfn);
       }
       const WV ff = wv_make([&](int lane) { const int v = lane >> 2, a = lane & 3; return (v < NVAR && a < TA) ? sF[v * TA + a] : 0.0; });
 #pragma unroll
@@ -523,10 +531,10 @@ struct InterpProgs {
 };
 
 // One warp per element, grid-stride over the elements of the launch.  smem_all: [offsets | one WarpSmem block per warp].
-template <class C, class PROGS>
+template <class C, class PROGS, bool SIDES = true>
 __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all) {
   using G = GenPhases<C>;
-  using B = BatPhases<C>;
+  using B = BatPhases<C, SIDES>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const WarpSmem<C> L(kp.tab.nq, kp.tp.transient != 0);
   int* offs = reinterpret_cast<int*>(smem_all);                        // offsets(var, basis) -> element slot, CTA-shared
@@ -593,7 +601,7 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
     } else {
       for (int it = lane; it < nq * n1; it += 32) B::prep(kp, L, sm, it, n1);
     }
-    if (lane == 31 && (NeedsElementSize<C::PHYS>::value || kp.is_side)) B::element_size(L, sm, kp.is_side != 0);       // h enters volume terms through the stabilisation only
+    if (lane == 31 && (NeedsElementSize<C::PHYS>::value || B::is_side(kp))) B::element_size(L, sm, B::is_side(kp));       // h enters volume terms through the stabilisation only
     __syncwarp();
     for (int it = lane; it < nq * B::NCH; it += 32) B::point_chunk(kp, L, sm, it);
     __syncwarp();

@@ -212,7 +212,11 @@ struct ThermalHexQ1 {
 #pragma unroll
     for (int k = 0; k < NK; ++k) K.set(k, 0.0);
 
+#if defined(MRH_WS_QUNROLL)              // tuning experiment: two points per trip, so that the scheduler can interleave their chains
+#pragma unroll MRH_WS_QUNROLL
+#else
 #pragma unroll 1
+#endif
     for (int q = 0; q < 8; ++q) {
       const double g = HexQ1::g;
       const double sx = (q & 1) ? -g : g, sy = (q & 2) ? -g : g, sz = (q & 4) ? -g : g;

@@ -27,15 +27,17 @@ template <class C> struct BatBounds { static constexpr int THREADS = 32 * MRH_BA
 template <> struct BatBounds<GenCfg<PHYS_NS, 3, 1>> { static constexpr int THREADS = 160, MINB = 2; };   // <= 204 registers: 10 warps per SM
 #endif
 
-template <class C>
+// SIDES: the side-launch branches (side measure, normals, boundary() and Flux terms) exist only in the instantiation that
+// serves the side launches; the volume instantiation compiles them away
+template <class C, bool SIDES>
 __global__ void __launch_bounds__(BatBounds<C>::THREADS, BatBounds<C>::MINB) batched_assembly_kernel(const __grid_constant__ KParams kp) {
   extern __shared__ __align__(16) double smem_all[];
-  batched_body<C, InterpProgs>(kp, smem_all);
+  batched_body<C, InterpProgs, SIDES>(kp, smem_all);
 }
 
-template <class C>
+template <class C, bool SIDES>
 bool launch_batched(int num_sms, KParams& kp, cudaStream_t stream) {
-  auto kern = batched_assembly_kernel<C>;
+  auto kern = batched_assembly_kernel<C, SIDES>;
   const bool tr = kp.tp.transient != 0;
   static int set_smem = 0;                                   // per instantiation: largest opt-in size requested so far
   const int want = (int)std::min<size_t>(batched_smem<C>(kp.tab.nq, tr, BatBounds<C>::THREADS / 32), (size_t)227 * 1024);
@@ -60,7 +62,7 @@ bool launch_batched_assembly(int phys, int dim, int order, int num_sms, KParams&
   bool launched = false;
   dispatch_cfg(phys, dim, order, [&](auto c) {
     using C = decltype(c);
-    launched = launch_batched<C>(num_sms, kp, (cudaStream_t)stream);
+    launched = kp.is_side ? launch_batched<C, true>(num_sms, kp, (cudaStream_t)stream) : launch_batched<C, false>(num_sms, kp, (cudaStream_t)stream);
   });
   return launched;
 }

@@ -5,7 +5,7 @@ constexpr int XCH_RESERVE_SMS = 4;     // SMs the interior launch leaves free fo
 #define MRH_WSK_DEFAULT 0      // K-in-registers thermal kernel: MRH_WSK=1 enables it
 #endif
 #if !defined(MRH_TILED2D_DEFAULT)
-#define MRH_TILED2D_DEFAULT 1  // tile-staged scatter for the Q1 quadrilateral kernel (MRH_TILED2D=0: direct scatter)
+#define MRH_TILED2D_DEFAULT 0  // tile-staged scatter for the Q1 quadrilateral kernel: measured slower than the direct scatter (1.72 vs 1.60 ms at 4096^2), MRH_TILED2D=1 enables it
 #endif
 #if !defined(MRH_WS8_DEFAULT)
 #define MRH_WS8_DEFAULT 0      // lane-per-point thermal kernel off until it is measured faster (MRH_WS8=1 enables it)
@@ -106,7 +106,7 @@ void device_finalize(mrh_engine* h) {
         // sin / cos calls hoisted into a lane-parallel atom table when they fit the kernel's scratch (the smallest D region of a
         // point is 33 doubles); MRH_BAT_ATOMS=0 keeps the plain printer
         int natoms = 0;
-        static const int atoms_env = [] { const char* ev = getenv("MRH_BAT_ATOMS"); return ev ? atoi(ev) : 1; }();
+        static const int atoms_env = [] { const char* ev = getenv("MRH_BAT_ATOMS"); return ev ? atoi(ev) : 0; }();   // measured slower on B200 (C3 53.1 vs 48.6 ms, C4 94 vs 86 ms): off
         std::string src = atoms_env ? jit_batched_atom_source(H.vol_progs, MRH_NCOEF, H.ec.code, H.ec.cpool, 32, natoms) : std::string();
         if (src.empty() || natoms == 0) {
           natoms = 0; src.clear();

@@ -8,7 +8,7 @@ for v in "1 3" "1 4" "1 5" "0 3"; do set -- $v
   echo "C1 TILED2D=$1 MINB2D=$2" >> $T
   MRH_TILED2D=$1 MRH_JIT_MINB2D=$2 timeout 120 python bench.py --config C1 --steps 10 --warmup 3 --kernel-only 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['ms_per_step'], d['config'].get('volume_kernel'))" >> $T 2>&1
 done
-MRH_JIT_DEFINE=MRH_WS_BULK timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "ragged_meshes or default_path or mid_size_c2 or host_buffer" > gpurun_out/r2_e4_bulk.log 2>&1; echo "bulk parity rc=$?"; tail -3 gpurun_out/r2_e4_bulk.log
+MRH_WS_BULK=1 timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "ragged_meshes or default_path or mid_size_c2 or host_buffer" > gpurun_out/r2_e4_bulk.log 2>&1; echo "bulk parity rc=$?"; tail -3 gpurun_out/r2_e4_bulk.log
 for v in "MRH_JIT_EXTRA=0" "MRH_WS_BULK"; do
   echo "C2 define $v" >> $T
   MRH_JIT_DEFINE=$v timeout 120 python bench.py --steps 10 --warmup 3 --kernel-only 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['ms_per_step'], d['config'].get('volume_kernel'))" >> $T 2>&1

@@ -12,6 +12,9 @@ done
 for v in "MRH_JIT_EXTRA=0" "MRH_WS_BULK"; do
   run "C2 define $v" MRH_JIT_DEFINE=$v timeout 120 python bench.py --steps 10 --warmup 3 --kernel-only
 done
+for v in 2 4; do
+  run "C2 QUNROLL=$v" MRH_JIT_DEFINE=MRH_WS_QUNROLL=$v timeout 120 python bench.py --steps 10 --warmup 3 --kernel-only
+done
 for v in "216 64" "224 48" "208 88"; do set -- $v
   run "C2 WSK CREG=$1 SREG=$2" MRH_WSK=1 MRH_WSK_CREG=$1 MRH_WSK_SREG=$2 timeout 90 python bench.py --steps 10 --warmup 3 --kernel-only
 done
