@@ -60,7 +60,8 @@ typedef struct mrh_config {
   int32_t flags;              /* bit 0: force the generic kernel; bit 1: no NVRTC specialisation;
                                * bit 2: direct instead of tile-staged scatter; bit 3: no warp-specialised kernel; bit 4: no batched kernel;
                                * bit 5: NVRTC-specialise the batched kernel on small meshes too (tests); bit 6: no lane-per-point thermal kernel;
-                               * bit 7: no exchange inside mrh_assemble_* when a communicator is attached */
+                               * bit 7: no exchange inside mrh_assemble_* when a communicator is attached;
+                               * bit 8: tile-staged scatter for the Q1 quadrilateral kernel (off by default: measured slower than its direct scatter) */
   int32_t use_lsic;           /* stokes "useLSIC" (stokes.cpp:44) */
   int32_t reserved_;
 } mrh_config;

@@ -212,7 +212,7 @@ struct ThermalHexQ1 {
 #pragma unroll
     for (int k = 0; k < NK; ++k) K.set(k, 0.0);
 
-#if defined(MRH_WS_QUNROLL)              // tuning experiment: two points per trip, so that the scheduler can interleave their chains
+#if defined(MRH_WS_QUNROLL)              // NVRTC build: two points per trip, so that the scheduler can interleave their dependent chains
 #pragma unroll MRH_WS_QUNROLL
 #else
 #pragma unroll 1

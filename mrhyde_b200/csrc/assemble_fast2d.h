@@ -51,12 +51,42 @@ struct ThermalQuadQ1 {
 
   // gather + element residual r (not yet negated) and element matrix K of element e
   MRH_HDN static void compute(const KParams& kp, int64_t e, int (&lid)[4], double (&r)[4], double (&K)[NK]) {
-    // ---- gather ----------------------------------------------------------------------------------------------
+    double X[4][2], us[4], ud[4];
+    gather(kp, e, lid, X, us, ud);
+    work(kp, X, us, ud, r, K);
+  }
+
+#if defined(__CUDACC__)
+  // grid-stride loop of the direct-scatter kernel, software-pipelined one element deep: the index rows and the vertex / solution
+  // values of the thread's NEXT element are in flight while the current one is computed and scattered (ncu of the plain loop: 3.4
+  // long-scoreboard stall cycles per issued instruction at 12 warps per SM - the gather's two dependent load levels were exposed)
+  __device__ static void run_direct(const KParams& kp) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= kp.nwork) return;
+    int lid[4]; double X[4][2], us[4], ud[4];
+    gather(kp, e, lid, X, us, ud);
+    for (;;) {
+      const int64_t en = e + stride;
+      const bool more = en < kp.nwork;
+      int lidn[4]; double Xn[4][2], usn[4], udn[4];
+      if (more) gather(kp, en, lidn, Xn, usn, udn);
+      double r[4], K[NK];
+      work(kp, X, us, ud, r, K);
+      scatter_direct(kp, e, lid, r, K);
+      if (!more) break;
+#pragma unroll
+      for (int s = 0; s < 4; ++s) { lid[s] = lidn[s]; X[s][0] = Xn[s][0]; X[s][1] = Xn[s][1]; us[s] = usn[s]; ud[s] = udn[s]; }
+      e = en;
+    }
+  }
+#endif
+
+  MRH_HDN static void gather(const KParams& kp, int64_t e, int (&lid)[4], double (&X)[4][2], double (&us)[4], double (&ud)[4]) {
     {
       const int4 a = *reinterpret_cast<const int4*>(kp.lids + e * 4);
       lid[0] = a.x; lid[1] = a.y; lid[2] = a.z; lid[3] = a.w;
     }
-    double X[4][2], us[4], ud[4];
     {
       const int4 a = *reinterpret_cast<const int4*>(kp.e2n + e * 4);
       const int nd[4] = {a.x, a.y, a.z, a.w};
@@ -78,6 +108,10 @@ struct ThermalQuadQ1 {
         ud[s] = tp.alpha_t * uval + beta_t * tp.timewt;
       }
     }
+  }
+
+  // element residual r (not yet negated) and element matrix K from the gathered vertices X and solution us / ud
+  MRH_HDN static void work(const KParams& kp, const double (&X)[4][2], const double (&us)[4], const double (&ud)[4], double (&r)[4], double (&K)[NK]) {
     const double au = TRANSIENT ? kp.tp.alpha_u : 1.0, at = TRANSIENT ? kp.tp.alpha_t : 0.0;
 
     // ---- monomial coefficients, index m = i + 2 j for xi^i eta^j ------------------------------------------------
@@ -105,7 +139,11 @@ struct ThermalQuadQ1 {
     for (int k = 0; k < NK; ++k) K[k] = 0.0;
 
     // ---- point loop -------------------------------------------------------------------------------------------------
+#if defined(MRH_Q2D_UNROLL)                // tuning experiment: rolled point loop (fewer registers, more resident warps)
+#pragma unroll MRH_Q2D_UNROLL
+#else
 #pragma unroll
+#endif
     for (int q = 0; q < 4; ++q) {
       const double g = HexQ1::g;
       const double sx = (q & 1) ? -g : g, sy = (q & 2) ? -g : g;

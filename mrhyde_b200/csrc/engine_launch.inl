@@ -71,7 +71,8 @@ void device_finalize(mrh_engine* h) {
     if (!D.tiles->ok) h->err = "tile-staged scatter unavailable (" + why + "), using direct scatter";
   }
   static const int tiled2d_env = [] { const char* ev = getenv("MRH_TILED2D"); return ev ? atoi(ev) : MRH_TILED2D_DEFAULT; }();
-  if (tiled2d_env && !(H.cfg.flags & 5) && thermal_quad_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
+  D.jit.tiled2d = (tiled2d_env || (H.cfg.flags & 256)) != 0;
+  if (D.jit.tiled2d && !(H.cfg.flags & 5) && thermal_quad_q1_eligible(H.phys, H.dim, H.order, H.ref.vol.nq, H.volumeStateIndependent(), H.cfg.lump_mass)) {
     const std::string why = build_tile_plan<4>(H.tileOrder(nullptr), H.mesh.nelem, D.lids.p, D.fixed.p, D.rowptr.p, D.colind.p,
                                                H.cfg.include_advection ? 16 : 10, *D.tiles);
     if (!D.tiles->ok) h->err = "tile-staged scatter unavailable (" + why + "), using direct scatter";
@@ -580,7 +581,10 @@ int mrh_assemble_jacres_host(mrh_handle h, const mrh_state* st_host, double* res
   mrh_state st = *st_host; st.u = D.h_u.p;
   build_chunk_plan(H, D);
   HostCopy hc; hc.jac_host = jac_host;
-  const int rc = device_assemble(h, &st, D.h_res.p, D.h_jac.p, &hc);
+  // with a communicator attached the interface rows change after the kernels (exchange): no chunk may leave early, the whole
+  // matrix is copied once the exchange is done
+  const bool exchanging = D.xch && D.xch->ready && !(H.cfg.flags & 128);
+  const int rc = device_assemble(h, &st, D.h_res.p, D.h_jac.p, exchanging ? nullptr : &hc);
   CUDA_CK(cudaMemcpyAsync(res_host, D.h_res.p, nl * sizeof(double), cudaMemcpyDeviceToHost, s));
   if (!hc.used) CUDA_CK(cudaMemcpyAsync(jac_host, D.h_jac.p, nnz * sizeof(double), cudaMemcpyDeviceToHost, s));
   CUDA_CK(cudaStreamSynchronize(s));

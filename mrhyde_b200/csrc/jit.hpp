@@ -247,6 +247,7 @@ struct JitKernel {
 class JitCache {
  public:
   std::string last_error;
+  bool tiled2d = false;        // the quadrilateral kernel is built with its tile-staged path (flag bit 8 / MRH_TILED2D=1)
   ~JitCache() { clear(); }
   void clear() {
     for (auto& kv : kernels_) if (kv.second.mod && JitApi::get().ok) JitApi::get().ModuleUnload(kv.second.mod);
@@ -271,9 +272,10 @@ class JitCache {
       K.source = std::string("#include \"assemble_fast2d.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
           "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB2D) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
           "  typedef mrh::ThermalQuadQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n" +
-          (jac ? "  extern __shared__ double dsm[];\n  if (kp.tile.ntiles > 0) { Kern::tiled(kp, dsm); return; }\n" : "") +
+          (jac ? "#if defined(MRH_TILED2D_ON)\n  extern __shared__ double dsm[];\n  if (kp.tile.ntiles > 0) { Kern::tiled(kp, dsm); return; }\n#endif\n" : "") +
+          "#if defined(MRH_Q2D_NOPIPE)\n"
           "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
-          "    Kern::element(kp, e);\n}\n";
+          "    Kern::element(kp, e);\n#else\n  Kern::run_direct(kp);\n#endif\n}\n";
     } else {
     K.source = std::string("#include \"assemble_fast.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
         "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
@@ -306,6 +308,10 @@ class JitCache {
     std::string extra = "-DMRH_JIT_EXTRA=0";
     if (const char* ev = getenv("MRH_JIT_DEFINE")) extra = std::string("-D") + ev;                    // tuning experiments
     // slot / row lists of a tile staged by two bulk copies (TMA unit) instead of per-thread 4-byte cp.async: measured 6.28 vs 6.46 ms (C2)
+    std::string qun = "-DMRH_WS_QUNROLL=2";                                                          // two points per trip of the hexahedron's point loop: 6.27 -> 6.16 ms (C2); 4: 6.79
+    if (const char* ev = getenv("MRH_WS_QUNROLL")) qun = std::string("-DMRH_WS_QUNROLL=") + ev;
+    std::string t2d = "-DMRH_TILED2D_OFF=1";                                                         // the quadrilateral kernel carries its tile-staged path only when asked to
+    if (tiled2d) t2d = "-DMRH_TILED2D_ON=1";
     std::string bulk = "-DMRH_WS_BULK=1";
     if (const char* ev = getenv("MRH_WS_BULK")) { if (atoi(ev) == 0) bulk = "-DMRH_WS_NOBULK=1"; }
     std::string creg = "-DMRH_WS_CREG=200", sreg = "-DMRH_WS_SREG=96";                              // 256 * CREG + 128 * SREG <= 384 * 168
@@ -322,8 +328,8 @@ class JitCache {
     if (const char* ev = getenv("MRH_WSK_CREG")) cregk = std::string("-DMRH_WSK_CREG=") + ev;
     if (const char* ev = getenv("MRH_WSK_SREG")) sregk = std::string("-DMRH_WSK_SREG=") + ev;
     const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-DMRH_JIT=1", minb.c_str(), extra.c_str(), creg.c_str(), sreg.c_str(),
-                          ncg8.c_str(), creg8.c_str(), sreg8.c_str(), cregk.c_str(), sregk.c_str(), minb2d.c_str(), bulk.c_str()};
-    const nvrtcResult rc = api.CompileProgram(prog, 15, opts);
+                          ncg8.c_str(), creg8.c_str(), sreg8.c_str(), cregk.c_str(), sregk.c_str(), minb2d.c_str(), bulk.c_str(), t2d.c_str(), qun.c_str()};
+    const nvrtcResult rc = api.CompileProgram(prog, 17, opts);
     size_t ls = 0; api.GetProgramLogSize(prog, &ls);
     if (ls > 1) { K.log.resize(ls); api.GetProgramLog(prog, &K.log[0]); }
     if (rc != NVRTC_SUCCESS) { last_error = "NVRTC compile failed: " + K.log.substr(0, 2000); api.DestroyProgram(&prog); return nullptr; }

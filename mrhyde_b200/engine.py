@@ -150,7 +150,7 @@ class Engine:
     """One assembly engine handle (== one AssemblyManager on one GPU)."""
 
     def __init__(self, physics, dim, order=1, lib=None, device=0, quadrature=-1, side_quadrature=-1,
-                 use_strong_dbc=True, fix_zero_rows=False, lump_mass=False, settings=None, force_generic=False, no_jit=False, no_tiles=False, no_ws=False, no_batched=False, jit_batched=False):
+                 use_strong_dbc=True, fix_zero_rows=False, lump_mass=False, settings=None, force_generic=False, no_jit=False, no_tiles=False, no_ws=False, no_batched=False, jit_batched=False, tiled2d=False):
         self.L = load_library(lib)
         settings = settings or {}
         cfg = MrhConfig()
@@ -166,7 +166,7 @@ class Engine:
         cfg.form_param = float(settings.get("form_param", 1.0))
         cfg.le_penalty = float(settings.get("penalty", 10.0))
         cfg.device = device
-        cfg.flags = (1 if force_generic else 0) | (2 if no_jit else 0) | (4 if no_tiles else 0) | (8 if no_ws else 0) | (16 if no_batched else 0) | (32 if jit_batched else 0)
+        cfg.flags = (1 if force_generic else 0) | (2 if no_jit else 0) | (4 if no_tiles else 0) | (8 if no_ws else 0) | (16 if no_batched else 0) | (32 if jit_batched else 0) | (256 if tiled2d else 0)
         self.h = C.c_void_p()
         rc = self.L.mrh_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:
@@ -192,7 +192,7 @@ class Engine:
 
     @classmethod
     def from_problem(cls, p, lib=None, device=0, finalize=True, host_only=False, force_generic=False, no_jit=False, no_tiles=False, no_ws=False,
-                     no_batched=False, jit_batched=False, part=None, comm_id=None):
+                     no_batched=False, jit_batched=False, part=None, comm_id=None, tiled2d=False):
         """Build an engine from a tests/problems.py style dict (same dict drives the oracle)."""
         extra = p.get("extra", {})
         weak = bool(extra.get("use weak Dirichlet", False))
@@ -201,7 +201,7 @@ class Engine:
                 quadrature=extra.get("quadrature", -1), side_quadrature=extra.get("side quadrature", -1),
                 use_strong_dbc=extra.get("use strong DBCs", True), fix_zero_rows=extra.get("fix zero rows", False),
                 lump_mass=extra.get("lump mass", False), settings=p.get("settings", {}),
-                force_generic=force_generic, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws, no_batched=no_batched, jit_batched=jit_batched)
+                force_generic=force_generic, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws, no_batched=no_batched, jit_batched=jit_batched, tiled2d=tiled2d)
         n = [m["NX"], m["NY"], m.get("NZ", 1)]
         lo = [m.get("xmin", 0.0), m.get("ymin", 0.0), m.get("zmin", 0.0)]
         hi = [m.get("xmax", 1.0), m.get("ymax", 1.0), m.get("zmax", 1.0)]

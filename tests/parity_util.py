@@ -210,10 +210,10 @@ def rel_errors(a, b, rowptr=None):
     return g, (dmax[ok] / bmax[ok]).max() if ok.any() else 0.0
 
 
-def check_case(p, kw, lib, on_gpu, force_generic=False, jacobian=True, no_jit=False, no_tiles=False, no_ws=False, no_batched=False, jit_batched=False):
+def check_case(p, kw, lib, on_gpu, force_generic=False, jacobian=True, no_jit=False, no_tiles=False, no_ws=False, no_batched=False, jit_batched=False, tiled2d=False):
     from mrhyde_b200 import Engine
     o = Oracle(oracle_problem(p))
-    e = Engine.from_problem(p, lib=lib, force_generic=force_generic, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws, no_batched=no_batched, jit_batched=jit_batched)
+    e = Engine.from_problem(p, lib=lib, force_generic=force_generic, no_jit=no_jit, no_tiles=no_tiles, no_ws=no_ws, no_batched=no_batched, jit_batched=jit_batched, tiled2d=tiled2d)
     s = e.sizes()
     assert (s["nlocal"], s["nnz"], s["nelem"]) == (o.nlocal, o.nnz, o.nelem)
     lids, offs, fixed, xyz, var = e.dofmap()

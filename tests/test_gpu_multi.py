@@ -53,6 +53,11 @@ def _worker(rank, world, port, procs, mk, n, q):
                 torch.cuda.synchronize()
             outs.append((res.cpu().numpy(), jac.cpu().numpy()))
         path, launches = e.kernel_path(), e.launch_count()
+        # host-buffer entry point: with a communicator attached it exchanges before the copy-out (same rows as the device buffers)
+        hres, hjac = np.zeros(s["nlocal"]), np.zeros(s["nnz"])
+        e.assemble_jacres_host(u, hres, hjac)
+        assert np.abs(hres - outs[0][0]).max() <= 1e-13 * max(np.abs(outs[0][0]).max(), 1e-300), "host-buffer residual differs after the exchange"
+        assert np.abs(hjac - outs[0][1]).max() <= 1e-13 * np.abs(outs[0][1]).max(), "host-buffer Jacobian differs after the exchange"
         grow_, gcol_, gval = e.ghost_block(values=False)
         (res, jac), (res_only, _) = outs
         # ghost values of the LAST Jacobian exchange were overwritten by nothing (the residual-only pass does not touch them)
