@@ -1,6 +1,8 @@
 // Part of engine.cu: device set-up, launch logic and the GPU-side C-ABI entry points.
 
-constexpr int XCH_RESERVE_SMS = 4;     // SMs the interior launch leaves free for the exchange kernels when it overlaps them
+// SMs the interior launch leaves free for the exchange kernels when it overlaps them (MRH_XCH_SMS overrides; every reserved SM costs
+// 1/148 of the interior's throughput, too few serialise the pack / NCCL / unpack kernels behind the persistent CTAs)
+static const int XCH_RESERVE_SMS = [] { const char* ev = getenv("MRH_XCH_SMS"); return ev ? std::max(0, atoi(ev)) : 4; }();
 #if !defined(MRH_WSK_DEFAULT)
 #define MRH_WSK_DEFAULT 0      // K-in-registers thermal kernel: MRH_WSK=1 enables it
 #endif

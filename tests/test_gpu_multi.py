@@ -52,7 +52,8 @@ def _worker(rank, world, port, procs, mk, n, q):
                     e.assemble_res(tu, res)
                 torch.cuda.synchronize()
             outs.append((res.cpu().numpy(), jac.cpu().numpy()))
-        path, launches = e.kernel_path(), e.launch_count()
+            if jacobian:
+                path, launches = e.kernel_path(), e.launch_count()          # (residual-only passes scatter directly)
         # host-buffer entry point: with a communicator attached it exchanges before the copy-out (same rows as the device buffers)
         hres, hjac = np.zeros(s["nlocal"]), np.zeros(s["nnz"])
         e.assemble_jacres_host(u, hres, hjac)
