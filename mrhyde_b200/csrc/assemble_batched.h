@@ -594,9 +594,17 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
       }
       for (int q = lane; q < nq; q += 32) {
         const double x = sm[L.oXq() + (size_t)q * 3], y = sm[L.oXq() + (size_t)q * 3 + 1], z = sm[L.oXq() + (size_t)q * 3 + 2];
+        // the point's atoms go to registers once and every program is evaluated before the first store: with the stores in between
+        // the compiler had to assume they alias the atom table and re-read the atoms for every term of every program
+        double areg[PROGS::NA > 0 ? PROGS::NA : 1];
+#pragma unroll
+        for (int i = 0; i < PROGS::NA; ++i) areg[i] = at[q * PROGS::NA + i];
+        double val[MRH_NCOEF];
+#pragma unroll
+        for (int k = 0; k < MRH_NCOEF; ++k) val[k] = PROGS::eval(k, x, y, z, kp.tp.time, areg);
 #pragma unroll
         for (int k = 0; k < MRH_NCOEF; ++k)
-          if (kp.progs[k].kind == 1) sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = PROGS::eval(k, x, y, z, kp.tp.time, at + q * PROGS::NA);
+          if (kp.progs[k].kind == 1) sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = val[k];
       }
     } else {
       for (int it = lane; it < nq * n1; it += 32) B::prep(kp, L, sm, it, n1);

@@ -110,7 +110,8 @@ void device_finalize(mrh_engine* h) {
         // point is 33 doubles); MRH_BAT_ATOMS=0 keeps the plain printer
         int natoms = 0;
         static const int atoms_env = [] { const char* ev = getenv("MRH_BAT_ATOMS"); return ev ? atoi(ev) : 0; }();   // measured slower on B200 (C3 53.1 vs 48.6 ms, C4 94 vs 86 ms): off
-        std::string src = atoms_env ? jit_batched_atom_source(H.vol_progs, MRH_NCOEF, H.ec.code, H.ec.cpool, 32, natoms) : std::string();
+        std::string preamble;
+        std::string src = atoms_env ? jit_batched_atom_source(H.vol_progs, MRH_NCOEF, H.ec.code, H.ec.cpool, 32, natoms, &preamble) : std::string();
         if (src.empty() || natoms == 0) {
           natoms = 0; src.clear();
           for (int k = 0; k < MRH_NCOEF; ++k) {
@@ -119,7 +120,7 @@ void device_finalize(mrh_engine* h) {
             else src += "  static __device__ __forceinline__ double " + name + "(double, double, double, double) { return 0.0; }\n";
           }
         }
-        D.jit.setBatchedSource(src, H.phys, H.dim, H.order, 192, 0, natoms);
+        D.jit.setBatchedSource(src, H.phys, H.dim, H.order, 192, 0, natoms, natoms > 0 ? preamble : std::string());
         if (!D.jit.batched()) h->err = "NVRTC specialisation of the batched kernel unavailable, using the in-kernel interpreter: " + D.jit.last_error;
       } catch (const std::exception& ex) { h->err = std::string("NVRTC specialisation of the batched kernel skipped: ") + ex.what(); }
     }

@@ -155,16 +155,21 @@ inline std::string jit_function_source(const std::string& name, const Prog& pr, 
 // therefore collects the distinct (function, argument expression) pairs of ALL programs of the launch; the kernel evaluates the atoms
 // of all points with every lane busy and uniform code (argument by a small switch, then one trig_fast call), and the programs read
 // them from shared memory.
+struct JitAffine {            // c[0] + c[1] x + c[2] y + c[3] z + c[4] t, when the sub-expression is of that form
+  bool ok = false; double c[5] = {0, 0, 0, 0, 0};
+};
 struct JitAtomTable {
   std::vector<std::string> arg; std::vector<int> shift;      // shift 0: sin, 1: cos
-  int find_or_add(const std::string& a, int sh) {
+  std::vector<JitAffine> aff;                                 // affine form of the argument (all atoms affine: table-driven, uniform code)
+  int find_or_add(const std::string& a, int sh, const JitAffine& f) {
     for (size_t i = 0; i < arg.size(); ++i) if (arg[i] == a && shift[i] == sh) return (int)i;
-    arg.push_back(a); shift.push_back(sh); return (int)arg.size() - 1;
+    arg.push_back(a); shift.push_back(sh); aff.push_back(f); return (int)arg.size() - 1;
   }
 };
 // program -> one fully parenthesised expression; sin / cos nodes become at[i]
 inline std::string jit_expr_with_atoms(const Prog& pr, const std::vector<Instr>& code, const std::vector<double>& cpool, JitAtomTable& T) {
   std::vector<std::string> st;
+  std::vector<JitAffine> sa;                       // affine form of every stack entry (ok = false: not affine)
   auto leaf = [&](uint8_t op, uint16_t cidx) -> std::string {
     switch (op) {
       case OP_CONST: return jit_literal(cpool[cidx]);
@@ -172,14 +177,33 @@ inline std::string jit_expr_with_atoms(const Prog& pr, const std::vector<Instr>&
       default: return "(0.0)";
     }
   };
+  auto leaf_aff = [&](uint8_t op, uint16_t cidx) -> JitAffine {
+    JitAffine f;
+    switch (op) {
+      case OP_CONST: f.ok = true; f.c[0] = cpool[cidx]; break;
+      case OP_X: f.ok = true; f.c[1] = 1.0; break; case OP_Y: f.ok = true; f.c[2] = 1.0; break;
+      case OP_Z: f.ok = true; f.c[3] = 1.0; break; case OP_TIME: f.ok = true; f.c[4] = 1.0; break;
+      default: break;
+    }
+    return f;
+  };
+  auto is_const = [](const JitAffine& f) { return f.ok && f.c[1] == 0.0 && f.c[2] == 0.0 && f.c[3] == 0.0 && f.c[4] == 0.0; };
   for (int pc = pr.start; pc < pr.start + pr.len; ++pc) {
     const Instr in = code[pc];
     if (in.op == OP_FIELD) throw std::runtime_error("state-dependent coefficient cannot be specialised");
-    if (in.op < OP_FIELD) { st.push_back(leaf(in.op, in.cidx)); continue; }
+    if (in.op < OP_FIELD) { st.push_back(leaf(in.op, in.cidx)); sa.push_back(leaf_aff(in.op, in.cidx)); continue; }
     if (in.op <= OP_MEAN) {
-      std::string b;
-      if (in.arg != 0) b = leaf(in.arg - 1, in.cidx); else { b = st.back(); st.pop_back(); }
+      std::string b; JitAffine fb;
+      if (in.arg != 0) { b = leaf(in.arg - 1, in.cidx); fb = leaf_aff(in.arg - 1, in.cidx); } else { b = st.back(); st.pop_back(); fb = sa.back(); sa.pop_back(); }
       const std::string a = st.back(); st.pop_back();
+      const JitAffine fa = sa.back(); sa.pop_back();
+      JitAffine fr;
+      if (fa.ok && fb.ok) {
+        if (in.op == OP_ADD || in.op == OP_SUB) { fr.ok = true; for (int i = 0; i < 5; ++i) fr.c[i] = in.op == OP_ADD ? fa.c[i] + fb.c[i] : fa.c[i] - fb.c[i]; }
+        else if (in.op == OP_MUL && (is_const(fa) || is_const(fb))) { const JitAffine& k = is_const(fa) ? fa : fb; const JitAffine& v = is_const(fa) ? fb : fa; fr.ok = true; for (int i = 0; i < 5; ++i) fr.c[i] = k.c[0] * v.c[i]; }
+        else if (in.op == OP_DIV && is_const(fb) && fb.c[0] != 0.0) { fr.ok = true; for (int i = 0; i < 5; ++i) fr.c[i] = fa.c[i] / fb.c[0]; }
+      }
+      sa.push_back(fr);
       std::string r;
       switch (in.op) {
         case OP_ADD: r = "(" + a + " + " + b + ")"; break;
@@ -198,11 +222,14 @@ inline std::string jit_expr_with_atoms(const Prog& pr, const std::vector<Instr>&
       st.push_back(r);
       continue;
     }
-    if (in.op == OP_NIP) { const std::string top = st.back(); st.pop_back(); st.pop_back(); st.push_back(top); continue; }
+    if (in.op == OP_NIP) { const std::string top = st.back(); st.pop_back(); st.pop_back(); st.push_back(top);
+                           const JitAffine ft = sa.back(); sa.pop_back(); sa.pop_back(); sa.push_back(ft); continue; }
     const std::string a = st.back(); st.pop_back();
+    const JitAffine fa = sa.back(); sa.pop_back();
+    sa.push_back(JitAffine());                       // the result of a unary function is not affine
     switch (in.op) {
-      case OP_SIN: st.push_back("at[" + std::to_string(T.find_or_add(a, 0)) + "]"); break;
-      case OP_COS: st.push_back("at[" + std::to_string(T.find_or_add(a, 1)) + "]"); break;
+      case OP_SIN: st.push_back("at[" + std::to_string(T.find_or_add(a, 0, fa)) + "]"); break;
+      case OP_COS: st.push_back("at[" + std::to_string(T.find_or_add(a, 1, fa)) + "]"); break;
       case OP_TAN: st.push_back("tan(" + a + ")"); break;
       case OP_EXP: st.push_back("exp(" + a + ")"); break;
       case OP_LOG: st.push_back("log(" + a + ")"); break;
@@ -216,7 +243,8 @@ inline std::string jit_expr_with_atoms(const Prog& pr, const std::vector<Instr>&
 }
 // source of struct JitProgs' members for the batched kernel: NA, atom_arg, atom_shift, p0..p7(x, y, z, t, at).  An atom whose argument
 // itself contains an atom (sin(cos(x))) cannot be hoisted: the caller then falls back to the plain printer (returns "").
-inline std::string jit_batched_atom_source(const Prog* progs, int nprog, const std::vector<Instr>& code, const std::vector<double>& cpool, int max_atoms, int& natoms) {
+inline std::string jit_batched_atom_source(const Prog* progs, int nprog, const std::vector<Instr>& code, const std::vector<double>& cpool, int max_atoms, int& natoms,
+                                           std::string* preamble = nullptr) {
   JitAtomTable T;
   std::string fns;
   for (int k = 0; k < nprog; ++k) {
@@ -232,10 +260,25 @@ inline std::string jit_batched_atom_source(const Prog* progs, int nprog, const s
   std::string out = "  static __device__ __forceinline__ double mrh_jmax(double a, double b) { return (a < b) ? b : a; }\n"
                     "  static __device__ __forceinline__ double mrh_jmin(double a, double b) { return (a > b) ? b : a; }\n"
                     "  static __device__ __forceinline__ double mrh_jsqrt0(double a) { return (a <= 0.0) ? 0.0 : sqrt(a); }\n"
-                    "  static constexpr int NA = " + std::to_string(natoms) + ";\n"
-                    "  static __device__ __forceinline__ double atom_arg(int a, double x, double y, double z, double t) {\n    switch (a) {\n";
-  for (int i = 0; i < natoms; ++i) { out += "      case " + std::to_string(i) + ": return " + T.arg[i] + ";\n"; if (T.shift[i]) mask |= 1ull << i; }
-  out += "      default: return 0.0;\n    }\n  }\n  static __device__ __forceinline__ int atom_shift(int a) { return (int)((" + std::to_string(mask) + "ull >> a) & 1ull); }\n";
+                    "  static constexpr int NA = " + std::to_string(natoms) + ";\n";
+  bool all_affine = preamble != nullptr && natoms > 0;
+  for (auto& f : T.aff) all_affine = all_affine && f.ok;
+  for (int i = 0; i < natoms; ++i) if (T.shift[i]) mask |= 1ull << i;
+  if (all_affine) {
+    // every argument is c0 + cx x + cy y + cz z + ct t: one table row per atom in global memory, the same five instructions for every
+    // lane (a switch over the atom index diverges: measured 930 warp instructions per element of C4 in that switch alone)
+    std::string tab = "namespace mrh { __device__ const double mrh_atom_tab[" + std::to_string(natoms * 5) + "] = {";
+    for (int i = 0; i < natoms; ++i) for (int k = 0; k < 5; ++k) tab += jit_literal(T.aff[i].c[k]) + ((i == natoms - 1 && k == 4) ? "" : ", ");
+    *preamble = tab + "}; }\n";
+    out += "  static __device__ __forceinline__ double atom_arg(int a, double x, double y, double z, double t) {\n"
+           "    const double* c = mrh_atom_tab + a * 5;\n    return fma(c[4], t, fma(c[3], z, fma(c[2], y, fma(c[1], x, c[0]))));\n  }\n";
+  } else {
+    if (preamble) preamble->clear();
+    out += "  static __device__ __forceinline__ double atom_arg(int a, double x, double y, double z, double t) {\n    switch (a) {\n";
+    for (int i = 0; i < natoms; ++i) out += "      case " + std::to_string(i) + ": return " + T.arg[i] + ";\n";
+    out += "      default: return 0.0;\n    }\n  }\n";
+  }
+  out += "  static __device__ __forceinline__ int atom_shift(int a) { return (int)((" + std::to_string(mask) + "ull >> a) & 1ull); }\n";
   return out + fns;
 }
 
@@ -273,9 +316,9 @@ class JitCache {
           "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB2D) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
           "  typedef mrh::ThermalQuadQ1<" + B(transient) + ", " + B(adv) + ", " + B(jac) + ", mrh::JitCoefs> Kern;\n" +
           (jac ? "#if defined(MRH_TILED2D_ON)\n  extern __shared__ double dsm[];\n  if (kp.tile.ntiles > 0) { Kern::tiled(kp, dsm); return; }\n#endif\n" : "") +
-          "#if defined(MRH_Q2D_NOPIPE)\n"
+          "#if defined(MRH_Q2D_PIPE)\n  Kern::run_direct(kp);\n#else\n"      // software-pipelined gather: measured slower (2.01 / 1.53 ms against 1.60 / 1.37 ms at 160 / 128 registers)
           "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
-          "    Kern::element(kp, e);\n#else\n  Kern::run_direct(kp);\n#endif\n}\n";
+          "    Kern::element(kp, e);\n#endif\n}\n";
     } else {
     K.source = std::string("#include \"assemble_fast.h\"\nnamespace mrh {\nstruct JitCoefs {\n  static constexpr bool staged = false;\n") + coef_src_ +
         "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) mrh_jit_thermal_hex_q1(const __grid_constant__ mrh::KParams kp) {\n"
@@ -303,7 +346,7 @@ class JitCache {
     if (api.CreateProgram(&prog, K.source.c_str(), "mrh_jit_thermal.cu", (int)hdr_src.size(), hdr_src.data(), hdr_name.data()) != NVRTC_SUCCESS) { last_error = "nvrtcCreateProgram failed"; return nullptr; }
     std::string minb = "-DMRH_JIT_MINB=2";                                                          // CTAs of 128 threads per SM the register allocation targets
     if (const char* ev = getenv("MRH_JIT_MINB")) minb = std::string("-DMRH_JIT_MINB=") + ev;          // tuning experiments
-    std::string minb2d = "-DMRH_JIT_MINB2D=1";                                                      // same for the quadrilateral kernel (ptxas' own choice: 180 registers)
+    std::string minb2d = "-DMRH_JIT_MINB2D=4";                                                      // same for the quadrilateral kernel: 128 registers, 16 warps per SM (1.37 ms at 4096^2 against 1.60 ms at 160 registers / 12 warps)
     if (const char* ev = getenv("MRH_JIT_MINB2D")) minb2d = std::string("-DMRH_JIT_MINB2D=") + ev;    // tuning experiments
     std::string extra = "-DMRH_JIT_EXTRA=0";
     if (const char* ev = getenv("MRH_JIT_DEFINE")) extra = std::string("-D") + ev;                    // tuning experiments
@@ -314,7 +357,7 @@ class JitCache {
     if (tiled2d) t2d = "-DMRH_TILED2D_ON=1";
     std::string bulk = "-DMRH_WS_BULK=1";
     if (const char* ev = getenv("MRH_WS_BULK")) { if (atoi(ev) == 0) bulk = "-DMRH_WS_NOBULK=1"; }
-    std::string creg = "-DMRH_WS_CREG=200", sreg = "-DMRH_WS_SREG=96";                              // 256 * CREG + 128 * SREG <= 384 * 168
+    std::string creg = "-DMRH_WS_CREG=208", sreg = "-DMRH_WS_SREG=88";                              // 256 * CREG + 128 * SREG <= 384 * 168 (208 / 88: 6.16 ms, 200 / 96: 6.18, 216 / 64: 6.46)
     if (const char* ev = getenv("MRH_WS_CREG")) creg = std::string("-DMRH_WS_CREG=") + ev;
     if (const char* ev = getenv("MRH_WS_SREG")) sreg = std::string("-DMRH_WS_SREG=") + ev;
     ws8_ncg = 3;                                                                                    // compute warpgroups of the lane-per-point kernel
@@ -349,13 +392,13 @@ class JitCache {
   // ---- batched volume kernel (assemble_batched.h) with the state-independent programs printed as functions p0..p7 ----
   // threads / minb: launch bounds of the kernel (minb > 0: register budget 65536 / (threads * minb); 0: ptxas' own choice)
   int bat_natoms = 0;          // sin / cos atoms hoisted out of the batched kernel's programs (0: plain printer)
-  void setBatchedSource(const std::string& progs, int phys, int dim, int order, int threads = 192, int minb = 0, int natoms = 0) {
+  void setBatchedSource(const std::string& progs, int phys, int dim, int order, int threads = 192, int minb = 0, int natoms = 0, const std::string& preamble = "") {
     bat_natoms = natoms;
     bat_bounds_ = "-DMRH_BAT_BOUNDS=" + std::to_string(threads) + (minb > 0 ? "," + std::to_string(minb) : std::string()); bat_max_threads = threads;
     if (const char* ev = getenv("MRH_BAT_BOUNDS")) { bat_bounds_ = std::string("-DMRH_BAT_BOUNDS=") + ev; bat_max_threads = atoi(ev); }   // tuning experiments
     if (bat_.mod && JitApi::get().ok) JitApi::get().ModuleUnload(bat_.mod);
     bat_ = JitKernel(); bat_tried_ = false;
-    bat_.source = std::string("#include \"assemble_batched.h\"\nnamespace mrh {\nstruct JitProgs {\n  static constexpr bool jit = true;\n") + progs +
+    bat_.source = std::string("#include \"assemble_batched.h\"\n") + preamble + "namespace mrh {\nstruct JitProgs {\n  static constexpr bool jit = true;\n" + progs +
         (natoms > 0 ?
         "  static __device__ __forceinline__ double eval(int k, double x, double y, double z, double t, const double* at) {\n    switch (k) {\n"
         "      case 0: return p0(x, y, z, t, at); case 1: return p1(x, y, z, t, at); case 2: return p2(x, y, z, t, at); case 3: return p3(x, y, z, t, at);\n"

@@ -45,9 +45,9 @@ int main() {
       "};\n}\nextern \"C\" __global__ void __launch_bounds__(128, MRH_JIT_MINB) k(const __grid_constant__ mrh::KParams kp) {\n"
       "  typedef mrh::ThermalQuadQ1<false, false, true, mrh::JitCoefs> Kern;\n"
       "#if defined(MRH_TILED2D_ON)\n  extern __shared__ double dsm[];\n  if (kp.tile.ntiles > 0) { Kern::tiled(kp, dsm); return; }\n#endif\n"
-      "#if defined(MRH_Q2D_NOPIPE)\n"
+      "#if defined(MRH_Q2D_PIPE)\n  Kern::run_direct(kp);\n#else\n"
       "  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < kp.nwork; e += (long long)gridDim.x * blockDim.x)\n"
-      "    Kern::element(kp, e);\n#else\n  Kern::run_direct(kp);\n#endif\n}\n";
+      "    Kern::element(kp, e);\n#endif\n}\n";
   std::vector<const char*> hs, hn;
   for (int i = 0; i < k_num_embedded_headers; ++i) { hn.push_back(k_embedded_headers[i].name); hs.push_back(k_embedded_headers[i].text); }
   nvrtcProgram p; nvrtcCreateProgram(&p, full.c_str(), "probe.cu", (int)hs.size(), hs.data(), hn.data());

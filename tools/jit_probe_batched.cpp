@@ -38,12 +38,12 @@ int main(int argc, char** argv) {
   ec.addFunction("source dx", "(lambda+2.0*mu)*dxxx + mu*(dxyy+dyxy+dxzz+dzxz) + lambda*(dyxy+dzxz)", "ip");
   ec.addFunction("source dy", "(lambda+2.0*mu)*dyyy + mu*(dyxx+dxxy+dyzz+dzyz) + lambda*(dxxy+dzyz)", "ip");
   ec.addFunction("source dz", "(lambda+2.0*mu)*dzzz + mu*(dzxx+dxxz+dzyy+dyyz) + lambda*(dxxz+dyyz)", "ip");
-  std::string src;
+  std::string src, preamble;
   int natoms = 0;
   if (!getenv("MRH_PROBE_NOATOMS")) {
     Prog progs[MRH_MAXPROG] = {};
     for (int k = 2; k < 5; ++k) progs[k] = ec.compile(k == 2 ? "source dx" : k == 3 ? "source dy" : "source dz", "ip");
-    src = jit_batched_atom_source(progs, 8, ec.code, ec.cpool, 32, natoms);
+    src = jit_batched_atom_source(progs, 8, ec.code, ec.cpool, 32, natoms, &preamble);
     printf("atoms: %d\n", natoms);
   }
   if (src.empty())
@@ -53,7 +53,7 @@ int main(int argc, char** argv) {
     else src += "  static __device__ __forceinline__ double " + name + "(double, double, double, double) { return 0.0; }\n";
   }
   const int thr = getenv("MRH_PROBE_THREADS") ? atoi(getenv("MRH_PROBE_THREADS")) : 192, mb = getenv("MRH_PROBE_MINB") ? atoi(getenv("MRH_PROBE_MINB")) : 0;
-  JitCache jc; jc.setBatchedSource(src, phys, dim, order, thr, mb, natoms);
+  JitCache jc; jc.setBatchedSource(src, phys, dim, order, thr, mb, natoms, natoms > 0 ? preamble : std::string());
   const std::string o1 = "-DMRH_BAT_BOUNDS=" + std::to_string(thr) + (mb > 0 ? "," + std::to_string(mb) : std::string()), o2 = "-DMRH_PROBE_X=1";
   // same steps as JitCache::batched(), with ptxas -v and without loading the module
   std::vector<const char*> hs, hn;
