@@ -348,10 +348,11 @@ def run_gpu(args):
                     other[oc] = {"error": str(ex)[:200]}
         traffic, traffic_src = None, None
         try:      # DRAM bytes of one launch of the dominant kernel from the committed ncu --set full capture of this command
-            prof = json.load(open(os.path.join(ROOT, "profiles", "r1_ws_thermal_n256_ncu_summary.json")))
+            pname = next(f for f in ("r2_ws_thermal_n256_ncu_summary.json", "r1_ws_thermal_n256_ncu_summary.json") if os.path.exists(os.path.join(ROOT, "profiles", f)))
+            prof = json.load(open(os.path.join(ROOT, "profiles", pname)))
             if cfg == "C2" and n == 256 and world == 1 and kpath == prof.get("kernel_path", "nvrtc-specialised+tiled-ws"):
                 traffic = prof["derived"]["dram_bytes_per_launch"]
-                traffic_src = "profiles/r1_ws_thermal_n256_ncu_summary.json (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+                traffic_src = f"profiles/{pname} (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
         except Exception:
             pass
         out = {

@@ -44,7 +44,7 @@ enum { MRH_BC_NONE = 0, MRH_BC_DIRICHLET = 1, MRH_BC_WEAK_DIRICHLET = 2, MRH_BC_
  * module settings (thermal.cpp:24-41, linearelasticity.cpp:21-61, navierstokes.cpp:20-62). */
 typedef struct mrh_config {
   int32_t dim;                /* 2 or 3 */
-  const char* physics;        /* "thermal" | "cdr" | "linearelasticity" | "navierstokes" | "stokes" */
+  const char* physics;        /* "thermal" | "cdr" | "linearelasticity" | "navierstokes" | "stokes" | "helmholtz" */
   int32_t order;              /* HGRAD order, 1 or 2 (order 2 in 3-D: thermal and cdr only - the vector-valued modules return
                                * MRH_EUNSUPPORTED from mrh_assemble_*) */
   int32_t quadrature;         /* volume cubature degree; <0 = 2*order (discretizationInterface.cpp:166) */

@@ -2,7 +2,7 @@
 // hot path, so that code written against MrHyDE's classes reads the same against this engine:
 //   PhysicsBase<EvalT>   /root/reference/src/physics/physicsBase.hpp:30-205   (ctor(settings, dimension), defineFunctions,
 //                        volumeResidual, boundaryResidual, faceResidual, computeFlux, setWorkset; label, myvars, mybasistypes)
-//   thermal / cdr / linearelasticity / navierstokes   /root/reference/src/physics/{thermal,cdr,linearelasticity,navierstokes}.hpp
+//   thermal / cdr / linearelasticity / navierstokes / stokes / helmholtz   /root/reference/src/physics/{thermal,cdr,linearelasticity,navierstokes,stokes,helmholtz}.hpp
 //   FunctionManager      /root/reference/src/managers/functionManager.hpp     (addFunction(name, expr, location), evaluate)
 //   Workset              /root/reference/src/tools/workset.hpp:21-584         (time data, varlist, var_bcs, offsets)
 //   AssemblyManager      /root/reference/src/managers/assemblyManager.hpp:173-245, 383-494
@@ -223,6 +223,17 @@ class stokes : public PhysicsBase<EvalT> {           // stokes.cpp:17-46; variab
   bool useLSIC, usePSPG;
 };
 
+template <class EvalT = ScalarT>
+class helmholtz : public PhysicsBase<EvalT> {        // helmholtz.cpp:17-28; variables ureal, uimag (non-fractional branch only)
+ public:
+  helmholtz(ParameterList& settings, const int& dimension_) : PhysicsBase<EvalT>(settings, dimension_) {
+    this->label = "helmholtz";
+    this->myvars = {"ureal", "uimag"};
+    this->mybasistypes.assign(2, "HGRAD");
+    if (settings.template get<bool>("fractional", false)) throw std::runtime_error("helmholtz: the 'fractional' branch is not on the hot path");
+  }
+};
+
 // PhysicsImporter::import (physicsImporter.cpp:60-190), hot-path modules only
 template <class EvalT = ScalarT>
 inline RCP<PhysicsBase<EvalT>> importPhysics(const string& name, ParameterList& settings, const int& dimension) {
@@ -231,6 +242,7 @@ inline RCP<PhysicsBase<EvalT>> importPhysics(const string& name, ParameterList& 
   if (name == "linearelasticity") return std::make_shared<linearelasticity<EvalT>>(settings, dimension);
   if (name == "navierstokes") return std::make_shared<navierstokes<EvalT>>(settings, dimension);
   if (name == "stokes" || name == "Stokes") return std::make_shared<stokes<EvalT>>(settings, dimension);
+  if (name == "helmholtz") return std::make_shared<helmholtz<EvalT>>(settings, dimension);
   throw std::runtime_error("physics module not on the hot path: '" + name + "'");
 }
 

@@ -12,6 +12,7 @@ inline bool dispatch_cfg(int phys, int dim, int order, F&& f) {
   MRH_CASE(PHYS_LE, 2, 1) MRH_CASE(PHYS_LE, 2, 2) MRH_CASE(PHYS_LE, 3, 1)
   MRH_CASE(PHYS_NS, 2, 1) MRH_CASE(PHYS_NS, 2, 2) MRH_CASE(PHYS_NS, 3, 1)
   MRH_CASE(PHYS_STOKES, 2, 1) MRH_CASE(PHYS_STOKES, 2, 2) MRH_CASE(PHYS_STOKES, 3, 1)
+  MRH_CASE(PHYS_HELMHOLTZ, 2, 1) MRH_CASE(PHYS_HELMHOLTZ, 2, 2) MRH_CASE(PHYS_HELMHOLTZ, 3, 1)
 #undef MRH_CASE
   return false;
 }

@@ -7,7 +7,7 @@
 
 namespace mrh {
 
-enum Phys { PHYS_THERMAL = 0, PHYS_CDR = 1, PHYS_LE = 2, PHYS_NS = 3, PHYS_STOKES = 4 };      // stokes: the first module of SURVEY.md 8f3
+enum Phys { PHYS_THERMAL = 0, PHYS_CDR = 1, PHYS_LE = 2, PHYS_NS = 3, PHYS_STOKES = 4, PHYS_HELMHOLTZ = 5 };      // stokes, helmholtz: the next HGRAD modules of SURVEY.md 8f3
 enum BC { BC_NONE = 0, BC_DIRICHLET = 1, BC_WEAK_DIRICHLET = 2, BC_NEUMANN = 3, BC_FLUX = 4 };
 
 // program slots inside KParams::progs
@@ -15,6 +15,9 @@ enum { TH_SOURCE = 0, TH_DIFF, TH_CP, TH_RHO, TH_BX, TH_BY, TH_BZ };            
 enum { CDR_SOURCE = 0, CDR_DIFF, CDR_CP, CDR_RHO, CDR_REACTION, CDR_XVEL, CDR_YVEL, CDR_ZVEL };
 enum { LE_LAMBDA = 0, LE_MU, LE_SRC0, LE_SRC1, LE_SRC2 };
 enum { NS_SRC_UX = 0, NS_SRC_PR, NS_SRC_UY, NS_SRC_UZ, NS_DENSITY, NS_VISCOSITY };
+// helmholtz: c2r_x, c2i_x, c2r_y, c2i_y, c2r_z, c2i_z at 0..5 (volume and side launches alike); volume: sources in the pre-evaluated
+// slots, omega2 beyond them (evaluated on the fly); side: Robin coefficients, then the side sources in the slots of the unused variables 2, 3
+enum { HZ_C2 = 0, HZ_SRC_R = 6, HZ_SRC_I = 7, HZ_OMEGA2R = 8, HZ_OMEGA2I = 9, HZ_SIDE_ALPHA_R = 6, HZ_SIDE_ALPHA_I = 7, HZ_SIDE_SRC_R = 10, HZ_SIDE_SRC_I = 11 };
 enum { SIDE_DIFF = 0, SIDE_LAMBDA = 0, SIDE_MU = 1, SIDE_BCSRC = 8, SIDE_FLUX = 12 };     // "side ip"
 enum { VOL_INIT = 8 };                                                                   // "initial <var>" at "ip" (projection launches)
 enum { PROJ_NONE = 0, PROJ_DIRICHLET = 1, PROJ_INITIAL = 2 };

@@ -31,6 +31,7 @@ template <int DIM> struct PhysTraits<PHYS_CDR, DIM> { static constexpr int NVAR 
 template <int DIM> struct PhysTraits<PHYS_LE, DIM> { static constexpr int NVAR = DIM; };
 template <int DIM> struct PhysTraits<PHYS_NS, DIM> { static constexpr int NVAR = DIM + 1; };
 template <int DIM> struct PhysTraits<PHYS_STOKES, DIM> { static constexpr int NVAR = DIM + 1; };
+template <int DIM> struct PhysTraits<PHYS_HELMHOLTZ, DIM> { static constexpr int NVAR = 2; };
 // modules whose volume terms need the element size h = (sum w)^(1/d) (stabilisation parameters)
 template <int PHYS> struct NeedsElementSize { static constexpr bool value = PHYS == PHYS_NS || PHYS == PHYS_STOKES; };
 
@@ -281,6 +282,47 @@ struct Physics<PHYS_STOKES, DIM, S> {
     }
   }
   template <class IN> MRH_HDN static void boundary(const IN&, S (&)[NVAR][1 + DIM]) {}     // stokes.cpp:445-447 is empty
+};
+
+// -------------------------------------------------------------------------------------------- helmholtz
+// /root/reference/src/physics/helmholtz.cpp:71-240 (volume, non-fractional branch), :245-420 (boundary: Robin condition
+// alpha u + du/dn - source = 0 on sides where ureal is "Neumann").  Variables ureal, uimag on the same basis, so the reference's
+// test functions vr and vi are the same number: row (ureal, i) collects the coefficients of vr and vi together.
+template <int DIM, class S>
+struct Physics<PHYS_HELMHOLTZ, DIM, S> {
+  static constexpr int NVAR = 2;
+  template <class IN> MRH_HD static void volume(const IN& in, S (&F)[NVAR][1 + DIM]) {
+    const double w = in.w;
+    const S o2r = in.fn(HZ_OMEGA2R), o2i = in.fn(HZ_OMEGA2I), sr = in.fn(HZ_SRC_R), si = in.fn(HZ_SRC_I);
+    const S ur = in.U(0), ui = in.U(1);
+    F[0][0] = (-o2r * (ur + ui) + o2i * (ui - ur) - (sr + si)) * w;
+    F[1][0] = (-o2r * (ui - ur) - o2i * (ur + ui) - (si - sr)) * w;
+#pragma unroll
+    for (int c = 0; c < DIM; ++c) {
+      const S c2r = in.fn(HZ_C2 + 2 * c), c2i = in.fn(HZ_C2 + 2 * c + 1);
+      const S dur = in.dU(0, c), dui = in.dU(1, c);
+      F[0][1 + c] = (c2r * (dur + dui) - c2i * (dui - dur)) * w;
+      F[1][1 + c] = (c2r * (dui - dur) + c2i * (dur + dui)) * w;
+    }
+  }
+  template <class IN> MRH_HDN static void boundary(const IN& in, S (&F)[NVAR][1 + DIM]) {
+    if (in.kp->ph.bc[0] != BC_NEUMANN) return;
+    const double w = in.w;
+    const S ar = in.fn(HZ_SIDE_ALPHA_R), ai = in.fn(HZ_SIDE_ALPHA_I), sr = in.fn(HZ_SIDE_SRC_R), si = in.fn(HZ_SIDE_SRC_I);
+    const S ur = in.U(0), ui = in.U(1);
+    S durdn = S(0.0), duidn = S(0.0), c2durdn = S(0.0), c2duidn = S(0.0);
+#pragma unroll
+    for (int c = 0; c < DIM; ++c) {
+      const S c2r = in.fn(HZ_C2 + 2 * c), c2i = in.fn(HZ_C2 + 2 * c + 1);
+      const S dur = in.dU(0, c), dui = in.dU(1, c);
+      const double n = in.ps.nrm[c];
+      durdn = durdn + dur * n; duidn = duidn + dui * n;
+      c2durdn = c2durdn + (c2r * dur - c2i * dui) * n;
+      c2duidn = c2duidn + (c2r * dui + c2i * dur) * n;
+    }
+    F[0][0] = F[0][0] + (((ar * (ur + ui) - ai * (ui - ur)) + (durdn + duidn) - (sr + si)) - (c2durdn + c2duidn)) * w;
+    F[1][0] = F[1][0] + (((ar * (ui - ur) + ai * (ur + ui)) + (duidn - durdn) - (si - sr)) - (c2duidn - c2durdn)) * w;
+  }
 };
 
 }  // namespace mrh

@@ -564,12 +564,104 @@ struct stokes : PhysicsBase<EvalT> {
   void boundaryResidual() override {}
 };
 
+// ================================================================================================
+// helmholtz (frequency-domain wave equation, real / imaginary parts as two HGRAD variables), non-fractional branch:
+// /root/reference/src/physics/helmholtz.cpp:17-66 (variables, functions), :71-240 (volumeResidual), :245-420 (boundaryResidual:
+// Robin condition on sides where ureal is "Neumann").  Both variables use the same basis, so the reference's vr / vi (and their
+// gradients) are the same numbers; its formulas are kept term by term.
+template <class EvalT>
+struct helmholtz : PhysicsBase<EvalT> {
+  using PhysicsBase<EvalT>::wkset; using PhysicsBase<EvalT>::functionManager;
+  int ur_num = 0, ui_num = 1;
+  helmholtz(const StrMap& settings, int) {
+    this->label = "helmholtz"; this->myvars = {"ureal", "uimag"}; this->mybasistypes = {"HGRAD", "HGRAD"};
+    if (getOr(settings, "fractional", "false") == "true") throw std::runtime_error("oracle: helmholtz 'fractional' branch is not restated");
+  }
+  void defineFunctions(const StrMap& fs, FunctionManager<EvalT>* fm) override {
+    functionManager = fm;
+    for (const char* n : {"c2r_x", "c2i_x", "c2r_y", "c2i_y", "c2r_z", "c2i_z", "omega2r", "omega2i", "omegar", "omegai", "source_r", "source_i"})
+      fm->addFunction(n, getOr(fs, n, "0.0"), "ip");
+    for (const char* n : {"omega2r", "omega2i", "source_r_side", "source_i_side", "robin_alpha_r", "robin_alpha_i", "c2r_x", "c2i_x", "c2r_y", "c2i_y", "c2r_z", "c2i_z"})
+      fm->addFunction(n, getOr(fs, n, "0.0"), "side ip");
+  }
+  void setWorkset(Workset<EvalT>* w) override { wkset = w; ur_num = this->varnum("ureal"); ui_num = this->varnum("uimag"); }
+  void volumeResidual() override {
+    const int dim = wkset->dim, nb = wkset->nb, nq = wkset->gd->nq;
+    const char* XN[3] = {"x", "y", "z"};
+    Vista<EvalT> c2r[3], c2i[3];
+    for (int c = 0; c < 3; ++c) { c2r[c] = functionManager->evaluate(std::string("c2r_") + XN[c], "ip"); c2i[c] = functionManager->evaluate(std::string("c2i_") + XN[c], "ip"); }
+    auto omega2r = functionManager->evaluate("omega2r", "ip"), omega2i = functionManager->evaluate("omega2i", "ip");
+    auto source_r = functionManager->evaluate("source_r", "ip"), source_i = functionManager->evaluate("source_i", "ip");
+    auto& Ur = wkset->getSolutionField("ureal"); auto& Ui = wkset->getSolutionField("uimag");
+    Arr2<EvalT>* dUr[3]; Arr2<EvalT>* dUi[3];
+    for (int c = 0; c < dim; ++c) { dUr[c] = &wkset->getSolutionField(gradname("ureal", c)); dUi[c] = &wkset->getSolutionField(gradname("uimag", c)); }
+    auto& res = wkset->res; const GroupData& g = *wkset->gd;
+    for (int e = 0; e < wkset->numElem; ++e)
+      for (int k = 0; k < nq; ++k) {
+        const EvalT ur = Ur(e, k), ui = Ui(e, k);
+        const double w = wkset->wt(e, k);
+        for (int i = 0; i < nb; ++i) {
+          const double vr = g.B(e, i, k), vi = g.B(e, i, k);
+          EvalT sr = -omega2r(e, k) * (ur * vr + ui * vi) + omega2i(e, k) * (ui * vr - ur * vi);
+          EvalT si = -omega2r(e, k) * (ui * vr - ur * vi) - omega2i(e, k) * (ur * vr + ui * vi);
+          for (int c = 0; c < dim; ++c) {
+            const double dvr = g.G(e, i, k, c), dvi = g.G(e, i, k, c);
+            const EvalT dur = (*dUr[c])(e, k), dui = (*dUi[c])(e, k);
+            sr = sr + c2r[c](e, k) * (dur * dvr + dui * dvi) - c2i[c](e, k) * (dui * dvr - dur * dvi);
+            si = si + c2r[c](e, k) * (dui * dvr - dur * dvi) + c2i[c](e, k) * (dur * dvr + dui * dvi);
+          }
+          sr = sr - (source_r(e, k) * vr + source_i(e, k) * vi);
+          si = si - (source_i(e, k) * vr - source_r(e, k) * vi);
+          res(e, wkset->off(ur_num, i)) += sr * w;
+          res(e, wkset->off(ui_num, i)) += si * w;
+        }
+      }
+  }
+  void boundaryResidual() override {
+    const int dim = wkset->dim, nb = wkset->nb, nq = wkset->gd->nq;
+    const char* XN[3] = {"x", "y", "z"};
+    Vista<EvalT> c2r[3], c2i[3];
+    for (int c = 0; c < 3; ++c) { c2r[c] = functionManager->evaluate(std::string("c2r_") + XN[c], "side ip"); c2i[c] = functionManager->evaluate(std::string("c2i_") + XN[c], "side ip"); }
+    auto alpha_r = functionManager->evaluate("robin_alpha_r", "side ip"), alpha_i = functionManager->evaluate("robin_alpha_i", "side ip");
+    auto src_r = functionManager->evaluate("source_r_side", "side ip"), src_i = functionManager->evaluate("source_i_side", "side ip");
+    if (wkset->var_bcs[ur_num][wkset->currentside] != "Neumann") return;       // Robin condition alpha u + du/dn - source = 0
+    auto& Ur = wkset->getSolutionField("ureal"); auto& Ui = wkset->getSolutionField("uimag");
+    Arr2<EvalT>* dUr[3]; Arr2<EvalT>* dUi[3]; Arr2<double>* n[3];
+    for (int c = 0; c < dim; ++c) {
+      dUr[c] = &wkset->getSolutionField(gradname("ureal", c)); dUi[c] = &wkset->getSolutionField(gradname("uimag", c));
+      n[c] = &wkset->getScalarField(std::string("n[") + XYZ[c] + "]");
+    }
+    auto& res = wkset->res; const GroupData& g = *wkset->gd;
+    for (int e = 0; e < wkset->numElem; ++e)
+      for (int k = 0; k < nq; ++k) {
+        const EvalT ur = Ur(e, k), ui = Ui(e, k);
+        EvalT durdn = EvalT(0.0), duidn = EvalT(0.0), c2durdn = EvalT(0.0), c2duidn = EvalT(0.0);
+        for (int c = 0; c < dim; ++c) {
+          const EvalT dur = (*dUr[c])(e, k), dui = (*dUi[c])(e, k);
+          const double nc = (*n[c])(e, k);
+          durdn = durdn + dur * nc; duidn = duidn + dui * nc;
+          c2durdn = c2durdn + (c2r[c](e, k) * dur - c2i[c](e, k) * dui) * nc;
+          c2duidn = c2duidn + (c2r[c](e, k) * dui + c2i[c](e, k) * dur) * nc;
+        }
+        const double w = wkset->wt(e, k);
+        for (int i = 0; i < nb; ++i) {
+          const double vr = g.B(e, i, k), vi = g.B(e, i, k);
+          res(e, wkset->off(ur_num, i)) += (((alpha_r(e, k) * (ur * vr + ui * vi) - alpha_i(e, k) * (ui * vr - ur * vi)) + (durdn * vr + duidn * vi)
+                                            - (src_r(e, k) * vr + src_i(e, k) * vi)) - (c2durdn * vr + c2duidn * vi)) * w;
+          res(e, wkset->off(ui_num, i)) += (((alpha_r(e, k) * (ui * vr - ur * vi) + alpha_i(e, k) * (ur * vr + ui * vi)) + (duidn * vr - durdn * vi)
+                                            - (src_i(e, k) * vr - src_r(e, k) * vi)) - (c2duidn * vr - c2durdn * vi)) * w;
+        }
+      }
+  }
+};
+
 template <class EvalT>
 inline std::unique_ptr<PhysicsBase<EvalT>> importPhysics(const std::string& name, const StrMap& settings, int dim) {
   if (name == "thermal") return std::unique_ptr<PhysicsBase<EvalT>>(new thermal<EvalT>(settings, dim));
   if (name == "cdr") return std::unique_ptr<PhysicsBase<EvalT>>(new cdr<EvalT>(settings, dim));
   if (name == "linearelasticity") return std::unique_ptr<PhysicsBase<EvalT>>(new linearelasticity<EvalT>(settings, dim));
   if (name == "navierstokes") return std::unique_ptr<PhysicsBase<EvalT>>(new navierstokes<EvalT>(settings, dim));
+  if (name == "helmholtz") return std::unique_ptr<PhysicsBase<EvalT>>(new helmholtz<EvalT>(settings, dim));
   if (name == "stokes" || name == "Stokes") return std::unique_ptr<PhysicsBase<EvalT>>(new stokes<EvalT>(settings, dim));
   throw std::runtime_error("oracle: physics module not restated: " + name);
 }

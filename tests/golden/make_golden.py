@@ -56,7 +56,7 @@ if __name__ == "__main__":
     data = {"hgrad": hgrad(), "l2": {}}
     for p in ["thermal/2D_verification", "thermal/3D_verification", "cdr/2D_manufactured", "le/3D_manufactured",
               "le/2D_manufactured", "navierstokes/channel", "thermal/2D_mixed_bcs", "thermal/2D_verification_nonzeroDBC",
-              "stokes/2D_verification_pspg"]:
+              "stokes/2D_verification_pspg", "helmholtz/manufactured_solution"]:
         data["l2"][p] = l2(p)
     data["l2_series"] = {"thermal/2D_verification_transient": l2_series("thermal/2D_verification_transient")}
     json.dump(data, open(OUT, "w"), indent=1)

@@ -105,6 +105,19 @@ def cases():
     out.append((p["name"], p, {}))
     p = shrink(P.regression_stokes_2d(5)); p["name"] = "stokes 2D Q2"; p["order"] = 2; p["settings"] = {"useLSIC": True}
     out.append((p["name"], p, {}))
+    # helmholtz: the reference's 2-D deck (Robin side on the right), and a 3-D case with every coefficient non-trivial
+    p = shrink(P.regression_helmholtz_2d(8)); p["name"] = "helmholtz 2D robin"
+    p["functions"] = dict(p["functions"]); p["functions"].update({"robin_alpha_r": "0.5+y", "robin_alpha_i": "0.25*x", "omega2i": "0.3"})
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_helmholtz_2d(4)); p["name"] = "helmholtz 3D"
+    p["mesh"] = shrink(P.config_c5(4))["mesh"]
+    p["functions"] = {"c2r_x": "1.0+x*x", "c2i_x": "0.5*y", "c2r_y": "2.0-z", "c2i_y": "0.1", "c2r_z": "1.5", "c2i_z": "x*y*z", "omega2r": "2.0+x", "omega2i": "0.3*y",
+                      "source_r": "sin(2*pi*x)*z", "source_i": "cos(pi*y)", "robin_alpha_r": "1.0+z", "robin_alpha_i": "0.5", "source_r_side": "x+y", "source_i_side": "1.0-z"}
+    p["dirichlet"] = {v: {s: "0.0" for s in ("left", "bottom", "back")} for v in ("ureal", "uimag")}
+    p["neumann"] = {v: {s: "0.0" for s in ("right", "top")} for v in ("ureal", "uimag")}
+    out.append((p["name"], p, {}))
+    p = shrink(P.regression_helmholtz_2d(5)); p["name"] = "helmholtz 2D Q2"; p["order"] = 2
+    out.append((p["name"], p, {}))
     # lumped mass, fix-zero-rows
     p = shrink(P.regression_thermal_2d()); p["extra"] = {"lump mass": True, "fix zero rows": True}; p["name"] = "thermal 2D lump mass"
     out.append((p["name"], p, {}))

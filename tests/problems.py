@@ -33,6 +33,20 @@ def regression_thermal_2d_mixed_bcs(n=40):
                 true={"e": "sin(2*pi*x)*sin(2*pi*y)"})
 
 
+def regression_helmholtz_2d(n=100):
+    """regression/helmholtz/manufactured_solution: complex-valued Helmholtz operator as two HGRAD variables, Dirichlet on three sides,
+    Robin condition (sides where ureal is "Neumann") on the right"""
+    f = {"source_r_side": "2.0*pi*cos(2*pi*x)*sin(2*pi*y)", "source_i_side": "2.0*pi*cos(2*pi*x)*sin(2*pi*y)", "omega": "1.0",
+         "scoeff": "8*pi*pi*(x*x-2*x-1)-1.0", "scoeffi": "8*pi*pi*(x*x+2*x-1)-1.0", "srcoeff": "2.0-2*x", "sicoeff": "-2.0-2*x",
+         "source_r": "scoeff*sin(2*pi*x)*sin(2*pi*y) + srcoeff*2*pi*cos(2*pi*x)*sin(2*pi*y)",
+         "source_i": "scoeffi*sin(2*pi*x)*sin(2*pi*y) + sicoeff*2*pi*cos(2*pi*x)*sin(2*pi*y)",
+         "c2r_x": "x*x-1.0", "c2i_x": "2.0*x", "c2r_y": "x*x-1.0", "c2i_y": "2.0*x", "omega2r": "1.0", "omega2i": "0.0"}
+    d = {v: {"left": "0.0", "top": "0.0", "bottom": "0.0"} for v in ("ureal", "uimag")}
+    return dict(name="helmholtz/manufactured_solution", mesh=_mesh(2, (n, n)), physics="helmholtz", order=1, functions=f, dirichlet=d,
+                neumann={"ureal": {"right": "0.0"}, "uimag": {"right": "0.0"}},
+                true={"ureal": "sin(2*pi*x)*sin(2*pi*y)", "uimag": "sin(2*pi*x)*sin(2*pi*y)"})
+
+
 def regression_thermal_2d_nonzero_dbc(n=40):
     """regression/thermal/2D_verification_nonzeroDBC: Dirichlet data sin(x) sin(y), L2-projected onto the boundary DOFs"""
     return dict(name="thermal/2D_verification_nonzeroDBC", mesh=_mesh(2, (n, n)), physics="thermal", order=1,

@@ -22,8 +22,9 @@ CASES = [
     ("navierstokes/channel", problems.regression_ns_channel, 0),
     ("thermal/2D_mixed_bcs", problems.regression_thermal_2d_mixed_bcs, 1),
     ("stokes/2D_verification_pspg", problems.regression_stokes_2d, 0),
+    ("helmholtz/manufactured_solution", problems.regression_helmholtz_2d, 0),
 ]
-VARS = {"thermal": ["e"], "cdr": ["c"], "linearelasticity": ["dx", "dy", "dz"], "navierstokes": ["ux", "pr", "uy", "uz"], "stokes": ["ux", "pr", "uy", "uz"]}
+VARS = {"thermal": ["e"], "cdr": ["c"], "linearelasticity": ["dx", "dy", "dz"], "navierstokes": ["ux", "pr", "uy", "uz"], "stokes": ["ux", "pr", "uy", "uz"], "helmholtz": ["ureal", "uimag"]}
 
 
 @pytest.fixture(scope="module")
@@ -57,7 +58,8 @@ def test_reference_golds_from_the_gpu_solution(lib, path, make, method):
     assert info["last_linear_relres"] <= 1e-10, info
     o = Oracle(U.oracle_problem(p))
     uh = u.cpu().numpy()
-    names = VARS[p["physics"]][: (o.dim if p["physics"] == "linearelasticity" else o.dim + 1 if p["physics"] in ("navierstokes", "stokes") else 1)]
+    names = VARS[p["physics"]][: (o.dim if p["physics"] == "linearelasticity" else o.dim + 1 if p["physics"] in ("navierstokes", "stokes") else
+                                  2 if p["physics"] == "helmholtz" else 1)]
     for var, gold in GOLD["l2"][path].items():
         if var not in p["true"]:
             continue

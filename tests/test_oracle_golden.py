@@ -73,6 +73,7 @@ CASES = [
     ("navierstokes/channel", problems.regression_ns_channel),
     ("thermal/2D_mixed_bcs", problems.regression_thermal_2d_mixed_bcs),
     ("stokes/2D_verification_pspg", problems.regression_stokes_2d),
+    ("helmholtz/manufactured_solution", problems.regression_helmholtz_2d),
 ]
 
 
@@ -82,7 +83,8 @@ def test_regression_l2_errors(path, make):
     o = Oracle(config_text(**p))
     u = newton(o)
     names = {"thermal": ["e"], "cdr": ["c"], "linearelasticity": ["dx", "dy", "dz"][: o.dim],
-             "navierstokes": ["ux", "pr", "uy", "uz"][: o.dim + 1], "stokes": ["ux", "pr", "uy", "uz"][: o.dim + 1]}[p["physics"]]
+             "navierstokes": ["ux", "pr", "uy", "uz"][: o.dim + 1], "stokes": ["ux", "pr", "uy", "uz"][: o.dim + 1],
+             "helmholtz": ["ureal", "uimag"]}[p["physics"]]
     for var, gold in GOLD["l2"][path].items():
         if var not in p["true"]:
             continue
