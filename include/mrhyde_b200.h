@@ -44,7 +44,7 @@ enum { MRH_BC_NONE = 0, MRH_BC_DIRICHLET = 1, MRH_BC_WEAK_DIRICHLET = 2, MRH_BC_
  * module settings (thermal.cpp:24-41, linearelasticity.cpp:21-61, navierstokes.cpp:20-62). */
 typedef struct mrh_config {
   int32_t dim;                /* 2 or 3 */
-  const char* physics;        /* "thermal" | "cdr" | "linearelasticity" | "navierstokes" | "stokes" | "helmholtz" */
+  const char* physics;        /* "thermal" | "cdr" | "linearelasticity" | "navierstokes" | "stokes" | "helmholtz" | "burgers" */
   int32_t order;              /* HGRAD order, 1 or 2 (order 2 in 3-D: thermal and cdr only - the vector-valued modules return
                                * MRH_EUNSUPPORTED from mrh_assemble_*) */
   int32_t quadrature;         /* volume cubature degree; <0 = 2*order (discretizationInterface.cpp:166) */
@@ -64,7 +64,7 @@ typedef struct mrh_config {
                                * bit 7: no exchange inside mrh_assemble_* when a communicator is attached;
                                * bit 8: tile-staged scatter for the Q1 quadrilateral kernel (off by default: measured slower than its direct scatter) */
   int32_t use_lsic;           /* stokes "useLSIC" (stokes.cpp:44) */
-  int32_t reserved_;
+  int32_t use_evisc;          /* Burgers "use entropy viscosity" (burgers.cpp:24); its "use SUPG" travels in use_supg */
 } mrh_config;
 
 /* Workset time data: Workset::{time,deltat,isTransient,current_stage,butcher_A,butcher_b,BDF_wts}

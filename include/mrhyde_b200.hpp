@@ -234,6 +234,20 @@ class helmholtz : public PhysicsBase<EvalT> {        // helmholtz.cpp:17-28; var
   }
 };
 
+template <class EvalT = ScalarT>
+class Burgers : public PhysicsBase<EvalT> {          // burgers.cpp:17-26; variable u
+ public:
+  Burgers(ParameterList& settings, const int& dimension_) : PhysicsBase<EvalT>(settings, dimension_) {
+    this->label = "Burgers";
+    this->myvars = {"u"};
+    this->mybasistypes.assign(1, "HGRAD");
+    use_evisc = settings.template get<bool>("use entropy viscosity", false);
+    use_SUPG = settings.template get<bool>("use SUPG", false);
+  }
+  void configure(mrh_config& cfg) const override { cfg.use_evisc = use_evisc; cfg.use_supg = use_SUPG; }
+  bool use_evisc, use_SUPG;
+};
+
 // PhysicsImporter::import (physicsImporter.cpp:60-190), hot-path modules only
 template <class EvalT = ScalarT>
 inline RCP<PhysicsBase<EvalT>> importPhysics(const string& name, ParameterList& settings, const int& dimension) {
@@ -243,6 +257,7 @@ inline RCP<PhysicsBase<EvalT>> importPhysics(const string& name, ParameterList& 
   if (name == "navierstokes") return std::make_shared<navierstokes<EvalT>>(settings, dimension);
   if (name == "stokes" || name == "Stokes") return std::make_shared<stokes<EvalT>>(settings, dimension);
   if (name == "helmholtz") return std::make_shared<helmholtz<EvalT>>(settings, dimension);
+  if (name == "burgers" || name == "Burgers") return std::make_shared<Burgers<EvalT>>(settings, dimension);
   throw std::runtime_error("physics module not on the hot path: '" + name + "'");
 }
 

@@ -13,6 +13,7 @@ inline bool dispatch_cfg(int phys, int dim, int order, F&& f) {
   MRH_CASE(PHYS_NS, 2, 1) MRH_CASE(PHYS_NS, 2, 2) MRH_CASE(PHYS_NS, 3, 1)
   MRH_CASE(PHYS_STOKES, 2, 1) MRH_CASE(PHYS_STOKES, 2, 2) MRH_CASE(PHYS_STOKES, 3, 1)
   MRH_CASE(PHYS_HELMHOLTZ, 2, 1) MRH_CASE(PHYS_HELMHOLTZ, 2, 2) MRH_CASE(PHYS_HELMHOLTZ, 3, 1)
+  MRH_CASE(PHYS_BURGERS, 2, 1) MRH_CASE(PHYS_BURGERS, 2, 2) MRH_CASE(PHYS_BURGERS, 3, 1) MRH_CASE(PHYS_BURGERS, 3, 2)
 #undef MRH_CASE
   return false;
 }

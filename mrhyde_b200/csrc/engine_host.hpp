@@ -65,6 +65,7 @@ class EngineHost {
     else if (physics == "navierstokes") { phys = PHYS_NS; varlist = {"ux", "pr", "uy", "uz"}; varlist.resize(dim + 1); }
     else if (physics == "stokes" || physics == "Stokes") { phys = PHYS_STOKES; varlist = {"ux", "pr", "uy", "uz"}; varlist.resize(dim + 1); }
     else if (physics == "helmholtz") { phys = PHYS_HELMHOLTZ; varlist = {"ureal", "uimag"}; }
+    else if (physics == "burgers" || physics == "Burgers") { phys = PHYS_BURGERS; varlist = {"u"}; }
     else throw std::runtime_error("physics module not on the hot path: '" + physics + "'");
     nvar = (int)varlist.size();
     lay.build(dim, order);
@@ -228,7 +229,7 @@ class EngineHost {
     kp.u = st.u; kp.u_prev = st.u_prev; kp.u_stage = st.u_stage; kp.res = res; kp.jac = jac;
     kp.compute_jac = jac ? 1 : 0; kp.lump_mass = cfg.lump_mass;
     timeParams(kp.tp, st);
-    kp.ph.have_advection = cfg.include_advection; kp.ph.useSUPG = cfg.use_supg; kp.ph.usePSPG = cfg.use_pspg; kp.ph.useLSIC = cfg.use_lsic;
+    kp.ph.have_advection = cfg.include_advection; kp.ph.useSUPG = cfg.use_supg; kp.ph.usePSPG = cfg.use_pspg; kp.ph.useLSIC = cfg.use_lsic; kp.ph.useEvisc = cfg.use_evisc;
     kp.ph.formparam = cfg.form_param; kp.ph.le_penalty = cfg.le_penalty;
     for (int i = 0; i < nvar * nb; ++i) kp.offsets[i] = dofs.offsets[i];
     if (side < 0) {
@@ -340,6 +341,10 @@ class EngineHost {
       reg("lambda", "lambda", "1.0", "ip"); reg("mu", "mu", "0.5", "ip");
       reg("source dx", "source dx", "0.0", "ip"); reg("source dy", "source dy", "0.0", "ip"); reg("source dz", "source dz", "0.0", "ip");
       reg("lambda", "lambda", "1.0", "side ip"); reg("mu", "mu", "0.5", "side ip");
+    } else if (phys == PHYS_BURGERS) {         // burgers.cpp:31-45; "C1", "C2", "supg C", "supg C1", "supg C2" have no module defaults (0.0 here when absent and unused)
+      reg("Burgers source", "Burgers source", "0.0", "ip"); reg("diffusion", "diffusion", "0.0", "ip");
+      reg("xvel", "xvel", "1.0", "ip"); reg("yvel", "yvel", "1.0", "ip"); reg("zvel", "zvel", "1.0", "ip");
+      reg("xvel", "xvel", "1.0", "side ip"); reg("yvel", "yvel", "1.0", "side ip"); reg("zvel", "zvel", "1.0", "side ip");
     } else if (phys == PHYS_HELMHOLTZ) {       // helmholtz.cpp:33-66 (functions of the non-fractional branch)
       for (const char* n : {"c2r_x", "c2i_x", "c2r_y", "c2i_y", "c2r_z", "c2i_z", "omega2r", "omega2i", "source_r", "source_i"}) reg(n, n, "0.0", "ip");
       for (const char* n : {"c2r_x", "c2i_x", "c2r_y", "c2i_y", "c2r_z", "c2i_z", "robin_alpha_r", "robin_alpha_i", "source_r_side", "source_i_side"}) reg(n, n, "0.0", "side ip");
@@ -357,6 +362,12 @@ class EngineHost {
     if (phys == PHYS_CDR) return {{CDR_SOURCE, "source"}, {CDR_DIFF, "diffusion"}, {CDR_CP, "specific heat"}, {CDR_RHO, "density"},
                                   {CDR_REACTION, "reaction"}, {CDR_XVEL, "xvel"}, {CDR_YVEL, "yvel"}, {CDR_ZVEL, "zvel"}};
     if (phys == PHYS_LE) return {{LE_LAMBDA, "lambda"}, {LE_MU, "mu"}, {LE_SRC0, "source dx"}, {LE_SRC1, "source dy"}, {LE_SRC2, "source dz"}};
+    if (phys == PHYS_BURGERS) {
+      std::vector<std::pair<int, std::string>> v = {{BG_SRC, "Burgers source"}, {BG_DIFF, "diffusion"}, {BG_VEL, "xvel"}, {BG_VEL + 1, "yvel"}, {BG_VEL + 2, "zvel"}};
+      if (dim == 2 && cfg.use_evisc) { v.push_back({BG_C1, "C1"}); v.push_back({BG_C2, "C2"}); }
+      if (dim == 2 && cfg.use_supg) { v.push_back({BG_SUPG_C, "supg C"}); v.push_back({BG_SUPG_C1, "supg C1"}); v.push_back({BG_SUPG_C2, "supg C2"}); }
+      return v;
+    }
     if (phys == PHYS_HELMHOLTZ) return {{HZ_C2 + 0, "c2r_x"}, {HZ_C2 + 1, "c2i_x"}, {HZ_C2 + 2, "c2r_y"}, {HZ_C2 + 3, "c2i_y"}, {HZ_C2 + 4, "c2r_z"}, {HZ_C2 + 5, "c2i_z"},
                                         {HZ_SRC_R, "source_r"}, {HZ_SRC_I, "source_i"}, {HZ_OMEGA2R, "omega2r"}, {HZ_OMEGA2I, "omega2i"}};
     if (phys == PHYS_STOKES) return {{NS_SRC_UX, "source ux"}, {NS_SRC_PR, "source pr"}, {NS_SRC_UY, "source uy"}, {NS_SRC_UZ, "source uz"}, {NS_VISCOSITY, "viscosity"}};
@@ -366,6 +377,7 @@ class EngineHost {
   std::vector<std::pair<int, std::string>> sideNames() const {
     if (phys == PHYS_THERMAL) return {{SIDE_DIFF, "thermal diffusion"}};
     if (phys == PHYS_LE) return {{SIDE_LAMBDA, "lambda"}, {SIDE_MU, "mu"}};
+    if (phys == PHYS_BURGERS) return {{BG_SIDE_VEL, "xvel"}, {BG_SIDE_VEL + 1, "yvel"}};
     if (phys == PHYS_HELMHOLTZ) return {{HZ_C2 + 0, "c2r_x"}, {HZ_C2 + 1, "c2i_x"}, {HZ_C2 + 2, "c2r_y"}, {HZ_C2 + 3, "c2i_y"}, {HZ_C2 + 4, "c2r_z"}, {HZ_C2 + 5, "c2i_z"},
                                         {HZ_SIDE_ALPHA_R, "robin_alpha_r"}, {HZ_SIDE_ALPHA_I, "robin_alpha_i"}, {HZ_SIDE_SRC_R, "source_r_side"}, {HZ_SIDE_SRC_I, "source_i_side"}};
     return {};

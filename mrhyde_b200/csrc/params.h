@@ -7,7 +7,7 @@
 
 namespace mrh {
 
-enum Phys { PHYS_THERMAL = 0, PHYS_CDR = 1, PHYS_LE = 2, PHYS_NS = 3, PHYS_STOKES = 4, PHYS_HELMHOLTZ = 5 };      // stokes, helmholtz: the next HGRAD modules of SURVEY.md 8f3
+enum Phys { PHYS_THERMAL = 0, PHYS_CDR = 1, PHYS_LE = 2, PHYS_NS = 3, PHYS_STOKES = 4, PHYS_HELMHOLTZ = 5, PHYS_BURGERS = 6 };      // stokes, helmholtz: the next HGRAD modules of SURVEY.md 8f3
 enum BC { BC_NONE = 0, BC_DIRICHLET = 1, BC_WEAK_DIRICHLET = 2, BC_NEUMANN = 3, BC_FLUX = 4 };
 
 // program slots inside KParams::progs
@@ -17,6 +17,7 @@ enum { LE_LAMBDA = 0, LE_MU, LE_SRC0, LE_SRC1, LE_SRC2 };
 enum { NS_SRC_UX = 0, NS_SRC_PR, NS_SRC_UY, NS_SRC_UZ, NS_DENSITY, NS_VISCOSITY };
 // helmholtz: c2r_x, c2i_x, c2r_y, c2i_y, c2r_z, c2i_z at 0..5 (volume and side launches alike); volume: sources in the pre-evaluated
 // slots, omega2 beyond them (evaluated on the fly); side: Robin coefficients, then the side sources in the slots of the unused variables 2, 3
+enum { BG_SRC = 0, BG_DIFF, BG_VEL, BG_C1 = 5, BG_C2, BG_SUPG_C, BG_SUPG_C1, BG_SUPG_C2, BG_SIDE_VEL = 0 };      // Burgers ("supg C1" / "supg C2" beyond the pre-evaluated slots)
 enum { HZ_C2 = 0, HZ_SRC_R = 6, HZ_SRC_I = 7, HZ_OMEGA2R = 8, HZ_OMEGA2I = 9, HZ_SIDE_ALPHA_R = 6, HZ_SIDE_ALPHA_I = 7, HZ_SIDE_SRC_R = 10, HZ_SIDE_SRC_I = 11 };
 enum { SIDE_DIFF = 0, SIDE_LAMBDA = 0, SIDE_MU = 1, SIDE_BCSRC = 8, SIDE_FLUX = 12 };     // "side ip"
 enum { VOL_INIT = 8 };                                                                   // "initial <var>" at "ip" (projection launches)
@@ -49,6 +50,7 @@ struct PhysParams {
   double le_penalty;     // LE "penalty"
   int proj;              // L2-projection launch (assemble.h projection): PROJ_DIRICHLET on a side set, PROJ_INITIAL over the volume
   int useLSIC;           // stokes "useLSIC"
+  int useEvisc;          // Burgers "use entropy viscosity" (its "use SUPG" travels in useSUPG)
 };
 
 struct TilePlan {          // tile-staged scatter of the specialised kernels (built at finalize, engine_tiles.inl)

@@ -32,8 +32,9 @@ template <int DIM> struct PhysTraits<PHYS_LE, DIM> { static constexpr int NVAR =
 template <int DIM> struct PhysTraits<PHYS_NS, DIM> { static constexpr int NVAR = DIM + 1; };
 template <int DIM> struct PhysTraits<PHYS_STOKES, DIM> { static constexpr int NVAR = DIM + 1; };
 template <int DIM> struct PhysTraits<PHYS_HELMHOLTZ, DIM> { static constexpr int NVAR = 2; };
+template <int DIM> struct PhysTraits<PHYS_BURGERS, DIM> { static constexpr int NVAR = 1; };
 // modules whose volume terms need the element size h = (sum w)^(1/d) (stabilisation parameters)
-template <int PHYS> struct NeedsElementSize { static constexpr bool value = PHYS == PHYS_NS || PHYS == PHYS_STOKES; };
+template <int PHYS> struct NeedsElementSize { static constexpr bool value = PHYS == PHYS_NS || PHYS == PHYS_STOKES || PHYS == PHYS_BURGERS; };
 
 template <int PHYS, int DIM, class S> struct Physics;
 
@@ -322,6 +323,48 @@ struct Physics<PHYS_HELMHOLTZ, DIM, S> {
     }
     F[0][0] = F[0][0] + (((ar * (ur + ui) - ai * (ui - ur)) + (durdn + duidn) - (sr + si)) - (c2durdn + c2duidn)) * w;
     F[1][0] = F[1][0] + (((ar * (ui - ur) + ai * (ur + ui)) + (duidn - durdn) - (si - sr)) - (c2duidn - c2durdn)) * w;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------- Burgers
+// /root/reference/src/physics/burgers.cpp:50-164 (volume: 2-D with optional entropy viscosity and SUPG, 3-D plain), :169-205 (2-D
+// Neumann flux 1/2 u^2 v.n).  Quirks kept: the entropy viscosity is clamped to the plain number 0.1 (derivatives dropped), |v| stays
+// squared when |v|^2 <= 1e-12.
+template <int DIM, class S>
+struct Physics<PHYS_BURGERS, DIM, S> {
+  static constexpr int NVAR = 1;
+  template <class IN> MRH_HD static void volume(const IN& in, S (&F)[NVAR][1 + DIM]) {
+    const double w = in.w;
+    const S source = in.fn(BG_SRC), eps = in.fn(BG_DIFF);
+    const S u = in.U(0), dudt = in.Ut(0);
+    S v[DIM];
+#pragma unroll
+    for (int c = 0; c < DIM; ++c) v[c] = in.fn(BG_VEL + c);
+    S evisc = S(0.0);
+    if (DIM == 2 && in.kp->ph.useEvisc) {
+      const S entres = u * (dudt + u * in.dU(0, 0) + u * in.dU(0, 1));
+      S a = 1.0e-12 + entres;
+      if (val(a) < 0.0) a = -a;
+      evisc = in.fn(BG_C1) * in.h * in.h * a / in.fn(BG_C2);
+    }
+    if (val(evisc) > 0.1) evisc = S(0.1);
+    const S usq = 0.5 * u * u;
+    F[0][0] = (dudt - source) * w;
+#pragma unroll
+    for (int c = 0; c < DIM; ++c) F[0][1 + c] = ((eps + evisc) * in.dU(0, c) - v[c] * usq) * w;
+    if (DIM == 2 && in.kp->ph.useSUPG) {
+      S nvel = v[0] * v[0] + v[1] * v[1];
+      if (val(nvel) > 1E-12) nvel = f_sqrt(nvel);
+      const S tau = in.fn(BG_SUPG_C) / (in.fn(BG_SUPG_C1) / in.kp->tp.dt + in.fn(BG_SUPG_C2) * nvel / in.h);
+      const S sres = tau * (dudt + v[0] * u * in.dU(0, 0) + v[1] * u * in.dU(0, 1) - source) * w;
+      F[0][1] = F[0][1] + sres * u * v[0];
+      F[0][2] = F[0][2] + sres * u * v[1];
+    }
+  }
+  template <class IN> MRH_HDN static void boundary(const IN& in, S (&F)[NVAR][1 + DIM]) {
+    if (DIM != 2 || in.kp->ph.bc[0] != BC_NEUMANN) return;
+    const S u = in.U(0);
+    F[0][0] = F[0][0] + 0.5 * u * u * in.w * (in.fn(BG_SIDE_VEL) * in.ps.nrm[0] + in.fn(BG_SIDE_VEL + 1) * in.ps.nrm[1]);
   }
 };
 

@@ -17,7 +17,7 @@ class MrhConfig(C.Structure):
                 ("side_quadrature", C.c_int32), ("use_strong_dbc", C.c_int32), ("fix_zero_rows", C.c_int32),
                 ("lump_mass", C.c_int32), ("include_advection", C.c_int32), ("use_supg", C.c_int32),
                 ("use_pspg", C.c_int32), ("form_param", C.c_double), ("le_penalty", C.c_double),
-                ("device", C.c_int32), ("flags", C.c_int32), ("use_lsic", C.c_int32), ("reserved_", C.c_int32)]
+                ("device", C.c_int32), ("flags", C.c_int32), ("use_lsic", C.c_int32), ("use_evisc", C.c_int32)]
 
 
 class MrhState(C.Structure):
@@ -160,9 +160,10 @@ class Engine:
         cfg.quadrature, cfg.side_quadrature = quadrature, side_quadrature
         cfg.use_strong_dbc, cfg.fix_zero_rows, cfg.lump_mass = int(use_strong_dbc), int(fix_zero_rows), int(lump_mass)
         cfg.include_advection = int(bool(settings.get("include advection", False)))
-        cfg.use_supg = int(bool(settings.get("useSUPG", False)))
+        cfg.use_supg = int(bool(settings.get("useSUPG", False) or settings.get("use SUPG", False)))     # "use SUPG": the Burgers spelling
         cfg.use_pspg = int(bool(settings.get("usePSPG", False)))
         cfg.use_lsic = int(bool(settings.get("useLSIC", False)))
+        cfg.use_evisc = int(bool(settings.get("use entropy viscosity", False)))
         cfg.form_param = float(settings.get("form_param", 1.0))
         cfg.le_penalty = float(settings.get("penalty", 10.0))
         cfg.device = device

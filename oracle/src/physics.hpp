@@ -655,12 +655,93 @@ struct helmholtz : PhysicsBase<EvalT> {
   }
 };
 
+// ================================================================================================
+// Burgers: du/dt + div(1/2 v u^2 - eps grad u) = source.  /root/reference/src/physics/burgers.cpp:17-26 (settings), :31-45 (functions),
+// :50-164 (volumeResidual: 2-D with optional entropy viscosity and SUPG, 3-D plain), :169-205 (boundaryResidual: 2-D Neumann flux).
+// Quirks kept: the entropy viscosity is clamped to the PLAIN number 0.1 (its derivatives vanish once clamped); |v| is left squared when
+// |v|^2 <= 1e-12; "C1", "C2", "supg C", "supg C1", "supg C2" are user functions without module defaults.
+template <class EvalT>
+struct burgers : PhysicsBase<EvalT> {
+  using PhysicsBase<EvalT>::wkset; using PhysicsBase<EvalT>::functionManager;
+  bool use_evisc = false, use_SUPG = false; int unum = 0;
+  burgers(const StrMap& settings, int) {
+    this->label = "Burgers"; this->myvars = {"u"}; this->mybasistypes = {"HGRAD"};
+    use_evisc = getOr(settings, "use entropy viscosity", "false") == "true";
+    use_SUPG = getOr(settings, "use SUPG", "false") == "true";
+  }
+  void defineFunctions(const StrMap& fs, FunctionManager<EvalT>* fm) override {
+    functionManager = fm;
+    fm->addFunction("Burgers source", getOr(fs, "Burgers source", "0.0"), "ip");
+    fm->addFunction("diffusion", getOr(fs, "diffusion", "0.0"), "ip");
+    for (const char* n : {"xvel", "yvel", "zvel"}) fm->addFunction(n, getOr(fs, n, "1.0"), "ip");
+    for (const char* n : {"xvel", "yvel", "zvel"}) fm->addFunction(n, getOr(fs, n, "1.0"), "side ip");
+  }
+  void setWorkset(Workset<EvalT>* w) override { wkset = w; unum = this->varnum("u"); }
+  void volumeResidual() override {
+    const int dim = wkset->dim, nb = wkset->nb, nq = wkset->gd->nq;
+    auto source = functionManager->evaluate("Burgers source", "ip");
+    auto eps = functionManager->evaluate("diffusion", "ip");
+    const char* vn[3] = {"xvel", "yvel", "zvel"};
+    Vista<EvalT> v[3]; for (int c = 0; c < dim; ++c) v[c] = functionManager->evaluate(vn[c], "ip");
+    Vista<EvalT> C1, C2, sC, sC1, sC2;
+    const bool ev = use_evisc && dim == 2, supg = use_SUPG && dim == 2;          // the 3-D branch has neither (burgers.cpp:141-163)
+    if (ev) { C1 = functionManager->evaluate("C1", "ip"); C2 = functionManager->evaluate("C2", "ip"); }
+    if (supg) { sC = functionManager->evaluate("supg C", "ip"); sC1 = functionManager->evaluate("supg C1", "ip"); sC2 = functionManager->evaluate("supg C2", "ip"); }
+    auto& U = wkset->getSolutionField("u"); auto& dUdt = wkset->getSolutionField("u_t");
+    Arr2<EvalT>* dU[3]; for (int c = 0; c < dim; ++c) dU[c] = &wkset->getSolutionField(gradname("u", c));
+    auto h = wkset->getElementSize(); const double dt = wkset->deltat;
+    auto& res = wkset->res; const GroupData& g = *wkset->gd;
+    for (int elem = 0; elem < wkset->numElem; ++elem)
+      for (int pt = 0; pt < nq; ++pt) {
+        const EvalT u = U(elem, pt), dudt = dUdt(elem, pt);
+        const double w = wkset->wt(elem, pt);
+        EvalT evisc = EvalT(0.0);
+        if (ev) {
+          EvalT entres = u * (dudt + u * (*dU[0])(elem, pt) + u * (*dU[1])(elem, pt));
+          EvalT a = 1.0e-12 + entres; if (value_of(a) < 0.0) a = -a;
+          evisc = C1(elem, pt) * h[elem] * h[elem] * a / C2(elem, pt);
+        }
+        if (value_of(evisc) > 0.1) evisc = EvalT(0.1);
+        const EvalT usq = 0.5 * u * u;
+        const EvalT f = (dudt - source(elem, pt)) * w;
+        EvalT F[3];
+        for (int c = 0; c < dim; ++c) F[c] = ((eps(elem, pt) + evisc) * (*dU[c])(elem, pt) - v[c](elem, pt) * usq) * w;
+        if (supg) {
+          EvalT nvel = v[0](elem, pt) * v[0](elem, pt) + v[1](elem, pt) * v[1](elem, pt);
+          if (value_of(nvel) > 1E-12) nvel = sqrt(nvel);
+          const EvalT tau = sC(elem, pt) / (sC1(elem, pt) / dt + sC2(elem, pt) * nvel / h[elem]);
+          const EvalT sres = tau * (dudt + v[0](elem, pt) * u * (*dU[0])(elem, pt) + v[1](elem, pt) * u * (*dU[1])(elem, pt) - source(elem, pt)) * w;
+          F[0] = F[0] + sres * u * v[0](elem, pt);
+          F[1] = F[1] + sres * u * v[1](elem, pt);
+        }
+        for (int dof = 0; dof < nb; ++dof) {
+          EvalT r = f * g.B(elem, dof, pt);
+          for (int c = 0; c < dim; ++c) r = r + F[c] * g.G(elem, dof, pt, c);
+          res(elem, wkset->off(unum, dof)) += r;
+        }
+      }
+  }
+  void boundaryResidual() override {
+    const int dim = wkset->dim, nb = wkset->nb, nq = wkset->gd->nq;
+    if (!(dim == 2 && wkset->var_bcs[unum][wkset->currentside] == "Neumann")) return;
+    auto& U = wkset->getSolutionField("u");
+    auto vx = functionManager->evaluate("xvel", "side ip"), vy = functionManager->evaluate("yvel", "side ip");
+    auto& nx = wkset->getScalarField("n[x]"); auto& ny = wkset->getScalarField("n[y]");
+    auto& res = wkset->res; const GroupData& g = *wkset->gd;
+    for (int elem = 0; elem < wkset->numElem; ++elem)
+      for (int dof = 0; dof < nb; ++dof)
+        for (int pt = 0; pt < nq; ++pt)
+          res(elem, wkset->off(unum, dof)) += 0.5 * U(elem, pt) * U(elem, pt) * wkset->wt(elem, pt) * g.B(elem, dof, pt) * (vx(elem, pt) * nx(elem, pt) + vy(elem, pt) * ny(elem, pt));
+  }
+};
+
 template <class EvalT>
 inline std::unique_ptr<PhysicsBase<EvalT>> importPhysics(const std::string& name, const StrMap& settings, int dim) {
   if (name == "thermal") return std::unique_ptr<PhysicsBase<EvalT>>(new thermal<EvalT>(settings, dim));
   if (name == "cdr") return std::unique_ptr<PhysicsBase<EvalT>>(new cdr<EvalT>(settings, dim));
   if (name == "linearelasticity") return std::unique_ptr<PhysicsBase<EvalT>>(new linearelasticity<EvalT>(settings, dim));
   if (name == "navierstokes") return std::unique_ptr<PhysicsBase<EvalT>>(new navierstokes<EvalT>(settings, dim));
+  if (name == "burgers" || name == "Burgers") return std::unique_ptr<PhysicsBase<EvalT>>(new burgers<EvalT>(settings, dim));
   if (name == "helmholtz") return std::unique_ptr<PhysicsBase<EvalT>>(new helmholtz<EvalT>(settings, dim));
   if (name == "stokes" || name == "Stokes") return std::unique_ptr<PhysicsBase<EvalT>>(new stokes<EvalT>(settings, dim));
   throw std::runtime_error("oracle: physics module not restated: " + name);

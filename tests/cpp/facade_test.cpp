@@ -31,7 +31,7 @@ static int layout() {
   F(mrh_config, use_strong_dbc); F(mrh_config, fix_zero_rows); F(mrh_config, lump_mass); F(mrh_config, include_advection);
   F(mrh_config, use_supg); F(mrh_config, use_pspg); F(mrh_config, form_param); F(mrh_config, le_penalty); F(mrh_config, device);
   F(mrh_config, flags); F(mrh_config, use_lsic);
-  printf("\"reserved_\": %zu}, \"state\": {", offsetof(mrh_config, reserved_));
+  printf("\"use_evisc\": %zu}, \"state\": {", offsetof(mrh_config, use_evisc));
   F(mrh_state, u); F(mrh_state, u_prev); F(mrh_state, u_stage); F(mrh_state, is_transient); F(mrh_state, nstages); F(mrh_state, nsteps);
   F(mrh_state, stage); F(mrh_state, butcher_A); F(mrh_state, butcher_b); F(mrh_state, bdf_wts); F(mrh_state, time); F(mrh_state, deltat);
   printf("\"stream\": %zu}}\n", offsetof(mrh_state, stream));

@@ -118,6 +118,21 @@ def cases():
     out.append((p["name"], p, {}))
     p = shrink(P.regression_helmholtz_2d(5)); p["name"] = "helmholtz 2D Q2"; p["order"] = 2
     out.append((p["name"], p, {}))
+    # Burgers (the reference's own decks are 1-D, so these are oracle-pinned only): plain 2-D with a Neumann flux side,
+    # 2-D with entropy viscosity + SUPG (transient: dt enters tau), plain 3-D, 2-D Q2
+    bg = dict(name="burgers 2D neumann", mesh=shrink(P.regression_thermal_2d())["mesh"], physics="burgers", order=1,
+              functions={"Burgers source": "sin(pi*x)*y", "diffusion": "0.05+0.1*x", "xvel": "1.0+0.5*y", "yvel": "0.5-x"},
+              dirichlet={"u": {"left": "0.0", "bottom": "0.0"}}, neumann={"u": {"right": "0.0", "top": "0.0"}}, true={})
+    out.append((bg["name"], bg, {}))
+    p = copy.deepcopy(bg); p["name"] = "burgers 2D evisc+supg transient"; p["extra"] = {"transient": True}
+    p["settings"] = {"use entropy viscosity": True, "use SUPG": True}
+    p["functions"].update({"C1": "1.0+x", "C2": "2.0", "supg C": "0.5", "supg C1": "1.0", "supg C2": "2.0+y"})
+    out.append((p["name"], p, {"transient": be}))
+    p = copy.deepcopy(bg); p["name"] = "burgers 3D"; p["mesh"] = shrink(P.config_c5(4))["mesh"]
+    p["functions"]["zvel"] = "0.25+x*y"; p["dirichlet"] = {"u": {"left": "0.0", "bottom": "0.0", "back": "0.0"}}; p["neumann"] = {}
+    out.append((p["name"], p, {}))
+    p = copy.deepcopy(bg); p["name"] = "burgers 2D Q2"; p["order"] = 2
+    out.append((p["name"], p, {}))
     # lumped mass, fix-zero-rows
     p = shrink(P.regression_thermal_2d()); p["extra"] = {"lump mass": True, "fix zero rows": True}; p["name"] = "thermal 2D lump mass"
     out.append((p["name"], p, {}))
