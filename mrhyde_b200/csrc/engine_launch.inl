@@ -1,8 +1,9 @@
 // Part of engine.cu: device set-up, launch logic and the GPU-side C-ABI entry points.
 
-// SMs the interior launch leaves free for the exchange kernels when it overlaps them (MRH_XCH_SMS overrides; every reserved SM costs
-// 1/148 of the interior's throughput, too few serialise the pack / NCCL / unpack kernels behind the persistent CTAs)
-static const int XCH_RESERVE_SMS = [] { const char* ev = getenv("MRH_XCH_SMS"); return ev ? std::max(0, atoi(ev)) : 4; }();
+// SMs the interior launch leaves free for the exchange kernels when it overlaps them (MRH_XCH_SMS overrides).  Measured on 2 B200s
+// (256^3 per GPU): 4 reserved SMs 6.35 ms, 2: 6.27, 1: 6.27, 0: 6.20 (one GPU: 6.16) - every reserved SM costs 1/148 of the interior's
+// throughput, while with none the pack / NCCL / unpack kernels slip in as the persistent CTAs of the interior launch retire.
+static const int XCH_RESERVE_SMS = [] { const char* ev = getenv("MRH_XCH_SMS"); return ev ? std::max(0, atoi(ev)) : 0; }();
 #if !defined(MRH_WSK_DEFAULT)
 #define MRH_WSK_DEFAULT 0      // K-in-registers thermal kernel: MRH_WSK=1 enables it
 #endif
