@@ -104,6 +104,7 @@ int orc_eval_expression(void* h, const char* expr, int g, double time, double* o
     Workset<double> wk; wk.setup(o->cfg.dim, o->varlist, o->ref.nb, o->dofs.offsets, G.numElem, o->ref.nq, o->ref.nqs, false);
     wk.time = time; wk.attach(&G, false);
     FunctionManager<double> fm(G.numElem, o->ref.nq, o->ref.nqs); fm.wkset = &wk;
+    fm.parameters = o->cfg.parameters;
     for (auto& f : o->cfg.functions) fm.addFunction(f.first, f.second, "ip");
     fm.addFunction("__expr__", expr, "ip");
     std::vector<double> zero((size_t)G.numElem * o->dofs.ndof_elem, 0.0);

@@ -118,6 +118,33 @@ def test_expression_known_answers(lib):
         np.testing.assert_allclose(e.eval_function(k, pts), o.eval_expression(k, 0, 16).ravel(), rtol=1e-14, atol=1e-15, err_msg=k)
 
 
+def test_parameter_leaves_known_answers(lib):
+    """Scalar / vector parameters as leaves `name`, `name(k)`, `name(kk)` (functionManager.cpp:270-355): product compiler vs numpy and
+    vs the oracle; a parameter shadows a function of the same name (it is looked up first), a component out of range is an error"""
+    from mrhyde_b200 import Engine, MrhError
+    p = problems.regression_thermal_2d(4)
+    p["functions"] = dict(p["functions"])
+    p["parameters"] = {"kap": [1.25, -7.0, 0.5], "amp": 0.75, "long": list(np.arange(12.0) * 0.5)}
+    p["functions"].update({"g1": "kap+kap(2)*x*y+amp*y", "g2": "sin(kap(1)*x)+long(11)*y", "amp2": "amp*amp", "g3": "amp2+x", "kap": "100.0", "g4": "kap+1.0"})
+    e = Engine.from_problem(p, lib=lib, host_only=True)
+    rng = np.random.default_rng(5)
+    X = rng.random((40, 2))
+    x, y = X[:, 0], X[:, 1]
+    want = {"g1": 1.25 + 0.5 * x * y + 0.75 * y, "g2": np.sin(-7.0 * x) + 5.5 * y, "g3": 0.75 * 0.75 + x, "g4": 1.25 + 1.0 + 0 * x}
+    for k, w in want.items():
+        np.testing.assert_allclose(e.eval_function(k, X), w, rtol=1e-14, atol=1e-15, err_msg=k)
+    from oracle.pyoracle import Oracle
+    o = Oracle(U.oracle_problem(p))
+    _, _, _, ip = o.group_basis(0, 16)
+    pts = np.stack([ip[0].ravel(), ip[1].ravel()], axis=1)
+    for k in want:
+        np.testing.assert_allclose(e.eval_function(k, pts), o.eval_expression(k, 0, 16).ravel(), rtol=1e-14, atol=1e-15, err_msg=k)
+    p["functions"]["bad"] = "kap(7)+x"
+    p["functions"]["thermal diffusion"] = "bad"
+    with pytest.raises(MrhError, match="out of range"):
+        Engine.from_problem(p, lib=lib, host_only=True)
+
+
 def test_errors_are_reported_not_thrown(lib):
     from mrhyde_b200 import Engine, MrhError
     with pytest.raises(MrhError):
