@@ -110,9 +110,14 @@ void device_finalize(mrh_engine* h) {
         // sin / cos calls hoisted into a lane-parallel atom table when they fit the kernel's scratch (the smallest D region of a
         // point is 33 doubles); MRH_BAT_ATOMS=0 keeps the plain printer
         int natoms = 0;
-        static const int atoms_env = [] { const char* ev = getenv("MRH_BAT_ATOMS"); return ev ? atoi(ev) : 0; }();   // measured slower on B200 (C3 53.1 vs 48.6 ms, C4 94 vs 86 ms): off
+        // MRH_BAT_ATOMS: 0 off, 1 on, default automatic - the programs are evaluated by one lane per point, so hoisting pays when few
+        // lanes are busy there: measured with the table-driven atoms, C4 (8 points, 18 atoms) 59.4 -> 53.8 ms, C3 (27 points, 6 atoms)
+        // 45.4 -> 48.3 ms
+        static const int atoms_env = [] { const char* ev = getenv("MRH_BAT_ATOMS"); return ev ? atoi(ev) : -1; }();
+        const bool want_atoms = atoms_env > 0 || (atoms_env < 0 && H.ref.vol.nq <= 16);
         std::string preamble;
-        std::string src = atoms_env ? jit_batched_atom_source(H.vol_progs, MRH_NCOEF, H.ec.code, H.ec.cpool, 32, natoms, &preamble) : std::string();
+        std::string src = want_atoms ? jit_batched_atom_source(H.vol_progs, MRH_NCOEF, H.ec.code, H.ec.cpool, 32, natoms, &preamble) : std::string();
+        if (atoms_env < 0 && natoms < 4) { src.clear(); natoms = 0; }           // too few distinct calls to be worth the extra pass
         if (src.empty() || natoms == 0) {
           natoms = 0; src.clear();
           for (int k = 0; k < MRH_NCOEF; ++k) {
