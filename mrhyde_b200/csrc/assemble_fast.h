@@ -436,8 +436,8 @@ struct ThermalHexQ1 {
     fetch_rows(e_next);
     asm volatile("cp.async.commit_group;" ::: "memory");
     for (int64_t t = tfirst; t < tp.tile_end; t += tstep) {
-      const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
-      const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
+      const int64_t eb = tp.ebeg[t], rb = tp.rptr[t];
+      const int E = (int)(tp.eptr[t + 1] - tp.eptr[t]), R = (int)(tp.rptr[t + 1] - rb);
       for (int k = tid; k < E; k += 128) cp_async4(s_off + k, tp.off + eb + k);
       for (int k = tid; k < R; k += 128) cp_async4(s_rows + k, tp.rows + rb + k);
       asm volatile("cp.async.commit_group;" ::: "memory");
@@ -574,8 +574,8 @@ struct ThermalHexQ1 {
     struct TileMeta { int64_t eb, rb, base; int E, R, clid; };
     auto load_meta = [&](int64_t t, TileMeta& m) {
       if (t >= tp.tile_end) { m.E = m.R = 0; m.clid = 0; m.eb = m.rb = m.base = 0; return; }
-      m.eb = tp.eptr[t]; m.rb = tp.rptr[t]; m.base = tp.base[t];
-      m.E = (int)(tp.eptr[t + 1] - m.eb); m.R = (int)(tp.rptr[t + 1] - m.rb); m.clid = tp.cl_id[t];
+      m.eb = tp.ebeg[t]; m.rb = tp.rptr[t]; m.base = tp.base[t];
+      m.E = (int)(tp.eptr[t + 1] - tp.eptr[t]); m.R = (int)(tp.rptr[t + 1] - m.rb); m.clid = tp.cl_id[t];
     };
     TileMeta cur, nxt;
     load_meta(tile_of(0), cur);

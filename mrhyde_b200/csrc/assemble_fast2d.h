@@ -302,8 +302,8 @@ struct ThermalQuadQ1 {
     int* s_rows = reinterpret_cast<int*>(s_off + tp.max_e);
     if (tid == 0) Ks[NE * 128] = 0.0;                       // masked contributions and pads read this cell
     for (int64_t t = tp.tile_begin + blockIdx.x; t < tp.tile_end; t += gridDim.x) {
-      const int64_t eb = tp.eptr[t], rb = tp.rptr[t];
-      const int E = (int)(tp.eptr[t + 1] - eb), R = (int)(tp.rptr[t + 1] - rb);
+      const int64_t eb = tp.ebeg[t], rb = tp.rptr[t];
+      const int E = (int)(tp.eptr[t + 1] - tp.eptr[t]), R = (int)(tp.rptr[t + 1] - rb);
       for (int k = tid; k < E; k += 128) Hex::cp_async4(s_off + k, tp.off + eb + k);
       for (int k = tid; k < R; k += 128) Hex::cp_async4(s_rows + k, tp.rows + rb + k);
       asm volatile("cp.async.commit_group;" ::: "memory");

@@ -22,13 +22,13 @@ constexpr unsigned long long MASKED_DEST = KEY_SENTINEL >> SRC_BITS;
 
 struct TileDev {
   DevBuf<int> perm, rows, cl_id;
-  DevBuf<int64_t> eptr, rptr, base;
+  DevBuf<int64_t> eptr, rptr, base, ebeg;      // ebeg: start of each tile's slot list in `off` (lists are de-duplicated)
   DevBuf<uint32_t> off;
   DevBuf<uint16_t> clist, cbase;
-  int64_t ntiles = 0, npatterns = 0;
+  int64_t ntiles = 0, npatterns = 0, noffpatterns = 0;
   int max_acc = 0, nk = 0, max_e = 0, max_r = 0, nn = 8;
   bool ok = false;
-  void release() { perm.release(); rows.release(); cl_id.release(); eptr.release(); rptr.release(); base.release(); off.release();
+  void release() { perm.release(); rows.release(); cl_id.release(); eptr.release(); rptr.release(); base.release(); ebeg.release(); off.release();
                    clist.release(); cbase.release(); ok = false; }
 };
 
@@ -151,6 +151,38 @@ __global__ void clist_assign_kernel(const uint16_t* cl_all, const uint16_t* cbas
   for (int k = threadIdx.x; k < TILE_ELEMS; k += blockDim.x) if (cbase[lo * TILE_ELEMS + k] != cbase_all[t * TILE_ELEMS + k]) atomicExch(bad, 5);
 }
 
+// ---- dictionary of the slot lists: the lists hold CRS slots RELATIVE to the tile's first slot, which makes them identical for
+// all tiles of the same shape on a mesh whose numbering is translation-invariant (the brick's interior: 131 072 lists of 17 KB
+// collapse to a few dozen) - 136 B per element of DRAM traffic become L2 hits and 2.3 GB of device memory at 256^3 a megabyte
+__global__ void off_hash_kernel(const uint32_t* off_all, const int64_t* eptr, uint64_t* hash) {
+  __shared__ uint64_t part[128];
+  const int64_t t = blockIdx.x, b = eptr[t]; const int E = (int)(eptr[t + 1] - b);
+  uint64_t h = 0x2545f491ull + (uint64_t)threadIdx.x;
+  for (int k = threadIdx.x; k < E; k += 128) h = mix64(h, ((uint64_t)k << 32) | off_all[b + k]);
+  part[threadIdx.x] = h;
+  __syncthreads();
+  if (threadIdx.x == 0) { uint64_t g = mix64(0x9e37ull, (uint64_t)E); for (int k = 0; k < 128; ++k) g = mix64(g, part[k]); hash[t] = g; }
+}
+// pattern of every tile (binary search on the sorted unique hashes), its list start in the dictionary, and a full comparison
+__global__ void off_assign_kernel(const uint32_t* off_all, const int64_t* eptr, const uint64_t* hash, const uint64_t* uhash, int64_t npat,
+                                  const int* rep, const int64_t* dptr, int64_t* ebeg, int* bad) {
+  const int64_t t = blockIdx.x;
+  const uint64_t h = hash[t];
+  int64_t lo = 0, hi = npat;
+  while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (uhash[mid] < h) lo = mid + 1; else hi = mid; }
+  if (lo >= npat) { atomicExch(bad, 6); return; }
+  const int64_t r = rep[lo], b = eptr[t], br = eptr[r];
+  const int E = (int)(eptr[t + 1] - b);
+  if ((int)(eptr[r + 1] - br) != E) { atomicExch(bad, 6); return; }
+  for (int k = threadIdx.x; k < E; k += blockDim.x) if (off_all[b + k] != off_all[br + k]) atomicExch(bad, 6);
+  if (threadIdx.x == 0) ebeg[t] = dptr[lo];
+}
+__global__ void off_fill_kernel(const uint32_t* off_all, const int64_t* eptr, const int* rep, const int64_t* dptr, uint32_t* dict) {
+  const int64_t p = blockIdx.x, r = rep[p], b = eptr[r];
+  const int E = (int)(eptr[r + 1] - b);
+  for (int k = threadIdx.x; k < E; k += blockDim.x) dict[dptr[p] + k] = off_all[b + k];
+}
+
 // throws on CUDA errors; leaves T.ok = false (with a reason) when the plan cannot be used
 template <int NN>
 std::string build_tile_plan(const std::vector<int>& perm_host, int64_t nelem, const int* d_lids, const uint8_t* d_fixed,
@@ -178,12 +210,13 @@ std::string build_tile_plan(const std::vector<int>& perm_host, int64_t nelem, co
   for (int64_t t = 0; t < nt; ++t) { eptr[t + 1] = eptr[t] + hE[t]; rptr[t + 1] = rptr[t] + hR[t]; max_acc = std::max(max_acc, hE[t] + hR[t]); T.max_e = std::max(T.max_e, hE[t]); T.max_r = std::max(T.max_r, hR[t]); }
   T.max_acc = max_acc;
   T.eptr.upload(eptr); T.rptr.upload(rptr); T.base.alloc(nt);
-  T.off.alloc((size_t)eptr[nt] + 4); T.rows.alloc((size_t)rptr[nt] + 4);      // + 4: the bulk-copy staging reads whole 16-byte groups
+  DevBuf<uint32_t> off_all; off_all.alloc((size_t)eptr[nt] + 4);
+  T.rows.alloc((size_t)rptr[nt] + 4);      // + 4: the bulk-copy staging reads whole 16-byte groups
   constexpr size_t L = (size_t)TILE_ELEMS * tile_ncp<NN>();
   DevBuf<uint16_t> cl_all, cbase_all; cl_all.alloc((size_t)nt * L); cbase_all.alloc((size_t)nt * TILE_ELEMS);
   DevBuf<uint64_t> hash, skey; hash.alloc(nt); skey.alloc(nt); idx.alloc(nt);
   tile_plan_kernel<true, NN><<<(unsigned)nt, TILE_ELEMS, smem>>>(T.perm.p, nelem, d_lids, d_fixed, d_rowptr, d_colind, nk, nullptr, nullptr,
-                                                            T.eptr.p, T.rptr.p, T.base.p, T.off.p, T.rows.p, cl_all.p, cbase_all.p, hash.p, bad.p);
+                                                            T.eptr.p, T.rptr.p, T.base.p, off_all.p, T.rows.p, cl_all.p, cbase_all.p, hash.p, bad.p);
   CUDA_CK(cudaGetLastError());
   CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
   if (hbad) { T.release(); return hbad == 3 ? "a tile spans more than 2^32 CRS slots" : "a tile has more than 32000 destinations"; }
@@ -201,12 +234,51 @@ std::string build_tile_plan(const std::vector<int>& perm_host, int64_t nelem, co
   CUDA_CK(cudaGetLastError());
   CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
   if (hbad) { T.release(); return "contribution list dictionary verification failed (hash collision)"; }
+  cl_all.release(); cbase_all.release();
+  // slot-list dictionary (falls back to one list per tile when the lists do not repeat or a hash collides)
+  {
+    DevBuf<uint64_t> ohash, okey; ohash.alloc(nt); okey.alloc(nt);
+    off_hash_kernel<<<(unsigned)nt, 128>>>(off_all.p, T.eptr.p, ohash.p);
+    CUDA_CK(cudaGetLastError());
+    CUDA_CK(cudaMemcpy(okey.p, ohash.p, nt * sizeof(uint64_t), cudaMemcpyDeviceToDevice));
+    thrust::device_ptr<uint64_t> okp(okey.p);
+    thrust::sequence(thrust::device, ip, ip + nt);
+    thrust::sort_by_key(thrust::device, okp, okp + nt, ip);
+    auto oends = thrust::unique_by_key(thrust::device, okp, okp + nt, ip);
+    const int64_t nop = oends.first - okp;
+    bool dedupe = nop <= nt / 2;
+    if (dedupe) {
+      std::vector<int> rep((size_t)nop);
+      CUDA_CK(cudaMemcpy(rep.data(), idx.p, (size_t)nop * sizeof(int), cudaMemcpyDeviceToHost));
+      std::vector<int64_t> dptr((size_t)nop + 1, 0);
+      for (int64_t p = 0; p < nop; ++p) dptr[p + 1] = dptr[p] + ((hE[rep[p]] + 3) & ~3);       // every list starts on a 16-byte boundary
+      DevBuf<int64_t> ddptr; ddptr.upload(dptr);
+      T.ebeg.alloc(nt); T.off.alloc((size_t)dptr[nop] + 4);
+      CUDA_CK(cudaMemset(T.off.p, 0, ((size_t)dptr[nop] + 4) * sizeof(uint32_t)));
+      CUDA_CK(cudaMemset(bad.p, 0, sizeof(int)));
+      off_assign_kernel<<<(unsigned)nt, 128>>>(off_all.p, T.eptr.p, ohash.p, okey.p, nop, idx.p, ddptr.p, T.ebeg.p, bad.p);
+      CUDA_CK(cudaGetLastError());
+      off_fill_kernel<<<(unsigned)nop, 128>>>(off_all.p, T.eptr.p, idx.p, ddptr.p, T.off.p);
+      CUDA_CK(cudaGetLastError());
+      CUDA_CK(cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
+      if (hbad) { dedupe = false; T.ebeg.release(); T.off.release(); }
+      else T.noffpatterns = nop;
+    }
+    if (!dedupe) {               // one list per tile: the lists as the plan kernel wrote them
+      T.off.alloc((size_t)eptr[nt] + 4);
+      CUDA_CK(cudaMemcpy(T.off.p, off_all.p, ((size_t)eptr[nt] + 4) * sizeof(uint32_t), cudaMemcpyDeviceToDevice));
+      std::vector<int64_t> eb(eptr.begin(), eptr.begin() + nt);
+      T.ebeg.upload(eb);
+      T.noffpatterns = nt;
+    }
+  }
+  CUDA_CK(cudaDeviceSynchronize());
   T.ok = true;
   return "";
 }
 
 void fill_tile_params(const TileDev& T, TilePlan& tp) {
-  tp.perm = T.perm.p; tp.eptr = T.eptr.p; tp.rptr = T.rptr.p; tp.base = T.base.p; tp.off = T.off.p; tp.rows = T.rows.p;
+  tp.perm = T.perm.p; tp.eptr = T.eptr.p; tp.ebeg = T.ebeg.p; tp.rptr = T.rptr.p; tp.base = T.base.p; tp.off = T.off.p; tp.rows = T.rows.p;
   tp.clist = T.clist.p; tp.cbase = T.cbase.p; tp.cl_id = T.cl_id.p; tp.ntiles = T.ntiles; tp.tile_begin = 0; tp.tile_end = T.ntiles; tp.max_acc = T.max_acc; tp.nk = T.nk; tp.max_e = T.max_e; tp.max_r = T.max_r;
 }
 

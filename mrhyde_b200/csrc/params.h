@@ -55,10 +55,11 @@ struct PhysParams {
 
 struct TilePlan {          // tile-staged scatter of the specialised kernels (built at finalize, engine_tiles.inl)
   const int* perm;           // (nelem)   element order: tile t = perm[128 t .. 128 t + 127]
-  const int64_t* eptr;       // (ntiles+1) first CRS-slot entry of each tile in `off`
+  const int64_t* eptr;       // (ntiles+1) running count of distinct CRS slots: tile t has E_t = eptr[t + 1] - eptr[t] of them
+  const int64_t* ebeg;       // (ntiles)  start of the tile's slot list in `off` (lists are de-duplicated: tiles of one shape share one)
   const int64_t* rptr;       // (ntiles+1) first residual row of each tile in `rows`
   const int64_t* base;       // (ntiles)  smallest CRS slot of the tile
-  const uint32_t* off;       // (sum E_t) distinct CRS slots of each tile relative to base, ascending
+  const uint32_t* off;       // (dictionary) distinct CRS slots of a tile relative to base, ascending; every list 16-byte aligned
   const int* rows;           // (sum R_t) distinct residual rows (LIDs) of each tile, ascending
   const uint16_t* clist;     // (nlist, 128, 72) the tile's contributions sorted by destination; thread t reads row t:
                              //   bits 0..14 = entry * 128 + thread in the shared element store, bit 15 = first of its destination
