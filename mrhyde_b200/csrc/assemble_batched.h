@@ -406,6 +406,9 @@ struct BatPhases {
     WV tfn[NRT];
 #pragma unroll
     for (int rt = 0; rt < NRT; ++rt) tfn[rt] = basis_frag(0, rt, mfn);
+#if defined(MRH_BAT_QUNROLL)                   // tuning experiment: unrolled point loop (the one-ahead fragments then need no register copies)
+#pragma unroll MRH_BAT_QUNROLL
+#endif
     for (int q = 0; q < L.nq; ++q) {
       const double* sF = sm + L.oF() + (size_t)q * NVAR * TA;
       const double* Dq = sm + L.oD() + LAY::dq(q);
@@ -596,15 +599,21 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
         const double x = sm[L.oXq() + (size_t)q * 3], y = sm[L.oXq() + (size_t)q * 3 + 1], z = sm[L.oXq() + (size_t)q * 3 + 2];
         // the point's atoms go to registers once and every program is evaluated before the first store: with the stores in between
         // the compiler had to assume they alias the atom table and re-read the atoms for every term of every program
-        double areg[PROGS::NA > 0 ? PROGS::NA : 1];
+        if constexpr (PROGS::NA > 0) {
+          double areg[PROGS::NA > 0 ? PROGS::NA : 1];
 #pragma unroll
-        for (int i = 0; i < PROGS::NA; ++i) areg[i] = at[q * PROGS::NA + i];
-        double val[MRH_NCOEF];
+          for (int i = 0; i < PROGS::NA; ++i) areg[i] = at[q * PROGS::NA + i];
+          double val[MRH_NCOEF];
 #pragma unroll
-        for (int k = 0; k < MRH_NCOEF; ++k) val[k] = PROGS::eval(k, x, y, z, kp.tp.time, areg);
+          for (int k = 0; k < MRH_NCOEF; ++k) val[k] = PROGS::eval(k, x, y, z, kp.tp.time, areg);
 #pragma unroll
-        for (int k = 0; k < MRH_NCOEF; ++k)
-          if (kp.progs[k].kind == 1) sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = val[k];
+          for (int k = 0; k < MRH_NCOEF; ++k)
+            if (kp.progs[k].kind == 1) sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = val[k];
+        } else {
+#pragma unroll
+          for (int k = 0; k < MRH_NCOEF; ++k)
+            if (kp.progs[k].kind == 1) sm[L.oCoef() + (size_t)q * MRH_NCOEF + k] = PROGS::eval(k, x, y, z, kp.tp.time, nullptr);
+        }
       }
     } else {
       for (int it = lane; it < nq * n1; it += 32) B::prep(kp, L, sm, it, n1);
