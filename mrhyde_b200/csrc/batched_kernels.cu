@@ -57,13 +57,31 @@ bool launch_batched(int num_sms, KParams& kp, cudaStream_t stream) {
 
 }  // namespace
 
+// The translation unit is compiled twice (build.py): MRH_BAT_TU_SIDES = 0 holds the volume instantiations and the entry point,
+// MRH_BAT_TU_SIDES = 1 the side-launch instantiations - the two halves build in parallel (each is minutes of ptxas time).
+#if !defined(MRH_BAT_TU_SIDES)
+#define MRH_BAT_TU_SIDES 0
+#endif
 namespace mrh {
-bool launch_batched_assembly(int phys, int dim, int order, int num_sms, KParams& kp, void* stream) {
+#if MRH_BAT_TU_SIDES
+bool launch_batched_assembly_sides(int phys, int dim, int order, int num_sms, KParams& kp, void* stream) {
   bool launched = false;
   dispatch_cfg(phys, dim, order, [&](auto c) {
     using C = decltype(c);
-    launched = kp.is_side ? launch_batched<C, true>(num_sms, kp, (cudaStream_t)stream) : launch_batched<C, false>(num_sms, kp, (cudaStream_t)stream);
+    launched = launch_batched<C, true>(num_sms, kp, (cudaStream_t)stream);
   });
   return launched;
 }
+#else
+bool launch_batched_assembly_sides(int phys, int dim, int order, int num_sms, KParams& kp, void* stream);
+bool launch_batched_assembly(int phys, int dim, int order, int num_sms, KParams& kp, void* stream) {
+  if (kp.is_side) return launch_batched_assembly_sides(phys, dim, order, num_sms, kp, stream);
+  bool launched = false;
+  dispatch_cfg(phys, dim, order, [&](auto c) {
+    using C = decltype(c);
+    launched = launch_batched<C, false>(num_sms, kp, (cudaStream_t)stream);
+  });
+  return launched;
+}
+#endif
 }  // namespace mrh
