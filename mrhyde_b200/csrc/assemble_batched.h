@@ -243,22 +243,14 @@ struct BatPhases {
 
   // ---- point physics on one lane chunk, item = (point, variable m) ----------------------------------------
   MRH_HDN static void point_chunk(const KParams& kp, const LAY& L, double* sm, int item) {
-    const bool tr = kp.tp.transient != 0;
-    if (kp.compute_jac) { if (tr) point_chunk_t<true, true>(kp, L, sm, item); else point_chunk_t<true, false>(kp, L, sm, item); }
-    else { if (tr) point_chunk_t<false, true>(kp, L, sm, item); else point_chunk_t<false, false>(kp, L, sm, item); }
-  }
-  // JAC and TR (transient launch) are template switches on purpose: whether the compiler unswitched those branches by itself
-  // depended on what else was in the translation unit (C5 128^3: 24.2 ms with its own copies, 28.3 ms without - same source)
-  template <bool JAC, bool TR>
-  MRH_HDN static void point_chunk_t(const KParams& kp, const LAY& L, double* sm, int item) {
     const int q = item / NCH, ch = item - q * NCH;
-    if (!JAC && ch != 0) return;                                // residual-only pass: the values come from chunk 0 alone
+    if (!kp.compute_jac && ch != 0) return;                     // residual-only pass: the values come from chunk 0 alone
     const int lane0 = ch * LCH;
     const double* Ji = sm + L.oJi() + (size_t)q * DIM * DIM;
     const RefTab& tb = kp.tab;
     const double* U = sm + L.oU();
     const double* Ud = sm + L.oUd();
-    constexpr bool tr = TR;
+    const bool tr = kp.tp.transient != 0;
     const double au = tr ? kp.tp.alpha_u : 1.0;
     PointBat<S, NVAR, DIM> in;
 #pragma unroll
@@ -347,7 +339,7 @@ struct BatPhases {
 #pragma unroll
       for (int a = 0; a < 4; ++a) {
         if (a < TA && ch == 0) sF[v * TA + a] = F[v][a < TA ? a : 0].v;
-        if (!JAC) continue;
+        if (!kp.compute_jac) continue;
 #pragma unroll
         for (int l = 0; l < LCH; ++l) {
           const int b = b0 + l;
@@ -628,13 +620,7 @@ __device__ __forceinline__ void batched_body(const KParams& kp, double* smem_all
     }
     if (lane == 31 && (NeedsElementSize<C::PHYS>::value || B::is_side(kp))) B::element_size(L, sm, B::is_side(kp));       // h enters volume terms through the stabilisation only
     __syncwarp();
-    if (kp.compute_jac) {
-      if (kp.tp.transient) { for (int it = lane; it < nq * B::NCH; it += 32) B::template point_chunk_t<true, true>(kp, L, sm, it); }
-      else { for (int it = lane; it < nq * B::NCH; it += 32) B::template point_chunk_t<true, false>(kp, L, sm, it); }
-    } else {
-      if (kp.tp.transient) { for (int it = lane; it < nq * B::NCH; it += 32) B::template point_chunk_t<false, true>(kp, L, sm, it); }
-      else { for (int it = lane; it < nq * B::NCH; it += 32) B::template point_chunk_t<false, false>(kp, L, sm, it); }
-    }
+    for (int it = lane; it < nq * B::NCH; it += 32) B::point_chunk(kp, L, sm, it);
     __syncwarp();
     typename B::Acc acc;
     B::contract(kp, L, sm, acc);
