@@ -40,8 +40,6 @@ MRH_HD void wv_mma(WV& c0, WV& c1, const WV& a, const WV& b) {
                : "+d"(c0.x), "+d"(c1.x) : "d"(a.x), "d"(b.x));
 }
 MRH_HD void warp_sync() { __syncwarp(); }
-// value of lane src(lane) (a full-warp shuffle)
-template <class F> MRH_HD WV wv_shfl(const WV& v, F src) { return WV{__shfl_sync(0xffffffffu, v.x, src((int)(threadIdx.x & 31)))}; }
 #else
 struct WV { double x[32]; };
 MRH_HD double wv_get(const WV& v, int lane) { return v.x[lane]; }
@@ -58,7 +56,6 @@ MRH_HD void wv_mma(WV& c0, WV& c1, const WV& a, const WV& b) {
   }
 }
 MRH_HD void warp_sync() {}
-template <class F> MRH_HD WV wv_shfl(const WV& v, F src) { WV r; for (int l = 0; l < 32; ++l) r.x[l] = v.x[src(l)]; return r; }
 #endif
 
 MRH_HD void st2(double* p, double a, double b) {

@@ -153,7 +153,7 @@ inline std::string jit_function_source(const std::string& name, const Prog& pr, 
 // A manufactured source such as the linear-elasticity one calls sin / cos 63 times per point, 18 of them distinct; evaluated by one
 // lane per point that was 42 % of the batched kernel's instruction stream (profiles/r1_batched_final_C4_ncu_summary.txt).  The printer
 // therefore collects the distinct (function, argument expression) pairs of ALL programs of the launch; the kernel evaluates the atoms
-// of all points with every lane busy and uniform code (argument by a small switch, then one trig_fast call), and the programs read
+// of all points with every lane busy and uniform code (affine arguments from a table row per atom - a switch over the atom index diverges -, then one trig_fast call), and the programs read
 // them from shared memory.
 struct JitAffine {            // c[0] + c[1] x + c[2] y + c[3] z + c[4] t, when the sub-expression is of that form
   bool ok = false; double c[5] = {0, 0, 0, 0, 0};
