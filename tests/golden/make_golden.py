@@ -58,6 +58,7 @@ if __name__ == "__main__":
               "le/2D_manufactured", "navierstokes/channel", "thermal/2D_mixed_bcs", "thermal/2D_verification_nonzeroDBC",
               "stokes/2D_verification_pspg", "helmholtz/manufactured_solution"]:
         data["l2"][p] = l2(p)
-    data["l2_series"] = {"thermal/2D_verification_transient": l2_series("thermal/2D_verification_transient")}
+    data["l2_series"] = {"thermal/2D_verification_transient": l2_series("thermal/2D_verification_transient"),
+                         "cdr/2D_transient": l2_series("cdr/2D_transient")}
     json.dump(data, open(OUT, "w"), indent=1)
     print("wrote", OUT, {k: v for k, v in data["l2"].items()})

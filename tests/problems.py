@@ -62,6 +62,16 @@ def regression_thermal_2d_transient(n=40):
                 true={"e": "sin(2*pi*t)*sin(2*pi*x)*sin(2*pi*y)"}, time=dict(final=1.0, steps=20, tableau="BWE", bdf=1))
 
 
+def regression_cdr_2d_transient(n=40):
+    """regression/cdr/2D_transient: a Gaussian bubble advected with velocity (10, 0) and the nonlinear reaction 0.5 c^2, backward
+    Euler, 10 steps to t = 0.1; the initial state is the L2 projection of exp(bubble)"""
+    return dict(name="cdr/2D_transient", mesh=_mesh(2, (n, n)), physics="cdr", order=1,
+                functions={"source": "0.0", "xvel": "10.0", "yvel": "0.0", "reaction": "0.5*c*c", "SUPG tau": "0.0",
+                           "bubble": "-10.0*(x-0.2)*(x-0.2) - 10.0*(y-0.5)*(y-0.5)"},
+                dirichlet={"c": {"all boundaries": "0.0"}}, extra={"transient": True, "workset size": 100},
+                initial={"c": "exp(bubble)"}, true={"c": "0.0"}, time=dict(final=0.1, steps=10, tableau="BWE", bdf=1))
+
+
 def regression_thermal_3d(n=10):
     return dict(name="thermal/3D_verification", mesh=_mesh(3, (n, n, n)), physics="thermal", order=1,
                 functions={"thermal source": "12*(pi*pi)*sin(2*pi*x)*sin(2*pi*y)*sin(2*pi*z)"},

@@ -122,6 +122,33 @@ def test_transient_regression_series_from_the_gpu(lib):
     e.close()
 
 
+def test_cdr_transient_series_from_the_gpu(lib):
+    """regression/cdr/2D_transient on the device: mrh_set_initial (L2 projection of the Gaussian), Dirichlet DOFs to their data,
+    then mrh_transient_solve step by step (state-dependent reaction: batched kernel with the PAD interpreter, Newton + GMRES).
+    4-digit agreement with the reference's series (see tests/test_oracle_golden.py::test_cdr_transient_regression_series)."""
+    import torch
+    from mrhyde_b200 import Engine
+    from oracle.pyoracle import Oracle
+    p = problems.regression_cdr_2d_transient()
+    e = Engine.from_problem(p, lib=lib)
+    o = Oracle(U.oracle_problem(p))
+    u, res, jac = _buffers(e)
+    info = e.set_initial(u, res, jac)
+    assert info["status"] == 0, info
+    fixed = torch.from_numpy(e.dofmap(coords=False)[2].astype(bool)).to(u.device)
+    u[fixed] = 0.0
+    gold = GOLD["l2_series"]["cdr/2D_transient"]["c"]
+    assert o.l2_error(u.cpu().numpy(), 0, "0.0") == pytest.approx(gold[0][1], rel=5e-4)
+    nsteps, dt = p["time"]["steps"], p["time"]["final"] / p["time"]["steps"]
+    for k in range(nsteps):
+        info = e.transient_solve(u, res, jac, k * dt, (k + 1) * dt, dt, tableau="BWE", bdf_order=1,
+                                 linear_method=0, linear_tol=1e-12, max_linear_iters=5000, krylov_vectors=200, nonlinear_tol=1e-10, max_nonlinear_iters=10)
+        assert info["status"] == 0 and info["time_steps"] == 1, info
+        err = o.l2_error(u.cpu().numpy(), 0, "0.0", time=(k + 1) * dt)
+        assert err == pytest.approx(gold[k + 1][1], rel=5e-4), (k, err, gold[k + 1], info)
+    e.close()
+
+
 @pytest.mark.parametrize("method", [0, 1], ids=["gmres", "cg"])
 def test_linear_solve_against_a_direct_solver(lib, method):
     import scipy.sparse as sp

@@ -132,6 +132,58 @@ def test_transient_regression_series():
         assert err == pytest.approx(gold[k + 1][1], rel=3e-5), (k, err, gold[k + 1])
 
 
+def l2_project(o, fn):
+    """consistent-mass L2 projection of fn(x, y[, z]) built from the oracle's own basis values and weights (setInitial,
+    /root/reference/src/managers/assemblyManager.cpp:1185-1310)"""
+    lids = o.dofmap()[0]
+    N = o.nlocal
+    rows, cols, vals = [], [], []
+    b = np.zeros(N)
+    e0 = 0
+    for g in range(o.ngroups):
+        ne = min(100, o.nelem - e0)
+        B, _, W, IP = o.group_basis(g, ne)
+        f = fn(*IP)
+        L = lids[e0:e0 + ne]
+        Me = np.einsum("eiq,ejq,eq->eij", B, B, W)
+        be = np.einsum("eiq,eq,eq->ei", B, f, W)
+        for e in range(ne):
+            rows += np.repeat(L[e], o.nb).tolist(); cols += np.tile(L[e], o.nb).tolist(); vals += Me[e].ravel().tolist()
+            np.add.at(b, L[e], be[e])
+        e0 += ne
+    M = sp.csr_matrix((vals, (rows, cols)), shape=(N, N)).tocsc()
+    return spl.spsolve(M, b)
+
+
+def test_cdr_transient_regression_series():
+    """regression/cdr/2D_transient: advection + the state-dependent reaction 0.5 c^2, backward Euler, initial state = L2 projection of
+    a Gaussian with the Dirichlet DOFs set to their data.  Agreement with the reference's printed series is 4 digits, not 6: the t = 0
+    value itself differs in the fourth digit (0.370658 here, 0.370794 there - the reference solves its projection iteratively) and the
+    difference carries through the steps; any error in the transient seeding, the advection term or the reaction's derivative would
+    show in the first digit."""
+    p = problems.regression_cdr_2d_transient()
+    o = Oracle(config_text(**{k: v for k, v in p.items() if k not in ("true", "name", "time", "initial")}))
+    rp, ci = o.crs()
+    fixed = o.dofmap()[2].astype(bool)
+    gold = GOLD["l2_series"]["cdr/2D_transient"]["c"]
+    u = l2_project(o, lambda x, y: np.exp(-10.0 * (x - 0.2) ** 2 - 10.0 * (y - 0.5) ** 2))
+    u[fixed] = 0.0
+    assert o.l2_error(u, 0, "0.0") == pytest.approx(gold[0][1], rel=5e-4)
+    nsteps, dt = p["time"]["steps"], p["time"]["final"] / p["time"]["steps"]
+    for k in range(nsteps):
+        t = k * dt
+        prev = u.copy().reshape(-1, 1); stage = u.copy().reshape(-1, 1)
+        o.set_time([[1.0]], [1.0], [1.0, -1.0], dt, t + dt, 0)
+        for _ in range(10):
+            res, jac = o.assemble(u, jacobian=True, u_prev=prev, u_stage=stage)
+            if np.max(np.abs(res)) < 1e-10:
+                break
+            J = sp.csr_matrix((jac, ci, rp), shape=(o.nlocal, o.nlocal)).tocsc()
+            u = u + spl.spsolve(J, res)
+        err = o.l2_error(u, 0, "0.0", time=t + dt)
+        assert err == pytest.approx(gold[k + 1][1], rel=5e-4), (k, err, gold[k + 1])
+
+
 def test_interpreter_quirks():
     o = Oracle(config_text(mesh=problems._mesh(2, (2, 2)), physics="thermal", order=1,
                            functions={"A": "2.0", "f": "A*x+1.0"}))
